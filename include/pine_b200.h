@@ -1,0 +1,211 @@
+/* pine_b200.h -- C ABI of the B200 (sm_100a) path-tracing backend for Pine's PathIntegrator.
+ *
+ * This is the drop-in boundary: everything `PathIntegrator::render(Scene&)`
+ * (reference src/pine/impl/integrator/path.cpp:26-41, called through
+ * `class Integrator { virtual void render(Scene&) }`, src/pine/core/integrator.h:20-25) does from
+ * the moment the scene is complete until `Film::pixels` is filled happens behind these entry
+ * points. Plain pointers and sizes only; no C++ or torch types. All functions return 0 on success
+ * or a negative PB2_E_* code; `pb2_last_error()` gives the message of the calling thread's last
+ * failure. Nothing here falls back to the CPU: without a CUDA device every call fails.
+ *
+ * Shape records carry EXACTLY the data members of the reference's shape structs (cited per
+ * struct), so a Pine-side shim copies members verbatim and both sides intersect the same numbers.
+ * Matrices are column-major (Pine's Matrix4<T>{x,y,z,w} column vectors, vecmath.h:556-616).
+ */
+#ifndef PINE_B200_H
+#define PINE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PB2_OK 0
+#define PB2_E_INVALID -1     /* bad argument / malformed scene */
+#define PB2_E_UNSUPPORTED -2 /* scene content the CUDA path does not implement (no CPU fallback) */
+#define PB2_E_CUDA -3        /* CUDA runtime error or no device */
+#define PB2_E_STATE -4       /* call order violated (e.g. render before upload) */
+
+/* ---- shapes (members of the reference structs) ---------------------------------------------- */
+typedef struct pb2_rect { /* pine::Rect, geometry.h:79-96 */
+  float position[3], ex[3], ey[3], n[3];
+  float lx, ly;
+  float rx[3], ry[3];
+} pb2_rect;
+
+typedef struct pb2_aabb { /* pine::AABB, bbox.h:29-92 */
+  float lower[3], upper[3];
+} pb2_aabb;
+
+typedef struct pb2_obb { /* pine::OBB, bbox.h:94-109 (PRL `Box(aabb, m)`) */
+  pb2_aabb base;
+  float m[16], m_inv[16]; /* column-major; m_inv is the HOST's inverse(m) (vecmath.cpp:104-131) */
+} pb2_obb;
+
+typedef struct pb2_disk { /* pine::Disk, geometry.h:44-59 */
+  float position[3], n[3], u[3], v[3];
+  float r;
+} pb2_disk;
+
+typedef struct pb2_cone { /* pine::Cone, geometry.h:118-139 */
+  pb2_disk bottom;
+  float p[3], n[3];
+  float r, h, A, A2, S;
+} pb2_cone;
+
+typedef struct pb2_sphere { /* pine::Sphere, geometry.h:28-42 */
+  float c[3];
+  float r;
+} pb2_sphere;
+
+typedef struct pb2_triangle { /* pine::Triangle, geometry.h:98-116 */
+  float v0[3], v1[3], v2[3], n[3];
+} pb2_triangle;
+
+typedef struct pb2_mesh { /* pine::Mesh, geometry.h:158-224 */
+  const float* vertices; /* n_vertices x 3 */
+  const uint32_t* indices; /* n_triangles x 3 */
+  const float* normals;   /* n_vertices x 3 or NULL */
+  const float* texcoords; /* n_vertices x 2 or NULL */
+  uint32_t n_vertices, n_triangles;
+} pb2_mesh;
+
+enum pb2_shape_kind {
+  PB2_SHAPE_AABB = 0,
+  PB2_SHAPE_OBB = 1,
+  PB2_SHAPE_SPHERE = 2,
+  PB2_SHAPE_TRIANGLE = 3,
+  PB2_SHAPE_CONE = 4,
+  PB2_SHAPE_RECT = 5,
+  PB2_SHAPE_DISK = 6,
+  PB2_SHAPE_MESH = 7
+};
+
+/* ---- materials (material.h:18-131); Node3f/Nodef parameters must be constants ---------------- */
+enum pb2_material_kind {
+  PB2_MAT_EMISSIVE = 0,
+  PB2_MAT_DIFFUSE = 1,
+  PB2_MAT_METAL = 2,
+  PB2_MAT_GLOSSY = 3,
+  PB2_MAT_GLASS = 4,
+  PB2_MAT_UBER = 5,
+  PB2_MAT_SUBSURFACE = 6
+};
+typedef struct pb2_material {
+  int32_t kind;
+  float color[3]; /* albedo, or emitted radiance for EMISSIVE */
+  float roughness, ior, metallic, transmission;
+  float sigma_s[3];
+} pb2_material;
+
+/* One entry of Scene::geometries (scene.h:37), in the scene's order: geometry index == position. */
+typedef struct pb2_geometry {
+  int32_t shape_kind;  /* pb2_shape_kind */
+  int32_t shape_index; /* index into the per-kind array of pb2_scene_desc */
+  int32_t material;    /* index into pb2_scene_desc.materials */
+} pb2_geometry;
+
+typedef struct pb2_camera { /* pine::ThinLenCamera, camera.h:10-27 */
+  float position[3];
+  float c2w[9]; /* column-major mat3 (look_at(from,to) truncated, camera.cpp:10) */
+  float fov2d[2];
+  float len_radius, focus_distance;
+  int32_t width, height; /* Film size */
+  int32_t tonemapper;    /* 0 Uncharted2, 1 ACES (film.h:9-24); used by pb2_film_finalize only */
+} pb2_camera;
+
+typedef struct pb2_scene_desc {
+  const pb2_geometry* geometries; uint32_t n_geometries;
+  const pb2_material* materials;  uint32_t n_materials;
+  const pb2_aabb* aabbs;          uint32_t n_aabbs;
+  const pb2_obb* obbs;            uint32_t n_obbs;
+  const pb2_sphere* spheres;      uint32_t n_spheres;
+  const pb2_triangle* triangles;  uint32_t n_triangles;
+  const pb2_cone* cones;          uint32_t n_cones;
+  const pb2_rect* rects;          uint32_t n_rects;
+  const pb2_disk* disks;          uint32_t n_disks;
+  const pb2_mesh* meshes;         uint32_t n_meshes;
+  /* Scene::lights (scene.h:39): geometry index of every AreaLight, in scene order
+   * (scene.cpp:19-20 adds one per Emissive geometry). Delta and environment lights: unsupported. */
+  const int32_t* light_geometries; uint32_t n_lights;
+  pb2_camera camera;
+} pb2_scene_desc;
+
+typedef struct pb2_render_params {
+  int32_t spp;             /* BlueSobolSampler::spp() (already rounded up to a power of 2, <=256) */
+  int32_t max_path_length; /* PathIntegrator ctor argument (path.cpp:9-14), > 0 */
+  /* Multi-GPU sharding. Tile sharding: rows [row_begin,row_end) of the film, all samples
+   * (results bit-identical to one GPU). Sample sharding: all rows, samples
+   * [sample_begin,sample_end); the film then holds SUM over those samples / spp and per-pixel RNGs
+   * are seeded hash(p, sample_begin) (sampler.h:286-289 takes a sample_index). Use
+   * 0,height / 0,spp for a full render. */
+  int32_t row_begin, row_end;
+  int32_t sample_begin, sample_end;
+  int32_t accel; /* 0 = wide BVH (production), 1 = reference-order binary BVH (verification) */
+  int32_t flags; /* PB2_RENDER_* */
+} pb2_render_params;
+#define PB2_RENDER_SORT_BY_MATERIAL 1 /* bucket the shade queue by BxDF kind */
+
+typedef struct pb2_counters {
+  uint64_t closest_rays, shadow_rays, camera_samples, kernel_launches;
+  double last_render_ms;  /* device time of the last pb2_render* (CUDA events on its stream) */
+  double last_trace_ms;   /* device time of the traversal kernels inside it */
+  double bvh_build_ms;    /* host time spent building + uploading the BVH */
+  uint32_t bvh2_nodes, wide_nodes, n_primitives;
+} pb2_counters;
+
+typedef struct pb2_context pb2_context;
+
+const char* pb2_last_error(void);
+int pb2_device_count(void);
+/* Replaces: RTIntegrator ctor + per-render prologue (integrator.cpp:21-35). */
+int pb2_create(int device, pb2_context** out);
+void pb2_destroy(pb2_context* ctx);
+/* Replaces: accel.build(&scene) + light_sampler.build(&scene) (integrator.cpp:32-33,
+ * bvh.cpp:453-495, lightsampler.cpp:6-10). Copies everything it needs; builds the BVH on the host. */
+int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* scene);
+/* The Heitz et al. tables Pine links in (src/contrib/bluesobol/bluenoise_<spp>spp.cpp:2-12), as u8:
+ * sobol[256*256], scramble[128*128*8], rank[128*128*8]. */
+int pb2_upload_sampler_tables(pb2_context* ctx, int spp_pow2, const uint8_t* sobol,
+                              const uint8_t* scramble, const uint8_t* rank);
+/* Replaces: PathIntegrator::render's pixel loop (path.cpp:31-40). film_rgba: caller-owned HOST
+ * buffer of width*height*4 floats, row-major p.x + p.y*width (array.h:51-55), pre-tonemap. */
+int pb2_render(pb2_context* ctx, const pb2_render_params* params, float* film_rgba_host);
+/* Same, but leaves the film in DEVICE memory (for the multi-GPU NCCL reduce); pointer stays owned
+ * by ctx and valid until the next render/destroy. cuda_stream: a cudaStream_t or NULL. */
+int pb2_render_device(pb2_context* ctx, const pb2_render_params* params, void* cuda_stream,
+                      float** film_rgba_device);
+/* Film::finalize + to_uint8 (film.cpp:21-27, color.cpp:6-23, fileio.cpp:42-54) on the device film:
+ * tone-map, gamma 1/2.2, *256 clamp, optional y-flip. rgba8_host: width*height*4 bytes. */
+int pb2_film_finalize(pb2_context* ctx, const float* film_rgba_host, int flip_y,
+                      uint8_t* rgba8_host, float* tonemapped_rgba_host);
+/* Test hooks == Accel::intersect / Accel::hit (accel.h:16-24) on a caller ray set.
+ * rays: n x {o.xyz, d.xyz, tmin, tmax}. geom/prim = -1 on miss, t = ray.tmax after traversal.
+ * surf (optional, n x 8) = p, n, uv from compute_surface_info. accel as in pb2_render_params. */
+int pb2_trace_closest(pb2_context* ctx, const float* rays_host, size_t n, int accel,
+                      int32_t* geom, int32_t* prim, float* t, float* surf);
+int pb2_trace_any(pb2_context* ctx, const float* rays_host, size_t n, int accel,
+                  uint8_t* occluded);
+/* Device-resident variant for benchmarking the traversal kernel alone: rays stay in HBM. */
+int pb2_trace_closest_device(pb2_context* ctx, const float* rays_dev, size_t n, int accel,
+                             int32_t* geom_dev, int32_t* prim_dev, float* t_dev,
+                             void* cuda_stream);
+/* Known-answer hooks for the sampler/camera kernels (Sampler wrapper sampler.h:286-309,
+ * BlueSobolSampler sampler.h:166-201, ThinLenCamera::gen_ray camera.cpp:22-33). */
+int pb2_test_sampler(pb2_context* ctx, int spp, int px, int py, int sample_index, int n_rand,
+                     float* out_rand, const char* pattern, int n_samples, float* out_draws);
+int pb2_test_primary_rays(pb2_context* ctx, int sample_index, float* rays_host);
+int pb2_get_counters(pb2_context* ctx, pb2_counters* out);
+/* Dump of the host-built reference-order binary tree (which=-1 top level, k = k-th mesh tree) in
+ * the layout of oracle/ref_harness.cpp:ref_bvh_nodes, to pin the builder node for node. */
+int pb2_bvh_info(pb2_context* ctx, int which, int32_t* n_nodes, int32_t* root,
+                 int32_t* n_leaf_prims);
+int pb2_bvh_nodes(pb2_context* ctx, int which, float* aabbs, int32_t* children,
+                  int32_t* leaf_range, int32_t* leaf_prims);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PINE_B200_H */

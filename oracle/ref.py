@@ -1,0 +1,250 @@
+"""oracle/ref.py -- TEST INFRASTRUCTURE ONLY.
+
+ctypes binding of oracle/_ref/libpine_ref.so: the UNMODIFIED reference renderer (wicstas/pine)
+compiled in place by oracle/Makefile, behind the C harness oracle/ref_harness.cpp.
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import
+this module, and only as the checker or the timed CPU baseline -- never on the product path.
+
+`RefScene` exposes the same builder methods as `pine_b200.Scene` (add_material / add_rect / ...),
+so one scene-description function (pine_b200/scenes.py) feeds both sides identical numbers.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libpine_ref.so")
+
+_lib = None
+
+
+def available():
+    return os.path.exists(LIB_PATH)
+
+
+def _f(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(LIB_PATH)
+        L.ref_scene_new.restype = C.c_void_p
+        L.ref_scene_free.argtypes = [C.c_void_p]
+        L.ref_render.restype = C.c_double
+        L.ref_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.ref_accel_build.restype = C.c_double
+        L.ref_accel_build.argtypes = [C.c_void_p]
+        L.ref_bluenoise.restype = C.c_float
+        L.ref_hash_pixel.restype = C.c_uint64
+        for name in ("ref_add_material", "ref_add_rect", "ref_add_box", "ref_add_aabb",
+                     "ref_add_cone", "ref_add_sphere", "ref_add_disk", "ref_add_triangle",
+                     "ref_add_mesh", "ref_num_geometries", "ref_num_lights", "ref_bvh_info",
+                     "ref_bvh_num_lbvh", "ref_bvh_num_indices", "ref_load_gltf"):
+            getattr(L, name).restype = C.c_int
+        _lib = L
+    return _lib
+
+
+MATERIAL_KINDS = {"emissive": 0, "diffuse": 1, "metal": 2, "glossy": 3, "glass": 4, "uber": 5,
+                  "subsurface": 6}
+
+
+def pack_material(color, roughness=0.0, ior=1.4, metallic=0.0, transmission=0.0,
+                  sigma_s=(0.0, 0.0, 0.0)):
+    return _f([*color, roughness, ior, metallic, transmission, *sigma_s])
+
+
+def mat4(op, args):
+    out = np.zeros(16, np.float32)
+    a = _f(args)
+    lib().ref_mat4(C.c_int(op), _fp(a), _fp(out))
+    return out.reshape(4, 4)
+
+
+def mat4_mul(a, b):
+    out = np.zeros(16, np.float32)
+    a, b = _f(a), _f(b)
+    lib().ref_mat4_mul(_fp(a), _fp(b), _fp(out))
+    return out.reshape(4, 4)
+
+
+class RefScene:
+    def __init__(self):
+        self.L = lib()
+        self.h = C.c_void_p(self.L.ref_scene_new())
+        self.size = None
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_scene_free(self.h)
+            self.h = None
+
+    # ---- builder interface (mirrors pine_b200.Scene) ----
+    def add_material(self, kind, color, roughness=0.0, ior=1.4, metallic=0.0, transmission=0.0,
+                     sigma_s=(0.0, 0.0, 0.0)):
+        p = pack_material(color, roughness, ior, metallic, transmission, sigma_s)
+        return self.L.ref_add_material(self.h, MATERIAL_KINDS[kind], _fp(p))
+
+    def add_rect(self, pos, ex, ey, mat, flip=False):
+        a, b, c = _f(pos), _f(ex), _f(ey)
+        return self.L.ref_add_rect(self.h, _fp(a), _fp(b), _fp(c), int(flip), mat)
+
+    def add_box(self, lo, hi, m, mat):
+        a, b, c = _f(lo), _f(hi), _f(m).reshape(-1)
+        return self.L.ref_add_box(self.h, _fp(a), _fp(b), _fp(c), mat)
+
+    def add_aabb(self, lo, hi, mat):
+        a, b = _f(lo), _f(hi)
+        return self.L.ref_add_aabb(self.h, _fp(a), _fp(b), mat)
+
+    def add_cone(self, p, n, r, h, mat):
+        a, b = _f(p), _f(n)
+        return self.L.ref_add_cone(self.h, _fp(a), _fp(b), C.c_float(r), C.c_float(h), mat)
+
+    def add_sphere(self, c, r, mat):
+        a = _f(c)
+        return self.L.ref_add_sphere(self.h, _fp(a), C.c_float(r), mat)
+
+    def add_disk(self, p, n, r, mat):
+        a, b = _f(p), _f(n)
+        return self.L.ref_add_disk(self.h, _fp(a), _fp(b), C.c_float(r), mat)
+
+    def add_triangle(self, a, b, c, mat):
+        a, b, c = _f(a), _f(b), _f(c)
+        return self.L.ref_add_triangle(self.h, _fp(a), _fp(b), _fp(c), mat)
+
+    def add_mesh(self, verts, idx, mat, normals=None, uvs=None):
+        v = _f(verts).reshape(-1, 3)
+        i = np.ascontiguousarray(idx, dtype=np.uint32).reshape(-1, 3)
+        n = _f(normals) if normals is not None else None
+        t = _f(uvs) if uvs is not None else None
+        return self.L.ref_add_mesh(self.h, _fp(v), len(v), i.ctypes.data_as(C.c_void_p), len(i),
+                                   _fp(n) if n is not None else None,
+                                   _fp(t) if t is not None else None, mat)
+
+    def set_camera(self, size, frm, to, fov, len_radius=0.0, focus=1.0, tonemapper="uncharted2"):
+        self.size = (int(size[0]), int(size[1]))
+        a, b = _f(frm), _f(to)
+        self.L.ref_set_camera(self.h, self.size[0], self.size[1],
+                              0 if tonemapper == "uncharted2" else 1, _fp(a), _fp(b),
+                              C.c_float(fov), C.c_float(len_radius), C.c_float(focus))
+
+    def load_gltf(self, path):
+        return self.L.ref_load_gltf(self.h, path.encode())
+
+    # ---- reference operations ----
+    def render(self, spp, depth, sampler="blue"):
+        """PathIntegrator(BVH(), sampler(spp), UniformLightSampler(), depth).render(scene)
+        -> (film float32 [h, w, 4] pre-tonemap, wall seconds incl. BVH build)."""
+        w, h = self.size
+        film = np.zeros((h, w, 4), np.float32)
+        kind = {"blue": 0, "sobol": 1, "uniform": 2}[sampler]
+        secs = self.L.ref_render(self.h, kind, spp, depth, film.ctypes.data_as(C.c_void_p))
+        return film, secs
+
+    def finalize(self, film):
+        out = np.zeros_like(film)
+        f = _f(film)
+        self.L.ref_film_finalize(self.h, _fp(f), _fp(out))
+        return out
+
+    def accel_build(self):
+        return self.L.ref_accel_build(self.h)
+
+    def trace_closest(self, rays, surf=False, count_tests=False):
+        rays = _f(rays).reshape(-1, 8)
+        n = len(rays)
+        geom = np.zeros(n, np.int32)
+        prim = np.zeros(n, np.int32)
+        t = np.zeros(n, np.float32)
+        s = np.zeros((n, 8), np.float32) if surf else None
+        k = np.zeros(n, np.int32) if count_tests else None
+        self.L.ref_trace_closest(self.h, _fp(rays), C.c_int64(n), geom.ctypes.data_as(C.c_void_p),
+                                 prim.ctypes.data_as(C.c_void_p), _fp(t),
+                                 _fp(s) if surf else None,
+                                 k.ctypes.data_as(C.c_void_p) if count_tests else None)
+        out = {"geom": geom, "prim": prim, "t": t}
+        if surf:
+            out["surf"] = s
+        if count_tests:
+            out["n_prim_tests"] = k
+        return out
+
+    def trace_any(self, rays):
+        rays = _f(rays).reshape(-1, 8)
+        occ = np.zeros(len(rays), np.uint8)
+        self.L.ref_trace_any(self.h, _fp(rays), C.c_int64(len(rays)),
+                             occ.ctypes.data_as(C.c_void_p))
+        return occ
+
+    def primary_rays(self, si=0):
+        w, h = self.size
+        rays = np.zeros((h * w, 8), np.float32)
+        self.L.ref_primary_rays(self.h, si, _fp(rays))
+        return rays
+
+    def gen_rays(self, pfilm_u2):
+        a = _f(pfilm_u2).reshape(-1, 4)
+        rays = np.zeros((len(a), 8), np.float32)
+        self.L.ref_gen_rays(self.h, _fp(a), C.c_int64(len(a)), _fp(rays))
+        return rays
+
+    def geometry_aabbs(self):
+        n = self.L.ref_num_geometries(self.h)
+        out = np.zeros((n, 6), np.float32)
+        self.L.ref_geometry_aabbs(self.h, _fp(out))
+        return out
+
+    def shape_sample(self, g, p_u2_u1):
+        a = _f(p_u2_u1).reshape(-1, 6)
+        out = np.zeros((len(a), 12), np.float32)
+        self.L.ref_shape_sample(self.h, g, _fp(a), C.c_int64(len(a)), _fp(out))
+        return out
+
+    def bvh_tree(self, which=-1):
+        """Reference BVHImpl node array (which=-1 top level, k>=0 per-mesh tree k)."""
+        root = C.c_int32()
+        npr = C.c_int32()
+        n = self.L.ref_bvh_info(self.h, which, C.byref(root), C.byref(npr))
+        aabbs = np.zeros((n, 12), np.float32)
+        children = np.zeros((n, 2), np.int32)
+        leaf_range = np.zeros((n, 2), np.int32)
+        leaf_prims = np.zeros(max(npr.value, 1), np.int32)
+        self.L.ref_bvh_nodes(self.h, which, _fp(aabbs), children.ctypes.data_as(C.c_void_p),
+                             leaf_range.ctypes.data_as(C.c_void_p),
+                             leaf_prims.ctypes.data_as(C.c_void_p))
+        return {"root": root.value, "aabbs": aabbs, "children": children,
+                "leaf_range": leaf_range, "leaf_prims": leaf_prims[:npr.value]}
+
+    def bvh_indices(self):
+        n = self.L.ref_bvh_num_indices(self.h)
+        out = np.zeros(n, np.int32)
+        self.L.ref_bvh_indices(self.h, out.ctypes.data_as(C.c_void_p))
+        return out, self.L.ref_bvh_num_lbvh(self.h)
+
+
+def bluenoise(spp, px, py, index, dim):
+    return lib().ref_bluenoise(spp, px, py, index, dim)
+
+
+def sampler_stream(spp, px, py, sample_index, n_rand, pattern, n_samples):
+    width = sum(1 if c == "1" else 2 for c in pattern)
+    r = np.zeros(max(n_rand, 1), np.float32)
+    d = np.zeros(max(width * n_samples, 1), np.float32)
+    lib().ref_sampler_stream(spp, px, py, sample_index, n_rand, _fp(r), pattern.encode(),
+                             n_samples, _fp(d))
+    return r[:n_rand], d[:width * n_samples].reshape(n_samples, width)
+
+
+def spawn_rays(p_n_wo_dist):
+    a = _f(p_n_wo_dist).reshape(-1, 10)
+    rays = np.zeros((len(a), 8), np.float32)
+    lib().ref_spawn_rays(_fp(a), C.c_int64(len(a)), _fp(rays))
+    return rays
