@@ -1,0 +1,171 @@
+// api.cu -- context lifetime, sampler tables, and the traversal test hooks of include/pine_b200.h.
+#include <cstring>
+#include <string>
+
+#include "context.h"
+#include "kernels.cuh"
+
+using namespace pb2;
+
+namespace pb2 {
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+}  // namespace pb2
+
+extern "C" const char* pb2_last_error(void) { return g_error.c_str(); }
+
+extern "C" int pb2_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+extern "C" int pb2_create(int device, pb2_context** out) {
+  if (!out) { set_error("null out pointer"); return PB2_E_INVALID; }
+  *out = nullptr;
+  auto* ctx = new pb2_context();
+  ctx->device = device;
+  if (device >= 0) {
+    int n = pb2_device_count();
+    if (device >= n) {
+      delete ctx;
+      set_error("CUDA device " + std::to_string(device) + " not available (" + std::to_string(n) +
+                " visible); this backend has no CPU fallback");
+      return PB2_E_CUDA;
+    }
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev2);
+    if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev3);
+    if (e != cudaSuccess) {
+      set_error(std::string("pb2_create: ") + cudaGetErrorString(e));
+      delete ctx;
+      return PB2_E_CUDA;
+    }
+  }
+  *out = ctx;
+  return PB2_OK;
+}
+
+extern "C" void pb2_destroy(pb2_context* ctx) {
+  if (!ctx) return;
+  if (ctx->device >= 0) {
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    free_wavefront(ctx);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->ev2) cudaEventDestroy(ctx->ev2);
+    if (ctx->ev3) cudaEventDestroy(ctx->ev3);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  }
+  delete ctx;
+}
+
+static int log2_exact(int v) {
+  for (int i = 0; i < 9; i++)
+    if ((1 << i) == v) return i;
+  return -1;
+}
+
+extern "C" int pb2_upload_sampler_tables(pb2_context* ctx, int spp_pow2, const uint8_t* sobol,
+                                         const uint8_t* scramble, const uint8_t* rank) {
+  if (!ctx || !sobol || !scramble || !rank) { set_error("null argument"); return PB2_E_INVALID; }
+  int k = log2_exact(spp_pow2);
+  if (k < 0) { set_error("sampler tables exist for spp in {1,2,4,...,256} only"); return PB2_E_INVALID; }
+  ctx->tables[k].sobol.assign(sobol, sobol + 256 * 256);
+  ctx->tables[k].scramble.assign(scramble, scramble + 128 * 128 * 8);
+  ctx->tables[k].rank.assign(rank, rank + 128 * 128 * 8);
+  ctx->has_tables[k] = true;
+  if (ctx->tables_spp == spp_pow2) ctx->tables_spp = 0;  // force re-upload
+  return PB2_OK;
+}
+
+// Makes the tables of `spp` the active device tables.
+int pb2::activate_tables(pb2_context* ctx, int spp) {
+  int k = log2_exact(spp);
+  if (k < 0 || !ctx->has_tables[k]) {
+    set_error("no sampler tables uploaded for spp=" + std::to_string(spp));
+    return PB2_E_STATE;
+  }
+  if (ctx->tables_spp != spp) {
+    PB2_CUDA_CHECK(ctx->tab_sobol.upload(ctx->tables[k].sobol));
+    PB2_CUDA_CHECK(ctx->tab_scramble.upload(ctx->tables[k].scramble));
+    PB2_CUDA_CHECK(ctx->tab_rank.upload(ctx->tables[k].rank));
+    ctx->tables_spp = spp;
+  }
+  ctx->scene.sobol = ctx->tab_sobol.as<uint8_t>();
+  ctx->scene.scramble = ctx->tab_scramble.as<uint8_t>();
+  ctx->scene.rank = ctx->tab_rank.as<uint8_t>();
+  return PB2_OK;
+}
+
+static int require_device_scene(pb2_context* ctx) {
+  if (!ctx) { set_error("null context"); return PB2_E_INVALID; }
+  if (ctx->device < 0) { set_error("host-only context: no CUDA device, and there is no CPU fallback"); return PB2_E_CUDA; }
+  if (!ctx->scene_ready) { set_error("pb2_upload_scene has not succeeded on this context"); return PB2_E_STATE; }
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  return PB2_OK;
+}
+
+extern "C" int pb2_trace_closest_device(pb2_context* ctx, const float* rays_dev, size_t n, int accel,
+                                        int32_t* geom_dev, int32_t* prim_dev, float* t_dev,
+                                        void* cuda_stream) {
+  int rc = require_device_scene(ctx);
+  if (rc) return rc;
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
+  launch_trace_closest(ctx->scene, rays_dev, n, accel, geom_dev, prim_dev, t_dev, nullptr, st);
+  ctx->counters.kernel_launches++;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  return PB2_OK;
+}
+
+extern "C" int pb2_trace_closest(pb2_context* ctx, const float* rays, size_t n, int accel,
+                                 int32_t* geom, int32_t* prim, float* t, float* surf) {
+  int rc = require_device_scene(ctx);
+  if (rc) return rc;
+  if (n == 0) return PB2_OK;
+  PB2_CUDA_CHECK(ctx->rays.reserve(n * 32));
+  PB2_CUDA_CHECK(ctx->out_geom.reserve(n * 4));
+  PB2_CUDA_CHECK(ctx->out_prim.reserve(n * 4));
+  PB2_CUDA_CHECK(ctx->out_t.reserve(n * 4));
+  if (surf) PB2_CUDA_CHECK(ctx->out_surf.reserve(n * 32));
+  cudaStream_t st = ctx->stream;
+  PB2_CUDA_CHECK(cudaMemcpyAsync(ctx->rays.ptr, rays, n * 32, cudaMemcpyHostToDevice, st));
+  launch_trace_closest(ctx->scene, ctx->rays.as<float>(), n, accel, ctx->out_geom.as<int32_t>(),
+                       ctx->out_prim.as<int32_t>(), ctx->out_t.as<float>(),
+                       surf ? ctx->out_surf.as<float>() : nullptr, st);
+  ctx->counters.kernel_launches++;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  PB2_CUDA_CHECK(cudaMemcpyAsync(geom, ctx->out_geom.ptr, n * 4, cudaMemcpyDeviceToHost, st));
+  PB2_CUDA_CHECK(cudaMemcpyAsync(prim, ctx->out_prim.ptr, n * 4, cudaMemcpyDeviceToHost, st));
+  PB2_CUDA_CHECK(cudaMemcpyAsync(t, ctx->out_t.ptr, n * 4, cudaMemcpyDeviceToHost, st));
+  if (surf) PB2_CUDA_CHECK(cudaMemcpyAsync(surf, ctx->out_surf.ptr, n * 32, cudaMemcpyDeviceToHost, st));
+  PB2_CUDA_CHECK(cudaStreamSynchronize(st));
+  return PB2_OK;
+}
+
+extern "C" int pb2_trace_any(pb2_context* ctx, const float* rays, size_t n, int accel,
+                             uint8_t* occluded) {
+  int rc = require_device_scene(ctx);
+  if (rc) return rc;
+  if (n == 0) return PB2_OK;
+  PB2_CUDA_CHECK(ctx->rays.reserve(n * 32));
+  PB2_CUDA_CHECK(ctx->out_occ.reserve(n));
+  cudaStream_t st = ctx->stream;
+  PB2_CUDA_CHECK(cudaMemcpyAsync(ctx->rays.ptr, rays, n * 32, cudaMemcpyHostToDevice, st));
+  launch_trace_any(ctx->scene, ctx->rays.as<float>(), n, accel, ctx->out_occ.as<uint8_t>(), st);
+  ctx->counters.kernel_launches++;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  PB2_CUDA_CHECK(cudaMemcpyAsync(occluded, ctx->out_occ.ptr, n, cudaMemcpyDeviceToHost, st));
+  PB2_CUDA_CHECK(cudaStreamSynchronize(st));
+  return PB2_OK;
+}
+
+extern "C" int pb2_get_counters(pb2_context* ctx, pb2_counters* out) {
+  if (!ctx || !out) { set_error("null argument"); return PB2_E_INVALID; }
+  *out = ctx->counters;
+  return PB2_OK;
+}

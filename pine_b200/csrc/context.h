@@ -1,0 +1,87 @@
+// context.h -- host-side state behind the opaque pb2_context of include/pine_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "bvh_build.h"
+#include "device_scene.h"
+
+namespace pb2 {
+
+void set_error(const std::string& msg);
+#define PB2_CUDA_CHECK(expr)                                                              \
+  do {                                                                                    \
+    cudaError_t e_ = (expr);                                                              \
+    if (e_ != cudaSuccess) {                                                              \
+      pb2::set_error(std::string(#expr) + ": " + cudaGetErrorString(e_));                 \
+      return PB2_E_CUDA;                                                                  \
+    }                                                                                     \
+  } while (0)
+
+// Owning device allocation that grows on demand.
+struct DBuf {
+  void* ptr = nullptr;
+  size_t cap = 0;
+  ~DBuf() { release(); }
+  void release() {
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    cap = 0;
+  }
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    release();
+    cudaError_t e = cudaMalloc(&ptr, bytes ? bytes : 16);
+    if (e == cudaSuccess) cap = bytes ? bytes : 16;
+    return e;
+  }
+  template <class T>
+  cudaError_t upload(const std::vector<T>& v) {
+    cudaError_t e = reserve(v.size() * sizeof(T));
+    if (e != cudaSuccess || v.empty()) return e;
+    return cudaMemcpy(ptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+  }
+  template <class T>
+  T* as() const { return reinterpret_cast<T*>(ptr); }
+};
+
+struct SamplerTables {
+  std::vector<uint8_t> sobol, scramble, rank;  // host copies per spp variant
+};
+
+struct WavefrontBuffers;  // render.cu
+
+}  // namespace pb2
+
+struct pb2_context {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
+  bool scene_ready = false;       // device copy valid
+  bool host_scene_ready = false;  // host trees valid (also on a host-only context, device = -1)
+
+  // host copies kept for the dump API
+  pb2::Tree2 top_tree;
+  std::vector<pb2::Tree2> mesh_trees;
+
+  pb2::DScene scene{};  // device pointers
+  pb2::DBuf nodes2, nodes8, leaves, leaf_tris, leaf_prims, top_prims, meshes, geoms, materials, lights;
+  pb2::DBuf aabbs, obbs, spheres, triangles, cones, rects, disks;
+  pb2::DBuf verts, tris, normals, uvs;
+  pb2::DBuf tab_sobol, tab_scramble, tab_rank;
+  int tables_spp = 0;
+  pb2::SamplerTables tables[9];  // index = log2(spp)
+  bool has_tables[9] = {};
+  bool needs_rng_in_shading = false;  // Uber / Subsurface present (they draw randf(), material.cpp:9-28)
+  int n_pixels = 0;
+
+  // scratch for trace hooks / render
+  pb2::DBuf rays, out_geom, out_prim, out_t, out_surf, out_occ;
+  pb2::DBuf film, film_accum;
+  pb2::WavefrontBuffers* wf = nullptr;
+
+  pb2_counters counters{};
+};

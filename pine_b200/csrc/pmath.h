@@ -29,8 +29,8 @@ PB2_HD int pmin(int a, int b) { return a < b ? a : b; }
 PB2_HD int pmax(int a, int b) { return a > b ? a : b; }
 PB2_HD float sqr(float x) { return x * x; }
 PB2_HD float pabs(float x) { return fabsf(x); }
-PB2_HD float pclamp(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
-PB2_HD float plerp(float t, float a, float b) { return t * b + (1.0f - t) * a; }  // vecmath.h:873
+PB2_HD float pclamp(float v, float lo, float hi) { return pmin(pmax(v, lo), hi); }  // psl math.h:110
+PB2_HD float plerp(float t, float a, float b) { return a * (1.0f - t) + b * t; }     // psl math.h:119
 
 struct V2 {
   float x, y;

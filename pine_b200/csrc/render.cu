@@ -1,0 +1,693 @@
+// render.cu -- the wavefront path tracer: PathIntegrator::render / ::radiance
+// (reference src/pine/impl/integrator/path.cpp:26-124) as sm_100a kernels.
+//
+// One wave = a block of (pixel, sample) slots. Per path depth k:
+//   k_trace   closest hit for every live ray                     (Accel::intersect, path.cpp:48)
+//   k_shade   surface, emission/termination, material -> BxDF, light sample + shadow ray,
+//             BSDF sample + next ray, vertex record k            (path.cpp:74-120)
+//   k_shadow  any-hit for the shadow rays; occluded => zero the vertex's light term (path.cpp:100)
+// and after the last depth
+//   k_fold    the recursion's unwind: X = min(beta*(nee + (X*f)*s), 8) deepest vertex first
+//             (path.cpp:119-121 -- the clamp makes the estimator non-linear in the suffix, so it
+//             cannot be a running throughput product)
+//   k_resolve per pixel L += sample radiance in sample order (path.cpp:36), one writer per pixel.
+// Queues are compacted with warp ballots (one atomic per warp); counts live in device memory and
+// every kernel is a grid-stride loop over a grid that is a multiple of the SM count, so a whole
+// render is a stream of launches with no host synchronisation in between.
+#include <algorithm>
+#include <cstdlib>
+#include <vector>
+
+#include "bsdf.cuh"
+#include "context.h"
+#include "kernels.cuh"
+#include "surface.cuh"
+#include "traverse.cuh"
+
+namespace pb2 {
+
+struct WaveView {
+  // ray queues (double buffered): o.xyz + tmax, d.xyz + slot
+  float4* ray_o[2];
+  float4* ray_d[2];
+  float4* hit;            // per queue entry: t, geom, prim, -
+  float4* sh_o;           // shadow queue: o.xyz + tmax
+  float4* sh_d;           // d.xyz + (slot | depth << 24)
+  // per slot
+  float* pv_pdf;          // Vertex::pdf
+  int* pv_flags;          // length | diffuse_length << 8 | is_delta << 16
+  int* dim;               // BlueSobolSampler::dimension
+  float4* term;           // terminal radiance X.rgb, number of vertex records
+  float4* vtx;            // [depth][slot][2]: (nee.rgb, s) (f.rgb, beta code)
+  // per pixel of this render's row range
+  uint2* rng;             // 2 x u64 state as 4 x u32
+  float4* lacc;           // running L
+  int* counts;            // [0..D] live rays per depth, [D+1..2D+1] shadow rays per depth
+  int n_slots;            // capacity of this wave
+  int pixels;             // pixels per sample layer in this wave
+  int pixel0;             // first pixel (linear index in the row range) of this wave
+  int width, row_begin;
+  int s_batch, sample0;   // samples [sample0, sample0 + s_batch) of every pixel in the wave
+  int max_depth;          // PathIntegrator::max_path_length
+  int accel;
+};
+
+struct WavefrontBuffers {
+  DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, rng, lacc, counts;
+  std::vector<int> host_counts;
+};
+
+void free_wavefront(pb2_context* ctx) {
+  delete ctx->wf;
+  ctx->wf = nullptr;
+}
+
+// ---- helpers ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int warp_compact(bool keep, int* counter) {
+  unsigned mask = __ballot_sync(0xffffffffu, keep);
+  int lane = threadIdx.x & 31;
+  int base = 0;
+  if (lane == 0 && mask) base = atomicAdd(counter, __popc(mask));
+  base = __shfl_sync(0xffffffffu, base, 0);
+  return base + __popc(mask & ((1u << lane) - 1));
+}
+// Warp-uniform grid-stride loop: every lane of a warp runs the same number of iterations.
+#define PB2_WARP_LOOP(i, n)                                                                       \
+  for (int base_ = (blockIdx.x * blockDim.x + threadIdx.x) & ~31, i = base_ + (threadIdx.x & 31); \
+       base_ < (n); base_ += gridDim.x * blockDim.x, i = base_ + (threadIdx.x & 31))
+
+__device__ __forceinline__ Rng load_rng(const uint2* p, int pixel) {
+  uint2 a = p[2 * pixel], b = p[2 * pixel + 1];
+  Rng g;
+  g.s0 = uint64_t(a.x) | (uint64_t(a.y) << 32);
+  g.s1 = uint64_t(b.x) | (uint64_t(b.y) << 32);
+  return g;
+}
+__device__ __forceinline__ void store_rng(uint2* p, int pixel, const Rng& g) {
+  p[2 * pixel] = make_uint2(uint32_t(g.s0), uint32_t(g.s0 >> 32));
+  p[2 * pixel + 1] = make_uint2(uint32_t(g.s1), uint32_t(g.s1 >> 32));
+}
+
+// ---- raygen (path.cpp:32-35) -----------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_raygen(DScene sc, WaveView w, int seed_sample, int first_wave_of_pixel) {
+  PB2_WARP_LOOP(i, w.pixels) {
+    if (i >= w.pixels) continue;
+    int pix = w.pixel0 + i;  // linear in the row range
+    int px = pix % w.width, py = w.row_begin + pix / w.width;
+    Rng g = first_wave_of_pixel ? rng_seed(murmur_pixel(px, py, seed_sample)) : load_rng(w.rng, pix);
+    for (int s = 0; s < w.s_batch; s++) {
+      float r0 = rng_nextf(g), r1 = rng_nextf(g), r2 = rng_nextf(g), r3 = rng_nextf(g);
+      V2 p_film((float(px) + r0) / float(sc.camera.width), (float(py) + r1) / float(sc.camera.height));
+      Ray r = camera_ray(sc.camera, p_film, V2(r2, r3));
+      int slot = s * w.pixels + i;
+      w.ray_o[0][slot] = make_float4(r.o.x, r.o.y, r.o.z, r.tmax);
+      w.ray_d[0][slot] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float(slot));
+      w.pv_pdf[slot] = 0.0f;
+      w.pv_flags[slot] = 1 << 16;  // Vertex::first_vertex(): length 0, diffuse_length 0, is_delta
+      w.dim[slot] = 0;
+      w.term[slot] = make_float4(0, 0, 0, __int_as_float(0));
+    }
+    store_rng(w.rng, pix, g);
+    if (i == 0) w.counts[0] = w.pixels * w.s_batch;
+  }
+}
+
+// ---- closest hit -------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_trace(DScene sc, WaveView w, int depth) {
+  const int n = w.counts[depth];
+  const float4* ro = w.ray_o[depth & 1];
+  const float4* rd = w.ray_d[depth & 1];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    float4 a = ro[i], b = rd[i];
+    Ray ray;
+    ray.o = V3(a.x, a.y, a.z);
+    ray.d = V3(b.x, b.y, b.z);
+    ray.tmin = 0.0f;
+    ray.tmax = a.w;
+    Hit h;
+    bool hit = w.accel == 0 ? closest_wide(sc, ray, h) : closest_ref_order(sc, ray, h);
+    w.hit[i] = make_float4(ray.tmax, __int_as_float(hit ? h.geom : -1), __int_as_float(h.prim), 0.0f);
+  }
+}
+
+// ---- material -> BxDF (material.h:30-121, material.cpp:9-28) -------------------------------------------------
+__device__ __forceinline__ bool with_probability(float prob, Rng& g) {  // sampler.h:317-324
+  if (prob == 0) return false;
+  if (prob == 1) return true;
+  return rng_nextf(g) < prob;
+}
+__device__ inline Bxdf material_bxdf(const DScene& sc, const pb2_material& m, V3 wi_world, V3 n,
+                                     float min_roughness, bool diffused, BlueSampler& smp, Rng& g) {
+  Bxdf b;
+  b.albedo = V3(m.color[0], m.color[1], m.color[2]);
+  b.roughness = m.roughness;
+  b.ior = m.ior;
+  b.sigma_s = V3(m.sigma_s[0], m.sigma_s[1], m.sigma_s[2]);
+  b.kind = BX_DIFFUSE;
+  switch (m.kind) {
+    case PB2_MAT_DIFFUSE: b.kind = BX_DIFFUSE; break;
+    case PB2_MAT_METAL: b.kind = BX_CONDUCTOR; b.roughness = pmax(m.roughness, min_roughness); break;
+    case PB2_MAT_GLOSSY: b.kind = BX_DIFF_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); break;
+    case PB2_MAT_GLASS: b.kind = BX_REFR_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); break;
+    case PB2_MAT_UBER:
+      if (with_probability(m.metallic, g)) b.kind = BX_CONDUCTOR;
+      else if (with_probability(m.transmission, g)) b.kind = BX_REFR_DIELECTRIC;
+      else b.kind = BX_DIFF_DIELECTRIC;
+      break;
+    case PB2_MAT_SUBSURFACE: {
+      b.ior = 1.4f;  // SubsurfaceMaterial::ior (material.h:103)
+      float fr = FrDielectric(dot(wi_world, n), b.ior);
+      if (blue_get1d(sc, smp) < fr) { b.kind = BX_REFRACTIVE; b.roughness = pmax(m.roughness, min_roughness); }
+      else if (diffused) b.kind = BX_DIFFUSE;
+      else b.kind = BX_BSSRDF;
+    } break;
+  }
+  return b;
+}
+
+// BSSRDF::sample_p (bxdf.cpp:329-357): random walk inside the hit shape only. For analytic shapes
+// the reference's Shape::intersect leaves the exit interaction untouched (p = n = 0); reproduced.
+__device__ inline bool bssrdf_walk(const DScene& sc, const Bxdf& b, int geom, V3 wi_world, Surf& it,
+                                   BlueSampler& smp, Rng& g, V3& beta, V3& wi_out) {
+  V3 p = it.p;
+  V3 w = -wi_world;
+  if (!Refract(wi_world, it.n, b.ior, w)) return false;
+  int channel = int(rng_nextf(g) * 3);
+  beta = V3(0.0f);
+  beta[channel] = 3;
+  float sigma_t_inv = 1 / b.sigma_s[channel];
+  DGeom gm = sc.geoms[geom];
+  for (int i = 0; i < 4096; i++) {
+    Ray ray;
+    if (i == 0) {  // spawn_ray(p, n, w) (ray.h:39-46)
+      ray.o = offset_ray_origin(p, it.n);
+      ray.d = w; ray.tmin = 0; ray.tmax = kFloatMax * (1.0f - 1e-3f);
+    } else {
+      ray.o = p; ray.d = w; ray.tmin = 0; ray.tmax = kFloatMax;
+    }
+    Surf exit_it;
+    exit_it.p = V3(); exit_it.n = V3(); exit_it.uv = V2();
+    bool hit;
+    if (gm.kind == PB2_SHAPE_MESH) {
+      const DMesh& m = sc.meshes[gm.index];
+      Octant q = make_octant(ray);
+      int prim = -1;
+      hit = walk_ref_order<false>(sc, m.tree, ray, q, [&](int tri) {
+        V3 v0, v1, v2;
+        mesh_tri(sc, m, tri, v0, v1, v2);
+        bool ok = tri_intersect(ray, v0, v1, v2);
+        if (ok) prim = tri;
+        return ok;
+      });
+      if (hit) surface_info(sc, geom, prim, ray.o + ray.tmax * ray.d, exit_it);
+    } else {
+      hit = shape_intersect(sc, gm.kind, gm.index, ray);
+    }
+    if (!hit) return false;
+    float t = -logf(1 - blue_get1d(sc, smp)) * sigma_t_inv;
+    if (ray.tmax < t) {
+      wi_out = -w;
+      it.p = exit_it.p;
+      it.n = exit_it.n;
+      return true;
+    }
+    p = ray.o + t * ray.d;
+    w = uniform_sphere(blue_get2d(sc, smp));
+  }
+  return false;
+}
+
+// ---- shade ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void store_vertex(const WaveView& w, int depth, int slot, V3 nee, float s, V3 f, int beta_code) {
+  float4* v = w.vtx + (size_t(depth) * w.n_slots + slot) * 2;
+  v[0] = make_float4(nee.x, nee.y, nee.z, s);
+  v[1] = make_float4(f.x, f.y, f.z, __int_as_float(beta_code));
+}
+
+__global__ void __launch_bounds__(128) k_shade(DScene sc, WaveView w, int depth) {
+  const int n = w.counts[depth];
+  const int cur = depth & 1, nxt = cur ^ 1;
+  int* next_count = w.counts + depth + 1;
+  int* shadow_count = w.counts + w.max_depth + 1 + depth;
+  PB2_WARP_LOOP(i, n) {
+    const bool valid = i < n;
+    bool emit_next = false, emit_shadow = false;
+    Ray next_ray, shadow_ray;
+    int slot = 0;
+    if (valid) {
+      float4 a = w.ray_o[cur][i], b = w.ray_d[cur][i], hrec = w.hit[i];
+      V3 ro(a.x, a.y, a.z), rd(b.x, b.y, b.z);
+      slot = __float_as_int(b.w);
+      const float t = hrec.x;
+      const int geom = __float_as_int(hrec.y), prim = __float_as_int(hrec.z);
+      const int flags = w.pv_flags[slot];
+      const int pv_length = flags & 0xff, pv_diffuse = (flags >> 8) & 0xff;
+      const bool pv_delta = (flags >> 16) & 1;
+      const V3 wi = -rd;
+      // terminal radiance of this path (if it ends here) and number of vertex records so far
+      V3 X(0.0f);
+      bool terminated = true;
+      if (geom >= 0) {
+        Surf it;
+        surface_info(sc, geom, prim, ro + t * rd, it);
+        const DGeom g = sc.geoms[geom];
+        const pb2_material m = sc.materials[g.material];
+        if (m.kind == PB2_MAT_EMISSIVE) {
+          // Lo += Tr * le; light_pdf = light_sampler.pdf(ray, it) unless the previous vertex was delta
+          if (!(dot(wi, it.n) < 0.0f)) X = V3(1.0f) * V3(m.color[0], m.color[1], m.color[2]);
+          if (!pv_delta && depth > 0) {
+            float light_pdf = shape_pdf(sc, geom, ro, rd, t, it.n) / float(sc.n_lights);
+            float bs_pdf = w.pv_pdf[slot];
+            float mis = balance_heuristic(bs_pdf, light_pdf);
+            float4* v = w.vtx + (size_t(depth - 1) * w.n_slots + slot) * 2;
+            v[0].w = v[0].w * mis;  // s = cosine / bs.pdf * mis
+          }
+        } else if (pv_length + 1 < w.max_depth) {
+          terminated = false;
+          int pix = w.pixel0 + slot % w.pixels;
+          int px = pix % w.width, py = w.row_begin + pix / w.width;
+          BlueSampler smp{px, py, w.sample0 + slot / w.pixels, w.dim[slot]};
+          Rng g_rng;
+          const bool uses_rng = m.kind == PB2_MAT_UBER || m.kind == PB2_MAT_SUBSURFACE;
+          if (uses_rng) g_rng = load_rng(w.rng, pix);
+          const bool diffused = pv_diffuse > 0;
+          Bxdf bx = material_bxdf(sc, m, wi, it.n, diffused ? 0.6f : 0.0f, diffused, smp, g_rng);
+          M3 l2w = coordinate_system(it.n);
+          M3 w2l = transpose(l2w);
+          bx.wi = w2l * wi;
+          int beta_code = 0;
+          bool alive = true;
+          if (bx.kind == BX_BSSRDF) {
+            V3 beta, wi2;
+            if (bssrdf_walk(sc, bx, geom, wi, it, smp, g_rng, beta, wi2)) {
+              beta_code = beta.x != 0 ? 1 : (beta.y != 0 ? 2 : 3);
+              l2w = coordinate_system(it.n);
+              w2l = transpose(l2w);
+              bx.wi = w2l * wi2;
+            }
+          }
+          if (uses_rng) store_rng(w.rng, pix, g_rng);
+          // next-event estimation (path.cpp:98-113); draws get2d then get1d (g++ evaluates the
+          // arguments of light_sampler.sample(p, get1d(), get2d()) right to left, lightsampler.h:27)
+          V3 nee(0.0f);
+          if (!bxdf_is_delta(bx)) {
+            V2 u2 = blue_get2d(sc, smp);
+            float u1 = blue_get1d(sc, smp);
+            if (sc.n_lights > 0) {
+              u1 *= sc.n_lights;
+              int index = int(u1);
+              int lgeom = sc.lights[index];
+              ShapeSample ss;
+              if (shape_sample(sc, lgeom, it.p, u2, u1 - index, ss)) {
+                const pb2_material lm = sc.materials[sc.geoms[lgeom].material];
+                V3 le = dot(-ss.w, ss.n) < 0.0f ? V3(0.0f) : V3(lm.color[0], lm.color[1], lm.color[2]);
+                if (!is_zero(le)) {
+                  float ls_pdf = ss.pdf / sc.n_lights;
+                  float cosine = absdot(ss.w, it.n);
+                  V3 wo = w2l * ss.w;
+                  V3 f = bxdf_f(bx, wo);
+                  float mis = balance_heuristic(ls_pdf, bxdf_pdf(bx, wo));
+                  nee = le * V3(1.0f) * cosine * f / ls_pdf * mis;
+                  shadow_ray = spawn_ray(it.p, it.n, ss.w, ss.distance);
+                  emit_shadow = true;
+                }
+              }
+            }
+          }
+          BsdfSample bs;
+          if (bxdf_sample(sc, bx, smp, bs)) {
+            V3 wo_world = l2w * bs.wo;
+            float cosine = absdot(wo_world, it.n);
+            store_vertex(w, depth, slot, nee, cosine / bs.pdf * 1.0f, bs.f, beta_code);
+            next_ray = spawn_ray(it.p, it.n, wo_world);
+            emit_next = true;
+            w.pv_pdf[slot] = bs.pdf;
+            w.pv_flags[slot] = (pv_length + 1) | ((pv_diffuse + (bs.is_delta ? 0 : 1)) << 8) | (int(bs.is_delta) << 16);
+          } else {
+            store_vertex(w, depth, slot, nee, 0.0f, V3(0.0f), beta_code);
+            alive = false;
+          }
+          w.dim[slot] = smp.dim;
+          w.term[slot] = make_float4(0, 0, 0, __int_as_float(depth + 1));
+          (void)alive;
+        }
+      }
+      if (terminated) w.term[slot] = make_float4(X.x, X.y, X.z, __int_as_float(depth));
+    }
+    int pos = warp_compact(emit_next, next_count);
+    if (emit_next) {
+      w.ray_o[nxt][pos] = make_float4(next_ray.o.x, next_ray.o.y, next_ray.o.z, next_ray.tmax);
+      w.ray_d[nxt][pos] = make_float4(next_ray.d.x, next_ray.d.y, next_ray.d.z, __int_as_float(slot));
+    }
+    int spos = warp_compact(emit_shadow, shadow_count);
+    if (emit_shadow) {
+      w.sh_o[spos] = make_float4(shadow_ray.o.x, shadow_ray.o.y, shadow_ray.o.z, shadow_ray.tmax);
+      w.sh_d[spos] = make_float4(shadow_ray.d.x, shadow_ray.d.y, shadow_ray.d.z, __int_as_float(slot));
+    }
+  }
+}
+
+// ---- shadow rays (RTIntegrator::hit, path.cpp:100) ------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_shadow(DScene sc, WaveView w, int depth) {
+  const int n = w.counts[w.max_depth + 1 + depth];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    float4 a = w.sh_o[i], b = w.sh_d[i];
+    Ray ray;
+    ray.o = V3(a.x, a.y, a.z);
+    ray.d = V3(b.x, b.y, b.z);
+    ray.tmin = 0.0f;
+    ray.tmax = a.w;
+    bool occluded = w.accel == 0 ? any_wide(sc, ray) : any_ref_order(sc, ray);
+    if (occluded) {
+      int slot = __float_as_int(b.w);
+      float4* v = w.vtx + (size_t(depth) * w.n_slots + slot) * 2;
+      v[0].x = 0.0f; v[0].y = 0.0f; v[0].z = 0.0f;
+    }
+  }
+}
+
+// ---- unwind + per-pixel accumulation -----------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_fold_resolve(WaveView w) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w.pixels; i += gridDim.x * blockDim.x) {
+    int pix = w.pixel0 + i;
+    float4 acc = w.lacc[pix];
+    V3 L(acc.x, acc.y, acc.z);
+    for (int s = 0; s < w.s_batch; s++) {
+      int slot = s * w.pixels + i;
+      float4 tm = w.term[slot];
+      V3 X(tm.x, tm.y, tm.z);
+      int nv = __float_as_int(tm.w);
+      for (int k = nv - 1; k >= 0; k--) {
+        const float4* v = w.vtx + (size_t(k) * w.n_slots + slot) * 2;
+        float4 v0 = v[0], v1 = v[1];
+        V3 lo = V3(v0.x, v0.y, v0.z) + X * V3(v1.x, v1.y, v1.z) * v0.w;
+        int code = __float_as_int(v1.w);
+        V3 beta = code == 0 ? V3(1.0f) : V3(code == 1 ? 3.0f : 0.0f, code == 2 ? 3.0f : 0.0f, code == 3 ? 3.0f : 0.0f);
+        V3 c = V3(1.0f) * beta * lo;
+        X = V3(pmin(c.x, 8.0f), pmin(c.y, 8.0f), pmin(c.z, 8.0f));
+      }
+      L += X;
+    }
+    w.lacc[pix] = make_float4(L.x, L.y, L.z, 0.0f);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_film(const float4* lacc, float4* film, int pixels, int pixel_offset,
+                                            int spp, float alpha) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < pixels; i += gridDim.x * blockDim.x) {
+    float4 a = lacc[i];
+    film[pixel_offset + i] = make_float4(a.x / float(spp), a.y / float(spp), a.z / float(spp), alpha);
+  }
+}
+
+}  // namespace pb2
+
+// ======================================================================================================
+// host driver
+// ======================================================================================================
+using namespace pb2;
+
+namespace {
+
+int env_int(const char* name, int dflt) {
+  const char* v = std::getenv(name);
+  return v ? std::atoi(v) : dflt;
+}
+int sm_grid(int work_items, int block, int max_waves_per_sm) {
+  long want = (long(work_items) + block - 1) / block;
+  long cap = long(kNumSMs) * max_waves_per_sm;
+  if (want > cap) want = cap;
+  long g = ((want + kNumSMs - 1) / kNumSMs) * kNumSMs;
+  return int(g > 0 ? g : kNumSMs);
+}
+
+int check_params(pb2_context* ctx, const pb2_render_params* p) {
+  if (!ctx || !p) { set_error("null argument"); return PB2_E_INVALID; }
+  if (ctx->device < 0) { set_error("host-only context: no CUDA device, and there is no CPU fallback"); return PB2_E_CUDA; }
+  if (!ctx->scene_ready) { set_error("pb2_upload_scene has not succeeded on this context"); return PB2_E_STATE; }
+  if (p->max_path_length <= 0) {  // path.cpp:12-13
+    set_error("`PathIntegrator` expect `max_path_length` to be positive, get " + std::to_string(p->max_path_length));
+    return PB2_E_INVALID;
+  }
+  if (p->max_path_length > 250) { set_error("max_path_length > 250 is not supported"); return PB2_E_UNSUPPORTED; }
+  const int h = ctx->scene.camera.height;
+  if (p->spp <= 0 || p->spp > 256 || (p->spp & (p->spp - 1))) {
+    set_error("spp must be BlueSobolSampler::spp(): a power of two <= 256");
+    return PB2_E_INVALID;
+  }
+  if (p->row_begin < 0 || p->row_end > h || p->row_begin > p->row_end || p->sample_begin < 0 ||
+      p->sample_end > p->spp || p->sample_begin > p->sample_end) {
+    set_error("row/sample range out of bounds");
+    return PB2_E_INVALID;
+  }
+  return PB2_OK;
+}
+
+}  // namespace
+
+extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, void* cuda_stream,
+                                 float** film_rgba_device) {
+  int rc = check_params(ctx, p);
+  if (rc) return rc;
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  rc = activate_tables(ctx, p->spp);
+  if (rc) return rc;
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
+  const DScene& sc = ctx->scene;
+  const int W = sc.camera.width, H = sc.camera.height;
+  const int D = p->max_path_length;
+  const int rows = p->row_end - p->row_begin;
+  const long P = long(rows) * W;
+  const int n_samples = p->sample_end - p->sample_begin;
+
+  PB2_CUDA_CHECK(ctx->film.reserve(size_t(W) * H * 16));
+  PB2_CUDA_CHECK(cudaMemsetAsync(ctx->film.ptr, 0, size_t(W) * H * 16, st));
+  if (film_rgba_device) *film_rgba_device = ctx->film.as<float>();
+  ctx->counters.last_render_ms = 0;
+  if (P == 0 || n_samples == 0) { PB2_CUDA_CHECK(cudaStreamSynchronize(st)); return PB2_OK; }
+
+  // ---- wave plan ----
+  const long max_slots = long(env_int("PB2_MAX_SLOTS", 1 << 22));
+  long pixels_per_wave = std::min(P, std::max(long(W), (max_slots / W) * W));
+  int s_batch = int(std::max(1L, std::min(long(n_samples), max_slots / pixels_per_wave)));
+  if (ctx->needs_rng_in_shading) s_batch = 1;  // randf() draws in shading share the per-pixel RNG stream
+  const long n_slots = pixels_per_wave * s_batch;
+  const int n_vtx = std::max(D - 1, 1);
+
+  if (!ctx->wf) ctx->wf = new WavefrontBuffers();
+  WavefrontBuffers& B = *ctx->wf;
+  for (int k = 0; k < 2; k++) {
+    PB2_CUDA_CHECK(B.ray_o[k].reserve(n_slots * 16));
+    PB2_CUDA_CHECK(B.ray_d[k].reserve(n_slots * 16));
+  }
+  PB2_CUDA_CHECK(B.hit.reserve(n_slots * 16));
+  PB2_CUDA_CHECK(B.sh_o.reserve(n_slots * 16));
+  PB2_CUDA_CHECK(B.sh_d.reserve(n_slots * 16));
+  PB2_CUDA_CHECK(B.pv_pdf.reserve(n_slots * 4));
+  PB2_CUDA_CHECK(B.pv_flags.reserve(n_slots * 4));
+  PB2_CUDA_CHECK(B.dim.reserve(n_slots * 4));
+  PB2_CUDA_CHECK(B.term.reserve(n_slots * 16));
+  PB2_CUDA_CHECK(B.vtx.reserve(size_t(n_slots) * n_vtx * 32));
+  PB2_CUDA_CHECK(B.rng.reserve(size_t(P) * 16));
+  PB2_CUDA_CHECK(B.lacc.reserve(size_t(P) * 16));
+  PB2_CUDA_CHECK(cudaMemsetAsync(B.lacc.ptr, 0, size_t(P) * 16, st));
+
+  const int n_pixel_waves = int((P + pixels_per_wave - 1) / pixels_per_wave);
+  const int n_sample_waves = (n_samples + s_batch - 1) / s_batch;
+  const int n_waves = n_pixel_waves * n_sample_waves;
+  const int cstride = 2 * (D + 1);
+  PB2_CUDA_CHECK(B.counts.reserve(size_t(n_waves) * cstride * 4));
+  PB2_CUDA_CHECK(cudaMemsetAsync(B.counts.ptr, 0, size_t(n_waves) * cstride * 4, st));
+
+  WaveView w{};
+  for (int k = 0; k < 2; k++) { w.ray_o[k] = B.ray_o[k].as<float4>(); w.ray_d[k] = B.ray_d[k].as<float4>(); }
+  w.hit = B.hit.as<float4>(); w.sh_o = B.sh_o.as<float4>(); w.sh_d = B.sh_d.as<float4>();
+  w.pv_pdf = B.pv_pdf.as<float>(); w.pv_flags = B.pv_flags.as<int>(); w.dim = B.dim.as<int>();
+  w.term = B.term.as<float4>(); w.vtx = B.vtx.as<float4>();
+  w.rng = B.rng.as<uint2>(); w.lacc = B.lacc.as<float4>();
+  w.n_slots = int(n_slots); w.width = W; w.row_begin = p->row_begin; w.max_depth = D; w.accel = p->accel;
+
+  uint64_t launches = 0;
+  PB2_CUDA_CHECK(cudaEventRecord(ctx->ev0, st));
+  int wave = 0;
+  for (int pw = 0; pw < n_pixel_waves; pw++) {
+    w.pixel0 = int(long(pw) * pixels_per_wave);
+    w.pixels = int(std::min(pixels_per_wave, P - w.pixel0));
+    for (int sw = 0; sw < n_sample_waves; sw++, wave++) {
+      w.sample0 = p->sample_begin + sw * s_batch;
+      w.s_batch = std::min(s_batch, p->sample_end - w.sample0);
+      w.counts = B.counts.as<int>() + size_t(wave) * cstride;
+      const int live = w.pixels * w.s_batch;
+      k_raygen<<<sm_grid(w.pixels, 256, 8), 256, 0, st>>>(sc, w, p->sample_begin, sw == 0);
+      launches++;
+      for (int depth = 0; depth < D; depth++) {
+        k_trace<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
+        k_shade<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
+        launches += 2;
+        if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
+          k_shadow<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
+          launches++;
+        }
+      }
+      k_fold_resolve<<<sm_grid(w.pixels, 256, 8), 256, 0, st>>>(w);
+      launches++;
+    }
+  }
+  const float alpha = float(n_samples) / float(p->spp);
+  k_film<<<sm_grid(int(P), 256, 8), 256, 0, st>>>(B.lacc.as<float4>(), ctx->film.as<float4>(), int(P),
+                                                  p->row_begin * W, p->spp, alpha);
+  launches++;
+  PB2_CUDA_CHECK(cudaEventRecord(ctx->ev1, st));
+  PB2_CUDA_CHECK(cudaGetLastError());
+  B.host_counts.resize(size_t(n_waves) * cstride);
+  PB2_CUDA_CHECK(cudaMemcpyAsync(B.host_counts.data(), B.counts.ptr, B.host_counts.size() * 4,
+                                 cudaMemcpyDeviceToHost, st));
+  PB2_CUDA_CHECK(cudaStreamSynchronize(st));
+  float ms = 0;
+  PB2_CUDA_CHECK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  ctx->counters.last_render_ms = ms;
+  for (int wv = 0; wv < n_waves; wv++)
+    for (int k = 0; k <= D; k++) {
+      ctx->counters.closest_rays += uint64_t(B.host_counts[size_t(wv) * cstride + k]);
+      ctx->counters.shadow_rays += uint64_t(B.host_counts[size_t(wv) * cstride + D + 1 + k]);
+    }
+  ctx->counters.camera_samples += uint64_t(P) * n_samples;
+  ctx->counters.kernel_launches += launches;
+  return PB2_OK;
+}
+
+extern "C" int pb2_render(pb2_context* ctx, const pb2_render_params* p, float* film_rgba_host) {
+  if (!film_rgba_host) { set_error("null film pointer"); return PB2_E_INVALID; }
+  float* dev = nullptr;
+  int rc = pb2_render_device(ctx, p, nullptr, &dev);
+  if (rc) return rc;
+  const size_t bytes = size_t(ctx->scene.camera.width) * ctx->scene.camera.height * 16;
+  PB2_CUDA_CHECK(cudaMemcpyAsync(film_rgba_host, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  return PB2_OK;
+}
+
+// ---- film epilogue: Film::finalize + to_uint8 (film.cpp:21-27, color.cpp:6-23, fileio.cpp:42-54) --------
+namespace pb2 {
+__device__ __forceinline__ V3 uncharted2_map(V3 x) {
+  const V3 A(0.15f), B(0.50f), C(0.10f), D(0.20f), E(0.02f), F(0.30f);
+  return (x * (A * x + C * B) + D * E) / (x * (A * x + B) + D * F) - E / F;
+}
+__global__ void k_finalize(const float4* film, int w, int h, int tonemapper, int flip_y, float4* mapped,
+                           uchar4* rgba8) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w * h; i += gridDim.x * blockDim.x) {
+    float4 px = film[i];
+    V3 v = V3(px.x, px.y, px.z) * 1.0f;  // finalize(scale = 1)
+    V3 c;
+    if (tonemapper == 0) {
+      c = uncharted2_map(v * 2.0f) * V3(1.0f) / uncharted2_map(V3(11.2f));
+    } else {
+      const float a = 2.51f, b = 0.03f, cc = 2.43f, d = 0.59f, e = 0.14f;
+      V3 r = (v * (a * v + V3(b))) / (v * (cc * v + V3(d)) + V3(e));
+      c = V3(pclamp(r.x, 0.0f, 1.0f), pclamp(r.y, 0.0f, 1.0f), pclamp(r.z, 0.0f, 1.0f));
+    }
+    if (mapped) mapped[i] = make_float4(c.x, c.y, c.z, 1.0f);
+    if (rgba8) {
+      int x = i % w, y = i / w;
+      int o = flip_y ? (h - 1 - y) * w + x : i;
+      auto q = [](float f) { return (unsigned char)pclamp(powf(f, 1.0f / 2.2f) * 256.0f, 0.0f, 255.0f); };
+      rgba8[o] = make_uchar4(q(c.x), q(c.y), q(c.z), q(1.0f));
+    }
+  }
+}
+
+// ---- known-answer kernels ---------------------------------------------------------------------------------
+__global__ void k_test_sampler(DScene sc, int px, int py, int sample_index, int n_rand, float* out_rand,
+                               const char* pattern, int n_pattern, int n_samples, float* out_draws) {
+  if (blockIdx.x || threadIdx.x) return;
+  Rng g = rng_seed(murmur_pixel(px, py, sample_index));
+  for (int i = 0; i < n_rand; i++) out_rand[i] = rng_nextf(g);
+  BlueSampler s{px, py, sample_index, 0};
+  for (int k = 0; k < n_samples; k++) {
+    for (int c = 0; c < n_pattern; c++) {
+      if (pattern[c] == '1') {
+        *out_draws++ = blue_get1d(sc, s);
+      } else {
+        V2 u = blue_get2d(sc, s);
+        *out_draws++ = u.x;
+        *out_draws++ = u.y;
+      }
+    }
+    s.dim = 0;  // start_next_sample (sampler.h:178-181)
+    s.index++;
+  }
+}
+__global__ void k_test_primary(DScene sc, int si, float4* rays) {
+  const int W = sc.camera.width, H = sc.camera.height;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < W * H; i += gridDim.x * blockDim.x) {
+    int px = i % W, py = i / W;
+    Rng g = rng_seed(murmur_pixel(px, py, 0));
+    Ray r;
+    for (int s = 0; s <= si; s++) {
+      float r0 = rng_nextf(g), r1 = rng_nextf(g), r2 = rng_nextf(g), r3 = rng_nextf(g);
+      r = camera_ray(sc.camera, V2((float(px) + r0) / float(W), (float(py) + r1) / float(H)), V2(r2, r3));
+    }
+    rays[2 * i] = make_float4(r.o.x, r.o.y, r.o.z, r.d.x);
+    rays[2 * i + 1] = make_float4(r.d.y, r.d.z, r.tmin, r.tmax);
+  }
+}
+}  // namespace pb2
+
+extern "C" int pb2_film_finalize(pb2_context* ctx, const float* film_rgba_host, int flip_y,
+                                 uint8_t* rgba8_host, float* tonemapped_rgba_host) {
+  if (!ctx || ctx->device < 0 || !ctx->scene_ready) { set_error("no device scene"); return PB2_E_STATE; }
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  const int W = ctx->scene.camera.width, H = ctx->scene.camera.height;
+  const size_t n = size_t(W) * H;
+  DBuf in, mapped, q;
+  PB2_CUDA_CHECK(in.reserve(n * 16));
+  PB2_CUDA_CHECK(mapped.reserve(n * 16));
+  PB2_CUDA_CHECK(q.reserve(n * 4));
+  PB2_CUDA_CHECK(cudaMemcpyAsync(in.ptr, film_rgba_host, n * 16, cudaMemcpyHostToDevice, ctx->stream));
+  k_finalize<<<kNumSMs * 4, 256, 0, ctx->stream>>>(in.as<float4>(), W, H, ctx->scene.camera.tonemapper, flip_y,
+                                                   mapped.as<float4>(), q.as<uchar4>());
+  ctx->counters.kernel_launches++;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  if (rgba8_host) PB2_CUDA_CHECK(cudaMemcpyAsync(rgba8_host, q.ptr, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (tonemapped_rgba_host)
+    PB2_CUDA_CHECK(cudaMemcpyAsync(tonemapped_rgba_host, mapped.ptr, n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  return PB2_OK;
+}
+
+extern "C" int pb2_test_sampler(pb2_context* ctx, int spp, int px, int py, int sample_index, int n_rand,
+                                float* out_rand, const char* pattern, int n_samples, float* out_draws) {
+  if (!ctx || ctx->device < 0) { set_error("no CUDA device, and there is no CPU fallback"); return PB2_E_CUDA; }
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  int rc = activate_tables(ctx, spp);
+  if (rc) return rc;
+  int n_pattern = int(strlen(pattern)), width = 0;
+  for (int i = 0; i < n_pattern; i++) width += pattern[i] == '1' ? 1 : 2;
+  DBuf d_rand, d_draws, d_pat;
+  PB2_CUDA_CHECK(d_rand.reserve(size_t(n_rand + 1) * 4));
+  PB2_CUDA_CHECK(d_draws.reserve(size_t(width) * n_samples * 4 + 4));
+  PB2_CUDA_CHECK(d_pat.reserve(n_pattern + 1));
+  PB2_CUDA_CHECK(cudaMemcpy(d_pat.ptr, pattern, n_pattern, cudaMemcpyHostToDevice));
+  k_test_sampler<<<1, 1, 0, ctx->stream>>>(ctx->scene, px, py, sample_index, n_rand, d_rand.as<float>(),
+                                           d_pat.as<char>(), n_pattern, n_samples, d_draws.as<float>());
+  ctx->counters.kernel_launches++;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  if (n_rand) PB2_CUDA_CHECK(cudaMemcpy(out_rand, d_rand.ptr, size_t(n_rand) * 4, cudaMemcpyDeviceToHost));
+  if (width * n_samples)
+    PB2_CUDA_CHECK(cudaMemcpy(out_draws, d_draws.ptr, size_t(width) * n_samples * 4, cudaMemcpyDeviceToHost));
+  return PB2_OK;
+}
+
+extern "C" int pb2_test_primary_rays(pb2_context* ctx, int sample_index, float* rays_host) {
+  if (!ctx || ctx->device < 0 || !ctx->scene_ready) { set_error("no device scene"); return PB2_E_STATE; }
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  const size_t n = size_t(ctx->scene.camera.width) * ctx->scene.camera.height;
+  PB2_CUDA_CHECK(ctx->rays.reserve(n * 32));
+  k_test_primary<<<kNumSMs * 4, 256, 0, ctx->stream>>>(ctx->scene, sample_index, ctx->rays.as<float4>());
+  ctx->counters.kernel_launches++;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  PB2_CUDA_CHECK(cudaMemcpyAsync(rays_host, ctx->rays.ptr, n * 32, cudaMemcpyDeviceToHost, ctx->stream));
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  return PB2_OK;
+}
