@@ -159,17 +159,21 @@ DTree append_tree(const Tree2& t, LayoutOut& out, const pb2_mesh* mesh, int geom
     }
   }
   const Node2& root = t.nodes[t.root];
-  WideBuilder wb{t, out, mesh, geom, leaf_base, std::vector<int>(t.nodes.size(), -1)};
   if (root.leaf_count) {
     d.root = -1;
     d.root_count = root.leaf_count;
     d.root_link = leaf_base + root.leaf_offset;
+  } else {
+    d.root = remap[t.root];
+  }
+  if (!mesh) return d;  // the top-level tree is only ever walked in reference order (traverse.cuh)
+  WideBuilder wb{t, out, mesh, geom, leaf_base, std::vector<int>(t.nodes.size(), -1)};
+  if (root.leaf_count) {
     Box3 everything;  // a root leaf is tested without any box test (bvh.cpp:398-400)
     everything.lower = V3(-kFloatMax);
     everything.upper = V3(kFloatMax);
     d.wide_root = ~wb.make_leaf(t.root, &everything);
   } else {
-    d.root = remap[t.root];
     d.wide_root = wb.build(t.root);
   }
   return d;

@@ -96,7 +96,9 @@ __global__ void __launch_bounds__(256) k_raygen(DScene sc, WaveView w, int seed_
     int px = pix % w.width, py = w.row_begin + pix / w.width;
     Rng g = first_wave_of_pixel ? rng_seed(murmur_pixel(px, py, seed_sample)) : load_rng(w.rng, pix);
     for (int s = 0; s < w.s_batch; s++) {
-      float r0 = rng_nextf(g), r1 = rng_nextf(g), r2 = rng_nextf(g), r3 = rng_nextf(g);
+      // gen_ray((p + rand2f()) / size, rand2f()) (path.cpp:35): g++ evaluates the arguments right
+      // to left, so the lens sample is drawn BEFORE the pixel jitter.
+      float r2 = rng_nextf(g), r3 = rng_nextf(g), r0 = rng_nextf(g), r1 = rng_nextf(g);
       V2 p_film((float(px) + r0) / float(sc.camera.width), (float(py) + r1) / float(sc.camera.height));
       Ray r = camera_ray(sc.camera, p_film, V2(r2, r3));
       int slot = s * w.pixels + i;
@@ -624,7 +626,7 @@ __global__ void k_test_primary(DScene sc, int si, float4* rays) {
     Rng g = rng_seed(murmur_pixel(px, py, 0));
     Ray r;
     for (int s = 0; s <= si; s++) {
-      float r0 = rng_nextf(g), r1 = rng_nextf(g), r2 = rng_nextf(g), r3 = rng_nextf(g);
+      float r2 = rng_nextf(g), r3 = rng_nextf(g), r0 = rng_nextf(g), r1 = rng_nextf(g);
       r = camera_ray(sc.camera, V2((float(px) + r0) / float(W), (float(py) + r1) / float(H)), V2(r2, r3));
     }
     rays[2 * i] = make_float4(r.o.x, r.o.y, r.o.z, r.d.x);

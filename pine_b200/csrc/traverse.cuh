@@ -161,19 +161,20 @@ __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) 
 // ====================================================================================================
 // (2) wide traversal
 // ====================================================================================================
-// Results must equal the reference-order walk bit for bit. A wide walk visits primitives in a
-// different order, which only matters when two candidates are (nearly) tied. Let (p1, t1) be the
-// strict minimum over all primitives the reference could accept. The reference returns (p1, t1) if
-//   (i)  no other primitive reports exactly t1, and
+// Used for the triangles of one mesh; results must equal the reference-order walk of that mesh bit
+// for bit. A wide walk visits triangles in a different order, which only matters when two candidates
+// are (nearly) tied. Let (p1, t1) be the strict minimum over all triangles the reference could
+// accept. The reference returns (p1, t1) if
+//   (i)  no other triangle reports exactly t1, and
 //   (ii) p1's own leaf box passes the reference slab test with tmax = t1
 // (every tmax the reference ever holds is >= t1, slab tests are monotone in tmax and in the box, so
-// p1's leaf and all its ancestors pass whenever they are reached; p1 is then accepted and nothing
-// later can replace it). The wide walk culls with a slightly enlarged tmax (`slack`) so that a
-// primitive whose t ties or beats the current best is never hidden behind a box whose entry
-// distance differs from t by rounding, detects exact ties, checks (ii) for its winner, and treats
-// the order-dependent origin-inside-a-Box case as ambiguous. Ambiguous rays (a handful per million)
-// are re-traced in reference order, so the result is the reference's in all cases.
-constexpr int kWideStack = 96;
+// p1's leaf and all its ancestors pass whenever they are reached; p1 is then accepted -- the
+// triangle test is strict, geometry.cpp:557 -- and nothing later can replace it). The wide walk
+// culls with a slightly enlarged tmax (`slack`) so that a triangle whose t ties or beats the current
+// best is never hidden behind a box whose entry distance differs from t by rounding, detects exact
+// ties and checks (ii) for its winner. Ambiguous rays (a handful per million) re-trace the mesh in
+// reference order, so the result is the reference's in all cases.
+constexpr int kWideStack = 64;
 constexpr int kNoTree = 0x7fffffff;
 
 __device__ __forceinline__ float slack_of(float t) { return t + (t * 1.220703125e-4f + 1e-6f); }
@@ -244,32 +245,21 @@ __device__ __forceinline__ void load_tri(const DTri* tris, int idx, V3& v0, V3& 
   prim = __float_as_int(c.y); geom = __float_as_int(c.z);
 }
 
-__device__ inline bool closest_wide(const DScene& sc, Ray& ray, Hit& h) {
-  h.geom = -1;
-  h.prim = -1;
-  if (sc.top.wide_root == kNoTree) return false;
-  const Octant q = make_octant(ray);
-  const float tmax0 = ray.tmax;
+// Closest hit inside one mesh (the reference's lbvh[k].Intersect, bvh.cpp:523-527) over the wide
+// tree. `ray.tmax` on entry is whatever the top-level walk holds; a triangle reporting exactly that
+// value is rejected by the reference's strict `t >= tmax` test (geometry.cpp:557), so it is not a tie.
+__device__ inline bool mesh_closest_wide(const DScene& sc, const DMesh& mesh, Ray& ray, const Octant& q,
+                                         int& prim_out) {
+  const int root = mesh.tree.wide_root;
+  if (root == kNoTree) return false;
+  const float tmax_in = ray.tmax;
   int refs[kWideStack];
   float dists[kWideStack];
   int ptr = 0;
-  refs[ptr] = sc.top.wide_root; dists[ptr] = ray.tmin; ptr++;
+  refs[ptr] = root; dists[ptr] = ray.tmin; ptr++;
   bool have = false, ambiguous = false;
   float tie_t = -1.0f;
   int win_leaf = -1;
-
-  // classify one primitive test done with tmax bumped by one ulp
-  auto consider = [&](bool ok, float t, int geom, int prim, int leaf_id) {
-    if (!ok) return;
-    float cur = ray.tmax;
-    if (t < cur) {
-      ray.tmax = t; h.geom = geom; h.prim = prim; win_leaf = leaf_id; have = true;
-    } else if (t == cur) {
-      if (!have) ambiguous = true;  // ties the caller's own tmax: strictness decides, ask the reference walk
-      else tie_t = t;
-    }
-  };
-
   while (ptr > 0) {
     --ptr;
     int ref = refs[ptr];
@@ -293,95 +283,116 @@ __device__ inline bool closest_wide(const DScene& sc, Ray& ray, Hit& h) {
           }
         }
       }
-      for (int j = 0; j < m && ptr < kWideStack; j++) { refs[ptr] = cref[j]; dists[ptr] = ct[j]; ptr++; }
+      if (ptr + m > kWideStack) { ambiguous = true; break; }
+      for (int j = 0; j < m; j++) { refs[ptr] = cref[j]; dists[ptr] = ct[j]; ptr++; }
     } else {
       int leaf_id = ~ref;
       DLeaf L = load_leaf(sc.leaves, leaf_id);
       if (!leaf_gate(L, q, ray.tmin, lim)) continue;
       int count = L.count & 0x7fffffff;
-      if (L.count < 0) {
-        for (int i = 0; i < count; i++) {
-          V3 v0, v1, v2;
-          int prim, geom;
-          load_tri(sc.leaf_tris, L.link + i, v0, v1, v2, prim, geom);
-          Ray r2 = ray;
-          r2.tmax = next_up(ray.tmax);
-          bool ok = tri_intersect(r2, v0, v1, v2);
-          consider(ok, r2.tmax, geom, prim, leaf_id);
-        }
-      } else {
-        for (int i = 0; i < count; i++) {
-          DTopPrim tp = sc.top_prims[__ldg(sc.leaf_prims + L.link + i)];
-          if (tp.kind == PB2_SHAPE_MESH) {
-            int wr = sc.meshes[tp.index].tree.wide_root;
-            if (wr != kNoTree && ptr < kWideStack) { refs[ptr] = wr; dists[ptr] = ray.tmin; ptr++; }
-          } else {
-            Ray r2 = ray;
-            r2.tmax = next_up(ray.tmax);
-            bool inside = false;
-            bool ok = shape_intersect(sc, tp.kind, tp.index, r2, &inside);
-            if (ok && inside) ambiguous = true;
-            consider(ok, r2.tmax, tp.geom, 0, leaf_id);
+      for (int i = 0; i < count; i++) {
+        V3 v0, v1, v2;
+        int prim, geom;
+        load_tri(sc.leaf_tris, L.link + i, v0, v1, v2, prim, geom);
+        Ray r2 = ray;
+        r2.tmax = next_up(ray.tmax);  // lets t == current best through so that ties are seen
+        if (tri_intersect(r2, v0, v1, v2)) {
+          if (r2.tmax < ray.tmax) {
+            ray.tmax = r2.tmax; prim_out = prim; win_leaf = leaf_id; have = true;
+          } else if (have) {
+            tie_t = r2.tmax;
           }
         }
       }
     }
   }
-  if (have) {
+  if (have && !ambiguous) {
     if (tie_t == ray.tmax) ambiguous = true;
-    if (!ambiguous && !leaf_gate(load_leaf(sc.leaves, win_leaf), q, ray.tmin, ray.tmax)) ambiguous = true;
+    else if (!leaf_gate(load_leaf(sc.leaves, win_leaf), q, ray.tmin, ray.tmax)) ambiguous = true;
   }
-  if (ambiguous) {
-    ray.tmax = tmax0;
-    return closest_ref_order(sc, ray, h);
+  if (ambiguous) {  // re-trace this mesh in reference order
+    ray.tmax = tmax_in;
+    return walk_ref_order<false>(sc, mesh.tree, ray, q, [&](int tri) {
+      V3 v0, v1, v2;
+      mesh_tri(sc, mesh, tri, v0, v1, v2);
+      bool ok = tri_intersect(ray, v0, v1, v2);
+      if (ok) prim_out = tri;
+      return ok;
+    });
   }
   return have;
 }
 
-// Any-hit: the reference result is an OR over primitives whose leaf box passes with the ray's fixed
-// tmax (BVHImpl::hit never shrinks tmax), so visiting order is irrelevant and no fallback is needed.
-__device__ inline bool any_wide(const DScene& sc, const Ray& ray) {
-  if (sc.top.wide_root == kNoTree) return false;
-  const Octant q = make_octant(ray);
+// Any-hit inside one mesh (lbvh[k].hit, bvh.cpp:503-505): an OR over triangles whose leaf box passes
+// with the ray's fixed tmax, so visiting order is irrelevant and no fallback is needed.
+__device__ inline bool mesh_any_wide(const DScene& sc, const DMesh& mesh, const Ray& ray, const Octant& q) {
+  const int root = mesh.tree.wide_root;
+  if (root == kNoTree) return false;
   int refs[kWideStack];
   int ptr = 0;
-  refs[ptr++] = sc.top.wide_root;
+  refs[ptr++] = root;
   while (ptr > 0) {
     int ref = refs[--ptr];
     if (ref >= 0) {
       Node8Regs nd = load_node8(sc.nodes8, ref);
       int n = int((__float_as_uint(nd.a.w) >> 24) & 0xffu);
+      if (ptr + n > kWideStack) {  // cannot happen for sane trees; stay exact if it does
+        return walk_ref_order<true>(sc, mesh.tree, ray, q, [&](int tri) {
+          V3 v0, v1, v2;
+          mesh_tri(sc, mesh, tri, v0, v1, v2);
+          return tri_hit(ray, v0, v1, v2);
+        });
+      }
 #pragma unroll
       for (int i = 0; i < 8; i++) {
         float tn;
-        if (i < n && child_slab(nd, i, q, ray.tmin, ray.tmax, tn) && ptr < kWideStack)
+        if (i < n && child_slab(nd, i, q, ray.tmin, ray.tmax, tn))
           refs[ptr++] = i < 4 ? (&nd.c0.x)[i] : (&nd.c1.x)[i - 4];
       }
     } else {
       DLeaf L = load_leaf(sc.leaves, ~ref);
       if (!leaf_gate(L, q, ray.tmin, ray.tmax)) continue;
       int count = L.count & 0x7fffffff;
-      if (L.count < 0) {
-        for (int i = 0; i < count; i++) {
-          V3 v0, v1, v2;
-          int prim, geom;
-          load_tri(sc.leaf_tris, L.link + i, v0, v1, v2, prim, geom);
-          if (tri_hit(ray, v0, v1, v2)) return true;
-        }
-      } else {
-        for (int i = 0; i < count; i++) {
-          DTopPrim tp = sc.top_prims[__ldg(sc.leaf_prims + L.link + i)];
-          if (tp.kind == PB2_SHAPE_MESH) {
-            int wr = sc.meshes[tp.index].tree.wide_root;
-            if (wr != kNoTree && ptr < kWideStack) refs[ptr++] = wr;
-          } else if (shape_hit(sc, tp.kind, tp.index, ray)) {
-            return true;
-          }
-        }
+      for (int i = 0; i < count; i++) {
+        V3 v0, v1, v2;
+        int prim, geom;
+        load_tri(sc.leaf_tris, L.link + i, v0, v1, v2, prim, geom);
+        if (tri_hit(ray, v0, v1, v2)) return true;
       }
     }
   }
   return false;
+}
+
+// Production traversal: the top-level tree (one primitive per geometry) is walked in the reference's
+// order -- analytic shapes carry order-dependent quirks (a scaled Box compares a local-space entry
+// distance with the world-space tmax, bbox.cpp:149-161; an origin inside a Box reports
+// min(exit, tmax)), so their visiting order must be the reference's -- and every mesh below it uses
+// the wide tree.
+__device__ __forceinline__ bool closest_wide(const DScene& sc, Ray& ray, Hit& h) {
+  Octant q = make_octant(ray);
+  h.geom = -1;
+  h.prim = -1;
+  return walk_ref_order<false>(sc, sc.top, ray, q, [&](int top_id) {
+    DTopPrim tp = sc.top_prims[top_id];
+    if (tp.kind == PB2_SHAPE_MESH) {
+      int prim = -1;
+      bool hit = mesh_closest_wide(sc, sc.meshes[tp.index], ray, q, prim);
+      if (hit) { h.geom = tp.geom; h.prim = prim; }
+      return hit;
+    }
+    bool hit = shape_intersect(sc, tp.kind, tp.index, ray);
+    if (hit) { h.geom = tp.geom; h.prim = 0; }
+    return hit;
+  });
+}
+__device__ __forceinline__ bool any_wide(const DScene& sc, const Ray& ray) {
+  Octant q = make_octant(ray);
+  return walk_ref_order<true>(sc, sc.top, ray, q, [&](int top_id) {
+    DTopPrim tp = sc.top_prims[top_id];
+    if (tp.kind == PB2_SHAPE_MESH) return mesh_any_wide(sc, sc.meshes[tp.index], ray, q);
+    return shape_hit(sc, tp.kind, tp.index, ray);
+  });
 }
 
 }  // namespace pb2

@@ -1,0 +1,229 @@
+"""`PathIntegrator(BlueSampler(spp), depth).render(scene)` on a B200, through the C ABI.
+
+Mirrors the reference's script-level interface (program_context.cpp:76-81, path.h:7,
+sampler.cpp:115-121): same names, same argument meaning, same error behaviour
+(`max_path_length <= 0` is an error, spp > 256 warns and clamps, spp rounds up to a power of two).
+Everything numeric happens in pine_b200/lib/libpine_b200.so; there is no CPU path.
+"""
+import ctypes as C
+import os
+import struct
+import warnings
+import zlib
+
+import numpy as np
+
+from . import _abi as A
+
+TABLES_PATH = os.path.join(A.HERE, "data", "bluesobol_tables.bin")
+_tables = None
+
+
+def sampler_tables():
+    """{spp: (sobol u8[65536], scramble u8[131072], rank u8[131072])} from the extracted blob
+    (oracle/extract_tables.cpp documents the layout and provenance)."""
+    global _tables
+    if _tables is None:
+        if not os.path.exists(TABLES_PATH):
+            raise FileNotFoundError(
+                f"{TABLES_PATH} missing: `make -C oracle tables` extracts it from the reference's "
+                "vendored bluesobol sources (needs /root/reference)")
+        raw = np.fromfile(TABLES_PATH, dtype=np.uint8)
+        if bytes(raw[:8]) != b"PB2BLUE1":
+            raise ValueError("bad sampler table file")
+        n = struct.unpack_from("<I", raw, 8)[0]
+        off, out = 16, {}
+        for _ in range(n):
+            spp = struct.unpack_from("<I", raw, off)[0]
+            off += 8
+            sob = raw[off:off + 65536]; off += 65536
+            scr = raw[off:off + 131072]; off += 131072
+            rnk = raw[off:off + 131072]; off += 131072
+            out[spp] = (np.ascontiguousarray(sob), np.ascontiguousarray(scr),
+                        np.ascontiguousarray(rnk))
+        _tables = out
+    return _tables
+
+
+class BlueSampler:
+    """BlueSobolSampler (PRL name `BlueSampler`), sampler.cpp:115-121."""
+
+    def __init__(self, samples_per_pixel):
+        if samples_per_pixel > 256:
+            warnings.warn("[BlueSobolSampler]Only support up to 256 samples per pixel")
+            samples_per_pixel = 256
+        self.samples_per_pixel = A.lib().pb2h_round_spp(int(samples_per_pixel))
+        if self.samples_per_pixel <= 0:
+            raise ValueError("samples per pixel must be positive")
+
+    def spp(self):
+        return self.samples_per_pixel
+
+
+class Backend:
+    """One pb2_context (one GPU). `device=-1` makes a host-only context (BVH builder inspection)."""
+
+    def __init__(self, device=0):
+        self.L = A.lib()
+        h = C.c_void_p()
+        A.check(self.L.pb2_create(device, C.byref(h)))
+        self.h = h
+        self.device = device
+        self._tables_loaded = set()
+        self._scene_keep = None
+        self.size = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.pb2_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def upload_scene(self, scene):
+        d, keep = scene.desc()
+        A.check(self.L.pb2_upload_scene(self.h, C.byref(d)))
+        self._scene_keep = (scene, keep)
+        self.size = scene.size
+
+    def upload_tables(self, spp):
+        if spp in self._tables_loaded:
+            return
+        sob, scr, rnk = sampler_tables()[spp]
+        A.check(self.L.pb2_upload_sampler_tables(self.h, spp, sob.ctypes.data, scr.ctypes.data,
+                                                 rnk.ctypes.data))
+        self._tables_loaded.add(spp)
+
+    def _params(self, spp, depth, rows=None, samples=None, accel=0, flags=0):
+        p = A.RenderParams()
+        p.spp, p.max_path_length = spp, depth
+        p.row_begin, p.row_end = rows if rows else (0, self.size[1])
+        p.sample_begin, p.sample_end = samples if samples else (0, spp)
+        p.accel, p.flags = accel, flags
+        return p
+
+    def render(self, spp, depth, rows=None, samples=None, accel=0, out=None):
+        """-> film float32 [h, w, 4] in host memory (pre-tonemap)."""
+        self.upload_tables(spp)
+        w, h = self.size
+        film = out if out is not None else np.empty((h, w, 4), np.float32)
+        p = self._params(spp, depth, rows, samples, accel)
+        A.check(self.L.pb2_render(self.h, C.byref(p), film.ctypes.data))
+        return film
+
+    def render_device(self, spp, depth, rows=None, samples=None, accel=0, stream=None):
+        """-> device pointer (int) of the float4 film owned by the context."""
+        self.upload_tables(spp)
+        p = self._params(spp, depth, rows, samples, accel)
+        ptr = C.c_void_p()
+        A.check(self.L.pb2_render_device(self.h, C.byref(p), stream, C.byref(ptr)))
+        return ptr.value
+
+    def finalize(self, film, flip_y=True):
+        w, h = self.size
+        f = np.ascontiguousarray(film, np.float32)
+        rgba8 = np.empty((h, w, 4), np.uint8)
+        mapped = np.empty((h, w, 4), np.float32)
+        A.check(self.L.pb2_film_finalize(self.h, f.ctypes.data, int(flip_y), rgba8.ctypes.data,
+                                         mapped.ctypes.data))
+        return rgba8, mapped
+
+    def trace_closest(self, rays, accel=0, surf=False):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        n = len(rays)
+        geom, prim = np.empty(n, np.int32), np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        s = np.empty((n, 8), np.float32) if surf else None
+        A.check(self.L.pb2_trace_closest(self.h, rays.ctypes.data, n, accel, geom.ctypes.data,
+                                         prim.ctypes.data, t.ctypes.data,
+                                         s.ctypes.data if surf else None))
+        out = {"geom": geom, "prim": prim, "t": t}
+        if surf:
+            out["surf"] = s
+        return out
+
+    def trace_any(self, rays, accel=0):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        occ = np.empty(len(rays), np.uint8)
+        A.check(self.L.pb2_trace_any(self.h, rays.ctypes.data, len(rays), accel, occ.ctypes.data))
+        return occ
+
+    def test_sampler(self, spp, px, py, sample_index, n_rand, pattern, n_samples):
+        self.upload_tables(spp)
+        width = sum(1 if c == "1" else 2 for c in pattern)
+        r = np.zeros(max(n_rand, 1), np.float32)
+        d = np.zeros(max(width * n_samples, 1), np.float32)
+        A.check(self.L.pb2_test_sampler(self.h, spp, px, py, sample_index, n_rand, r.ctypes.data,
+                                        pattern.encode(), n_samples, d.ctypes.data))
+        return r[:n_rand], d[:width * n_samples].reshape(n_samples, width)
+
+    def primary_rays(self, si=0):
+        w, h = self.size
+        rays = np.empty((w * h, 8), np.float32)
+        A.check(self.L.pb2_test_primary_rays(self.h, si, rays.ctypes.data))
+        return rays
+
+    def counters(self):
+        c = A.Counters()
+        A.check(self.L.pb2_get_counters(self.h, C.byref(c)))
+        return {k: getattr(c, k) for k, _ in A.Counters._fields_}
+
+    def bvh_tree(self, which=-1):
+        n, root, npr = C.c_int32(), C.c_int32(), C.c_int32()
+        A.check(self.L.pb2_bvh_info(self.h, which, C.byref(n), C.byref(root), C.byref(npr)))
+        aabbs = np.zeros((n.value, 12), np.float32)
+        children = np.zeros((n.value, 2), np.int32)
+        leaf_range = np.zeros((n.value, 2), np.int32)
+        leaf_prims = np.zeros(max(npr.value, 1), np.int32)
+        if n.value:
+            A.check(self.L.pb2_bvh_nodes(self.h, which, aabbs.ctypes.data, children.ctypes.data,
+                                         leaf_range.ctypes.data, leaf_prims.ctypes.data))
+        return {"root": root.value, "aabbs": aabbs, "children": children,
+                "leaf_range": leaf_range, "leaf_prims": leaf_prims[:npr.value]}
+
+
+class PathIntegrator:
+    """PathIntegrator(sampler, max_path_length) -- path.cpp:9-14 / program_context.cpp:79-81."""
+
+    def __init__(self, sampler, max_path_length, device=0, accel=0):
+        if max_path_length <= 0:
+            raise ValueError(
+                f"`PathIntegrator` expect `max_path_length` to be positive, get{max_path_length}")
+        self.sampler, self.max_path_length = sampler, max_path_length
+        self.device, self.accel = device, accel
+        self.backend = None
+
+    def render(self, scene):
+        """Fills scene.camera.film().pixels (float32 [h, w, 4], pre-tonemap), like path.cpp:26-41."""
+        if self.backend is None:
+            self.backend = Backend(self.device)
+        self.backend.upload_scene(scene)
+        film = self.backend.render(self.sampler.spp(), self.max_path_length, accel=self.accel)
+        scene.camera.film().pixels = film
+        scene._backend = self.backend
+        return film
+
+
+def write_png(path, rgba8):
+    h, w, _ = rgba8.shape
+    raw = b"".join(b"\x00" + rgba8[y].tobytes() for y in range(h))
+
+    def chunk(tag, data):
+        return (struct.pack(">I", len(data)) + tag + data +
+                struct.pack(">I", zlib.crc32(tag + data) & 0xffffffff))
+
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 6, 0, 0, 0)) +
+                chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b""))
+
+
+def save_film(film, path, scene=None):
+    """Film::save: finalize (tone-map) on the device, gamma/quantise/y-flip, PNG on the host
+    (film.cpp:12-27, fileio.cpp:42-76)."""
+    backend = getattr(scene, "_backend", None) if scene is not None else None
+    if backend is None:
+        raise RuntimeError("save needs the scene that was rendered (its device context)")
+    rgba8, _ = backend.finalize(film.pixels, flip_y=True)
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    write_png(path, rgba8)

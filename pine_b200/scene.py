@@ -1,0 +1,284 @@
+"""Host-side scene model: the subset of Pine's scripting surface that feeds PathIntegrator.
+
+`Scene` offers the builder methods `add_material / add_rect / add_box / add_cone / ... /
+set_camera` (identical signatures on `oracle.ref.RefScene`, so one description feeds both sides)
+and the PRL-flavoured front (`scene.add("floor", Diffuse(...))`, `scene.add(Rect(...), "floor")`,
+`scene.set(ThinLenCamera(Film(size), frm, to, fov))`) mirroring program_context.cpp:23-125 and
+scene.cpp:8-44 of the reference. All derived shape members are computed by the C++ host layer
+(include/pine_b200_host.h), never in Python, so they carry the reference constructors' float ops.
+Matrices are 4x4 numpy float32 in math (row, column) convention; `mat4.*` helpers call the C++ layer.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi as A
+
+
+def _f(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+class mat4:
+    """translate / scale / rotate_* / inverse / look_at of vecmath.h:1088-1180, via the C++ host."""
+
+    @staticmethod
+    def _op(op, args):
+        out = np.zeros(16, np.float32)
+        a = _f(args).reshape(-1)
+        A.lib().pb2h_mat4(op, _fp(a), _fp(out))
+        return out.reshape(4, 4).T.copy()  # column-major storage -> math layout
+
+    @staticmethod
+    def translate(v): return mat4._op(0, v)
+    @staticmethod
+    def scale(v): return mat4._op(1, v)
+    @staticmethod
+    def rotate_x(r): return mat4._op(2, [r])
+    @staticmethod
+    def rotate_y(r): return mat4._op(3, [r])
+    @staticmethod
+    def rotate_z(r): return mat4._op(4, [r])
+    @staticmethod
+    def inverse(m): return mat4._op(5, _f(m).T.reshape(-1))
+    @staticmethod
+    def look_at(frm, to): return mat4._op(6, [*frm, *to])
+
+    @staticmethod
+    def mul(a, b):
+        out = np.zeros(16, np.float32)
+        ca, cb = _f(_f(a).T).reshape(-1), _f(_f(b).T).reshape(-1)
+        A.lib().pb2h_mat4_mul(_fp(ca), _fp(cb), _fp(out))
+        return out.reshape(4, 4).T.copy()
+
+
+# ---- PRL-flavoured value types ---------------------------------------------------------------------
+class _Mat:
+    def __init__(self, kind, color, roughness=0.0, ior=1.4, metallic=0.0, transmission=0.0,
+                 sigma_s=(0.0, 0.0, 0.0)):
+        self.kind, self.color, self.roughness, self.ior = kind, tuple(color), roughness, ior
+        self.metallic, self.transmission, self.sigma_s = metallic, transmission, tuple(sigma_s)
+
+
+def Emissive(color): return _Mat("emissive", color)
+def Diffuse(albedo): return _Mat("diffuse", albedo)
+def Metal(albedo, roughness): return _Mat("metal", albedo, roughness)
+def Glossy(albedo, roughness, ior=1.4): return _Mat("glossy", albedo, roughness, ior)
+def Glass(albedo, roughness, ior=1.4): return _Mat("glass", albedo, roughness, ior)
+def Uber(albedo, roughness, metallic=0.0, transmission=0.0, ior=1.45):
+    return _Mat("uber", albedo, roughness, ior, metallic, transmission)
+def Subsurface(albedo, roughness, sigma_s):
+    s = (sigma_s,) * 3 if np.isscalar(sigma_s) else tuple(sigma_s)
+    return _Mat("subsurface", albedo, roughness, 1.4, sigma_s=s)
+
+
+class _Shape:
+    def __init__(self, kind, *args, **kw):
+        self.kind, self.args, self.kw = kind, args, kw
+
+
+def Rect(pos, ex, ey, flip=False): return _Shape("rect", pos, ex, ey, flip=flip)
+def AABB(lo, hi): return _Shape("aabb", lo, hi)
+def Box(a, b=None, m=None):
+    """Box(lower, upper) -> AABB; Box(AABB, m) / Box(lower, upper, m) -> OBB (geometry.cpp:917-921)."""
+    if isinstance(a, _Shape) and a.kind == "aabb":
+        return _Shape("box", a.args[0], a.args[1], b)
+    if m is None:
+        return _Shape("aabb", a, b)
+    return _Shape("box", a, b, m)
+def Cone(p, n, r, h): return _Shape("cone", p, n, r, h)
+def Sphere(c, r): return _Shape("sphere", c, r)
+def Disk(p, n, r): return _Shape("disk", p, n, r)
+def Triangle(a, b, c): return _Shape("triangle", a, b, c)
+def Mesh(verts, idx, normals=None, uvs=None): return _Shape("mesh", verts, idx, normals=normals, uvs=uvs)
+
+
+class Film:
+    def __init__(self, size, tonemapper="uncharted2"):
+        self.size = (int(size[0]), int(size[1]))
+        self.tonemapper = tonemapper
+        self.pixels = None  # float32 [h, w, 4], filled by PathIntegrator.render
+
+    def save(self, path, scene=None):
+        from .integrator import save_film
+        save_film(self, path, scene)
+
+
+def Uncharted2(): return "uncharted2"
+def ACES(): return "aces"
+
+
+class ThinLenCamera:
+    def __init__(self, film, frm, to, fov, len_radius=0.0, focus_distance=1.0):
+        self._film, self.frm, self.to, self.fov = film, frm, to, fov
+        self.len_radius, self.focus_distance = len_radius, focus_distance
+
+    def film(self):
+        return self._film
+
+
+class Scene:
+    def __init__(self):
+        self.materials = []          # A.Material
+        self.named = {}
+        self.geometries = []         # (shape_kind, shape_index, material)
+        self.shapes = {k: [] for k in A.SHAPE_KINDS}
+        self.mesh_data = []          # keeps numpy arrays alive
+        self.camera = None
+        self._cam = None             # A.Camera
+        self.size = None
+
+    # ---- builder interface (shared with oracle.ref.RefScene) ----
+    def add_material(self, kind, color, roughness=0.0, ior=1.4, metallic=0.0, transmission=0.0,
+                     sigma_s=(0.0, 0.0, 0.0)):
+        m = A.Material()
+        m.kind = A.MATERIAL_KINDS[kind]
+        m.color = A.f3(*[float(c) for c in color])
+        m.roughness, m.ior, m.metallic, m.transmission = roughness, ior, metallic, transmission
+        m.sigma_s = A.f3(*[float(c) for c in sigma_s])
+        self.materials.append(m)
+        return len(self.materials) - 1
+
+    def _add(self, kind, rec, mat):
+        self.shapes[kind].append(rec)
+        self.geometries.append((A.SHAPE_KINDS[kind], len(self.shapes[kind]) - 1, mat))
+        return len(self.geometries) - 1
+
+    def add_rect(self, pos, ex, ey, mat, flip=False):
+        r = A.Rect()
+        a, b, c = _f(pos), _f(ex), _f(ey)
+        A.lib().pb2h_make_rect(_fp(a), _fp(b), _fp(c), int(flip), C.byref(r))
+        return self._add("rect", r, mat)
+
+    def add_box(self, lo, hi, m, mat):
+        o = A.Obb()
+        a, b = _f(lo), _f(hi)
+        cm = _f(_f(m).reshape(4, 4).T).reshape(-1)
+        A.lib().pb2h_make_obb(_fp(a), _fp(b), _fp(cm), C.byref(o))
+        return self._add("obb", o, mat)
+
+    def add_aabb(self, lo, hi, mat):
+        o = A.Aabb()
+        o.lower, o.upper = A.f3(*map(float, lo)), A.f3(*map(float, hi))
+        return self._add("aabb", o, mat)
+
+    def add_cone(self, p, n, r, h, mat):
+        o = A.Cone()
+        a, b = _f(p), _f(n)
+        A.lib().pb2h_make_cone(_fp(a), _fp(b), r, h, C.byref(o))
+        return self._add("cone", o, mat)
+
+    def add_sphere(self, c, r, mat):
+        o = A.Sphere()
+        o.c, o.r = A.f3(*map(float, c)), r
+        return self._add("sphere", o, mat)
+
+    def add_disk(self, p, n, r, mat):
+        o = A.Disk()
+        a, b = _f(p), _f(n)
+        A.lib().pb2h_make_disk(_fp(a), _fp(b), r, C.byref(o))
+        return self._add("disk", o, mat)
+
+    def add_triangle(self, a, b, c, mat):
+        o = A.Triangle()
+        a, b, c = _f(a), _f(b), _f(c)
+        A.lib().pb2h_make_triangle(_fp(a), _fp(b), _fp(c), C.byref(o))
+        return self._add("triangle", o, mat)
+
+    def add_mesh(self, verts, idx, mat, normals=None, uvs=None):
+        v = _f(verts).reshape(-1, 3)
+        i = np.ascontiguousarray(idx, dtype=np.uint32).reshape(-1, 3)
+        n = _f(normals).reshape(-1, 3) if normals is not None else None
+        t = _f(uvs).reshape(-1, 2) if uvs is not None else None
+        self.mesh_data.append((v, i, n, t))
+        m = A.Mesh()
+        m.vertices, m.indices = v.ctypes.data, i.ctypes.data
+        m.normals = n.ctypes.data if n is not None else None
+        m.texcoords = t.ctypes.data if t is not None else None
+        m.n_vertices, m.n_triangles = len(v), len(i)
+        return self._add("mesh", m, mat)
+
+    def set_camera(self, size, frm, to, fov, len_radius=0.0, focus=1.0, tonemapper="uncharted2"):
+        self.size = (int(size[0]), int(size[1]))
+        cam = A.Camera()
+        a, b = _f(frm), _f(to)
+        A.lib().pb2h_make_camera(self.size[0], self.size[1], 0 if tonemapper == "uncharted2" else 1,
+                                 _fp(a), _fp(b), fov, len_radius, focus, C.byref(cam))
+        self._cam = cam
+        if self.camera is None:
+            self.camera = ThinLenCamera(Film(self.size, tonemapper), frm, to, fov, len_radius, focus)
+
+    # ---- PRL-flavoured front (scene.cpp:8-44) ----
+    def add(self, a, b=None):
+        if isinstance(a, str):
+            self.named[a] = self.add_material(b.kind, b.color, b.roughness, b.ior, b.metallic,
+                                              b.transmission, b.sigma_s)
+            return self.named[a]
+        if isinstance(b, str):
+            if b not in self.named:
+                raise KeyError(f"Can't find material `{b}`")  # scene.cpp:52-57
+            mat = self.named[b]
+        else:
+            mat = self.add_material(b.kind, b.color, b.roughness, b.ior, b.metallic,
+                                    b.transmission, b.sigma_s)
+        s = a
+        fn = {"rect": lambda: self.add_rect(*s.args, mat, **s.kw),
+              "aabb": lambda: self.add_aabb(*s.args, mat),
+              "box": lambda: self.add_box(*s.args, mat),
+              "cone": lambda: self.add_cone(*s.args, mat),
+              "sphere": lambda: self.add_sphere(*s.args, mat),
+              "disk": lambda: self.add_disk(*s.args, mat),
+              "triangle": lambda: self.add_triangle(*s.args, mat),
+              "mesh": lambda: self.add_mesh(*s.args, mat, **s.kw)}[s.kind]
+        return fn()
+
+    def set(self, camera):
+        self.camera = camera
+        f = camera.film()
+        self.set_camera(f.size, camera.frm, camera.to, camera.fov, camera.len_radius,
+                        camera.focus_distance, f.tonemapper)
+
+    def lights(self):
+        """Scene::lights: one AreaLight per Emissive geometry, in insertion order (scene.cpp:19-20)."""
+        return [g for g, (_, _, m) in enumerate(self.geometries)
+                if self.materials[m].kind == A.MATERIAL_KINDS["emissive"]]
+
+    def desc(self):
+        """Flatten into the C-ABI pb2_scene_desc; returns (desc, keepalive)."""
+        if self._cam is None:
+            raise ValueError("scene has no camera")
+        d = A.SceneDesc()
+        keep = []
+
+        def put(field, typ, items):
+            arr = (typ * max(len(items), 1))(*items)
+            keep.append(arr)
+            setattr(d, field, C.cast(arr, C.POINTER(typ)))
+            setattr(d, "n_" + field, len(items))
+
+        geoms = []
+        for k, i, m in self.geometries:
+            g = A.Geometry()
+            g.shape_kind, g.shape_index, g.material = k, i, m
+            geoms.append(g)
+        put("geometries", A.Geometry, geoms)
+        put("materials", A.Material, self.materials)
+        put("aabbs", A.Aabb, self.shapes["aabb"])
+        put("obbs", A.Obb, self.shapes["obb"])
+        put("spheres", A.Sphere, self.shapes["sphere"])
+        put("triangles", A.Triangle, self.shapes["triangle"])
+        put("cones", A.Cone, self.shapes["cone"])
+        put("rects", A.Rect, self.shapes["rect"])
+        put("disks", A.Disk, self.shapes["disk"])
+        put("meshes", A.Mesh, self.shapes["mesh"])
+        ls = self.lights()
+        larr = (C.c_int32 * max(len(ls), 1))(*ls)
+        keep.append(larr)
+        d.light_geometries = C.cast(larr, C.POINTER(C.c_int32))
+        d.n_lights = len(ls)
+        d.camera = self._cam
+        return d, keep

@@ -1,0 +1,151 @@
+"""The benchmark scenes of BASELINE.json as builder-interface descriptions.
+
+Each function takes any object with the builder methods of `pine_b200.Scene` /
+`oracle.ref.RefScene` and feeds it plain numbers, so the reference and the CUDA backend see the
+same scene. Matrices come from `pine_b200.mat4` (the C++ host mirror of vecmath.h).
+"""
+import numpy as np
+
+from .scene import mat4
+
+
+def _frange(a, step, b):
+    """PRL `for x in a ~ step ~ b`: x = a; x <= b; x += step in f32 (jit.cpp:1534-1541)."""
+    x, step, b = np.float32(a), np.float32(step), np.float32(b)
+    out = []
+    while x <= b:
+        out.append(float(x))
+        x = np.float32(x + step)
+    return out
+
+
+def _trs(t, ry, s):
+    return mat4.mul(mat4.mul(mat4.translate(t), mat4.rotate_y(ry)), mat4.scale(s))
+
+
+def cbox_readme(B, size=(640, 640), cones=True):
+    """C1: the README scene (reference README.md:7-35): 5 walls, cone field, two boxes, one light.
+    PathIntegrator(BlueSampler(16), 4). The PRL float loop yields 20 x 20 cones (x stops at
+    0.9000002 because -1 + 20*0.1f accumulates to 1.0000001 > 1)."""
+    floor = B.add_material("diffuse", (0.9, 0.9, 0.9))
+    red = B.add_material("diffuse", (0.9, 0.1, 0.05))
+    green = B.add_material("diffuse", (0.2, 0.9, 0.05))
+    metal = B.add_material("metal", (1, 1, 1), roughness=0.0)
+    B.add_material("glossy", (0.25, 0.25, 0.25), roughness=0.05)          # declared, unassigned
+    B.add_material("subsurface", (1, 1, 1), roughness=0.0, sigma_s=(40.0,) * 3)  # declared, unassigned
+    B.add_rect((0, 0, 1), (2, 0, 0), (0, 0, 2), floor)
+    B.add_rect((0, 2, 1), (2, 0, 0), (0, 0, 2), floor)
+    B.add_rect((-1, 1, 1), (0, 0, 2), (0, 2, 0), red)
+    B.add_rect((1, 1, 1), (0, 0, 2), (0, 2, 0), green)
+    B.add_rect((0, 1, 2), (2, 0, 0), (0, 2, 0), floor)
+    if cones:
+        for x in _frange(-1.0, 0.1, 1.0):
+            for z in _frange(0.0, 0.1, 2.0):
+                B.add_cone((x, 0, z), (0, 1, 0), 0.05, 0.05, floor)
+    B.add_box((0, 0, 0), (1, 1, 1), _trs((0.0, 0.0, 0.6), 0.4, (0.6, 0.6, 0.6)), floor)
+    B.add_box((0, 0, 0), (1, 1, 1), _trs((-0.6, 0.0, 1.0), -0.4, (0.6, 1.3, 0.6)), metal)
+    light = B.add_material("emissive", tuple(np.float32(600) * np.float32(c) for c in (1.0, 0.64, 0.185)))
+    B.add_rect((0.0, 1.9, 0.5), (0.1, 0, 0), (0, 0, 0.1), light)
+    B.set_camera(size, (0, 1, -4), (0, 1, 0), 0.25)
+    return {"spp": 16, "depth": 4}
+
+
+def cbox_file(B, size=(1024, 1024)):
+    """C1b: scenes/cbox.pine as written on disk (1024x1024, BlueSampler(256), depth 8)."""
+    floor = B.add_material("diffuse", (0.9, 0.9, 0.9))
+    blue = B.add_material("diffuse", (0.2, 0.5, 0.9))
+    red = B.add_material("diffuse", (0.9, 0.1, 0.05))
+    green = B.add_material("diffuse", (0.2, 0.9, 0.05))
+    B.add_rect((0, 0, 1), (2, 0, 0), (0, 0, 2), floor, flip=True)
+    B.add_rect((0, 2, 1), (2, 0, 0), (0, 0, 2), floor)
+    B.add_rect((-1, 1, 1), (0, 0, 2), (0, 2, 0), red, flip=True)
+    B.add_rect((1, 1, 1), (0, 0, 2), (0, 2, 0), green)
+    B.add_rect((0, 1, 2), (2, 0, 0), (0, 2, 0), blue, flip=True)
+    B.add_box((0, 0, 0), (1, 1, 1), _trs((0.0, 0.0, 0.6), 0.4, (0.6, 0.6, 0.6)), floor)
+    B.add_box((0, 0, 0), (1, 1, 1), _trs((-0.6, 0.0, 1.0), -0.4, (0.6, 1.3, 0.6)), floor)
+    light = B.add_material("emissive", tuple(np.float32(600) * np.float32(c) for c in (1.0, 0.64, 0.185)))
+    B.add_rect((0.0, 1.9, 1), (0.1, 0, 0), (0, 0, 0.1), light)
+    B.set_camera(size, (0, 0, 0), (0, 0, 1), 0.4)
+    return {"spp": 256, "depth": 8}
+
+
+def cbox_indirect(B, size=(1024, 1024)):
+    """C3: scenes/cbox-indirect.pine geometry; BASELINE asks 1024x1024, 256 spp, depth 8
+    (the file itself says 720x360, 64 spp, depth 5). Film(image_size) default tonemapper."""
+    floor = B.add_material("diffuse", (0.95, 0.95, 0.95))
+    red = B.add_material("diffuse", (0.9, 0.1, 0.05))
+    green = B.add_material("diffuse", (0.2, 0.9, 0.05))
+    B.add_rect((0, 0, 1), (2, 0, 0), (0, 0, 2), floor)
+    B.add_rect((0, 2, 1), (2, 0, 0), (0, 0, 2), floor)
+    B.add_rect((0, 1, 2), (2, 0, 0), (0, 2, 0), floor)
+    B.add_rect((-1, 1, 1), (0, 0, 2), (0, 2, 0), red)
+    B.add_rect((1, 1, 1), (0, 0, 2), (0, 2, 0), green)
+    B.add_rect((0.2, 1.5, 1), (1.6, 0, 0), (0, 0, 2), floor)
+    light = B.add_material("emissive", tuple(np.float32(600) * np.float32(c) for c in (1.0, 0.64, 0.185)))
+    B.add_rect((0, 1.9, 1), (0.2, 0, 0), (0, 0, 0.2), light)
+    B.set_camera(size, (0, 1, -4), (0, 1, 0), 0.25)
+    return {"spp": 256, "depth": 8}
+
+
+# ---- procedural meshes ------------------------------------------------------------------------------
+def icosphere(subdiv):
+    t = (1.0 + 5.0 ** 0.5) / 2.0
+    v = [(-1, t, 0), (1, t, 0), (-1, -t, 0), (1, -t, 0), (0, -1, t), (0, 1, t), (0, -1, -t),
+         (0, 1, -t), (t, 0, -1), (t, 0, 1), (-t, 0, -1), (-t, 0, 1)]
+    f = [(0, 11, 5), (0, 5, 1), (0, 1, 7), (0, 7, 10), (0, 10, 11), (1, 5, 9), (5, 11, 4),
+         (11, 10, 2), (10, 7, 6), (7, 1, 8), (3, 9, 4), (3, 4, 2), (3, 2, 6), (3, 6, 8), (3, 8, 9),
+         (4, 9, 5), (2, 4, 11), (6, 2, 10), (8, 6, 7), (9, 8, 1)]
+    v = [np.array(p, np.float64) / np.linalg.norm(p) for p in v]
+    for _ in range(subdiv):
+        cache, nf = {}, []
+
+        def mid(a, b):
+            key = (min(a, b), max(a, b))
+            if key not in cache:
+                m = v[a] + v[b]
+                v.append(m / np.linalg.norm(m))
+                cache[key] = len(v) - 1
+            return cache[key]
+        for a, b, c in f:
+            ab, bc, ca = mid(a, b), mid(b, c), mid(c, a)
+            nf += [(a, ab, ca), (b, bc, ab), (c, ca, bc), (ab, bc, ca)]
+        f = nf
+    return np.array(v, np.float32), np.array(f, np.uint32)
+
+
+def mesh_field(B, n_instances=64, subdiv=3, seed=42, size=(640, 360), spp=16, depth=6,
+               with_shapes=True):
+    """Deterministic flattened-instancing scene (the C4/C5 family): `n_instances`
+    icospheres (20 * 4^subdiv triangles each) on a jittered grid as separate Mesh geometries
+    (Pine's own BVH ignores Scene::instancings, bvh.cpp:453-495), ground Rect, Rect emitters."""
+    rng = np.random.RandomState(seed)
+    bv, bf = icosphere(subdiv)
+    mats = [B.add_material("diffuse", (0.8, 0.8, 0.8)), B.add_material("diffuse", (0.8, 0.3, 0.2)),
+            B.add_material("metal", (0.9, 0.9, 0.9), roughness=0.2),
+            B.add_material("glossy", (0.3, 0.5, 0.8), roughness=0.1)]
+    g = int(np.ceil(n_instances ** (1 / 3)))
+    cell = 1.0
+    k = 0
+    for ix in range(g):
+        for iy in range(g):
+            for iz in range(g):
+                if k >= n_instances:
+                    break
+                c = (np.array([ix, iy, iz], np.float32) + 0.5 + (rng.rand(3).astype(np.float32) - 0.5) * 0.5) * cell
+                r = np.float32(0.25 + 0.15 * rng.rand())
+                B.add_mesh((bv * r + c).astype(np.float32), bf, mats[k % len(mats)])
+                k += 1
+    ext = g * cell
+    B.add_rect((ext / 2, -0.01, ext / 2), (4 * ext, 0, 0), (0, 0, 4 * ext), mats[0], flip=True)
+    light = B.add_material("emissive", (40.0, 36.0, 30.0))
+    for lx, lz in ((0.25, 0.25), (0.75, 0.25), (0.25, 0.75), (0.75, 0.75)):
+        B.add_rect((ext * lx, ext + 1.0, ext * lz), (ext * 0.3, 0, 0), (0, 0, ext * 0.3), light)
+    if with_shapes:
+        B.add_sphere((-0.6, 0.4, ext / 2), 0.4, mats[2])
+        B.add_disk((ext + 0.5, 0.3, ext / 2), (-1, 0.2, 0), 0.5, mats[1])
+    B.set_camera(size, (ext / 2, ext * 0.9, -ext * 1.6), (ext / 2, ext * 0.4, ext / 2), 0.35)
+    return {"spp": spp, "depth": depth}
+
+
+SCENES = {"cbox_readme": cbox_readme, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
+          "mesh_field": mesh_field}
