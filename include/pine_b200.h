@@ -147,13 +147,22 @@ typedef struct pb2_render_params {
   int32_t flags; /* PB2_RENDER_* */
 } pb2_render_params;
 #define PB2_RENDER_SORT_BY_MATERIAL 1 /* bucket the shade queue by BxDF kind */
+#define PB2_RENDER_TIME_KERNELS 2     /* fill pb2_counters.last_{trace,shadow,shade,other}_ms */
 
 typedef struct pb2_counters {
-  uint64_t closest_rays, shadow_rays, camera_samples, kernel_launches;
-  double last_render_ms;  /* device time of the last pb2_render* (CUDA events on its stream) */
-  double last_trace_ms;   /* device time of the traversal kernels inside it */
-  double bvh_build_ms;    /* host time spent building + uploading the BVH */
-  uint32_t bvh2_nodes, wide_nodes, n_primitives;
+  uint64_t closest_rays, shadow_rays, camera_samples, kernel_launches; /* cumulative */
+  /* Device times of the last pb2_render*, CUDA events on its stream. The per-kernel sums are only
+   * taken when PB2_RENDER_TIME_KERNELS is set (two event records around every launch). */
+  double last_render_ms;
+  double last_trace_ms;   /* closest-hit traversal kernels (Accel::intersect) */
+  double last_shadow_ms;  /* any-hit traversal kernels (Accel::hit) */
+  double last_shade_ms;   /* shading kernels */
+  double last_other_ms;   /* raygen + fold/resolve + film */
+  uint64_t last_closest_rays, last_shadow_rays, last_trace_launches; /* of the last render */
+  double bvh_build_ms;    /* host time of the last pb2_upload_scene: BVH build + layout */
+  double upload_ms;       /* host wall time of the last host->device staging of the scene */
+  uint64_t scene_bytes;   /* bytes that staging copies */
+  uint32_t bvh2_nodes, wide_nodes, n_primitives, build_threads;
 } pb2_counters;
 
 typedef struct pb2_context pb2_context;
@@ -166,6 +175,11 @@ void pb2_destroy(pb2_context* ctx);
 /* Replaces: accel.build(&scene) + light_sampler.build(&scene) (integrator.cpp:32-33,
  * bvh.cpp:453-495, lightsampler.cpp:6-10). Copies everything it needs; builds the BVH on the host. */
 int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* scene);
+/* Copies the already-built scene (BVH, primitives, materials, active sampler tables) from the
+ * context's pinned host staging to the device again, asynchronously on cuda_stream (NULL = the
+ * context's stream). What pb2_upload_scene does after the host build; exposed so that a caller
+ * (bench.py's end-to-end leg) can put the host->device transfer inside a timed region. */
+int pb2_restage_scene(pb2_context* ctx, void* cuda_stream);
 /* The Heitz et al. tables Pine links in (src/contrib/bluesobol/bluenoise_<spp>spp.cpp:2-12), as u8:
  * sobol[256*256], scramble[128*128*8], rank[128*128*8]. */
 int pb2_upload_sampler_tables(pb2_context* ctx, int spp_pow2, const uint8_t* sobol,

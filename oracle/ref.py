@@ -40,6 +40,10 @@ def lib():
         L.ref_render.restype = C.c_double
         L.ref_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.ref_accel_build.restype = C.c_double
+        L.ref_bounded_prepare.restype = C.c_double
+        L.ref_bounded_prepare.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.ref_bounded_render_rows.restype = C.c_double
+        L.ref_bounded_render_rows.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.ref_accel_build.argtypes = [C.c_void_p]
         L.ref_bluenoise.restype = C.c_float
         L.ref_hash_pixel.restype = C.c_uint64
@@ -148,6 +152,22 @@ class RefScene:
         kind = {"blue": 0, "sobol": 1, "uniform": 2}[sampler]
         secs = self.L.ref_render(self.h, kind, spp, depth, film.ctypes.data_as(C.c_void_p))
         return film, secs
+
+    def bounded_prepare(self, spp, depth):
+        """RTIntegrator::render prologue (sampler clones, BVH::build, light list) of a
+        PathIntegrator(BVH(), BlueSobolSampler(spp), UniformLightSampler(), depth); -> seconds."""
+        return self.L.ref_bounded_prepare(self.h, spp, depth)
+
+    def bounded_render_rows(self, row_begin, row_end, row_step=1, want_film=False):
+        """The reference pixel loop (path.cpp:31-40) over rows row_begin::row_step < row_end only,
+        all host threads; -> (wall seconds, film or None). Needs bounded_prepare first."""
+        w, h = self.size
+        film = np.zeros((h, w, 4), np.float32) if want_film else None
+        secs = self.L.ref_bounded_render_rows(self.h, row_begin, row_end, row_step,
+                                              film.ctypes.data_as(C.c_void_p) if want_film else None)
+        if secs < 0:
+            raise RuntimeError("bounded_prepare was not called")
+        return secs, film
 
     def finalize(self, film):
         out = np.zeros_like(film)

@@ -16,6 +16,9 @@
 #define private public
 #include <pine/impl/accel/bvh.h>
 #undef private
+// RTIntegrator::samplers/spp/accel are protected; BoundedPath below derives from PathIntegrator and
+// needs PathIntegrator::Vertex, which is only complete inside path.cpp -- so path.cpp is #included
+// here too (unmodified) instead of being linked as its own object.
 #include <pine/core/scene.h>
 #include <pine/core/parallel.h>
 #include <pine/core/integrator.h>
@@ -27,6 +30,7 @@
 #include <pine/impl/integrator/path.h>
 
 #include <pine/impl/accel/bvh.cpp>
+#include <pine/impl/integrator/path.cpp>
 
 #include <chrono>
 #include <cstdint>
@@ -46,11 +50,37 @@ extern float bluenoise_256spp(int, int, int, int);
 using namespace pine;
 
 namespace {
+// PathIntegrator whose prologue (RTIntegrator::render: sampler clones, accel.build,
+// light_sampler.build -- integrator.cpp:26-35) and pixel loop (path.cpp:31-40) can be run
+// separately, so that bench.py can time a BOUNDED SAMPLE of a big render (a subset of the film's
+// rows) without paying the reference's single-threaded BVH build once per timed step. The loop body
+// is the reference's, verbatim in meaning; radiance() is the reference's own code.
+struct BoundedPath : PathIntegrator {
+  using PathIntegrator::PathIntegrator;
+  void prepare(Scene& scene) { RTIntegrator::render(scene); }
+  // rows row_begin, row_begin + row_step, ... < row_end of the film
+  void render_rows(Scene& scene, int row_begin, int row_end, int row_step) {
+    auto& film = scene.camera.film();
+    const int n_rows = row_end > row_begin ? (row_end - row_begin + row_step - 1) / row_step : 0;
+    parallel_for(vec2i(film.size().x, n_rows), [&](vec2i q) {
+      vec2i p(q.x, row_begin + q.y * row_step);
+      Sampler& sampler = samplers[threadIdx].start_pixel(p, 0);
+      auto L = vec3(0.0f);
+      for (int si = 0; si < spp; si++, sampler.start_next_sample()) {
+        auto ray = scene.camera.gen_ray((p + sampler.rand2f()) / film.size(), sampler.rand2f());
+        L += radiance(scene, ray, sampler, Vertex::first_vertex()).Lo;
+      }
+      film[p] = vec4(L / spp, 1.0f);
+    });
+  }
+};
 struct RefScene {
   Scene scene;
   std::vector<psl::shared_ptr<Material>> materials;
   BVH bvh;
   bool bvh_built = false;
+  BoundedPath* bounded = nullptr;
+  ~RefScene() { delete bounded; }
 };
 vec3 v3(const float* p) { return vec3(p[0], p[1], p[2]); }
 mat4 m4_rowmajor(const float* m) {
@@ -159,6 +189,29 @@ double ref_render(void* h, int sampler_kind, int spp, int depth, float* film_rgb
                                    depth);
   auto t0 = std::chrono::steady_clock::now();
   integrator.render(S.scene);
+  auto t1 = std::chrono::steady_clock::now();
+  if (film_rgba) {
+    auto& film = S.scene.camera.film();
+    std::memcpy(film_rgba, film.data(), sizeof(float) * 4 * size_t(film.width()) * film.height());
+  }
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+// Bounded-sample variant for timing (see BoundedPath): prepare once (returns the seconds the
+// prologue took, dominated by BVH::build), then render row subsets. BlueSobolSampler only.
+double ref_bounded_prepare(void* h, int spp, int depth) {
+  auto& S = *(RefScene*)h;
+  delete S.bounded;
+  S.bounded = new BoundedPath(Accel(BVH()), Sampler(BlueSobolSampler(spp)),
+                              LightSampler(UniformLightSampler()), depth);
+  auto t0 = std::chrono::steady_clock::now();
+  S.bounded->prepare(S.scene);
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+double ref_bounded_render_rows(void* h, int row_begin, int row_end, int row_step, float* film_rgba) {
+  auto& S = *(RefScene*)h;
+  if (!S.bounded) return -1.0;
+  auto t0 = std::chrono::steady_clock::now();
+  S.bounded->render_rows(S.scene, row_begin, row_end, row_step);
   auto t1 = std::chrono::steady_clock::now();
   if (film_rgba) {
     auto& film = S.scene.camera.film();

@@ -91,8 +91,13 @@ class Counters(C.Structure):
     _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("camera_samples", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("last_render_ms", C.c_double), ("last_trace_ms", C.c_double),
-                ("bvh_build_ms", C.c_double), ("bvh2_nodes", C.c_uint32),
-                ("wide_nodes", C.c_uint32), ("n_primitives", C.c_uint32)]
+                ("last_shadow_ms", C.c_double), ("last_shade_ms", C.c_double),
+                ("last_other_ms", C.c_double), ("last_closest_rays", C.c_uint64),
+                ("last_shadow_rays", C.c_uint64), ("last_trace_launches", C.c_uint64),
+                ("bvh_build_ms", C.c_double), ("upload_ms", C.c_double),
+                ("scene_bytes", C.c_uint64), ("bvh2_nodes", C.c_uint32),
+                ("wide_nodes", C.c_uint32), ("n_primitives", C.c_uint32),
+                ("build_threads", C.c_uint32)]
 
 
 SHAPE_KINDS = {"aabb": 0, "obb": 1, "sphere": 2, "triangle": 3, "cone": 4, "rect": 5, "disk": 6,
@@ -103,6 +108,7 @@ MATERIAL_KINDS = {"emissive": 0, "diffuse": 1, "metal": 2, "glossy": 3, "glass":
 # every symbol include/*.h declares (tests check the built library exports all of them)
 ABI_SYMBOLS = [
     "pb2_last_error", "pb2_device_count", "pb2_create", "pb2_destroy", "pb2_upload_scene",
+    "pb2_restage_scene",
     "pb2_upload_sampler_tables", "pb2_render", "pb2_render_device", "pb2_film_finalize",
     "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler",
     "pb2_test_primary_rays", "pb2_get_counters", "pb2_bvh_info", "pb2_bvh_nodes",
@@ -132,6 +138,7 @@ def lib():
         L.pb2_destroy.argtypes = [C.c_void_p]
         L.pb2_destroy.restype = None
         L.pb2_upload_scene.argtypes = [C.c_void_p, C.POINTER(SceneDesc)]
+        L.pb2_restage_scene.argtypes = [C.c_void_p, C.c_void_p]
         L.pb2_upload_sampler_tables.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                                 C.c_void_p]
         L.pb2_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p]

@@ -55,6 +55,7 @@ extern "C" void pb2_destroy(pb2_context* ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     free_wavefront(ctx);
+    ctx->host.unpin();
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->ev2) cudaEventDestroy(ctx->ev2);

@@ -33,5 +33,8 @@ struct Tree2 {
 };
 
 void build_sah_binary(std::vector<BuildPrim> prims, Tree2& out);
+// Extra threads build_sah_binary may use for big trees (process-wide budget; the result does not
+// depend on it). pb2_upload_scene sets it to the number of idle hardware threads.
+void set_build_threads(int n);
 
 }  // namespace pb2

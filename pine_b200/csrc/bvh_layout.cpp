@@ -1,147 +1,33 @@
-// bvh_layout.cpp -- device layouts of a host Tree2 (see bvh_layout.h / device_scene.h).
+// bvh_layout.cpp -- device layouts of the host trees (see bvh_layout.h / device_scene.h).
 //
-// Wide tree: the binary tree is collapsed top-down, always opening the internal child with the
-// largest surface area until eight slots are used. Reference leaves are never merged or split --
-// each becomes one DLeaf carrying its exact fp32 box, because in the reference a primitive is only
-// tested when its own leaf's box passes (bvh.cpp:409-418); inner boxes are only ever looser.
-// Child boxes are stored as 8-bit offsets from the node's lower corner in units of a per-axis
-// power of two, rounded outward and verified with the same float expression the kernel evaluates.
+// Wide tree. The reference's two-level structure (top tree over {mesh, analytic shape}, one tree
+// per mesh: bvh.cpp:453-495) is viewed as ONE tree and collapsed top-down into 8-wide nodes, always
+// opening the open child with the largest surface area. Every wide child box therefore CONTAINS
+// the reference boxes of everything below it, and the kernel's (conservative) slab test passes
+// whenever the reference's test of any of those boxes would: the wide walk can only test MORE
+// primitives than the reference does, never fewer. What the reference additionally requires -- a
+// primitive is only tested when its own leaf's exact box passes (bvh.cpp:409-418) -- is kept as a
+// per-primitive `gate` (DLeaf) that the kernel checks for the winner only (traverse.cuh).
+// Leaf children hold at most 3 primitives (unary count in `meta`); bigger reference leaves are
+// spread over several slots with the same gate.
 #include "bvh_layout.h"
 
+#include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
+#include <thread>
 
 namespace pb2 {
-namespace {
 
-struct Slot {
-  Box3 box;
-  int node;       // binary node index (internal) or -1
-  int leaf_node;  // binary leaf node index or -1
-};
-
-inline float plane(float origin, uint8_t q, uint8_t e) {
-  return origin + float(q) * u2f(uint32_t(e) << 23);
-}
-
-struct WideBuilder {
-  const Tree2& t;
-  LayoutOut& out;
-  const pb2_mesh* mesh;
-  int geom;
-  int leaf_base;  // rebased offset of this tree's leaf_prims in out.leaf_prims
-  std::vector<int> leaf_of_node;  // binary leaf node -> DLeaf index
-
-  int make_leaf(int bnode, const Box3* gate) {
-    if (leaf_of_node[bnode] >= 0) return leaf_of_node[bnode];
-    const Node2& nd = t.nodes[bnode];
-    DLeaf L;
-    Box3 b = gate ? *gate : nd.box[0];
-    for (int k = 0; k < 3; k++) { L.box[k] = b.lower[k]; L.box[3 + k] = b.upper[k]; }
-    if (mesh) {
-      L.link = int32_t(out.leaf_tris.size());
-      L.count = int32_t(uint32_t(nd.leaf_count) | 0x80000000u);
-      for (int i = 0; i < nd.leaf_count; i++) {
-        int tri = t.leaf_prims[nd.leaf_offset + i];
-        const uint32_t* f = mesh->indices + 3 * size_t(tri);
-        DTri d;
-        std::memcpy(d.v0, mesh->vertices + 3 * size_t(f[0]), 12);
-        std::memcpy(d.v1, mesh->vertices + 3 * size_t(f[1]), 12);
-        std::memcpy(d.v2, mesh->vertices + 3 * size_t(f[2]), 12);
-        d.prim = tri; d.geom = geom; d.pad = 0;
-        out.leaf_tris.push_back(d);
-      }
-    } else {
-      L.link = leaf_base + nd.leaf_offset;
-      L.count = nd.leaf_count;
-    }
-    out.leaves.push_back(L);
-    return leaf_of_node[bnode] = int(out.leaves.size()) - 1;
-  }
-
-  // Builds the wide node for binary internal node `bnode`; returns its DNode8 index.
-  int build(int bnode) {
-    Slot slots[8];
-    int n = 0;
-    auto push_children = [&](int b) {
-      const Node2& nd = t.nodes[b];
-      for (int c = 0; c < 2; c++) {
-        const Node2& ch = t.nodes[nd.child[c]];
-        Slot s;
-        s.box = nd.box[c];
-        s.node = ch.leaf_count ? -1 : nd.child[c];
-        s.leaf_node = ch.leaf_count ? nd.child[c] : -1;
-        slots[n++] = s;
-      }
-    };
-    push_children(bnode);
-    while (n < 8) {
-      int best = -1;
-      float best_area = -1.0f;
-      for (int i = 0; i < n; i++)
-        if (slots[i].node >= 0) {
-          float a = slots[i].box.surface_area();
-          if (a > best_area) { best_area = a; best = i; }
-        }
-      if (best < 0) break;
-      int b = slots[best].node;
-      slots[best] = slots[n - 1];
-      n--;
-      push_children(b);
-    }
-    int idx = int(out.nodes8.size());
-    out.nodes8.emplace_back();
-    DNode8 nd;
-    std::memset(&nd, 0, sizeof(nd));
-    Box3 bounds;
-    for (int i = 0; i < n; i++) bounds.extend(slots[i].box);
-    for (int k = 0; k < 3; k++) {
-      nd.origin[k] = bounds.lower[k];
-      float extent = bounds.upper[k] - bounds.lower[k];
-      int e = 0;
-      if (extent > 0) {
-        std::frexp(extent / 255.0f, &e);  // extent/255 = m * 2^e, m in [0.5,1) => 2^e >= extent/255
-        // guard against rounding in origin + 255*scale falling short of upper
-        while (plane(nd.origin[k], 255, uint8_t(pmin(pmax(e + 127, 1), 254))) < bounds.upper[k]) e++;
-      } else {
-        e = -126;
-      }
-      nd.exp[k] = uint8_t(pmin(pmax(e + 127, 1), 254));
-    }
-    nd.n_children = uint8_t(n);
-    for (int i = 0; i < n; i++) {
-      for (int k = 0; k < 3; k++) {
-        float scale = u2f(uint32_t(nd.exp[k]) << 23);
-        int ql = int(std::floor((slots[i].box.lower[k] - nd.origin[k]) / scale));
-        int qh = int(std::ceil((slots[i].box.upper[k] - nd.origin[k]) / scale));
-        ql = pmin(pmax(ql, 0), 255);
-        qh = pmin(pmax(qh, 0), 255);
-        while (ql > 0 && plane(nd.origin[k], uint8_t(ql), nd.exp[k]) > slots[i].box.lower[k]) ql--;
-        while (qh < 255 && plane(nd.origin[k], uint8_t(qh), nd.exp[k]) < slots[i].box.upper[k]) qh++;
-        nd.qlo[k][i] = uint8_t(ql);
-        nd.qhi[k][i] = uint8_t(qh);
-      }
-    }
-    for (int i = n; i < 8; i++)
-      for (int k = 0; k < 3; k++) { nd.qlo[k][i] = 255; nd.qhi[k][i] = 0; }  // inverted = never hit
-    for (int i = 0; i < n; i++)
-      nd.child[i] = slots[i].node >= 0 ? build(slots[i].node) : ~make_leaf(slots[i].leaf_node, nullptr);
-    out.nodes8[idx] = nd;
-    return idx;
-  }
-};
-
-}  // namespace
-
-DTree append_tree(const Tree2& t, LayoutOut& out, const pb2_mesh* mesh, int geom) {
-  DTree d{-1, 0, 0, 0x7fffffff};
+DTree append_binary(const Tree2& t, LayoutOut& out) {
+  DTree d{-1, 0, 0, 0};
   if (t.root < 0) return d;
   const int node_base = int(out.nodes2.size());
   const int leaf_base = int(out.leaf_prims.size());
   out.leaf_prims.insert(out.leaf_prims.end(), t.leaf_prims.begin(), t.leaf_prims.end());
-
-  // binary layout: internal nodes only get a DNode2; children that are leaves are folded into the
-  // parent's link/count. Node indices are remapped densely over internal nodes.
+  // Internal nodes only get a DNode2; children that are leaves are folded into the parent's
+  // link/count. Node indices are remapped densely over internal nodes.
   std::vector<int> remap(t.nodes.size(), -1);
   int n_internal = 0;
   for (size_t i = 0; i < t.nodes.size(); i++)
@@ -166,17 +52,403 @@ DTree append_tree(const Tree2& t, LayoutOut& out, const pb2_mesh* mesh, int geom
   } else {
     d.root = remap[t.root];
   }
-  if (!mesh) return d;  // the top-level tree is only ever walked in reference order (traverse.cuh)
-  WideBuilder wb{t, out, mesh, geom, leaf_base, std::vector<int>(t.nodes.size(), -1)};
-  if (root.leaf_count) {
-    Box3 everything;  // a root leaf is tested without any box test (bvh.cpp:398-400)
-    everything.lower = V3(-kFloatMax);
-    everything.upper = V3(kFloatMax);
-    d.wide_root = ~wb.make_leaf(t.root, &everything);
-  } else {
-    d.wide_root = wb.build(t.root);
-  }
   return d;
+}
+
+namespace {
+
+enum HandleKind : int { H_TOP_NODE, H_TOP_LEAF, H_MESH_NODE, H_MESH_LEAF, H_SHAPE };
+struct Handle {
+  int kind = H_TOP_NODE;
+  int tree = -1;   // mesh tree index (H_MESH_*)
+  int node = -1;   // node index in its tree; H_SHAPE: top primitive id
+  int lo = 0, hi = 0;  // H_TOP_LEAF / H_MESH_LEAF: sub-range of the leaf's primitives
+  int gate = -1;   // DLeaf index of the reference leaf that gates the terminals below (-1: none)
+};
+struct Slot {
+  Handle h;
+  Box3 box;
+};
+
+struct Frag {
+  std::vector<DNode8> nodes;
+  std::vector<DPrim> prims;
+};
+
+struct Wide {
+  const WideInput& in;
+  std::vector<int> top_leaf_gate;                // top node -> DLeaf (leaves only)
+  std::vector<std::vector<int>> mesh_leaf_gate;  // tree -> node -> DLeaf (leaves only)
+  std::vector<int> tree_mesh, tree_geom;         // mesh tree -> mesh id / geometry index
+
+  const Tree2& top() const { return *in.top; }
+  const Tree2& mtree(int k) const { return (*in.mesh_trees)[k]; }
+
+  static bool terminal(const Handle& h) {
+    return h.kind == H_SHAPE || (h.kind == H_MESH_LEAF && h.hi - h.lo <= 3);
+  }
+  static int fanout(const Handle& h) {
+    switch (h.kind) {
+      case H_TOP_NODE: case H_MESH_NODE: return 2;
+      case H_TOP_LEAF: return std::min(8, h.hi - h.lo);
+      case H_MESH_LEAF: return std::min(8, (h.hi - h.lo + 2) / 3);
+      default: return 0;
+    }
+  }
+  Box3 tri_box(int k, int tri) const {
+    const pb2_mesh& m = in.meshes[tree_mesh[k]];
+    const uint32_t* f = m.indices + 3 * size_t(tri);
+    return aabb_of_tri(ld3(m.vertices + 3 * size_t(f[0])), ld3(m.vertices + 3 * size_t(f[1])),
+                       ld3(m.vertices + 3 * size_t(f[2])));
+  }
+  // One top-level primitive as a slot: a mesh becomes the root of its tree, a shape a terminal.
+  Slot prim_slot(int top_prim, const Box3& box, int gate) const {
+    const DTopPrim& tp = (*in.top_prims)[top_prim];
+    Slot s;
+    s.box = box;
+    if (tp.kind == PB2_SHAPE_MESH) {
+      const int k = (*in.mesh_tree_of)[tp.index];
+      const Tree2& t = mtree(k);
+      const Node2& root = t.nodes[t.root];
+      s.h.tree = k;
+      s.h.node = t.root;
+      if (root.leaf_count) {  // single-leaf mesh: no box test of its own (bvh.cpp:398-400)
+        s.h.kind = H_MESH_LEAF; s.h.lo = 0; s.h.hi = root.leaf_count; s.h.gate = gate;
+      } else {
+        s.h.kind = H_MESH_NODE;
+      }
+    } else {
+      s.h.kind = H_SHAPE; s.h.node = top_prim; s.h.gate = gate;
+    }
+    return s;
+  }
+  Slot top_leaf_slot(int leaf, int lo, int hi, const Box3& box) const {
+    const Node2& nd = top().nodes[leaf];
+    if (hi - lo == 1) return prim_slot(top().leaf_prims[nd.leaf_offset + lo], box, top_leaf_gate[leaf]);
+    Slot s;
+    s.h.kind = H_TOP_LEAF; s.h.node = leaf; s.h.lo = lo; s.h.hi = hi;
+    s.box = box;
+    return s;
+  }
+  void expand(const Handle& h, std::vector<Slot>& out) const {
+    switch (h.kind) {
+      case H_TOP_NODE: {
+        const Node2& nd = top().nodes[h.node];
+        for (int c = 0; c < 2; c++) {
+          const Node2& ch = top().nodes[nd.child[c]];
+          if (ch.leaf_count) out.push_back(top_leaf_slot(nd.child[c], 0, ch.leaf_count, nd.box[c]));
+          else { Slot s; s.h.kind = H_TOP_NODE; s.h.node = nd.child[c]; s.box = nd.box[c]; out.push_back(s); }
+        }
+      } break;
+      case H_TOP_LEAF: {
+        const Node2& nd = top().nodes[h.node];
+        const int n = h.hi - h.lo, parts = std::min(8, n);
+        for (int i = 0; i < parts; i++) {
+          const int a = h.lo + int(int64_t(n) * i / parts), b = h.lo + int(int64_t(n) * (i + 1) / parts);
+          Box3 box;
+          for (int j = a; j < b; j++) box.extend((*in.top_boxes)[top().leaf_prims[nd.leaf_offset + j]]);
+          out.push_back(top_leaf_slot(h.node, a, b, box));
+        }
+      } break;
+      case H_MESH_NODE: {
+        const Tree2& t = mtree(h.tree);
+        const Node2& nd = t.nodes[h.node];
+        for (int c = 0; c < 2; c++) {
+          const Node2& ch = t.nodes[nd.child[c]];
+          Slot s;
+          s.h.tree = h.tree; s.h.node = nd.child[c]; s.box = nd.box[c];
+          if (ch.leaf_count) {
+            s.h.kind = H_MESH_LEAF; s.h.lo = 0; s.h.hi = ch.leaf_count;
+            s.h.gate = mesh_leaf_gate[h.tree][nd.child[c]];
+          } else {
+            s.h.kind = H_MESH_NODE;
+          }
+          out.push_back(s);
+        }
+      } break;
+      case H_MESH_LEAF: {  // more than 3 triangles: chunks of <= 3 (or 8 sub-ranges of whole chunks)
+        const Tree2& t = mtree(h.tree);
+        const Node2& nd = t.nodes[h.node];
+        const int chunks = (h.hi - h.lo + 2) / 3, parts = std::min(8, chunks);
+        for (int i = 0; i < parts; i++) {
+          const int a = h.lo + 3 * int(int64_t(chunks) * i / parts);
+          const int b = std::min(h.hi, h.lo + 3 * int(int64_t(chunks) * (i + 1) / parts));
+          Slot s;
+          s.h = h; s.h.lo = a; s.h.hi = b;
+          for (int j = a; j < b; j++) s.box.extend(tri_box(h.tree, t.leaf_prims[nd.leaf_offset + j]));
+          out.push_back(s);
+        }
+      } break;
+      default: break;
+    }
+  }
+
+  void emit_prims(const Handle& h, std::vector<DPrim>& prims) const {
+    if (h.kind == H_SHAPE) {
+      const DTopPrim& tp = (*in.top_prims)[h.node];
+      DPrim d;
+      std::memset(&d, 0, sizeof(d));
+      std::memcpy(&d.v0[0], &tp.index, 4);
+      d.prim = -1 - tp.kind; d.geom = tp.geom; d.leaf = h.gate;
+      prims.push_back(d);
+      return;
+    }
+    const Tree2& t = mtree(h.tree);
+    const Node2& nd = t.nodes[h.node];
+    const pb2_mesh& m = in.meshes[tree_mesh[h.tree]];
+    for (int j = h.lo; j < h.hi; j++) {
+      const int tri = t.leaf_prims[nd.leaf_offset + j];
+      const uint32_t* f = m.indices + 3 * size_t(tri);
+      DPrim d;
+      std::memcpy(d.v0, m.vertices + 3 * size_t(f[0]), 12);
+      std::memcpy(d.v1, m.vertices + 3 * size_t(f[1]), 12);
+      std::memcpy(d.v2, m.vertices + 3 * size_t(f[2]), 12);
+      d.prim = tri; d.geom = tree_geom[h.tree]; d.leaf = h.gate;
+      prims.push_back(d);
+    }
+  }
+
+  // Quantisation frame of one axis: scale = 2^e and an origin that is a multiple of the scale,
+  // such that origin + q * scale is exactly representable for q in [0,255] and covers [lo,hi].
+  static void frame(float lo, float hi, float& origin, uint8_t& exp_out) {
+    int e;
+    const double extent = double(hi) - double(lo);
+    if (extent > 0) { std::frexp(extent / 255.0, &e); } else { e = -126; }
+    // exact representability: |origin / scale| + 255 < 2^24
+    const double amax = std::max(std::fabs(double(lo)), std::fabs(double(hi)));
+    if (amax > 0) {
+      int ea;
+      std::frexp(amax, &ea);  // amax < 2^ea
+      e = std::max(e, ea - 23);
+    }
+    e = std::min(std::max(e, -126), 127);
+    for (;; e++) {
+      const double scale = std::ldexp(1.0, e);
+      const double o = std::floor(double(lo) / scale) * scale;
+      if (o + 255.0 * scale >= double(hi) && std::fabs(o) / scale + 256.0 < 16777216.0) {
+        origin = float(o);
+        exp_out = uint8_t(e + 127);
+        return;
+      }
+    }
+  }
+
+  // Builds the wide node for `slots` (collapsed already) into `node`; appends terminals to `prims`
+  // and the handles of its internal children, in child order, to `kids`.
+  void make_node(std::vector<Slot>& slots, DNode8& node, std::vector<DPrim>& prims,
+                 std::vector<Handle>& kids, uint32_t child_base) const {
+    const int n = int(slots.size());
+    Box3 bounds;
+    for (auto& s : slots) bounds.extend(s.box);
+    // slot assignment: child c prefers the slot whose corner direction its centroid points to
+    const V3 center = bounds.centroid();
+    float cost[8][8];
+    for (int c = 0; c < n; c++) {
+      const V3 v = slots[c].box.centroid() - center;
+      for (int s = 0; s < 8; s++)
+        cost[c][s] = (s & 1 ? v.x : -v.x) + (s & 2 ? v.y : -v.y) + (s & 4 ? v.z : -v.z);
+    }
+    int slot_of[8], child_in[8];
+    for (int i = 0; i < 8; i++) { slot_of[i] = -1; child_in[i] = -1; }
+    for (int round = 0; round < n; round++) {
+      int bc = -1, bs = -1;
+      float best = -kFloatMax;
+      for (int c = 0; c < n; c++) {
+        if (slot_of[c] >= 0) continue;
+        for (int s = 0; s < 8; s++)
+          if (child_in[s] < 0 && (bc < 0 || cost[c][s] > best)) { best = cost[c][s]; bc = c; bs = s; }
+      }
+      slot_of[bc] = bs;
+      child_in[bs] = bc;
+    }
+    std::memset(&node, 0, sizeof(node));
+    double scale[3];
+    for (int k = 0; k < 3; k++) {
+      frame(bounds.lower[k], bounds.upper[k], node.origin[k], node.exp[k]);
+      scale[k] = std::ldexp(1.0, int(node.exp[k]) - 127);
+    }
+    node.child_base = child_base;
+    node.prim_base = uint32_t(prims.size());
+    int prim_offset = 0;
+    for (int s = 0; s < 8; s++) {
+      const int c = child_in[s];
+      if (c < 0) continue;
+      const Slot& sl = slots[c];
+      for (int k = 0; k < 3; k++) {
+        double ql = std::floor((double(sl.box.lower[k]) - double(node.origin[k])) / scale[k]);
+        double qh = std::ceil((double(sl.box.upper[k]) - double(node.origin[k])) / scale[k]);
+        ql = std::min(std::max(ql, 0.0), 255.0);
+        qh = std::min(std::max(qh, 0.0), 255.0);
+        // the planes are exact floats by construction; make sure they enclose the box
+        auto plane = [&](double q) { return float(double(node.origin[k]) + q * scale[k]); };
+        while (ql > 0 && plane(ql) > sl.box.lower[k]) ql -= 1;
+        while (qh < 255 && plane(qh) < sl.box.upper[k]) qh += 1;
+        node.qlo[k][s] = uint8_t(ql);
+        node.qhi[k][s] = uint8_t(qh);
+      }
+      if (terminal(sl.h)) {
+        const int before = int(prims.size());
+        emit_prims(sl.h, prims);
+        const int cnt = int(prims.size()) - before;  // 1..3
+        node.meta[s] = uint8_t((((1 << cnt) - 1) << 5) | prim_offset);
+        prim_offset += cnt;
+      } else {
+        node.imask |= uint8_t(1 << s);
+        node.meta[s] = uint8_t((1 << 5) | (24 + s));
+        kids.push_back(sl.h);
+      }
+    }
+  }
+
+  // Slots of the wide node that represents `h`.
+  void collapse(const Handle& h, std::vector<Slot>& slots) const {
+    slots.clear();
+    if (terminal(h)) { Slot s; s.h = h; slots.push_back(s); return; }  // only ever the root
+    expand(h, slots);
+    bool closed[8] = {};
+    while (slots.size() < 8) {
+      int best = -1;
+      float best_area = -1.0f;
+      for (size_t i = 0; i < slots.size(); i++) {
+        if (closed[i] || terminal(slots[i].h)) continue;
+        if (int(slots.size()) - 1 + fanout(slots[i].h) > 8) { closed[i] = true; continue; }
+        const float a = slots[i].box.surface_area();
+        if (a > best_area) { best_area = a; best = int(i); }
+      }
+      if (best < 0) break;
+      const Handle open = slots[best].h;
+      slots[best] = slots.back();
+      closed[best] = closed[slots.size() - 1];
+      closed[slots.size() - 1] = false;
+      slots.pop_back();
+      expand(open, slots);
+    }
+  }
+
+  // Breadth-first build of everything below `root` into `f` (local indices, root = node 0).
+  // Stops after `max_nodes` nodes have been PROCESSED (0 = no limit); the unprocessed tail of the
+  // queue is returned in `pending` as (handle, local node index).
+  void build_fragment(const Handle& root, Frag& f, size_t max_nodes,
+                      std::vector<std::pair<Handle, uint32_t>>* pending) const {
+    std::vector<Handle> queue{root};
+    f.nodes.emplace_back();
+    std::vector<Slot> slots;
+    std::vector<Handle> kids;
+    size_t head = 0;
+    for (; head < queue.size(); head++) {
+      if (max_nodes && head >= max_nodes) break;
+      collapse(queue[head], slots);
+      if (head == 0 && slots.size() == 1 && terminal(slots[0].h)) {
+        // degenerate scene: a single terminal; give the root the terminal's own box
+        slots[0].box = Box3();
+        if (root.kind == H_SHAPE) slots[0].box = (*in.top_boxes)[root.node];
+        else for (int j = root.lo; j < root.hi; j++)
+          slots[0].box.extend(tri_box(root.tree, mtree(root.tree).leaf_prims[mtree(root.tree).nodes[root.node].leaf_offset + j]));
+      }
+      kids.clear();
+      DNode8 nd;
+      make_node(slots, nd, f.prims, kids, uint32_t(f.nodes.size()));
+      f.nodes[head] = nd;
+      for (auto& k : kids) { queue.push_back(k); f.nodes.emplace_back(); }
+    }
+    if (pending)
+      for (; head < queue.size(); head++) pending->push_back({queue[head], uint32_t(head)});
+  }
+};
+
+}  // namespace
+
+void build_wide(const WideInput& in, LayoutOut& out, int threads) {
+  out.nodes8.clear();
+  out.leaves.clear();
+  out.wide_prims.clear();
+  const Tree2& top = *in.top;
+  if (top.root < 0) return;
+  Wide w{in};
+  auto push_gate = [&](const Box3& b) {
+    DLeaf L;
+    for (int k = 0; k < 3; k++) { L.box[k] = b.lower[k]; L.box[3 + k] = b.upper[k]; }
+    L.pad[0] = L.pad[1] = 0;
+    out.leaves.push_back(L);
+    return int(out.leaves.size()) - 1;
+  };
+  // gates: a leaf that is the ROOT of its tree is tested without a box test (bvh.cpp:398-400)
+  w.top_leaf_gate.assign(top.nodes.size(), -1);
+  for (size_t i = 0; i < top.nodes.size(); i++)
+    if (top.nodes[i].leaf_count && int(i) != top.root) w.top_leaf_gate[i] = push_gate(top.nodes[i].box[0]);
+  out.box_shapes.clear();
+  for (size_t i = 0; i < top.nodes.size(); i++) {
+    const Node2& nd = top.nodes[i];
+    for (int j = 0; j < nd.leaf_count; j++) {
+      const DTopPrim& tp = (*in.top_prims)[top.leaf_prims[nd.leaf_offset + j]];
+      if (tp.kind == PB2_SHAPE_AABB || tp.kind == PB2_SHAPE_OBB)
+        out.box_shapes.push_back(DBoxShape{tp.kind, tp.index, w.top_leaf_gate[i], tp.geom});
+    }
+  }
+  const size_t n_trees = in.mesh_trees->size();
+  w.tree_mesh.assign(n_trees, -1);
+  w.tree_geom.assign(n_trees, -1);
+  for (const DTopPrim& tp : *in.top_prims)
+    if (tp.kind == PB2_SHAPE_MESH) {
+      const int k = (*in.mesh_tree_of)[tp.index];
+      w.tree_mesh[k] = tp.index;
+      w.tree_geom[k] = tp.geom;
+    }
+  w.mesh_leaf_gate.resize(n_trees);
+  for (size_t k = 0; k < n_trees; k++) {
+    const Tree2& t = (*in.mesh_trees)[k];
+    w.mesh_leaf_gate[k].assign(t.nodes.size(), -1);
+    for (size_t i = 0; i < t.nodes.size(); i++)
+      if (t.nodes[i].leaf_count && int(i) != t.root) w.mesh_leaf_gate[k][i] = push_gate(t.nodes[i].box[0]);
+  }
+
+  Handle root;
+  const Node2& rn = top.nodes[top.root];
+  if (rn.leaf_count) {
+    Slot s = w.top_leaf_slot(top.root, 0, rn.leaf_count, rn.box[0]);
+    root = s.h;
+  } else {
+    root.kind = H_TOP_NODE;
+    root.node = top.root;
+  }
+
+  // top part sequentially (breadth first), then one fragment per pending node in parallel
+  threads = std::max(1, threads);
+  Frag head;
+  std::vector<std::pair<Handle, uint32_t>> pending;
+  w.build_fragment(root, head, threads > 1 ? size_t(threads) * 8 : 0, &pending);
+  std::vector<Frag> frags(pending.size());
+  if (!pending.empty()) {
+    std::atomic<size_t> next{0};
+    auto work = [&] {
+      for (size_t i; (i = next.fetch_add(1)) < pending.size();) w.build_fragment(pending[i].first, frags[i], 0, nullptr);
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; t++) pool.emplace_back(work);
+    work();
+    for (auto& th : pool) th.join();
+  }
+  size_t total_nodes = head.nodes.size(), total_prims = head.prims.size();
+  for (auto& f : frags) { total_nodes += f.nodes.size() - 1; total_prims += f.prims.size(); }
+  out.nodes8 = std::move(head.nodes);
+  out.wide_prims = std::move(head.prims);
+  out.nodes8.reserve(total_nodes);
+  out.wide_prims.reserve(total_prims);
+  for (size_t i = 0; i < frags.size(); i++) {
+    Frag& f = frags[i];
+    // local node j >= 1 lands at node_base + j - 1; local node 0 fills the slot reserved for it
+    const uint32_t node_base = uint32_t(out.nodes8.size()), prim_base = uint32_t(out.wide_prims.size());
+    for (size_t j = 0; j < f.nodes.size(); j++) {
+      DNode8 nd = f.nodes[j];
+      nd.child_base += node_base - 1;
+      nd.prim_base += prim_base;
+      if (j == 0) out.nodes8[pending[i].second] = nd;
+      else out.nodes8.push_back(nd);
+    }
+    out.wide_prims.insert(out.wide_prims.end(), f.prims.begin(), f.prims.end());
+    Frag().nodes.swap(f.nodes);
+    Frag().prims.swap(f.prims);
+  }
 }
 
 }  // namespace pb2

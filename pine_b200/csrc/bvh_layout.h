@@ -1,4 +1,6 @@
-// bvh_layout.h -- turn host Tree2 trees into the two device layouts of device_scene.h.
+// bvh_layout.h -- turn the host's reference-identical binary trees into the two device layouts of
+// device_scene.h: the binary nodes walked in reference order (verification / fallback / scenes
+// whose closest hit is order dependent) and the single 8-wide compressed tree used in production.
 #pragma once
 #include <vector>
 
@@ -8,16 +10,27 @@
 namespace pb2 {
 
 struct LayoutOut {
-  std::vector<DNode2> nodes2;
-  std::vector<DNode8> nodes8;
-  std::vector<DLeaf> leaves;
-  std::vector<DTri> leaf_tris;
-  std::vector<int32_t> leaf_prims;
+  std::vector<DNode2> nodes2;       // every binary tree (top level + one per mesh)
+  std::vector<int32_t> leaf_prims;  // primitive ids of the binary leaves
+  std::vector<DNode8> nodes8;       // the wide tree, breadth first, root = node 0
+  std::vector<DLeaf> leaves;        // reference leaf boxes (gates)
+  std::vector<DPrim> wide_prims;    // primitive records of the wide tree
+  std::vector<DBoxShape> box_shapes;  // AABB/OBB shapes with their gates (device_scene.h)
 };
 
-// Appends `t` (node indices and leaf offsets rebased) and its wide collapse; returns the roots.
-// For a mesh tree pass the mesh (vertices/indices) and its geometry index so that triangles are
-// gathered in leaf order; for the top-level tree pass mesh = nullptr.
-DTree append_tree(const Tree2& t, LayoutOut& out, const pb2_mesh* mesh = nullptr, int geom = -1);
+// Appends binary tree `t` (node indices and leaf offsets rebased); returns its root descriptor.
+DTree append_binary(const Tree2& t, LayoutOut& out);
+
+struct WideInput {
+  const Tree2* top = nullptr;                     // top-level tree over `top_prims`
+  const std::vector<DTopPrim>* top_prims = nullptr;
+  const std::vector<Box3>* top_boxes = nullptr;   // the box BVH::build gave each top primitive
+  const std::vector<Tree2>* mesh_trees = nullptr; // per-mesh trees ...
+  const std::vector<int>* mesh_tree_of = nullptr; // ... indexed through mesh id -> tree (or -1)
+  const pb2_mesh* meshes = nullptr;               // vertex / index data of every mesh
+};
+// Collapses top tree + mesh trees into out.nodes8 / out.leaves / out.wide_prims using up to
+// `threads` host threads (the result does not depend on the thread count).
+void build_wide(const WideInput& in, LayoutOut& out, int threads);
 
 }  // namespace pb2

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "bvh_build.h"
+#include "bvh_layout.h"
 #include "device_scene.h"
 
 namespace pb2 {
@@ -54,6 +55,34 @@ struct SamplerTables {
 
 struct WavefrontBuffers;  // render.cu
 
+// Host copy of everything pb2_upload_scene lays out for the device. The vectors stay alive (and
+// page-locked, cudaHostRegister) for as long as the scene is current, so that the host->device
+// staging can be repeated from pinned memory without rebuilding (pb2_restage_scene).
+struct HostScene {
+  LayoutOut lay;
+  std::vector<DTopPrim> top_prims;
+  std::vector<DMesh> meshes;
+  std::vector<DGeom> geoms;
+  std::vector<int32_t> lights;
+  std::vector<float> verts, normals, uvs;
+  std::vector<uint32_t> tris;
+  std::vector<pb2_material> materials;
+  std::vector<pb2_aabb> aabbs;
+  std::vector<pb2_obb> obbs;
+  std::vector<pb2_sphere> spheres;
+  std::vector<pb2_triangle> triangles;
+  std::vector<pb2_cone> cones;
+  std::vector<pb2_rect> rects;
+  std::vector<pb2_disk> disks;
+  struct Item { DBuf* dst; const void* src; size_t bytes; };
+  std::vector<Item> items;          // staging list, in upload order
+  std::vector<void*> registered;    // ranges currently page-locked
+  void unpin() {
+    for (void* p : registered) cudaHostUnregister(p);
+    registered.clear();
+  }
+};
+
 }  // namespace pb2
 
 struct pb2_context {
@@ -67,8 +96,9 @@ struct pb2_context {
   pb2::Tree2 top_tree;
   std::vector<pb2::Tree2> mesh_trees;
 
+  pb2::HostScene host;
   pb2::DScene scene{};  // device pointers
-  pb2::DBuf nodes2, nodes8, leaves, leaf_tris, leaf_prims, top_prims, meshes, geoms, materials, lights;
+  pb2::DBuf nodes2, nodes8, leaves, wide_prims, box_shapes, leaf_prims, top_prims, meshes, geoms, materials, lights;
   pb2::DBuf aabbs, obbs, spheres, triangles, cones, rects, disks;
   pb2::DBuf verts, tris, normals, uvs;
   pb2::DBuf tab_sobol, tab_scramble, tab_rank;

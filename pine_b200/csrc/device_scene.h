@@ -23,7 +23,7 @@ struct DTree {
   int32_t root;        // node index, or -1 for an empty tree
   int32_t root_count;  // >0: the root itself is a leaf (single-leaf tree, bvh.cpp:398-400)
   int32_t root_link;   // leaf offset when root_count > 0
-  int32_t wide_root;   // root of the wide tree for the same primitives (-1 if none)
+  int32_t pad;
 };
 
 struct DTopPrim {      // one primitive of the top-level tree (bvh.cpp:478-493)
@@ -46,40 +46,65 @@ struct DGeom {
 };
 
 // ---- wide BVH (production traversal) -------------------------------------------------------------
-// 8-wide node, child boxes quantised to 8 bits per plane relative to the node's own box, rounded
-// OUTWARD (conservative). 96 bytes = six 128-bit loads. Leaves reference a DLeaf: the reference
-// leaf's exact fp32 box (the gate the reference applies, bvh.cpp:409-418) + its primitive range.
+// ONE 8-wide tree over every primitive of the scene (all mesh triangles and all analytic shapes),
+// obtained by collapsing the reference-identical binary trees (top level with each mesh's tree
+// hanging below it). 80-byte nodes = five 128-bit loads, in the spirit of Ylitie et al. 2017:
+// child boxes are 8-bit offsets from the node's lower corner in units of a per-axis power of two,
+// rounded OUTWARD; the internal children of a node are consecutive in memory (child_base + rank)
+// and so are the primitive records of its leaf children (prim_base + offset); child slots are
+// assigned so that `slot ^ octant` enumerates them roughly front to back for every ray octant.
+// Nodes are laid out breadth first, so the top levels are one contiguous prefix (the L2 window).
 struct alignas(16) DNode8 {
   float origin[3];      // lower corner of the node box
-  uint8_t exp[3];       // per-axis scale = 2^(exp-127): child plane = origin + q * scale
-  uint8_t n_children;
+  uint8_t exp[3];       // per-axis scale = 2^(exp-127): plane = origin + q * scale (exact in fp32)
+  uint8_t imask;        // bit i set: child slot i is an internal node
+  uint32_t child_base;  // index of the first internal child
+  uint32_t prim_base;   // index of the first DPrim of this node's leaf children
+  uint8_t meta[8];      // internal: 001sssss (s = 24 + slot); leaf: unary count (1..3) << 5 | offset;
+                        // empty slot: 0
   uint8_t qlo[3][8];    // quantised lower planes, axis-major
   uint8_t qhi[3][8];    // quantised upper planes
-  int32_t child[8];     // >=0: DNode8 index; <0: ~leaf_index into DScene::leaves
 };
-static_assert(sizeof(DNode8) == 96, "DNode8 must be 96 bytes");
+static_assert(sizeof(DNode8) == 80, "DNode8 must be 80 bytes");
 
+// Exact fp32 box of a reference leaf: the gate the reference applies before it tests the leaf's
+// primitives (bvh.cpp:409-418). Read once per ray, for the winner only (traverse.cuh).
 struct alignas(16) DLeaf {
-  float box[6];         // exact reference leaf box
-  int32_t link;         // top-level leaf: offset into DScene::leaf_prims (ids of DTopPrim);
-                        // mesh leaf: offset into DScene::leaf_tris
-  int32_t count;        // bit 31 set = mesh leaf; low bits = number of primitives
+  float box[6];
+  int32_t pad[2];
 };
 static_assert(sizeof(DLeaf) == 32, "DLeaf must be 32 bytes");
 
-// Triangle gathered in leaf order for the wide traversal: 48 bytes = three 128-bit loads.
-struct alignas(16) DTri {
+// Primitive record of the wide tree, 48 bytes = three 128-bit loads. Triangle: the three vertices
+// gathered from the mesh; analytic shape: prim = -1 - shape_kind and v0[0] carries the index into
+// the per-kind array.
+struct alignas(16) DPrim {
   float v0[3], v1[3], v2[3];
-  int32_t prim, geom, pad;
+  int32_t prim;  // triangle index inside its mesh, or -1 - pb2_shape_kind
+  int32_t geom;  // Scene::geometries index
+  int32_t leaf;  // DLeaf that gates this primitive in the reference, or -1 for "no gate"
 };
-static_assert(sizeof(DTri) == 48, "DTri must be 48 bytes");
+static_assert(sizeof(DPrim) == 48, "DPrim must be 48 bytes");
+
+// AABB/OBB shapes, tested one by one by the wide any-hit walk: a scaled Box compares a LOCAL-space
+// distance with the world-space tmax (bbox.cpp:149-161), so it can report a hit although the ray
+// segment [tmin,tmax] never reaches its world-space box -- box culling cannot be used for it.
+struct DBoxShape {
+  int32_t kind, index, gate, geom;
+};
 
 struct DScene {
   const DNode2* nodes2;
   const DNode8* nodes8;
   const DLeaf* leaves;
-  const DTri* leaf_tris;
+  const DPrim* wide_prims;
   const int32_t* leaf_prims;
+  const DBoxShape* box_shapes;
+  int32_t n_box_shapes;     // > kMaxBoxShapes: any-hit walks the reference-order tree instead
+  int32_t wide_ready;       // 1: nodes8/wide_prims hold a tree (root = node 0)
+  int32_t order_dependent;  // 1: the scene has AABB/OBB shapes, whose closest-hit result depends on
+                            // the visiting order (bbox.cpp:149-161) => closest hit walks the
+                            // reference-order tree; any-hit is order independent and stays wide
   DTree top;
   const DTopPrim* top_prims;
   const DMesh* meshes;
@@ -106,6 +131,8 @@ struct DScene {
   const uint8_t* rank;
   pb2_camera camera;
 };
+
+constexpr int kMaxBoxShapes = 16;
 
 struct Ray {
   V3 o, d;

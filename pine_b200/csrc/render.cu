@@ -55,6 +55,8 @@ struct WaveView {
 struct WavefrontBuffers {
   DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, rng, lacc, counts;
   std::vector<int> host_counts;
+  std::vector<cudaEvent_t> events;  // PB2_RENDER_TIME_KERNELS: one event between consecutive launches
+  ~WavefrontBuffers() { for (cudaEvent_t e : events) cudaEventDestroy(e); }
 };
 
 void free_wavefront(pb2_context* ctx) {
@@ -127,7 +129,7 @@ __global__ void __launch_bounds__(128) k_trace(DScene sc, WaveView w, int depth)
     ray.tmin = 0.0f;
     ray.tmax = a.w;
     Hit h;
-    bool hit = w.accel == 0 ? closest_wide(sc, ray, h) : closest_ref_order(sc, ray, h);
+    bool hit = w.accel == 0 ? closest_production(sc, ray, h) : closest_ref_order(sc, ray, h);
     w.hit[i] = make_float4(ray.tmax, __int_as_float(hit ? h.geom : -1), __int_as_float(h.prim), 0.0f);
   }
 }
@@ -469,7 +471,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   if (P == 0 || n_samples == 0) { PB2_CUDA_CHECK(cudaStreamSynchronize(st)); return PB2_OK; }
 
   // ---- wave plan ----
-  const long max_slots = long(env_int("PB2_MAX_SLOTS", 1 << 22));
+  const long max_slots = long(env_int("PB2_MAX_SLOTS", 1 << 24));
   long pixels_per_wave = std::min(P, std::max(long(W), (max_slots / W) * W));
   int s_batch = int(std::max(1L, std::min(long(n_samples), max_slots / pixels_per_wave)));
   if (ctx->needs_rng_in_shading) s_batch = 1;  // randf() draws in shading share the per-pixel RNG stream
@@ -510,7 +512,18 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   w.n_slots = int(n_slots); w.width = W; w.row_begin = p->row_begin; w.max_depth = D; w.accel = p->accel;
 
   uint64_t launches = 0;
+  // optional per-kernel timing: an event after every launch, classified on the host afterwards
+  const bool timed = (p->flags & PB2_RENDER_TIME_KERNELS) != 0;
+  std::vector<int> ev_class;  // 0 trace, 1 shadow, 2 shade, 3 other
+  size_t ev_used = 0;
+  auto mark = [&](int cls) {
+    if (!timed) return;
+    if (ev_used == B.events.size()) { cudaEvent_t e; cudaEventCreate(&e); B.events.push_back(e); }
+    cudaEventRecord(B.events[ev_used++], st);
+    ev_class.push_back(cls);
+  };
   PB2_CUDA_CHECK(cudaEventRecord(ctx->ev0, st));
+  mark(-1);
   int wave = 0;
   for (int pw = 0; pw < n_pixel_waves; pw++) {
     w.pixel0 = int(long(pw) * pixels_per_wave);
@@ -521,24 +534,26 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       w.counts = B.counts.as<int>() + size_t(wave) * cstride;
       const int live = w.pixels * w.s_batch;
       k_raygen<<<sm_grid(w.pixels, 256, 8), 256, 0, st>>>(sc, w, p->sample_begin, sw == 0);
-      launches++;
+      launches++; mark(3);
       for (int depth = 0; depth < D; depth++) {
         k_trace<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
+        mark(0);
         k_shade<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
+        mark(2);
         launches += 2;
         if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
           k_shadow<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
-          launches++;
+          launches++; mark(1);
         }
       }
       k_fold_resolve<<<sm_grid(w.pixels, 256, 8), 256, 0, st>>>(w);
-      launches++;
+      launches++; mark(3);
     }
   }
   const float alpha = float(n_samples) / float(p->spp);
   k_film<<<sm_grid(int(P), 256, 8), 256, 0, st>>>(B.lacc.as<float4>(), ctx->film.as<float4>(), int(P),
                                                   p->row_begin * W, p->spp, alpha);
-  launches++;
+  launches++; mark(3);
   PB2_CUDA_CHECK(cudaEventRecord(ctx->ev1, st));
   PB2_CUDA_CHECK(cudaGetLastError());
   B.host_counts.resize(size_t(n_waves) * cstride);
@@ -548,11 +563,29 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   float ms = 0;
   PB2_CUDA_CHECK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
   ctx->counters.last_render_ms = ms;
+  double cls_ms[4] = {0, 0, 0, 0};
+  uint64_t trace_launches = 0;
+  for (size_t i = 1; i < ev_used; i++) {
+    float e = 0;
+    cudaEventElapsedTime(&e, B.events[i - 1], B.events[i]);
+    cls_ms[ev_class[i]] += e;
+    trace_launches += ev_class[i] == 0;
+  }
+  ctx->counters.last_trace_ms = cls_ms[0];
+  ctx->counters.last_shadow_ms = cls_ms[1];
+  ctx->counters.last_shade_ms = cls_ms[2];
+  ctx->counters.last_other_ms = cls_ms[3];
+  ctx->counters.last_trace_launches = trace_launches;
+  uint64_t closest = 0, shadow = 0;
   for (int wv = 0; wv < n_waves; wv++)
     for (int k = 0; k <= D; k++) {
-      ctx->counters.closest_rays += uint64_t(B.host_counts[size_t(wv) * cstride + k]);
-      ctx->counters.shadow_rays += uint64_t(B.host_counts[size_t(wv) * cstride + D + 1 + k]);
+      closest += uint64_t(B.host_counts[size_t(wv) * cstride + k]);
+      shadow += uint64_t(B.host_counts[size_t(wv) * cstride + D + 1 + k]);
     }
+  ctx->counters.closest_rays += closest;
+  ctx->counters.shadow_rays += shadow;
+  ctx->counters.last_closest_rays = closest;
+  ctx->counters.last_shadow_rays = shadow;
   ctx->counters.camera_samples += uint64_t(P) * n_samples;
   ctx->counters.kernel_launches += launches;
   return PB2_OK;

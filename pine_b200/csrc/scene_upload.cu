@@ -1,8 +1,13 @@
 // scene_upload.cu -- pb2_upload_scene: validate the flattened scene, build the BVHs on the host
 // (reference-identical binary trees, then the wide collapse) and lay everything out in HBM.
 // Replaces accel.build(&scene) + light_sampler.build(&scene) (integrator.cpp:32-33).
+#include <algorithm>
+#include <atomic>
 #include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
 
 #include "bvh_layout.h"
 #include "context.h"
@@ -10,6 +15,18 @@
 using namespace pb2;
 
 namespace {
+
+// Runs fn(0..n-1) on up to `threads` host threads (dynamic distribution).
+template <class F>
+void parallel_jobs(size_t n, int threads, F&& fn) {
+  if (n == 0) return;
+  std::atomic<size_t> next{0};
+  auto work = [&] { for (size_t i; (i = next.fetch_add(1)) < n;) fn(i); };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads && size_t(t) < n; t++) pool.emplace_back(work);
+  work();
+  for (auto& th : pool) th.join();
+}
 
 bool valid_material(const pb2_material& m) {
   return m.kind >= PB2_MAT_EMISSIVE && m.kind <= PB2_MAT_SUBSURFACE;
@@ -22,6 +39,12 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   if (ctx->device >= 0) PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
   ctx->host_scene_ready = false;
   auto t0 = std::chrono::steady_clock::now();
+  const bool verbose = std::getenv("PB2_VERBOSE") != nullptr;
+  auto stage = [&](const char* name) {
+    if (verbose)
+      fprintf(stderr, "[pb2_upload_scene] %-28s +%.1f ms\n", name,
+              std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+  };
   ctx->scene_ready = false;
   if (sd->camera.width <= 0 || sd->camera.height <= 0) {
     set_error("camera film size must be positive");
@@ -64,48 +87,88 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     geoms[lights[l]].light = int32_t(l);
   }
 
-  // ---- per-mesh trees (bvh.cpp:460-476): meshes with >=1 triangle, in geometry order ----
-  std::vector<DMesh> meshes(sd->n_meshes);
-  std::vector<float> verts, normals, uvs;
-  std::vector<uint32_t> tris;
+  // ---- host copies (kept, pinned, for re-staging) ----
+  HostScene& H = ctx->host;
+  H.unpin();
+  H = HostScene();
+  H.geoms = std::move(geoms);
+  H.lights = std::move(lights);
+  H.materials.assign(sd->materials, sd->materials + sd->n_materials);
+  H.aabbs.assign(sd->aabbs, sd->aabbs + sd->n_aabbs);
+  H.obbs.assign(sd->obbs, sd->obbs + sd->n_obbs);
+  H.spheres.assign(sd->spheres, sd->spheres + sd->n_spheres);
+  H.triangles.assign(sd->triangles, sd->triangles + sd->n_triangles);
+  H.cones.assign(sd->cones, sd->cones + sd->n_cones);
+  H.rects.assign(sd->rects, sd->rects + sd->n_rects);
+  H.disks.assign(sd->disks, sd->disks + sd->n_disks);
+
+  // ---- mesh pools ----
+  H.meshes.resize(sd->n_meshes);
   bool any_normals = false, any_uvs = false;
+  size_t n_verts = 0, n_tris = 0;
   for (uint32_t k = 0; k < sd->n_meshes; k++) {
     any_normals |= sd->meshes[k].normals != nullptr;
     any_uvs |= sd->meshes[k].texcoords != nullptr;
+    n_verts += sd->meshes[k].n_vertices;
+    n_tris += sd->meshes[k].n_triangles;
   }
+  H.verts.resize(n_verts * 3);
+  H.tris.resize(n_tris * 3);
+  if (any_normals) H.normals.assign(n_verts * 3, 0.0f);
+  if (any_uvs) H.uvs.assign(n_verts * 2, 0.0f);
+  {
+    size_t vb = 0, tb = 0;
+    for (uint32_t k = 0; k < sd->n_meshes; k++) {
+      const pb2_mesh& m = sd->meshes[k];
+      DMesh& dm = H.meshes[k];
+      std::memset(&dm, 0, sizeof(dm));
+      dm.tree = DTree{-1, 0, 0, 0};
+      dm.vert_base = uint32_t(vb);
+      dm.tri_base = uint32_t(tb);
+      dm.n_tris = m.n_triangles;
+      dm.has_normals = m.normals != nullptr;
+      dm.has_uvs = m.texcoords != nullptr;
+      vb += m.n_vertices;
+      tb += m.n_triangles;
+    }
+  }
+  const int hw = int(std::thread::hardware_concurrency());
+  const char* env_threads = std::getenv("PB2_BUILD_THREADS");
+  const int n_threads = env_threads ? std::max(1, std::atoi(env_threads)) : std::max(1, std::min(hw > 0 ? hw : 1, 64));
+  ctx->counters.build_threads = uint32_t(n_threads);
+  std::atomic<bool> bad_index{false};
+  parallel_jobs(sd->n_meshes, n_threads, [&](size_t k) {
+    const pb2_mesh& m = sd->meshes[k];
+    const DMesh& dm = H.meshes[k];
+    for (size_t t = 0; t < size_t(m.n_triangles) * 3; t++)
+      if (m.indices[t] >= m.n_vertices) { bad_index = true; return; }
+    std::memcpy(H.verts.data() + size_t(dm.vert_base) * 3, m.vertices, size_t(m.n_vertices) * 12);
+    std::memcpy(H.tris.data() + size_t(dm.tri_base) * 3, m.indices, size_t(m.n_triangles) * 12);
+    if (m.normals) std::memcpy(H.normals.data() + size_t(dm.vert_base) * 3, m.normals, size_t(m.n_vertices) * 12);
+    if (m.texcoords) std::memcpy(H.uvs.data() + size_t(dm.vert_base) * 2, m.texcoords, size_t(m.n_vertices) * 8);
+  });
+  if (bad_index) { set_error("mesh index out of range"); return PB2_E_INVALID; }
+
+  stage("validate + mesh pools");
+  // ---- per-mesh trees (bvh.cpp:460-476): meshes with >=1 triangle, in geometry order ----
   ctx->mesh_trees.clear();
   std::vector<int> mesh_tree_of(sd->n_meshes, -1);
   std::vector<BuildPrim> top;
-  std::vector<DTopPrim> top_prims;
-  for (uint32_t k = 0; k < sd->n_meshes; k++) {
-    const pb2_mesh& m = sd->meshes[k];
-    DMesh& dm = meshes[k];
-    std::memset(&dm, 0, sizeof(dm));
-    dm.tree = DTree{-1, 0, 0, -1};
-    dm.vert_base = uint32_t(verts.size() / 3);
-    dm.tri_base = uint32_t(tris.size() / 3);
-    dm.n_tris = m.n_triangles;
-    dm.has_normals = m.normals != nullptr;
-    dm.has_uvs = m.texcoords != nullptr;
-    for (uint32_t t = 0; t < m.n_triangles * 3; t++)
-      if (m.indices[t] >= m.n_vertices) { set_error("mesh index out of range"); return PB2_E_INVALID; }
-    verts.insert(verts.end(), m.vertices, m.vertices + size_t(m.n_vertices) * 3);
-    tris.insert(tris.end(), m.indices, m.indices + size_t(m.n_triangles) * 3);
-    if (any_normals) {
-      if (m.normals) normals.insert(normals.end(), m.normals, m.normals + size_t(m.n_vertices) * 3);
-      else normals.resize(normals.size() + size_t(m.n_vertices) * 3, 0.0f);
-    }
-    if (any_uvs) {
-      if (m.texcoords) uvs.insert(uvs.end(), m.texcoords, m.texcoords + size_t(m.n_vertices) * 2);
-      else uvs.resize(uvs.size() + size_t(m.n_vertices) * 2, 0.0f);
-    }
-  }
+  struct MeshJob { uint32_t geom; int mesh; };
+  std::vector<MeshJob> jobs;
   for (uint32_t i = 0; i < sd->n_geometries; i++) {
     const pb2_geometry& g = sd->geometries[i];
     if (g.shape_kind != PB2_SHAPE_MESH) continue;
-    const pb2_mesh& m = sd->meshes[g.shape_index];
-    if (m.n_triangles == 0) continue;
+    if (sd->meshes[g.shape_index].n_triangles == 0) continue;
     if (mesh_tree_of[g.shape_index] != -1) { set_error("a mesh may back only one geometry"); return PB2_E_INVALID; }
+    mesh_tree_of[g.shape_index] = int(jobs.size());
+    jobs.push_back(MeshJob{i, g.shape_index});
+  }
+  ctx->mesh_trees.resize(jobs.size());
+  // Small meshes: one job per mesh. Big meshes additionally split inside build_sah_binary.
+  set_build_threads(jobs.size() >= size_t(n_threads) ? 1 : n_threads);
+  parallel_jobs(jobs.size(), n_threads, [&](size_t j) {
+    const pb2_mesh& m = sd->meshes[jobs[j].mesh];
     std::vector<BuildPrim> prims(m.n_triangles);
     for (uint32_t t = 0; t < m.n_triangles; t++) {
       const uint32_t* f = m.indices + 3 * size_t(t);
@@ -113,14 +176,14 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
                                  ld3(m.vertices + 3 * size_t(f[2])));
       prims[t].index = int(t);
     }
-    mesh_tree_of[g.shape_index] = int(ctx->mesh_trees.size());
-    ctx->mesh_trees.emplace_back();
-    build_sah_binary(std::move(prims), ctx->mesh_trees.back());
+    build_sah_binary(std::move(prims), ctx->mesh_trees[j]);
+  });
+  for (size_t j = 0; j < jobs.size(); j++) {
     BuildPrim tp;
-    tp.box = ctx->mesh_trees.back().bounds();
+    tp.box = ctx->mesh_trees[j].bounds();
     tp.index = int(top.size());
     top.push_back(tp);
-    top_prims.push_back(DTopPrim{int32_t(i), PB2_SHAPE_MESH, g.shape_index, 0});
+    H.top_prims.push_back(DTopPrim{int32_t(jobs[j].geom), PB2_SHAPE_MESH, jobs[j].mesh, 0});
   }
   // ---- analytic shapes (bvh.cpp:485-493) ----
   for (uint32_t i = 0; i < sd->n_geometries; i++) {
@@ -138,64 +201,103 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     }
     tp.index = int(top.size());
     top.push_back(tp);
-    top_prims.push_back(DTopPrim{int32_t(i), g.shape_kind, g.shape_index, 0});
+    H.top_prims.push_back(DTopPrim{int32_t(i), g.shape_kind, g.shape_index, 0});
   }
+  stage("mesh trees");
+  set_build_threads(n_threads);
+  std::vector<Box3> top_boxes(top.size());
+  for (size_t i = 0; i < top.size(); i++) top_boxes[i] = top[i].box;
   build_sah_binary(top, ctx->top_tree);
 
   // ---- device layouts ----
-  LayoutOut lay;
-  DTree top_tree = append_tree(ctx->top_tree, lay);
-  std::vector<int> geom_of_mesh(sd->n_meshes, -1);
-  for (uint32_t i = 0; i < sd->n_geometries; i++)
-    if (sd->geometries[i].shape_kind == PB2_SHAPE_MESH) geom_of_mesh[sd->geometries[i].shape_index] = int(i);
+  LayoutOut& lay = H.lay;
+  DTree top_tree = append_binary(ctx->top_tree, lay);
   for (uint32_t k = 0; k < sd->n_meshes; k++)
-    if (mesh_tree_of[k] >= 0)
-      meshes[k].tree = append_tree(ctx->mesh_trees[mesh_tree_of[k]], lay, &sd->meshes[k], geom_of_mesh[k]);
+    if (mesh_tree_of[k] >= 0) H.meshes[k].tree = append_binary(ctx->mesh_trees[mesh_tree_of[k]], lay);
+  stage("top tree + binary layout");
+  WideInput wi;
+  wi.top = &ctx->top_tree; wi.top_prims = &H.top_prims; wi.top_boxes = &top_boxes;
+  wi.mesh_trees = &ctx->mesh_trees; wi.mesh_tree_of = &mesh_tree_of; wi.meshes = sd->meshes;
+  build_wide(wi, lay, n_threads);
+  stage("wide tree");
+  bool order_dependent = false;
+  for (uint32_t i = 0; i < sd->n_geometries; i++)
+    order_dependent |= sd->geometries[i].shape_kind == PB2_SHAPE_AABB || sd->geometries[i].shape_kind == PB2_SHAPE_OBB;
+
   ctx->counters.bvh2_nodes = uint32_t(lay.nodes2.size());
   ctx->counters.wide_nodes = uint32_t(lay.nodes8.size());
   ctx->counters.n_primitives = uint32_t(lay.leaf_prims.size());
   ctx->counters.bvh_build_ms =
       std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  DScene& s = ctx->scene;
+  s.top = top_tree;
+  s.n_lights = int32_t(sd->n_lights); s.n_geoms = int32_t(sd->n_geometries);
+  s.wide_ready = lay.nodes8.empty() ? 0 : 1;
+  s.n_box_shapes = int32_t(lay.box_shapes.size());
+  s.order_dependent = order_dependent ? 1 : 0;
+  s.camera = sd->camera;
+  ctx->n_pixels = sd->camera.width * sd->camera.height;
   ctx->host_scene_ready = true;
   if (ctx->device < 0) return PB2_OK;  // host-only context: builder inspection, no device work
 
-#define UP(buf, vec) PB2_CUDA_CHECK(ctx->buf.upload(vec))
-  UP(nodes2, lay.nodes2); UP(nodes8, lay.nodes8); UP(leaves, lay.leaves); UP(leaf_tris, lay.leaf_tris); UP(leaf_prims, lay.leaf_prims);
-  UP(top_prims, top_prims); UP(meshes, meshes); UP(geoms, geoms); UP(lights, lights);
-  UP(verts, verts); UP(tris, tris); UP(normals, normals); UP(uvs, uvs);
-#undef UP
-#define UPA(buf, ptr, n, T) \
-  PB2_CUDA_CHECK(ctx->buf.upload(std::vector<T>(ptr, ptr + n)))
-  UPA(materials, sd->materials, sd->n_materials, pb2_material);
-  UPA(aabbs, sd->aabbs, sd->n_aabbs, pb2_aabb);
-  UPA(obbs, sd->obbs, sd->n_obbs, pb2_obb);
-  UPA(spheres, sd->spheres, sd->n_spheres, pb2_sphere);
-  UPA(triangles, sd->triangles, sd->n_triangles, pb2_triangle);
-  UPA(cones, sd->cones, sd->n_cones, pb2_cone);
-  UPA(rects, sd->rects, sd->n_rects, pb2_rect);
-  UPA(disks, sd->disks, sd->n_disks, pb2_disk);
-#undef UPA
+  // ---- staging list + page-lock ----
+  uint64_t bytes = 0;
+  auto item = [&](DBuf& dst, const void* src, size_t n) {
+    H.items.push_back(HostScene::Item{&dst, src, n});
+    bytes += n;
+    if (n >= (1u << 16) && cudaHostRegister(const_cast<void*>(src), n, cudaHostRegisterDefault) == cudaSuccess)
+      H.registered.push_back(const_cast<void*>(src));
+    else
+      cudaGetLastError();
+  };
+#define ITEM(buf, vec) item(ctx->buf, (vec).data(), (vec).size() * sizeof((vec)[0]))
+  ITEM(nodes2, lay.nodes2); ITEM(nodes8, lay.nodes8); ITEM(leaves, lay.leaves);
+  ITEM(wide_prims, lay.wide_prims); ITEM(box_shapes, lay.box_shapes); ITEM(leaf_prims, lay.leaf_prims);
+  ITEM(top_prims, H.top_prims); ITEM(meshes, H.meshes); ITEM(geoms, H.geoms); ITEM(lights, H.lights);
+  ITEM(verts, H.verts); ITEM(tris, H.tris); ITEM(normals, H.normals); ITEM(uvs, H.uvs);
+  ITEM(materials, H.materials); ITEM(aabbs, H.aabbs); ITEM(obbs, H.obbs); ITEM(spheres, H.spheres);
+  ITEM(triangles, H.triangles); ITEM(cones, H.cones); ITEM(rects, H.rects); ITEM(disks, H.disks);
+#undef ITEM
+  stage("page-lock");
+  ctx->counters.scene_bytes = bytes;
+  int rc = pb2_restage_scene(ctx, nullptr);
+  if (rc) return rc;
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  ctx->scene_ready = true;
+  return PB2_OK;
+}
 
+extern "C" int pb2_restage_scene(pb2_context* ctx, void* cuda_stream) {
+  if (!ctx || !ctx->host_scene_ready || ctx->device < 0) { set_error("no host scene / no device"); return PB2_E_STATE; }
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
+  auto t0 = std::chrono::steady_clock::now();
+  for (const HostScene::Item& it : ctx->host.items) {
+    PB2_CUDA_CHECK(it.dst->reserve(it.bytes));
+    if (it.bytes) PB2_CUDA_CHECK(cudaMemcpyAsync(it.dst->ptr, it.src, it.bytes, cudaMemcpyHostToDevice, st));
+  }
+  if (ctx->tables_spp) {  // the active sampler tables travel with the scene
+    int k = 0;
+    while ((1 << k) != ctx->tables_spp) k++;
+    const SamplerTables& T = ctx->tables[k];
+    PB2_CUDA_CHECK(cudaMemcpyAsync(ctx->tab_sobol.ptr, T.sobol.data(), T.sobol.size(), cudaMemcpyHostToDevice, st));
+    PB2_CUDA_CHECK(cudaMemcpyAsync(ctx->tab_scramble.ptr, T.scramble.data(), T.scramble.size(), cudaMemcpyHostToDevice, st));
+    PB2_CUDA_CHECK(cudaMemcpyAsync(ctx->tab_rank.ptr, T.rank.data(), T.rank.size(), cudaMemcpyHostToDevice, st));
+  }
   DScene& s = ctx->scene;
   s.nodes2 = ctx->nodes2.as<DNode2>(); s.nodes8 = ctx->nodes8.as<DNode8>();
-  s.leaves = ctx->leaves.as<DLeaf>(); s.leaf_tris = ctx->leaf_tris.as<DTri>(); s.leaf_prims = ctx->leaf_prims.as<int32_t>();
-  s.top = top_tree;
+  s.leaves = ctx->leaves.as<DLeaf>(); s.wide_prims = ctx->wide_prims.as<DPrim>(); s.box_shapes = ctx->box_shapes.as<DBoxShape>(); s.leaf_prims = ctx->leaf_prims.as<int32_t>();
   s.top_prims = ctx->top_prims.as<DTopPrim>(); s.meshes = ctx->meshes.as<DMesh>();
   s.geoms = ctx->geoms.as<DGeom>(); s.materials = ctx->materials.as<pb2_material>();
   s.lights = ctx->lights.as<int32_t>();
-  s.n_lights = int32_t(sd->n_lights); s.n_geoms = int32_t(sd->n_geometries);
   s.aabbs = ctx->aabbs.as<pb2_aabb>(); s.obbs = ctx->obbs.as<pb2_obb>();
   s.spheres = ctx->spheres.as<pb2_sphere>(); s.triangles = ctx->triangles.as<pb2_triangle>();
   s.cones = ctx->cones.as<pb2_cone>(); s.rects = ctx->rects.as<pb2_rect>();
   s.disks = ctx->disks.as<pb2_disk>();
   s.verts = ctx->verts.as<float>(); s.tris = ctx->tris.as<uint32_t>();
   s.normals = ctx->normals.as<float>(); s.uvs = ctx->uvs.as<float>();
-  s.camera = sd->camera;
-  ctx->n_pixels = sd->camera.width * sd->camera.height;
-
-  ctx->counters.bvh_build_ms =
+  ctx->counters.upload_ms =
       std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-  ctx->scene_ready = true;
   return PB2_OK;
 }
 

@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(128) k_trace_closest(DScene sc, const float* _
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
     Ray ray = load_ray(rays, i);
     Hit h;
-    bool hit = ACCEL == 0 ? closest_wide(sc, ray, h) : closest_ref_order(sc, ray, h);
+    bool hit = ACCEL == 0 ? closest_production(sc, ray, h) : closest_ref_order(sc, ray, h);
     geom[i] = hit ? h.geom : -1;
     prim[i] = hit ? h.prim : -1;
     t[i] = ray.tmax;

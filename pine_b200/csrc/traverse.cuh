@@ -10,7 +10,8 @@
 //       * a leaf child is intersected immediately, inside the node visit, before the sibling's box
 //         test; internal children go near-first with the other pushed on a stack.
 //     This is the verification path and the fallback of (2); results are bit-identical.
-// (2) `*_wide`: 8-wide quantised tree (device_scene.h DNode8) for production.
+// (2) `*_wide`: ONE 8-wide compressed tree over the whole scene (device_scene.h DNode8) for
+//     production, made exact by detection + fallback to (1).
 #pragma once
 #include "shapes.cuh"
 
@@ -161,238 +162,245 @@ __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) 
 // ====================================================================================================
 // (2) wide traversal
 // ====================================================================================================
-// Used for the triangles of one mesh; results must equal the reference-order walk of that mesh bit
-// for bit. A wide walk visits triangles in a different order, which only matters when two candidates
-// are (nearly) tied. Let (p1, t1) be the strict minimum over all triangles the reference could
-// accept. The reference returns (p1, t1) if
-//   (i)  no other triangle reports exactly t1, and
-//   (ii) p1's own leaf box passes the reference slab test with tmax = t1
-// (every tmax the reference ever holds is >= t1, slab tests are monotone in tmax and in the box, so
-// p1's leaf and all its ancestors pass whenever they are reached; p1 is then accepted -- the
-// triangle test is strict, geometry.cpp:557 -- and nothing later can replace it). The wide walk
-// culls with a slightly enlarged tmax (`slack`) so that a triangle whose t ties or beats the current
-// best is never hidden behind a box whose entry distance differs from t by rounding, detects exact
-// ties and checks (ii) for its winner. Ambiguous rays (a handful per million) re-trace the mesh in
-// reference order, so the result is the reference's in all cases.
-constexpr int kWideStack = 64;
-constexpr int kNoTree = 0x7fffffff;
+// The wide walk visits primitives in a different order than the reference and tests a superset of
+// the primitives the reference tests (bvh_layout.cpp). Its result equals the reference's whenever
+//   (i)   no two accepted candidates report exactly the same t as the winner (ties are broken by
+//         visiting order in the reference: strict `t < tmax` for Rect/Triangle, geometry.cpp:296,557),
+//   (ii)  the winner's own reference leaf box ("gate") passes the reference slab test with
+//         tmax = t_winner -- then the reference, whose tmax is always >= t_winner and whose
+//         ancestor boxes contain the leaf box, reaches and accepts the winner, and nothing it sees
+//         later can replace it (slab tests are monotone in tmax and in the box),
+//   (iii) no primitive's reported t depends on the incoming tmax (true for everything but
+//         AABB/OBB shapes, bbox.cpp:149-161; scenes that contain those walk the reference-order
+//         tree for closest hits: DScene::order_dependent).
+// Boxes are culled against a slightly enlarged tmax (`slack_of`), so a primitive whose t ties or
+// beats the current best is never hidden behind a box whose computed entry distance exceeds t by
+// rounding. Rays for which (i) or (ii) fails, or whose stack overflows (a handful per million),
+// are re-traced in reference order: the result is the reference's in all cases.
+// Any-hit (shadow rays) is an OR over primitives whose gate passes with the ray's fixed tmax, so the
+// visiting order is irrelevant and no fallback is needed; it is valid for AABB/OBB shapes too.
+constexpr int kWideStack = 28;
 
 __device__ __forceinline__ float slack_of(float t) { return t + (t * 1.220703125e-4f + 1e-6f); }
 __device__ __forceinline__ float next_up(float t) {
   return (t >= kFloatMax || t < 0) ? t : __uint_as_float(__float_as_uint(t) + 1u);
 }
+__device__ __forceinline__ bool leaf_gate(const DLeaf* leaves, int leaf, const Octant& q, float tmin, float tmax) {
+  if (leaf < 0) return true;
+  const float4* p = reinterpret_cast<const float4*>(leaves + leaf);
+  float4 a = __ldg(p), b = __ldg(p + 1);
+  float box[6] = {a.x, a.y, a.z, a.w, b.x, b.y};
+  float t = tmax;
+  return slab(box, q, tmin, t);
+}
 
-struct Node8Regs {
-  float4 a;        // origin.xyz, {exp x,y,z, n_children}
-  uint4 q0, q1, q2;  // qlo[x][8] qlo[y][8] | qlo[z][8] qhi[x][8] | qhi[y][8] qhi[z][8]
-  int4 c0, c1;
+// Per-ray constants of the conservative child-box test. For axis k the exact plane q of a node is
+// P = origin + q * 2^e; the reference evaluates fl(fl(P * inv) - ood). We evaluate
+// fma(q, a, b -/+ delta) with a = 2^e * inv (exact), b = fl(fl(origin * inv) - ood) and
+// delta = 2^-21 * (|origin * inv| + 255 |a| + |ood|), which bounds the difference of the two
+// expressions (at most ~6 roundings of magnitude <= that sum), so near planes come out no larger
+// and far planes no smaller than the reference's value for any box inside the quantised one.
+struct WideRay {
+  V3 inv, ood;
+  uint32_t octinv4;  // (7 ^ octant) replicated into 4 bytes
+  uint32_t neg;      // bit k: d[k] < 0
 };
-__device__ __forceinline__ Node8Regs load_node8(const DNode8* nodes, int idx) {
-  const uint4* p = reinterpret_cast<const uint4*>(nodes + idx);
-  Node8Regs r;
-  uint4 a = __ldg(p);
-  r.a = make_float4(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z), __uint_as_float(a.w));
-  r.q0 = __ldg(p + 1); r.q1 = __ldg(p + 2); r.q2 = __ldg(p + 3);
-  uint4 c0 = __ldg(p + 4), c1 = __ldg(p + 5);
-  r.c0 = make_int4(c0.x, c0.y, c0.z, c0.w);
-  r.c1 = make_int4(c1.x, c1.y, c1.z, c1.w);
+__device__ __forceinline__ float byte_f(uint32_t w, int k) {  // byte k of w as a float, exact
+  return __uint_as_float(0x4B000000u | ((w >> (8 * k)) & 0xffu)) - 8388608.0f;
+}
+
+struct PrimRec {
+  V3 v0, v1, v2;
+  int prim, geom, leaf;
+};
+__device__ __forceinline__ PrimRec load_prim(const DPrim* prims, uint32_t idx) {
+  const float4* p = reinterpret_cast<const float4*>(prims + idx);
+  float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+  PrimRec r;
+  r.v0 = V3(a.x, a.y, a.z); r.v1 = V3(a.w, b.x, b.y); r.v2 = V3(b.z, b.w, c.x);
+  r.prim = __float_as_int(c.y); r.geom = __float_as_int(c.z); r.leaf = __float_as_int(c.w);
   return r;
 }
-__device__ __forceinline__ uint32_t byte_of(uint32_t lo, uint32_t hi, int i) {
-  return ((i < 4 ? lo : hi) >> ((i & 3) * 8)) & 0xffu;
+
+// Tests the 8 children of node `idx`; returns the hit mask (bits 24..31: internal children in
+// traversal order, bits 0..23: primitives) and the node's child_base / prim_base / imask.
+__device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx, const WideRay& w, float tmin,
+                                               float lim, uint32_t& child_base, uint32_t& prim_base,
+                                               uint32_t& imask) {
+  const uint4* p = reinterpret_cast<const uint4*>(nodes + idx);
+  const uint4 n0 = __ldg(p), n1 = __ldg(p + 1), n2 = __ldg(p + 2), n3 = __ldg(p + 3), n4 = __ldg(p + 4);
+  const float ox = __uint_as_float(n0.x), oy = __uint_as_float(n0.y), oz = __uint_as_float(n0.z);
+  const float ax = __uint_as_float((n0.w & 0xffu) << 23) * w.inv.x;
+  const float ay = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * w.inv.y;
+  const float az = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * w.inv.z;
+  imask = n0.w >> 24;
+  child_base = n1.x;
+  prim_base = n1.y;
+  const float ux = ox * w.inv.x, uy = oy * w.inv.y, uz = oz * w.inv.z;
+  const float dx = (fabsf(ux) + 255.0f * fabsf(ax) + fabsf(w.ood.x)) * 4.76837158203125e-7f;
+  const float dy = (fabsf(uy) + 255.0f * fabsf(ay) + fabsf(w.ood.y)) * 4.76837158203125e-7f;
+  const float dz = (fabsf(uz) + 255.0f * fabsf(az) + fabsf(w.ood.z)) * 4.76837158203125e-7f;
+  const float bx = ux - w.ood.x, by = uy - w.ood.y, bz = uz - w.ood.z;
+  const float bnx = bx - dx, bfx = bx + dx, bny = by - dy, bfy = by + dy, bnz = bz - dz, bfz = bz + dz;
+  // qlo: x = n2.xy, y = n2.zw, z = n3.xy; qhi: x = n3.zw, y = n4.xy, z = n4.zw. near = lo unless d < 0
+  const bool nx = w.neg & 1, ny = w.neg & 2, nz = w.neg & 4;
+  uint32_t hitmask = 0;
+#pragma unroll
+  for (int j = 0; j < 2; j++) {
+    const uint32_t meta4 = j ? n1.w : n1.z;
+    const uint32_t lox = j ? n2.y : n2.x, loy = j ? n2.w : n2.z, loz = j ? n3.y : n3.x;
+    const uint32_t hix = j ? n3.w : n3.z, hiy = j ? n4.y : n4.x, hiz = j ? n4.w : n4.z;
+    const uint32_t qnx = nx ? hix : lox, qfx = nx ? lox : hix;
+    const uint32_t qny = ny ? hiy : loy, qfy = ny ? loy : hiy;
+    const uint32_t qnz = nz ? hiz : loz, qfz = nz ? loz : hiz;
+    const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+    const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+    const uint32_t bit_index4 = (meta4 ^ (w.octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+    const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const float tnx = __fmaf_rn(byte_f(qnx, k), ax, bnx), tfx = __fmaf_rn(byte_f(qfx, k), ax, bfx);
+      const float tny = __fmaf_rn(byte_f(qny, k), ay, bny), tfy = __fmaf_rn(byte_f(qfy, k), ay, bfy);
+      const float tnz = __fmaf_rn(byte_f(qnz, k), az, bnz), tfz = __fmaf_rn(byte_f(qfz, k), az, bfz);
+      const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+      const float tf = fminf(fminf(tfx, tfy), fminf(tfz, lim));
+      if (tn <= tf) hitmask |= ((child_bits4 >> (8 * k)) & 0xffu) << ((bit_index4 >> (8 * k)) & 0xffu);
+    }
+  }
+  return hitmask;
 }
 
-// Slab test of child i of a wide node with the reference's expression on the dequantised planes.
-__device__ __forceinline__ bool child_slab(const Node8Regs& nd, int i, const Octant& q, float tmin,
-                                           float tmax, float& tnear) {
-  uint32_t ew = __float_as_uint(nd.a.w);
-  float sx = __uint_as_float((ew & 0xffu) << 23), sy = __uint_as_float(((ew >> 8) & 0xffu) << 23),
-        sz = __uint_as_float(((ew >> 16) & 0xffu) << 23);
-  float p[6];
-  p[0] = nd.a.x + float(byte_of(nd.q0.x, nd.q0.y, i)) * sx;
-  p[1] = nd.a.y + float(byte_of(nd.q0.z, nd.q0.w, i)) * sy;
-  p[2] = nd.a.z + float(byte_of(nd.q1.x, nd.q1.y, i)) * sz;
-  p[3] = nd.a.x + float(byte_of(nd.q1.z, nd.q1.w, i)) * sx;
-  p[4] = nd.a.y + float(byte_of(nd.q2.x, nd.q2.y, i)) * sy;
-  p[5] = nd.a.z + float(byte_of(nd.q2.z, nd.q2.w, i)) * sz;
-  float tmin0 = p[0 + q.ox] * q.inv.x - q.ood.x;
-  float tmin1 = p[1 + q.oy] * q.inv.y - q.ood.y;
-  float tmin2 = p[2 + q.oz] * q.inv.z - q.ood.z;
-  float tmax0 = p[3 - q.ox] * q.inv.x - q.ood.x;
-  float tmax1 = p[4 - q.oy] * q.inv.y - q.ood.y;
-  float tmax2 = p[5 - q.oz] * q.inv.z - q.ood.z;
-  tnear = pmax(tmin0, pmax(tmin1, pmax(tmin2, tmin)));
-  float tfar = pmin(tmax0, pmin(tmax1, pmin(tmax2, tmax)));
-  return tnear <= tfar;
-}
-__device__ __forceinline__ bool leaf_gate(const DLeaf& L, const Octant& q, float tmin, float tmax) {
-  float t = tmax;
-  return slab(L.box, q, tmin, t);
-}
-__device__ __forceinline__ DLeaf load_leaf(const DLeaf* leaves, int idx) {
-  const float4* p = reinterpret_cast<const float4*>(leaves + idx);
-  float4 a = __ldg(p), b = __ldg(p + 1);
-  DLeaf L;
-  L.box[0] = a.x; L.box[1] = a.y; L.box[2] = a.z; L.box[3] = a.w; L.box[4] = b.x; L.box[5] = b.y;
-  L.link = __float_as_int(b.z); L.count = __float_as_int(b.w);
-  return L;
-}
-__device__ __forceinline__ void load_tri(const DTri* tris, int idx, V3& v0, V3& v1, V3& v2, int& prim,
-                                         int& geom) {
-  const float4* p = reinterpret_cast<const float4*>(tris + idx);
-  float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-  v0 = V3(a.x, a.y, a.z); v1 = V3(a.w, b.x, b.y); v2 = V3(b.z, b.w, c.x);
-  prim = __float_as_int(c.y); geom = __float_as_int(c.z);
+__device__ __forceinline__ WideRay make_wide_ray(const Ray& ray, const Octant& q) {
+  WideRay w;
+  w.inv = q.inv;
+  w.ood = q.ood;
+  w.neg = (ray.d.x < 0 ? 1u : 0u) | (ray.d.y < 0 ? 2u : 0u) | (ray.d.z < 0 ? 4u : 0u);
+  w.octinv4 = (7u ^ w.neg) * 0x01010101u;
+  return w;
 }
 
-// Closest hit inside one mesh (the reference's lbvh[k].Intersect, bvh.cpp:523-527) over the wide
-// tree. `ray.tmax` on entry is whatever the top-level walk holds; a triangle reporting exactly that
-// value is rejected by the reference's strict `t >= tmax` test (geometry.cpp:557), so it is not a tie.
-__device__ inline bool mesh_closest_wide(const DScene& sc, const DMesh& mesh, Ray& ray, const Octant& q,
-                                         int& prim_out) {
-  const int root = mesh.tree.wide_root;
-  if (root == kNoTree) return false;
+// Closest hit over the whole scene. Only valid when !sc.order_dependent.
+__device__ inline bool closest_wide(const DScene& sc, Ray& ray, Hit& h) {
+  const Octant q = make_octant(ray);
+  h.geom = -1;
+  h.prim = -1;
+  if (!sc.wide_ready) return false;
+  const WideRay w = make_wide_ray(ray, q);
   const float tmax_in = ray.tmax;
-  int refs[kWideStack];
-  float dists[kWideStack];
-  int ptr = 0;
-  refs[ptr] = root; dists[ptr] = ray.tmin; ptr++;
+  uint2 stack[kWideStack];
+  int sp = 0;
+  uint2 ngroup = make_uint2(0u, 0x80000000u);
   bool have = false, ambiguous = false;
   float tie_t = -1.0f;
   int win_leaf = -1;
-  while (ptr > 0) {
-    --ptr;
-    int ref = refs[ptr];
-    const float lim = slack_of(ray.tmax);
-    if (dists[ptr] > lim) continue;
-    if (ref >= 0) {
-      Node8Regs nd = load_node8(sc.nodes8, ref);
-      int n = int((__float_as_uint(nd.a.w) >> 24) & 0xffu);
-      int cref[8];
-      float ct[8];
-      int m = 0;
-#pragma unroll
-      for (int i = 0; i < 8; i++) {
-        if (i < n) {
-          float tn;
-          if (child_slab(nd, i, q, ray.tmin, lim, tn)) {
-            int c = i < 4 ? (&nd.c0.x)[i] : (&nd.c1.x)[i - 4];
-            int j = m++;
-            while (j > 0 && ct[j - 1] < tn) { ct[j] = ct[j - 1]; cref[j] = cref[j - 1]; j--; }
-            ct[j] = tn; cref[j] = c;  // descending: farthest first, nearest pushed last
-          }
-        }
+  while (true) {
+    uint2 tgroup;
+    if (ngroup.y > 0x00ffffffu) {
+      const uint32_t hits = ngroup.y, imask = hits & 0xffu;
+      const int bit = 31 - __clz(hits);
+      ngroup.y &= ~(1u << bit);
+      if (ngroup.y > 0x00ffffffu) {
+        if (sp < kWideStack) stack[sp++] = ngroup;
+        else { ambiguous = true; break; }
       }
-      if (ptr + m > kWideStack) { ambiguous = true; break; }
-      for (int j = 0; j < m; j++) { refs[ptr] = cref[j]; dists[ptr] = ct[j]; ptr++; }
+      const uint32_t slot = uint32_t(bit - 24) ^ (w.octinv4 & 7u);
+      const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
+      uint32_t child_base, prim_base, cmask;
+      const uint32_t hm = test_node8(sc.nodes8, ngroup.x + rel, w, ray.tmin, slack_of(ray.tmax), child_base,
+                                     prim_base, cmask);
+      ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
+      tgroup = make_uint2(prim_base, hm & 0x00ffffffu);
     } else {
-      int leaf_id = ~ref;
-      DLeaf L = load_leaf(sc.leaves, leaf_id);
-      if (!leaf_gate(L, q, ray.tmin, lim)) continue;
-      int count = L.count & 0x7fffffff;
-      for (int i = 0; i < count; i++) {
-        V3 v0, v1, v2;
-        int prim, geom;
-        load_tri(sc.leaf_tris, L.link + i, v0, v1, v2, prim, geom);
-        Ray r2 = ray;
-        r2.tmax = next_up(ray.tmax);  // lets t == current best through so that ties are seen
-        if (tri_intersect(r2, v0, v1, v2)) {
-          if (r2.tmax < ray.tmax) {
-            ray.tmax = r2.tmax; prim_out = prim; win_leaf = leaf_id; have = true;
-          } else if (have) {
-            tie_t = r2.tmax;
-          }
+      tgroup = ngroup;
+      ngroup = make_uint2(0u, 0u);
+    }
+    while (tgroup.y) {
+      const int i = __ffs(tgroup.y) - 1;
+      tgroup.y &= tgroup.y - 1;
+      const PrimRec r = load_prim(sc.wide_prims, tgroup.x + i);
+      Ray r2 = ray;
+      r2.tmax = next_up(ray.tmax);  // lets t == current best through so that ties are seen
+      bool ok;
+      if (r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
+      else ok = shape_intersect(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
+      if (ok) {
+        if (r2.tmax < ray.tmax) {
+          ray.tmax = r2.tmax; h.geom = r.geom; h.prim = r.prim >= 0 ? r.prim : 0; win_leaf = r.leaf; have = true;
+        } else if (r2.tmax == ray.tmax) {
+          if (have) tie_t = r2.tmax;
+          else ambiguous = true;  // t == the incoming tmax: strict and non-strict shapes differ
         }
       }
+    }
+    if (ngroup.y <= 0x00ffffffu) {
+      if (sp == 0) break;
+      ngroup = stack[--sp];
     }
   }
   if (have && !ambiguous) {
     if (tie_t == ray.tmax) ambiguous = true;
-    else if (!leaf_gate(load_leaf(sc.leaves, win_leaf), q, ray.tmin, ray.tmax)) ambiguous = true;
+    else if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, ray.tmax)) ambiguous = true;
   }
-  if (ambiguous) {  // re-trace this mesh in reference order
+  if (ambiguous) {
     ray.tmax = tmax_in;
-    return walk_ref_order<false>(sc, mesh.tree, ray, q, [&](int tri) {
-      V3 v0, v1, v2;
-      mesh_tri(sc, mesh, tri, v0, v1, v2);
-      bool ok = tri_intersect(ray, v0, v1, v2);
-      if (ok) prim_out = tri;
-      return ok;
-    });
+    return closest_ref_order(sc, ray, h);
   }
   return have;
 }
 
-// Any-hit inside one mesh (lbvh[k].hit, bvh.cpp:503-505): an OR over triangles whose leaf box passes
-// with the ray's fixed tmax, so visiting order is irrelevant and no fallback is needed.
-__device__ inline bool mesh_any_wide(const DScene& sc, const DMesh& mesh, const Ray& ray, const Octant& q) {
-  const int root = mesh.tree.wide_root;
-  if (root == kNoTree) return false;
-  int refs[kWideStack];
-  int ptr = 0;
-  refs[ptr++] = root;
-  while (ptr > 0) {
-    int ref = refs[--ptr];
-    if (ref >= 0) {
-      Node8Regs nd = load_node8(sc.nodes8, ref);
-      int n = int((__float_as_uint(nd.a.w) >> 24) & 0xffu);
-      if (ptr + n > kWideStack) {  // cannot happen for sane trees; stay exact if it does
-        return walk_ref_order<true>(sc, mesh.tree, ray, q, [&](int tri) {
-          V3 v0, v1, v2;
-          mesh_tri(sc, mesh, tri, v0, v1, v2);
-          return tri_hit(ray, v0, v1, v2);
-        });
+__device__ inline bool any_wide(const DScene& sc, const Ray& ray) {
+  if (!sc.wide_ready) return false;
+  if (sc.n_box_shapes > kMaxBoxShapes) return any_ref_order(sc, ray);
+  const Octant q = make_octant(ray);
+  for (int i = 0; i < sc.n_box_shapes; i++) {  // see DBoxShape
+    const int4 b = __ldg(reinterpret_cast<const int4*>(sc.box_shapes) + i);
+    if (shape_hit(sc, b.x, b.y, ray) && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax)) return true;
+  }
+  const WideRay w = make_wide_ray(ray, q);
+  uint2 stack[kWideStack];
+  int sp = 0;
+  uint2 ngroup = make_uint2(0u, 0x80000000u);
+  while (true) {
+    uint2 tgroup;
+    if (ngroup.y > 0x00ffffffu) {
+      const uint32_t hits = ngroup.y, imask = hits & 0xffu;
+      const int bit = 31 - __clz(hits);
+      ngroup.y &= ~(1u << bit);
+      if (ngroup.y > 0x00ffffffu) {
+        if (sp < kWideStack) stack[sp++] = ngroup;
+        else return any_ref_order(sc, ray);  // cannot happen for sane trees; stay exact if it does
       }
-#pragma unroll
-      for (int i = 0; i < 8; i++) {
-        float tn;
-        if (i < n && child_slab(nd, i, q, ray.tmin, ray.tmax, tn))
-          refs[ptr++] = i < 4 ? (&nd.c0.x)[i] : (&nd.c1.x)[i - 4];
-      }
+      const uint32_t slot = uint32_t(bit - 24) ^ (w.octinv4 & 7u);
+      const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
+      uint32_t child_base, prim_base, cmask;
+      const uint32_t hm = test_node8(sc.nodes8, ngroup.x + rel, w, ray.tmin, ray.tmax, child_base, prim_base, cmask);
+      ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
+      tgroup = make_uint2(prim_base, hm & 0x00ffffffu);
     } else {
-      DLeaf L = load_leaf(sc.leaves, ~ref);
-      if (!leaf_gate(L, q, ray.tmin, ray.tmax)) continue;
-      int count = L.count & 0x7fffffff;
-      for (int i = 0; i < count; i++) {
-        V3 v0, v1, v2;
-        int prim, geom;
-        load_tri(sc.leaf_tris, L.link + i, v0, v1, v2, prim, geom);
-        if (tri_hit(ray, v0, v1, v2)) return true;
-      }
+      tgroup = ngroup;
+      ngroup = make_uint2(0u, 0u);
+    }
+    while (tgroup.y) {
+      const int i = __ffs(tgroup.y) - 1;
+      tgroup.y &= tgroup.y - 1;
+      const PrimRec r = load_prim(sc.wide_prims, tgroup.x + i);
+      bool ok;
+      if (r.prim >= 0) ok = tri_hit(ray, r.v0, r.v1, r.v2);
+      else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: done above
+      else ok = shape_hit(sc, -1 - r.prim, __float_as_int(r.v0.x), ray);
+      if (ok && leaf_gate(sc.leaves, r.leaf, q, ray.tmin, ray.tmax)) return true;
+    }
+    if (ngroup.y <= 0x00ffffffu) {
+      if (sp == 0) break;
+      ngroup = stack[--sp];
     }
   }
   return false;
 }
 
-// Production traversal: the top-level tree (one primitive per geometry) is walked in the reference's
-// order -- analytic shapes carry order-dependent quirks (a scaled Box compares a local-space entry
-// distance with the world-space tmax, bbox.cpp:149-161; an origin inside a Box reports
-// min(exit, tmax)), so their visiting order must be the reference's -- and every mesh below it uses
-// the wide tree.
-__device__ __forceinline__ bool closest_wide(const DScene& sc, Ray& ray, Hit& h) {
-  Octant q = make_octant(ray);
-  h.geom = -1;
-  h.prim = -1;
-  return walk_ref_order<false>(sc, sc.top, ray, q, [&](int top_id) {
-    DTopPrim tp = sc.top_prims[top_id];
-    if (tp.kind == PB2_SHAPE_MESH) {
-      int prim = -1;
-      bool hit = mesh_closest_wide(sc, sc.meshes[tp.index], ray, q, prim);
-      if (hit) { h.geom = tp.geom; h.prim = prim; }
-      return hit;
-    }
-    bool hit = shape_intersect(sc, tp.kind, tp.index, ray);
-    if (hit) { h.geom = tp.geom; h.prim = 0; }
-    return hit;
-  });
-}
-__device__ __forceinline__ bool any_wide(const DScene& sc, const Ray& ray) {
-  Octant q = make_octant(ray);
-  return walk_ref_order<true>(sc, sc.top, ray, q, [&](int top_id) {
-    DTopPrim tp = sc.top_prims[top_id];
-    if (tp.kind == PB2_SHAPE_MESH) return mesh_any_wide(sc, sc.meshes[tp.index], ray, q);
-    return shape_hit(sc, tp.kind, tp.index, ray);
-  });
+// Production entry points: accel 0.
+__device__ __forceinline__ bool closest_production(const DScene& sc, Ray& ray, Hit& h) {
+  return sc.order_dependent ? closest_ref_order(sc, ray, h) : closest_wide(sc, ray, h);
 }
 
 }  // namespace pb2

@@ -103,19 +103,24 @@ class Backend:
         p.accel, p.flags = accel, flags
         return p
 
-    def render(self, spp, depth, rows=None, samples=None, accel=0, out=None):
-        """-> film float32 [h, w, 4] in host memory (pre-tonemap)."""
+    def restage(self, stream=None):
+        """Copy the built scene host->device again (asynchronously on `stream`)."""
+        A.check(self.L.pb2_restage_scene(self.h, stream))
+
+    def render(self, spp, depth, rows=None, samples=None, accel=0, out=None, flags=0):
+        """-> film float32 [h, w, 4] in host memory (pre-tonemap). `out` may be any writable
+        C-contiguous float32 buffer object of that size (e.g. a pinned torch tensor's numpy view)."""
         self.upload_tables(spp)
         w, h = self.size
         film = out if out is not None else np.empty((h, w, 4), np.float32)
-        p = self._params(spp, depth, rows, samples, accel)
+        p = self._params(spp, depth, rows, samples, accel, flags)
         A.check(self.L.pb2_render(self.h, C.byref(p), film.ctypes.data))
         return film
 
-    def render_device(self, spp, depth, rows=None, samples=None, accel=0, stream=None):
+    def render_device(self, spp, depth, rows=None, samples=None, accel=0, stream=None, flags=0):
         """-> device pointer (int) of the float4 film owned by the context."""
         self.upload_tables(spp)
-        p = self._params(spp, depth, rows, samples, accel)
+        p = self._params(spp, depth, rows, samples, accel, flags)
         ptr = C.c_void_p()
         A.check(self.L.pb2_render_device(self.h, C.byref(p), stream, C.byref(ptr)))
         return ptr.value
