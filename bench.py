@@ -38,6 +38,9 @@ WORKLOADS = {
     "c5": ("mesh_field", dict(n_instances=2000, subdiv=4, seed=42, size=(3840, 2160), spp=64, depth=6,
                               with_shapes=False),
            "C5: 2000 x icosphere(4) flattened = 10.24M triangles, 3840x2160, BlueSampler(64), depth 6"),
+    "c5s": ("mesh_field", dict(n_instances=2000, subdiv=4, seed=42, size=(960, 540), spp=16, depth=6,
+                               with_shapes=False),
+            "C5 geometry (10.24M triangles) at 960x540, BlueSampler(16), depth 6 -- profiling size"),
     "c4": ("mesh_field", dict(n_instances=400, subdiv=4, seed=1234, size=(1920, 1080), spp=64, depth=6,
                               with_shapes=True),
            "C4 stand-in (room.glb is missing): 400 x icosphere(4) = 2.05M triangles + sphere/disk, "

@@ -117,7 +117,9 @@ extern "C" int pb2_trace_closest_device(pb2_context* ctx, const float* rays_dev,
   int rc = require_device_scene(ctx);
   if (rc) return rc;
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
-  launch_trace_closest(ctx->scene, rays_dev, n, accel, geom_dev, prim_dev, t_dev, nullptr, st);
+  PB2_CUDA_CHECK(ctx->trace_scratch.reserve((n + 2) * 4));
+  launch_trace_closest(ctx->scene, rays_dev, n, accel, geom_dev, prim_dev, t_dev, nullptr,
+                       ctx->trace_scratch.as<int>(), st);
   ctx->counters.kernel_launches++;
   PB2_CUDA_CHECK(cudaGetLastError());
   return PB2_OK;
@@ -133,11 +135,12 @@ extern "C" int pb2_trace_closest(pb2_context* ctx, const float* rays, size_t n, 
   PB2_CUDA_CHECK(ctx->out_prim.reserve(n * 4));
   PB2_CUDA_CHECK(ctx->out_t.reserve(n * 4));
   if (surf) PB2_CUDA_CHECK(ctx->out_surf.reserve(n * 32));
+  PB2_CUDA_CHECK(ctx->trace_scratch.reserve((n + 2) * 4));
   cudaStream_t st = ctx->stream;
   PB2_CUDA_CHECK(cudaMemcpyAsync(ctx->rays.ptr, rays, n * 32, cudaMemcpyHostToDevice, st));
   launch_trace_closest(ctx->scene, ctx->rays.as<float>(), n, accel, ctx->out_geom.as<int32_t>(),
                        ctx->out_prim.as<int32_t>(), ctx->out_t.as<float>(),
-                       surf ? ctx->out_surf.as<float>() : nullptr, st);
+                       surf ? ctx->out_surf.as<float>() : nullptr, ctx->trace_scratch.as<int>(), st);
   ctx->counters.kernel_launches++;
   PB2_CUDA_CHECK(cudaGetLastError());
   PB2_CUDA_CHECK(cudaMemcpyAsync(geom, ctx->out_geom.ptr, n * 4, cudaMemcpyDeviceToHost, st));
@@ -155,9 +158,11 @@ extern "C" int pb2_trace_any(pb2_context* ctx, const float* rays, size_t n, int 
   if (n == 0) return PB2_OK;
   PB2_CUDA_CHECK(ctx->rays.reserve(n * 32));
   PB2_CUDA_CHECK(ctx->out_occ.reserve(n));
+  PB2_CUDA_CHECK(ctx->trace_scratch.reserve((n + 2) * 4));
   cudaStream_t st = ctx->stream;
   PB2_CUDA_CHECK(cudaMemcpyAsync(ctx->rays.ptr, rays, n * 32, cudaMemcpyHostToDevice, st));
-  launch_trace_any(ctx->scene, ctx->rays.as<float>(), n, accel, ctx->out_occ.as<uint8_t>(), st);
+  launch_trace_any(ctx->scene, ctx->rays.as<float>(), n, accel, ctx->out_occ.as<uint8_t>(),
+                   ctx->trace_scratch.as<int>(), st);
   ctx->counters.kernel_launches++;
   PB2_CUDA_CHECK(cudaGetLastError());
   PB2_CUDA_CHECK(cudaMemcpyAsync(occluded, ctx->out_occ.ptr, n, cudaMemcpyDeviceToHost, st));

@@ -145,8 +145,14 @@ struct Wide {
         const int n = h.hi - h.lo, parts = std::min(8, n);
         for (int i = 0; i < parts; i++) {
           const int a = h.lo + int(int64_t(n) * i / parts), b = h.lo + int(int64_t(n) * (i + 1) / parts);
+          // A mesh stays inside its own box, but an analytic shape need not (a Cone is unbounded
+          // below its base, geometry.cpp:415-446): the reference tests it whenever the LEAF's box is
+          // hit, so that is the box it gets here.
           Box3 box;
-          for (int j = a; j < b; j++) box.extend((*in.top_boxes)[top().leaf_prims[nd.leaf_offset + j]]);
+          for (int j = a; j < b; j++) {
+            const int prim = top().leaf_prims[nd.leaf_offset + j];
+            box.extend((*in.top_prims)[prim].kind == PB2_SHAPE_MESH ? (*in.top_boxes)[prim] : nd.box[0]);
+          }
           out.push_back(top_leaf_slot(h.node, a, b, box));
         }
       } break;

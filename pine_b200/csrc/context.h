@@ -109,7 +109,7 @@ struct pb2_context {
   int n_pixels = 0;
 
   // scratch for trace hooks / render
-  pb2::DBuf rays, out_geom, out_prim, out_t, out_surf, out_occ;
+  pb2::DBuf rays, out_geom, out_prim, out_t, out_surf, out_occ, trace_scratch;
   pb2::DBuf film, film_accum;
   pb2::WavefrontBuffers* wf = nullptr;
 

@@ -22,7 +22,7 @@
 #include "context.h"
 #include "kernels.cuh"
 #include "surface.cuh"
-#include "traverse.cuh"
+#include "wide_persistent.cuh"
 
 namespace pb2 {
 
@@ -42,7 +42,9 @@ struct WaveView {
   // per pixel of this render's row range
   uint2* rng;             // 2 x u64 state as 4 x u32
   float4* lacc;           // running L
-  int* counts;            // [0..D] live rays per depth, [D+1..2D+1] shadow rays per depth
+  int* counts;            // [0..D] live rays per depth, [D+1..2D+1] shadow rays per depth, then per
+                          // depth {closest cursor, closest fallbacks, shadow cursor, shadow fallbacks}
+  int* fb_list;           // fallback list shared by the traversal kernels (used one at a time)
   int n_slots;            // capacity of this wave
   int pixels;             // pixels per sample layer in this wave
   int pixel0;             // first pixel (linear index in the row range) of this wave
@@ -53,7 +55,7 @@ struct WaveView {
 };
 
 struct WavefrontBuffers {
-  DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, rng, lacc, counts;
+  DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, rng, lacc, counts, fb_list;
   std::vector<int> host_counts;
   std::vector<cudaEvent_t> events;  // PB2_RENDER_TIME_KERNELS: one event between consecutive launches
   ~WavefrontBuffers() { for (cudaEvent_t e : events) cudaEventDestroy(e); }
@@ -116,22 +118,74 @@ __global__ void __launch_bounds__(256) k_raygen(DScene sc, WaveView w, int seed_
   }
 }
 
-// ---- closest hit -------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_trace(DScene sc, WaveView w, int depth) {
-  const int n = w.counts[depth];
-  const float4* ro = w.ray_o[depth & 1];
-  const float4* rd = w.ray_d[depth & 1];
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+// ---- closest hit (Accel::intersect, path.cpp:48) ------------------------------------------------------------
+struct TraceIO {
+  const float4* ro;
+  const float4* rd;
+  float4* hit;
+  __device__ __forceinline__ Ray load(int i) const {
     float4 a = ro[i], b = rd[i];
     Ray ray;
     ray.o = V3(a.x, a.y, a.z);
     ray.d = V3(b.x, b.y, b.z);
     ray.tmin = 0.0f;
     ray.tmax = a.w;
-    Hit h;
-    bool hit = w.accel == 0 ? closest_production(sc, ray, h) : closest_ref_order(sc, ray, h);
-    w.hit[i] = make_float4(ray.tmax, __int_as_float(hit ? h.geom : -1), __int_as_float(h.prim), 0.0f);
+    return ray;
   }
+  __device__ __forceinline__ void store_closest(const DScene&, int i, const Ray& ray, bool ok, Hit h) const {
+    hit[i] = make_float4(ray.tmax, __int_as_float(ok ? h.geom : -1), __int_as_float(h.prim), 0.0f);
+  }
+  __device__ __forceinline__ void store_any(int, bool) const {}
+};
+// ---- shadow rays (RTIntegrator::hit, path.cpp:100): occluded => zero the vertex's light term ----------------
+struct ShadowIO {
+  const float4* so;
+  const float4* sd;
+  float4* vtx;  // records of this depth: [slot][2]
+  __device__ __forceinline__ Ray load(int i) const {
+    float4 a = so[i], b = sd[i];
+    Ray ray;
+    ray.o = V3(a.x, a.y, a.z);
+    ray.d = V3(b.x, b.y, b.z);
+    ray.tmin = 0.0f;
+    ray.tmax = a.w;
+    return ray;
+  }
+  __device__ __forceinline__ void store_closest(const DScene&, int, const Ray&, bool, Hit) const {}
+  __device__ __forceinline__ void store_any(int i, bool occluded) const {
+    if (!occluded) return;
+    const int slot = __float_as_int(sd[i].w);
+    float4* v = vtx + size_t(slot) * 2;
+    v[0].x = 0.0f; v[0].y = 0.0f; v[0].z = 0.0f;
+  }
+};
+__device__ __forceinline__ WideQueue wave_queue(const WaveView& w, int depth, int which) {
+  int* c = w.counts + 2 * (w.max_depth + 1) + 4 * depth + 2 * which;
+  return WideQueue{c, c + 1, w.fb_list};
+}
+__device__ __forceinline__ TraceIO trace_io(const WaveView& w, int depth) {
+  return TraceIO{w.ray_o[depth & 1], w.ray_d[depth & 1], w.hit};
+}
+__device__ __forceinline__ ShadowIO shadow_io(const WaveView& w, int depth) {
+  return ShadowIO{w.sh_o, w.sh_d, w.vtx + size_t(depth) * w.n_slots * 2};
+}
+__global__ void __launch_bounds__(kTraceBlock) k_trace(DScene sc, WaveView w, int depth) {
+  wide_persistent<false>(sc, w.counts[depth], wave_queue(w, depth, 0), trace_io(w, depth));
+}
+__global__ void __launch_bounds__(kTraceBlock) k_trace_fallback(DScene sc, WaveView w, int depth) {
+  wide_fallback<false>(sc, wave_queue(w, depth, 0), trace_io(w, depth));
+}
+__global__ void __launch_bounds__(kTraceBlock) k_trace_ref(DScene sc, WaveView w, int depth) {
+  ref_order_all<false>(sc, w.counts[depth], trace_io(w, depth));
+}
+__global__ void __launch_bounds__(kTraceBlock) k_shadow(DScene sc, WaveView w, int depth) {
+  wide_persistent<true>(sc, w.counts[w.max_depth + 1 + depth], wave_queue(w, depth, 1), shadow_io(w, depth));
+}
+__global__ void __launch_bounds__(kTraceBlock) k_shadow_fallback(DScene sc, WaveView w, int depth) {
+  wide_fallback<true>(sc, wave_queue(w, depth, 1), shadow_io(w, depth));
+}
+__global__ void __launch_bounds__(kTraceBlock) k_shadow_ref(DScene sc, WaveView w, int depth) {
+  ref_order_all<true>(sc, w.counts[w.max_depth + 1 + depth], shadow_io(w, depth));
 }
 
 // ---- material -> BxDF (material.h:30-121, material.cpp:9-28) -------------------------------------------------
@@ -351,25 +405,6 @@ __global__ void __launch_bounds__(128) k_shade(DScene sc, WaveView w, int depth)
   }
 }
 
-// ---- shadow rays (RTIntegrator::hit, path.cpp:100) ------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_shadow(DScene sc, WaveView w, int depth) {
-  const int n = w.counts[w.max_depth + 1 + depth];
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    float4 a = w.sh_o[i], b = w.sh_d[i];
-    Ray ray;
-    ray.o = V3(a.x, a.y, a.z);
-    ray.d = V3(b.x, b.y, b.z);
-    ray.tmin = 0.0f;
-    ray.tmax = a.w;
-    bool occluded = w.accel == 0 ? any_wide(sc, ray) : any_ref_order(sc, ray);
-    if (occluded) {
-      int slot = __float_as_int(b.w);
-      float4* v = w.vtx + (size_t(depth) * w.n_slots + slot) * 2;
-      v[0].x = 0.0f; v[0].y = 0.0f; v[0].z = 0.0f;
-    }
-  }
-}
-
 // ---- unwind + per-pixel accumulation -----------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_fold_resolve(WaveView w) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w.pixels; i += gridDim.x * blockDim.x) {
@@ -499,7 +534,8 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   const int n_pixel_waves = int((P + pixels_per_wave - 1) / pixels_per_wave);
   const int n_sample_waves = (n_samples + s_batch - 1) / s_batch;
   const int n_waves = n_pixel_waves * n_sample_waves;
-  const int cstride = 2 * (D + 1);
+  const int cstride = 6 * (D + 1);
+  PB2_CUDA_CHECK(B.fb_list.reserve(size_t(n_slots) * 4));
   PB2_CUDA_CHECK(B.counts.reserve(size_t(n_waves) * cstride * 4));
   PB2_CUDA_CHECK(cudaMemsetAsync(B.counts.ptr, 0, size_t(n_waves) * cstride * 4, st));
 
@@ -508,7 +544,11 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   w.hit = B.hit.as<float4>(); w.sh_o = B.sh_o.as<float4>(); w.sh_d = B.sh_d.as<float4>();
   w.pv_pdf = B.pv_pdf.as<float>(); w.pv_flags = B.pv_flags.as<int>(); w.dim = B.dim.as<int>();
   w.term = B.term.as<float4>(); w.vtx = B.vtx.as<float4>();
-  w.rng = B.rng.as<uint2>(); w.lacc = B.lacc.as<float4>();
+  w.rng = B.rng.as<uint2>(); w.lacc = B.lacc.as<float4>(); w.fb_list = B.fb_list.as<int>();
+  const bool ref_order = p->accel != 0 || !sc.wide_ready;
+  const bool closest_wide_ok = !ref_order && !sc.order_dependent;
+  const bool any_wide_ok = !ref_order && sc.n_box_shapes <= kMaxBoxShapes;
+  const int pgrid = persistent_grid();
   w.n_slots = int(n_slots); w.width = W; w.row_begin = p->row_begin; w.max_depth = D; w.accel = p->accel;
 
   uint64_t launches = 0;
@@ -536,14 +576,27 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       k_raygen<<<sm_grid(w.pixels, 256, 8), 256, 0, st>>>(sc, w, p->sample_begin, sw == 0);
       launches++; mark(3);
       for (int depth = 0; depth < D; depth++) {
-        k_trace<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
+        if (closest_wide_ok) {
+          k_trace<<<pgrid, kTraceBlock, 0, st>>>(sc, w, depth);
+          k_trace_fallback<<<kNumSMs, kTraceBlock, 0, st>>>(sc, w, depth);
+          launches += 2;
+        } else {
+          k_trace_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, st>>>(sc, w, depth);
+          launches++;
+        }
         mark(0);
         k_shade<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
-        mark(2);
-        launches += 2;
+        launches++; mark(2);
         if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
-          k_shadow<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
-          launches++; mark(1);
+          if (any_wide_ok) {
+            k_shadow<<<pgrid, kTraceBlock, 0, st>>>(sc, w, depth);
+            k_shadow_fallback<<<kNumSMs, kTraceBlock, 0, st>>>(sc, w, depth);
+            launches += 2;
+          } else {
+            k_shadow_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, st>>>(sc, w, depth);
+            launches++;
+          }
+          mark(1);
         }
       }
       k_fold_resolve<<<sm_grid(w.pixels, 256, 8), 256, 0, st>>>(w);

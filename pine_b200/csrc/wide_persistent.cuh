@@ -1,0 +1,186 @@
+// wide_persistent.cuh -- the production traversal kernels' inner loop.
+//
+// Ray lengths in a path tracer are heavy tailed (ncu on the one-ray-per-thread version: 2.4 of 32
+// lanes active per instruction in the shadow kernel), so the walk of traverse.cuh (2) is run as a
+// per-lane state machine inside PERSISTENT warps: a lane that finishes its ray takes the next ray
+// of the queue (one atomicAdd per warp, ranks from a ballot) instead of idling until the slowest
+// lane of its warp is done. One iteration = at most one wide-node test plus the primitive tests it
+// produced. Rays whose result the wide walk cannot certify (tie, gate failure, stack overflow --
+// see traverse.cuh) are appended to a fallback list and re-traced in reference order by a second,
+// tiny kernel, which keeps the slow path out of the hot loop's registers.
+//
+// IO concept (POD, passed by value):
+//   __device__ Ray  load(int i) const;
+//   __device__ void store_closest(const DScene&, int i, const Ray& ray_after, bool hit, Hit h) const;
+//   __device__ void store_any(int i, bool occluded) const;
+#pragma once
+#include "traverse.cuh"
+
+namespace pb2 {
+
+constexpr int kRefillThreshold = 8;  // refill a warp when at least this many lanes are idle
+
+struct WideQueue {
+  int* next;      // next unclaimed queue index (zero before the launch)
+  int* fb_count;  // number of entries in fb_list (zero before the launch)
+  int* fb_list;   // queue indices that need the reference-order walk
+};
+
+template <bool ANY, class IO>
+__device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQueue wq, const IO& io) {
+  const unsigned lane = threadIdx.x & 31u;
+  uint2 stack[kWideStack];
+  int sp = 0;
+  bool active = false, drained = false;
+  int idx = 0;
+  Ray ray;
+  Octant q;
+  WideRay w;
+  uint2 ngroup = make_uint2(0u, 0u);
+  bool have = false, ambiguous = false;
+  float tie_t = -1.0f, tmax_in = 0.0f;
+  int win_leaf = -1;
+  Hit h;
+  h.geom = h.prim = -1;
+
+  while (true) {
+    // ---- refill idle lanes ----
+    const unsigned idle = __ballot_sync(0xffffffffu, !active);
+    if (idle && !drained && (__popc(idle) >= kRefillThreshold || idle == 0xffffffffu)) {
+      int base = 0;
+      const int want = __popc(idle);
+      if (lane == unsigned(__ffs(idle) - 1)) base = atomicAdd(wq.next, want);
+      base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
+      if (base + want >= n) drained = true;
+      if (!active) {
+        const int my = base + __popc(idle & ((1u << lane) - 1u));
+        if (my < n) {
+          idx = my;
+          ray = io.load(idx);
+          q = make_octant(ray);
+          w = make_wide_ray(ray, q);
+          tmax_in = ray.tmax;
+          ngroup = make_uint2(0u, 0x80000000u);
+          sp = 0;
+          have = false; ambiguous = false; tie_t = -1.0f; win_leaf = -1;
+          h.geom = h.prim = -1;
+          active = true;
+          if (ANY && sc.n_box_shapes) {  // see DBoxShape
+            bool occ = false;
+            for (int i = 0; i < sc.n_box_shapes && !occ; i++) {
+              const int4 b = __ldg(reinterpret_cast<const int4*>(sc.box_shapes) + i);
+              occ = shape_hit(sc, b.x, b.y, ray) && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax);
+            }
+            if (occ) { io.store_any(idx, true); active = false; }
+          }
+        }
+      }
+    }
+    if (__ballot_sync(0xffffffffu, active) == 0u) {
+      if (drained) break;
+      continue;
+    }
+    if (!active) continue;
+
+    // ---- one step ----
+    uint2 tgroup;
+    if (ngroup.y > 0x00ffffffu) {
+      const uint32_t hits = ngroup.y, imask = hits & 0xffu;
+      const int bit = 31 - __clz(hits);
+      ngroup.y &= ~(1u << bit);
+      if (ngroup.y > 0x00ffffffu) {
+        if (sp < kWideStack) stack[sp++] = ngroup;
+        else ambiguous = true;
+      }
+      const uint32_t slot = uint32_t(bit - 24) ^ (w.octinv4 & 7u);
+      const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
+      uint32_t child_base, prim_base, cmask;
+      const uint32_t hm = test_node8(sc.nodes8, ngroup.x + rel, w, ray.tmin, ANY ? ray.tmax : slack_of(ray.tmax),
+                                     child_base, prim_base, cmask);
+      ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
+      tgroup = make_uint2(prim_base, hm & 0x00ffffffu);
+    } else {
+      tgroup = ngroup;
+      ngroup = make_uint2(0u, 0u);
+    }
+    bool done = ambiguous;
+    while (tgroup.y && !done) {
+      const int i = __ffs(tgroup.y) - 1;
+      tgroup.y &= tgroup.y - 1;
+      const PrimRec r = load_prim(sc.wide_prims, tgroup.x + i);
+      if (ANY) {
+        bool ok;
+        if (r.prim >= 0) ok = tri_hit(ray, r.v0, r.v1, r.v2);
+        else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: tested at refill
+        else ok = shape_hit(sc, -1 - r.prim, __float_as_int(r.v0.x), ray);
+        if (ok && leaf_gate(sc.leaves, r.leaf, q, ray.tmin, ray.tmax)) { have = true; done = true; }
+      } else {
+        Ray r2 = ray;
+        r2.tmax = next_up(ray.tmax);  // lets t == current best through so that ties are seen
+        bool ok;
+        if (r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
+        else ok = shape_intersect(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
+        if (ok) {
+          if (r2.tmax < ray.tmax) {
+            ray.tmax = r2.tmax; h.geom = r.geom; h.prim = r.prim >= 0 ? r.prim : 0; win_leaf = r.leaf; have = true;
+          } else if (r2.tmax == ray.tmax) {
+            if (have) tie_t = r2.tmax;
+            else { ambiguous = true; done = true; }
+          }
+        }
+      }
+    }
+    if (!done && ngroup.y <= 0x00ffffffu) {
+      if (sp == 0) done = true;
+      else ngroup = stack[--sp];
+    }
+    if (done) {
+      if (ANY) {
+        if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
+        else io.store_any(idx, have);
+      } else {
+        if (have && !ambiguous) {
+          if (tie_t == ray.tmax) ambiguous = true;
+          else if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, ray.tmax)) ambiguous = true;
+        }
+        if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
+        else io.store_closest(sc, idx, ray, have, h);
+      }
+      active = false;
+    }
+  }
+}
+
+// Reference-order re-trace of the rays the wide walk could not certify.
+template <bool ANY, class IO>
+__device__ __forceinline__ void wide_fallback(const DScene& sc, WideQueue wq, const IO& io) {
+  const int n = *wq.fb_count;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+    const int idx = wq.fb_list[k];
+    Ray ray = io.load(idx);
+    if (ANY) {
+      io.store_any(idx, any_ref_order(sc, ray));
+    } else {
+      Hit h;
+      const bool hit = closest_ref_order(sc, ray, h);
+      io.store_closest(sc, idx, ray, hit, h);
+    }
+  }
+}
+
+// One ray per thread in reference order (accel = 1, and closest hits of order-dependent scenes).
+template <bool ANY, class IO>
+__device__ __forceinline__ void ref_order_all(const DScene& sc, int n, const IO& io) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    Ray ray = io.load(i);
+    if (ANY) {
+      io.store_any(i, any_ref_order(sc, ray));
+    } else {
+      Hit h;
+      const bool hit = closest_ref_order(sc, ray, h);
+      io.store_closest(sc, i, ray, hit, h);
+    }
+  }
+}
+
+}  // namespace pb2

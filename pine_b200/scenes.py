@@ -147,5 +147,24 @@ def mesh_field(B, n_instances=64, subdiv=3, seed=42, size=(640, 360), spp=16, de
     return {"spp": spp, "depth": depth}
 
 
-SCENES = {"cbox_readme": cbox_readme, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
+def cbox_readme_noboxes(B, size=(640, 640)):
+    """The README scene without its two Box geometries: cones + rects only, i.e. a scene whose
+    closest hits go through the wide tree although a Cone is unbounded below its base."""
+    floor = B.add_material("diffuse", (0.9, 0.9, 0.9))
+    red = B.add_material("metal", (0.9, 0.4, 0.3), roughness=0.3)
+    B.add_rect((0, 0, 1), (2, 0, 0), (0, 0, 2), floor)
+    B.add_rect((0, 2, 1), (2, 0, 0), (0, 0, 2), floor)
+    B.add_rect((-1, 1, 1), (0, 0, 2), (0, 2, 0), red)
+    B.add_rect((1, 1, 1), (0, 0, 2), (0, 2, 0), floor)
+    B.add_rect((0, 1, 2), (2, 0, 0), (0, 2, 0), floor)
+    for x in _frange(-1.0, 0.1, 1.0):
+        for z in _frange(0.0, 0.1, 2.0):
+            B.add_cone((x, 0.3, z), (0, 1, 0), 0.05, 0.05, red if int(round(x * 10)) % 2 else floor)
+    light = B.add_material("emissive", (600.0, 384.0, 111.0))
+    B.add_rect((0.0, 1.9, 0.5), (0.1, 0, 0), (0, 0, 0.1), light)
+    B.set_camera(size, (0, 1, -4), (0, 1, 0), 0.25)
+    return {"spp": 16, "depth": 4}
+
+
+SCENES = {"cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
           "mesh_field": mesh_field}

@@ -5,6 +5,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
 def pytest_configure(config):
@@ -24,15 +25,20 @@ def _built():
     yield
 
 
+def _has_ref():
+    return os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libpine_ref.so"))
+
+
+needs_ref = pytest.mark.skipif(not _has_ref(), reason="oracle/_ref (compiled reference) not built")
+
+
 @pytest.fixture(scope="session")
-def golden_dir():
-    return os.path.join(ROOT, "tests", "golden")
+def golden():
+    import numpy as np
+    cache = {}
 
-
-def has_ref():
-    from oracle import ref
-    return ref.available()
-
-
-needs_ref = pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libpine_ref.so")),
-                               reason="oracle/_ref (compiled reference) not built")
+    def load(name):
+        if name not in cache:
+            cache[name] = dict(np.load(os.path.join(ROOT, "tests", "golden", name + ".npz")))
+        return cache[name]
+    return load

@@ -1,0 +1,110 @@
+"""Generates tests/golden/*.npz from the compiled reference (oracle/_ref, i.e. the unmodified
+wicstas/pine sources under /root/reference built by oracle/Makefile). Run in the build container:
+
+    python tests/golden/make_golden.py
+
+The reference ships no known-answer vectors for this path, so these files ARE the
+pin: every vector is an output of the reference's own code on inputs described here.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import common  # noqa: E402
+from oracle import ref  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def kats():
+    out = {}
+    pixels = [(0, 0), (37, 411), (639, 12), (1000, 999)]
+    for spp in (1, 2, 16, 64, 256):
+        for i, (px, py) in enumerate(pixels):
+            r, d = ref.sampler_stream(spp, px, py, i, 8, "21221", 6)
+            out[f"rand_{spp}_{i}"] = r
+            out[f"draws_{spp}_{i}"] = d
+        # wrap-around of the dimension counter (sampler.h:182-193): 140 get2d draws in one sample
+        _, d = ref.sampler_stream(spp, 5, 7, 0, 0, "2" * 140 + "1", 1)
+        out[f"wrap_{spp}"] = d
+    out["pixels"] = np.array(pixels, np.int32)
+    hp = [(x, y, s) for x in (0, 1, 77, 3839) for y in (0, 5, 2159) for s in (0, 3)]
+    out["hash_in"] = np.array(hp, np.int32)
+    out["hash_out"] = np.array([ref.lib().ref_hash_pixel(*p) for p in hp], np.uint64)
+    seeds = np.array([0, 1, 0xdeadbeef, 2 ** 63 + 5], np.uint64)
+    rng = np.zeros((len(seeds), 8), np.uint64)
+    for i, s in enumerate(seeds):
+        import ctypes as C
+        ref.lib().ref_rng_u64(C.c_uint64(int(s)), 8, rng[i].ctypes.data_as(C.c_void_p))
+    out["rng_seeds"], out["rng_out"] = seeds, rng
+    grid = np.zeros((5, 8, 8, 4, 8), np.float32)
+    for a, spp in enumerate((1, 4, 16, 64, 256)):
+        for px in range(8):
+            for py in range(8):
+                for idx in range(4):
+                    for dim in range(8):
+                        grid[a, px, py, idx, dim] = ref.bluenoise(spp, px * 17, py * 29, idx * 5, dim * 3)
+    out["bluenoise_grid"] = grid
+    out["nee_draw_order_2d_first"] = np.array([ref.lib().ref_nee_draw_order_2d_first()], np.int32)
+    np.savez_compressed(os.path.join(OUT, "kats.npz"), **out)
+
+
+def scene(name):
+    fn, kw, spp, depth = common.SMALL_SCENES[name]
+    R = ref.RefScene()
+    common.build(R, name)
+    out = {}
+    rays = R.primary_rays(0)
+    out["primary0"] = rays
+    out["primary2"] = R.primary_rays(2)
+    h = R.trace_closest(rays, surf=True, count_tests=True)
+    for k in ("geom", "prim", "t", "surf", "n_prim_tests"):
+        out["p_" + k] = h[k]
+    inp = common.secondary_inputs(h["surf"], h["geom"], 1)
+    sec = ref.spawn_rays(inp)
+    out["spawn_in"], out["secondary"] = inp, sec
+    h2 = R.trace_closest(sec, surf=True)
+    for k in ("geom", "prim", "t", "surf"):
+        out["s_" + k] = h2[k]
+    sh = common.shadow_from(sec, 2)
+    out["shadow"], out["shadow_occ"] = sh, R.trace_any(sh)
+    film, _ = R.render(spp, depth)
+    out["film"] = film
+    conv, _ = R.render(4096, depth, sampler="sobol")   # converged reference for relMSE
+    out["film_converged"] = conv
+    out["geometry_aabbs"] = R.geometry_aabbs()
+    R.accel_build()
+    t = R.bvh_tree(-1)
+    for k, v in t.items():
+        out["top_" + k] = np.asarray(v)
+    idx, n_lbvh = R.bvh_indices()
+    out["bvh_indices"], out["n_lbvh"] = idx, np.array([n_lbvh], np.int32)
+    if n_lbvh:
+        t = R.bvh_tree(0)
+        for k, v in t.items():
+            out["mesh0_" + k] = np.asarray(v)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(name, {k: v.shape for k, v in out.items() if k in ("primary0", "secondary", "film")})
+
+
+def camera_lens():
+    R = ref.RefScene()
+    m = R.add_material("diffuse", (0.5, 0.5, 0.5))
+    R.add_rect((0, 0, 1), (2, 0, 0), (0, 0, 2), m)
+    R.set_camera((32, 24), (0.3, 1.1, -4), (0.1, 0.9, 0.2), 0.3, len_radius=0.05, focus=3.5)
+    rng = np.random.RandomState(3)
+    inp = rng.rand(512, 4).astype(np.float32)
+    np.savez_compressed(os.path.join(OUT, "camera_lens.npz"), inp=inp, rays=R.gen_rays(inp))
+
+
+if __name__ == "__main__":
+    if not ref.available():
+        raise SystemExit("oracle/_ref/libpine_ref.so missing: make -C oracle ref")
+    kats()
+    camera_lens()
+    for name in common.SMALL_SCENES:
+        scene(name)
