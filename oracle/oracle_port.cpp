@@ -410,7 +410,14 @@ bool slab(const Box& b, const Octant& q, float tmin, float& tmax) {
   return tmin <= tmax;
 }
 
-struct Counters { int nodes = 0, prim_tests = 0; };
+struct Counters { int nodes = 0, prim_tests = 0; long prim_bytes = 0; };
+// information content of one primitive test under the reference traversal -- 48 B per
+// triangle (3 x vec3 + 12 B index), the shape struct's own members otherwise.
+static inline int shape_bytes(int kind) {
+  static const int b[8] = {24, 152, 16, 48, 64, 76, 52, 48};  // AABB OBB SPHERE TRIANGLE CONE RECT DISK (MESH)
+  return b[kind & 7];
+}
+static long g_last_nodes = 0, g_last_prim_tests = 0, g_last_prim_bytes = 0;
 
 // BVHImpl::Intersect (ANY=false) / BVHImpl::hit (ANY=true). `leaf(prim)` returns true on an accepted
 // hit (closest: after shrinking ray.tmax).
@@ -549,7 +556,7 @@ struct Scene {
         const MeshData& m = meshes[g.index];
         int p = -1;
         bool hit = walk<false>(lbvh[top_id], ray, q, cnt, [&](int tri) {
-          cnt.prim_tests++;
+          cnt.prim_tests++; cnt.prim_bytes += 48;
           float t;
           if (!tri_test(ray, m.verts[m.idx[3 * tri]], m.verts[m.idx[3 * tri + 1]], m.verts[m.idx[3 * tri + 2]], false, t)) return false;
           ray.tmax = t;
@@ -559,7 +566,7 @@ struct Scene {
         if (hit) { geom = indices[top_id]; prim = p; }
         return hit;
       }
-      cnt.prim_tests++;
+      cnt.prim_tests++; cnt.prim_bytes += shape_bytes(g.kind);
       float t;
       if (!shape_test(g, ray, false, t)) return false;
       ray.tmax = t;
@@ -576,12 +583,12 @@ struct Scene {
       if (top_id < int(lbvh.size())) {
         const MeshData& m = meshes[g.index];
         return walk<true>(lbvh[top_id], ray, q, cnt, [&](int tri) {
-          cnt.prim_tests++;
+          cnt.prim_tests++; cnt.prim_bytes += 48;
           float t;
           return tri_test(ray, m.verts[m.idx[3 * tri]], m.verts[m.idx[3 * tri + 1]], m.verts[m.idx[3 * tri + 2]], true, t);
         });
       }
-      cnt.prim_tests++;
+      cnt.prim_tests++; cnt.prim_bytes += shape_bytes(g.kind);
       float t;
       return shape_test(g, ray, true, t);
     });
@@ -634,6 +641,7 @@ void port_trace_closest(void* h, const float* rays, int64_t n, int32_t* geom, in
                         int32_t* n_nodes, int32_t* n_prim_tests) {
   Scene& S = *static_cast<Scene*>(h);
   if (!S.built) S.build();
+  g_last_nodes = g_last_prim_tests = g_last_prim_bytes = 0;
   for (int64_t i = 0; i < n; i++) {
     const float* r = rays + 8 * i;
     Ray ray;
@@ -646,12 +654,14 @@ void port_trace_closest(void* h, const float* rays, int64_t n, int32_t* geom, in
     t[i] = ray.tmax;
     if (n_nodes) n_nodes[i] = c.nodes;
     if (n_prim_tests) n_prim_tests[i] = c.prim_tests;
+    g_last_nodes += c.nodes; g_last_prim_tests += c.prim_tests; g_last_prim_bytes += c.prim_bytes;
   }
 }
 void port_trace_any(void* h, const float* rays, int64_t n, uint8_t* occluded, int32_t* n_nodes,
                     int32_t* n_prim_tests) {
   Scene& S = *static_cast<Scene*>(h);
   if (!S.built) S.build();
+  g_last_nodes = g_last_prim_tests = g_last_prim_bytes = 0;
   for (int64_t i = 0; i < n; i++) {
     const float* r = rays + 8 * i;
     Ray ray;
@@ -660,8 +670,11 @@ void port_trace_any(void* h, const float* rays, int64_t n, uint8_t* occluded, in
     occluded[i] = S.any(ray, c) ? 1 : 0;
     if (n_nodes) n_nodes[i] = c.nodes;
     if (n_prim_tests) n_prim_tests[i] = c.prim_tests;
+    g_last_nodes += c.nodes; g_last_prim_tests += c.prim_tests; g_last_prim_bytes += c.prim_bytes;
   }
 }
+// Totals of the last port_trace_* call: {binary nodes visited, primitive tests, primitive bytes}.
+void port_last_totals(int64_t* out) { out[0] = g_last_nodes; out[1] = g_last_prim_tests; out[2] = g_last_prim_bytes; }
 // Tree dump in the layout of oracle/ref_harness.cpp:ref_bvh_nodes (which = -1 top, k = mesh tree k).
 static const Tree* pick(Scene& S, int which) {
   if (which < 0) return &S.top;
