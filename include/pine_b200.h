@@ -208,6 +208,17 @@ int pb2_trace_closest_device(pb2_context* ctx, const float* rays_dev, size_t n, 
                              void* cuda_stream);
 /* Known-answer hooks for the sampler/camera kernels (Sampler wrapper sampler.h:286-309,
  * BlueSobolSampler sampler.h:166-201, ThinLenCamera::gen_ray camera.cpp:22-33). */
+/* Test hook: every ray a render traces. Set before pb2_render* (NULL clears). The render must fit
+ * one wave (small films); it appends, per depth, the closest-hit queue with its results and the
+ * shadow queue with its occlusion results, up to `capacity` rays per kind (more => PB2_E_INVALID).
+ * Rays are n x {o.xyz, d.xyz, tmin, tmax}, exactly what Accel::intersect / Accel::hit received. */
+typedef struct pb2_ray_record {
+  uint64_t capacity;
+  uint64_t n_closest, n_shadow; /* out */
+  float* closest_rays; float* closest_t; int32_t* closest_geom; int32_t* closest_prim;
+  float* shadow_rays; uint8_t* shadow_occluded;
+} pb2_ray_record;
+int pb2_set_ray_record(pb2_context* ctx, pb2_ray_record* rec);
 int pb2_test_sampler(pb2_context* ctx, int spp, int px, int py, int sample_index, int n_rand,
                      float* out_rand, const char* pattern, int n_samples, float* out_draws);
 int pb2_test_primary_rays(pb2_context* ctx, int sample_index, float* rays_host);

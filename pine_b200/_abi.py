@@ -87,6 +87,13 @@ class RenderParams(C.Structure):
                 ("accel", C.c_int32), ("flags", C.c_int32)]
 
 
+class RayRecord(C.Structure):
+    _fields_ = [("capacity", C.c_uint64), ("n_closest", C.c_uint64), ("n_shadow", C.c_uint64),
+                ("closest_rays", C.c_void_p), ("closest_t", C.c_void_p),
+                ("closest_geom", C.c_void_p), ("closest_prim", C.c_void_p),
+                ("shadow_rays", C.c_void_p), ("shadow_occluded", C.c_void_p)]
+
+
 class Counters(C.Structure):
     _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("camera_samples", C.c_uint64), ("kernel_launches", C.c_uint64),
@@ -111,7 +118,7 @@ ABI_SYMBOLS = [
     "pb2_restage_scene",
     "pb2_upload_sampler_tables", "pb2_render", "pb2_render_device", "pb2_film_finalize",
     "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler",
-    "pb2_test_primary_rays", "pb2_get_counters", "pb2_bvh_info", "pb2_bvh_nodes",
+    "pb2_test_primary_rays", "pb2_get_counters", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
     "pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone", "pb2h_make_triangle",
     "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_round_spp",
 ]
@@ -153,6 +160,7 @@ def lib():
         L.pb2_test_sampler.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_void_p, C.c_char_p, C.c_int, C.c_void_p]
         L.pb2_test_primary_rays.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.pb2_set_ray_record.argtypes = [C.c_void_p, C.POINTER(RayRecord)]
         L.pb2_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
         L.pb2_bvh_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int32),
                                    C.POINTER(C.c_int32), C.POINTER(C.c_int32)]

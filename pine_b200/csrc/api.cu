@@ -170,6 +170,13 @@ extern "C" int pb2_trace_any(pb2_context* ctx, const float* rays, size_t n, int 
   return PB2_OK;
 }
 
+extern "C" int pb2_set_ray_record(pb2_context* ctx, pb2_ray_record* rec) {
+  if (!ctx) { set_error("null argument"); return PB2_E_INVALID; }
+  ctx->record = rec;
+  if (rec) rec->n_closest = rec->n_shadow = 0;
+  return PB2_OK;
+}
+
 extern "C" int pb2_get_counters(pb2_context* ctx, pb2_counters* out) {
   if (!ctx || !out) { set_error("null argument"); return PB2_E_INVALID; }
   *out = ctx->counters;

@@ -80,6 +80,41 @@ struct Wide {
   std::vector<int> top_leaf_gate;                // top node -> DLeaf (leaves only)
   std::vector<std::vector<int>> mesh_leaf_gate;  // tree -> node -> DLeaf (leaves only)
   std::vector<int> tree_mesh, tree_geom;         // mesh tree -> mesh id / geometry index
+  std::vector<char> top_unbounded;               // top node -> a Cone somewhere below it
+
+  // Shapes that can be hit outside their own box (traverse.cuh (iv)).
+  static bool unbounded_kind(int kind) { return kind == PB2_SHAPE_CONE; }
+  void mark_unbounded() {
+    const Tree2& t = top();
+    top_unbounded.assign(t.nodes.size(), 0);
+    // children precede their parent or not -- do not rely on the numbering: iterate to a fixpoint
+    for (size_t i = 0; i < t.nodes.size(); i++) {
+      const Node2& nd = t.nodes[i];
+      for (int j = 0; j < nd.leaf_count; j++)
+        if (unbounded_kind((*in.top_prims)[t.leaf_prims[nd.leaf_offset + j]].kind)) top_unbounded[i] = 1;
+    }
+    for (bool changed = true; changed;) {
+      changed = false;
+      for (size_t i = 0; i < t.nodes.size(); i++) {
+        const Node2& nd = t.nodes[i];
+        if (nd.leaf_count || top_unbounded[i]) continue;
+        if (top_unbounded[nd.child[0]] || top_unbounded[nd.child[1]]) { top_unbounded[i] = 1; changed = true; }
+      }
+    }
+  }
+  bool has_unbounded(const Handle& h) const {
+    switch (h.kind) {
+      case H_TOP_NODE: return top_unbounded[h.node];
+      case H_TOP_LEAF: {
+        const Node2& nd = top().nodes[h.node];
+        for (int j = h.lo; j < h.hi; j++)
+          if (unbounded_kind((*in.top_prims)[top().leaf_prims[nd.leaf_offset + j]].kind)) return true;
+        return false;
+      }
+      case H_SHAPE: return unbounded_kind((*in.top_prims)[h.node].kind);
+      default: return false;
+    }
+  }
 
   const Tree2& top() const { return *in.top; }
   const Tree2& mtree(int k) const { return (*in.mesh_trees)[k]; }
@@ -275,6 +310,8 @@ struct Wide {
     }
     node.child_base = child_base;
     node.prim_base = uint32_t(prims.size());
+    for (auto& sl : slots)
+      if (has_unbounded(sl.h)) node.prim_base |= 0x80000000u;  // kNoCullBit (traverse.cuh)
     int prim_offset = 0;
     for (int s = 0; s < 8; s++) {
       const int c = child_in[s];
@@ -371,6 +408,7 @@ void build_wide(const WideInput& in, LayoutOut& out, int threads) {
   const Tree2& top = *in.top;
   if (top.root < 0) return;
   Wide w{in};
+  w.mark_unbounded();
   auto push_gate = [&](const Box3& b) {
     DLeaf L;
     for (int k = 0; k < 3; k++) { L.box[k] = b.lower[k]; L.box[3 + k] = b.upper[k]; }

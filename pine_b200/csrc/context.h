@@ -113,5 +113,7 @@ struct pb2_context {
   pb2::DBuf film, film_accum;
   pb2::WavefrontBuffers* wf = nullptr;
 
+  pb2_ray_record* record = nullptr;  // test hook (pb2_set_ray_record)
+
   pb2_counters counters{};
 };

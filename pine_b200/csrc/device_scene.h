@@ -59,7 +59,7 @@ struct alignas(16) DNode8 {
   uint8_t exp[3];       // per-axis scale = 2^(exp-127): plane = origin + q * scale (exact in fp32)
   uint8_t imask;        // bit i set: child slot i is an internal node
   uint32_t child_base;  // index of the first internal child
-  uint32_t prim_base;   // index of the first DPrim of this node's leaf children
+  uint32_t prim_base;   // index of the first DPrim of this node's leaf children; bit 31 = kNoCullBit
   uint8_t meta[8];      // internal: 001sssss (s = 24 + slot); leaf: unary count (1..3) << 5 | offset;
                         // empty slot: 0
   uint8_t qlo[3][8];    // quantised lower planes, axis-major
@@ -102,9 +102,9 @@ struct DScene {
   const DBoxShape* box_shapes;
   int32_t n_box_shapes;     // > kMaxBoxShapes: any-hit walks the reference-order tree instead
   int32_t wide_ready;       // 1: nodes8/wide_prims hold a tree (root = node 0)
-  int32_t order_dependent;  // 1: the scene has AABB/OBB shapes, whose closest-hit result depends on
-                            // the visiting order (bbox.cpp:149-161) => closest hit walks the
-                            // reference-order tree; any-hit is order independent and stays wide
+  int32_t order_dependent;  // 1: more than kMaxBoxShapes AABB/OBB shapes, whose closest-hit result
+                            // depends on the visiting order (bbox.cpp:149-161) => every closest
+                            // hit walks the reference-order tree (traverse.cuh (iii))
   DTree top;
   const DTopPrim* top_prims;
   const DMesh* meshes;

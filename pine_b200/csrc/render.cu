@@ -16,6 +16,7 @@
 // render is a stream of launches with no host synchronisation in between.
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "bsdf.cuh"
@@ -45,6 +46,7 @@ struct WaveView {
   int* counts;            // [0..D] live rays per depth, [D+1..2D+1] shadow rays per depth, then per
                           // depth {closest cursor, closest fallbacks, shadow cursor, shadow fallbacks}
   int* fb_list;           // fallback list shared by the traversal kernels (used one at a time)
+  uint8_t* occ;           // NULL unless a ray record is being taken
   int n_slots;            // capacity of this wave
   int pixels;             // pixels per sample layer in this wave
   int pixel0;             // first pixel (linear index in the row range) of this wave
@@ -55,7 +57,7 @@ struct WaveView {
 };
 
 struct WavefrontBuffers {
-  DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, rng, lacc, counts, fb_list;
+  DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, rng, lacc, counts, fb_list, occ;
   std::vector<int> host_counts;
   std::vector<cudaEvent_t> events;  // PB2_RENDER_TIME_KERNELS: one event between consecutive launches
   ~WavefrontBuffers() { for (cudaEvent_t e : events) cudaEventDestroy(e); }
@@ -142,6 +144,7 @@ struct ShadowIO {
   const float4* so;
   const float4* sd;
   float4* vtx;  // records of this depth: [slot][2]
+  uint8_t* occ; // test hook (pb2_set_ray_record): occlusion per shadow-queue entry, else NULL
   __device__ __forceinline__ Ray load(int i) const {
     float4 a = so[i], b = sd[i];
     Ray ray;
@@ -153,6 +156,7 @@ struct ShadowIO {
   }
   __device__ __forceinline__ void store_closest(const DScene&, int, const Ray&, bool, Hit) const {}
   __device__ __forceinline__ void store_any(int i, bool occluded) const {
+    if (occ) occ[i] = occluded ? 1 : 0;
     if (!occluded) return;
     const int slot = __float_as_int(sd[i].w);
     float4* v = vtx + size_t(slot) * 2;
@@ -167,7 +171,7 @@ __device__ __forceinline__ TraceIO trace_io(const WaveView& w, int depth) {
   return TraceIO{w.ray_o[depth & 1], w.ray_d[depth & 1], w.hit};
 }
 __device__ __forceinline__ ShadowIO shadow_io(const WaveView& w, int depth) {
-  return ShadowIO{w.sh_o, w.sh_d, w.vtx + size_t(depth) * w.n_slots * 2};
+  return ShadowIO{w.sh_o, w.sh_d, w.vtx + size_t(depth) * w.n_slots * 2, w.occ};
 }
 __global__ void __launch_bounds__(kTraceBlock) k_trace(DScene sc, WaveView w, int depth) {
   wide_persistent<false>(sc, w.counts[depth], wave_queue(w, depth, 0), trace_io(w, depth));
@@ -538,8 +542,14 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   PB2_CUDA_CHECK(B.fb_list.reserve(size_t(n_slots) * 4));
   PB2_CUDA_CHECK(B.counts.reserve(size_t(n_waves) * cstride * 4));
   PB2_CUDA_CHECK(cudaMemsetAsync(B.counts.ptr, 0, size_t(n_waves) * cstride * 4, st));
+  pb2_ray_record* rec = ctx->record;
+  if (rec) {
+    if (n_waves != 1) { set_error("ray record: the render must fit one wave"); return PB2_E_INVALID; }
+    PB2_CUDA_CHECK(B.occ.reserve(size_t(n_slots)));
+  }
 
   WaveView w{};
+  w.occ = rec ? B.occ.as<uint8_t>() : nullptr;
   for (int k = 0; k < 2; k++) { w.ray_o[k] = B.ray_o[k].as<float4>(); w.ray_d[k] = B.ray_d[k].as<float4>(); }
   w.hit = B.hit.as<float4>(); w.sh_o = B.sh_o.as<float4>(); w.sh_d = B.sh_d.as<float4>();
   w.pv_pdf = B.pv_pdf.as<float>(); w.pv_flags = B.pv_flags.as<int>(); w.dim = B.dim.as<int>();
@@ -561,6 +571,48 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
     if (ev_used == B.events.size()) { cudaEvent_t e; cudaEventCreate(&e); B.events.push_back(e); }
     cudaEventRecord(B.events[ev_used++], st);
     ev_class.push_back(cls);
+  };
+  // ray record (test hook): synchronous copies of the queues after the traversal kernels ran
+  std::vector<float4> rec_a, rec_b, rec_c;
+  std::vector<uint8_t> rec_occ;
+  auto record = [&](bool shadow, int depth) -> int {
+    int n = 0;
+    const int* cnt = w.counts + (shadow ? D + 1 + depth : depth);
+    if (cudaStreamSynchronize(st) != cudaSuccess ||
+        cudaMemcpy(&n, cnt, 4, cudaMemcpyDeviceToHost) != cudaSuccess) { set_error("ray record: copy failed"); return PB2_E_CUDA; }
+    uint64_t& have = shadow ? rec->n_shadow : rec->n_closest;
+    if (have + uint64_t(n) > rec->capacity) { set_error("ray record: capacity exceeded"); return PB2_E_INVALID; }
+    if (!n) return PB2_OK;
+    rec_a.resize(n); rec_b.resize(n);
+    const float4* src_o = shadow ? w.sh_o : w.ray_o[depth & 1];
+    const float4* src_d = shadow ? w.sh_d : w.ray_d[depth & 1];
+    cudaMemcpy(rec_a.data(), src_o, size_t(n) * 16, cudaMemcpyDeviceToHost);
+    cudaMemcpy(rec_b.data(), src_d, size_t(n) * 16, cudaMemcpyDeviceToHost);
+    float* rays = (shadow ? rec->shadow_rays : rec->closest_rays) + have * 8;
+    for (int i = 0; i < n; i++) {
+      float* r = rays + size_t(i) * 8;
+      r[0] = rec_a[i].x; r[1] = rec_a[i].y; r[2] = rec_a[i].z;
+      r[3] = rec_b[i].x; r[4] = rec_b[i].y; r[5] = rec_b[i].z;
+      r[6] = 0.0f; r[7] = rec_a[i].w;
+    }
+    if (shadow) {
+      if (cudaMemcpy(rec->shadow_occluded + have, w.occ, size_t(n), cudaMemcpyDeviceToHost) != cudaSuccess) {
+        set_error("ray record: copy failed"); return PB2_E_CUDA;
+      }
+    } else {
+      rec_c.resize(n);
+      if (cudaMemcpy(rec_c.data(), w.hit, size_t(n) * 16, cudaMemcpyDeviceToHost) != cudaSuccess) {
+        set_error("ray record: copy failed"); return PB2_E_CUDA;
+      }
+      for (int i = 0; i < n; i++) {
+        rec->closest_t[have + i] = rec_c[i].x;
+        std::memcpy(&rec->closest_geom[have + i], &rec_c[i].y, 4);
+        std::memcpy(&rec->closest_prim[have + i], &rec_c[i].z, 4);
+        if (rec->closest_geom[have + i] < 0) rec->closest_prim[have + i] = -1;
+      }
+    }
+    have += uint64_t(n);
+    return PB2_OK;
   };
   PB2_CUDA_CHECK(cudaEventRecord(ctx->ev0, st));
   mark(-1);
@@ -585,6 +637,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
           launches++;
         }
         mark(0);
+        if (rec && (rc = record(false, depth))) return rc;
         k_shade<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
         launches++; mark(2);
         if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
@@ -597,6 +650,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
             launches++;
           }
           mark(1);
+          if (rec && (rc = record(true, depth))) return rc;
         }
       }
       k_fold_resolve<<<sm_grid(w.pixels, 256, 8), 256, 0, st>>>(w);

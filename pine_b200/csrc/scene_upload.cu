@@ -220,9 +220,8 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   wi.mesh_trees = &ctx->mesh_trees; wi.mesh_tree_of = &mesh_tree_of; wi.meshes = sd->meshes;
   build_wide(wi, lay, n_threads);
   stage("wide tree");
-  bool order_dependent = false;
-  for (uint32_t i = 0; i < sd->n_geometries; i++)
-    order_dependent |= sd->geometries[i].shape_kind == PB2_SHAPE_AABB || sd->geometries[i].shape_kind == PB2_SHAPE_OBB;
+  // more AABB/OBB shapes than the per-ray pre-test handles: every closest hit in reference order
+  const bool order_dependent = lay.box_shapes.size() > size_t(kMaxBoxShapes);
 
   ctx->counters.bvh2_nodes = uint32_t(lay.nodes2.size());
   ctx->counters.wide_nodes = uint32_t(lay.nodes8.size());

@@ -170,9 +170,18 @@ __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) 
 //         tmax = t_winner -- then the reference, whose tmax is always >= t_winner and whose
 //         ancestor boxes contain the leaf box, reaches and accepts the winner, and nothing it sees
 //         later can replace it (slab tests are monotone in tmax and in the box),
-//   (iii) no primitive's reported t depends on the incoming tmax (true for everything but
-//         AABB/OBB shapes, bbox.cpp:149-161; scenes that contain those walk the reference-order
-//         tree for closest hits: DScene::order_dependent).
+//   (iii) no primitive's reported t depends on the incoming tmax. True for everything but AABB/OBB
+//         shapes (bbox.cpp:149-161: a hit from inside reports the exit clipped by tmax, and a
+//         scaled OBB can even RAISE tmax). Their acceptance is monotone in tmax, so a ray for which
+//         every box shape is rejected at the ray's incoming tmax (shape test AND leaf gate) never
+//         has one accepted by the reference either: such rays take the wide walk with the box
+//         shapes left out, all others go to the reference-order walk (wide_persistent.cuh),
+//   (iv)  every primitive the reference accepts is also tested here. For primitives that lie
+//         inside their leaf box this follows from box containment; a Cone does not (it is
+//         unbounded below its base, geometry.cpp:415-446) and can be hit BEFORE the ray enters its
+//         leaf box, which the reference accepts if it reaches the leaf while tmax is still large.
+//         Nodes with a Cone anywhere below them (kNoCullBit) are therefore tested against the
+//         ray's incoming tmax, never the current best; a Cone hit outside its box then fails (ii).
 // Boxes are culled against a slightly enlarged tmax (`slack_of`), so a primitive whose t ties or
 // beats the current best is never hidden behind a box whose computed entry distance exceeds t by
 // rounding. Rays for which (i) or (ii) fails, or whose stack overflows (a handful per million),
@@ -224,9 +233,12 @@ __device__ __forceinline__ PrimRec load_prim(const DPrim* prims, uint32_t idx) {
 
 // Tests the 8 children of node `idx`; returns the hit mask (bits 24..31: internal children in
 // traversal order, bits 0..23: primitives) and the node's child_base / prim_base / imask.
+// `lim` culls by the current best t; nodes flagged kNoCullBit (an unbounded shape somewhere below,
+// see the header comment) are tested against `lim_nocull` = the ray's incoming tmax instead.
+constexpr uint32_t kNoCullBit = 0x80000000u;  // in DNode8::prim_base
 __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx, const WideRay& w, float tmin,
-                                               float lim, uint32_t& child_base, uint32_t& prim_base,
-                                               uint32_t& imask) {
+                                               float lim, float lim_nocull, uint32_t& child_base,
+                                               uint32_t& prim_base, uint32_t& imask) {
   const uint4* p = reinterpret_cast<const uint4*>(nodes + idx);
   const uint4 n0 = __ldg(p), n1 = __ldg(p + 1), n2 = __ldg(p + 2), n3 = __ldg(p + 3), n4 = __ldg(p + 4);
   const float ox = __uint_as_float(n0.x), oy = __uint_as_float(n0.y), oz = __uint_as_float(n0.z);
@@ -235,7 +247,8 @@ __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx
   const float az = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * w.inv.z;
   imask = n0.w >> 24;
   child_base = n1.x;
-  prim_base = n1.y;
+  prim_base = n1.y & ~kNoCullBit;
+  if (n1.y & kNoCullBit) lim = lim_nocull;
   const float ux = ox * w.inv.x, uy = oy * w.inv.y, uz = oz * w.inv.z;
   const float dx = (fabsf(ux) + 255.0f * fabsf(ax) + fabsf(w.ood.x)) * 4.76837158203125e-7f;
   const float dy = (fabsf(uy) + 255.0f * fabsf(ay) + fabsf(w.ood.y)) * 4.76837158203125e-7f;
@@ -277,130 +290,6 @@ __device__ __forceinline__ WideRay make_wide_ray(const Ray& ray, const Octant& q
   w.neg = (ray.d.x < 0 ? 1u : 0u) | (ray.d.y < 0 ? 2u : 0u) | (ray.d.z < 0 ? 4u : 0u);
   w.octinv4 = (7u ^ w.neg) * 0x01010101u;
   return w;
-}
-
-// Closest hit over the whole scene. Only valid when !sc.order_dependent.
-__device__ inline bool closest_wide(const DScene& sc, Ray& ray, Hit& h) {
-  const Octant q = make_octant(ray);
-  h.geom = -1;
-  h.prim = -1;
-  if (!sc.wide_ready) return false;
-  const WideRay w = make_wide_ray(ray, q);
-  const float tmax_in = ray.tmax;
-  uint2 stack[kWideStack];
-  int sp = 0;
-  uint2 ngroup = make_uint2(0u, 0x80000000u);
-  bool have = false, ambiguous = false;
-  float tie_t = -1.0f;
-  int win_leaf = -1;
-  while (true) {
-    uint2 tgroup;
-    if (ngroup.y > 0x00ffffffu) {
-      const uint32_t hits = ngroup.y, imask = hits & 0xffu;
-      const int bit = 31 - __clz(hits);
-      ngroup.y &= ~(1u << bit);
-      if (ngroup.y > 0x00ffffffu) {
-        if (sp < kWideStack) stack[sp++] = ngroup;
-        else { ambiguous = true; break; }
-      }
-      const uint32_t slot = uint32_t(bit - 24) ^ (w.octinv4 & 7u);
-      const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
-      uint32_t child_base, prim_base, cmask;
-      const uint32_t hm = test_node8(sc.nodes8, ngroup.x + rel, w, ray.tmin, slack_of(ray.tmax), child_base,
-                                     prim_base, cmask);
-      ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
-      tgroup = make_uint2(prim_base, hm & 0x00ffffffu);
-    } else {
-      tgroup = ngroup;
-      ngroup = make_uint2(0u, 0u);
-    }
-    while (tgroup.y) {
-      const int i = __ffs(tgroup.y) - 1;
-      tgroup.y &= tgroup.y - 1;
-      const PrimRec r = load_prim(sc.wide_prims, tgroup.x + i);
-      Ray r2 = ray;
-      r2.tmax = next_up(ray.tmax);  // lets t == current best through so that ties are seen
-      bool ok;
-      if (r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
-      else ok = shape_intersect(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
-      if (ok) {
-        if (r2.tmax < ray.tmax) {
-          ray.tmax = r2.tmax; h.geom = r.geom; h.prim = r.prim >= 0 ? r.prim : 0; win_leaf = r.leaf; have = true;
-        } else if (r2.tmax == ray.tmax) {
-          if (have) tie_t = r2.tmax;
-          else ambiguous = true;  // t == the incoming tmax: strict and non-strict shapes differ
-        }
-      }
-    }
-    if (ngroup.y <= 0x00ffffffu) {
-      if (sp == 0) break;
-      ngroup = stack[--sp];
-    }
-  }
-  if (have && !ambiguous) {
-    if (tie_t == ray.tmax) ambiguous = true;
-    else if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, ray.tmax)) ambiguous = true;
-  }
-  if (ambiguous) {
-    ray.tmax = tmax_in;
-    return closest_ref_order(sc, ray, h);
-  }
-  return have;
-}
-
-__device__ inline bool any_wide(const DScene& sc, const Ray& ray) {
-  if (!sc.wide_ready) return false;
-  if (sc.n_box_shapes > kMaxBoxShapes) return any_ref_order(sc, ray);
-  const Octant q = make_octant(ray);
-  for (int i = 0; i < sc.n_box_shapes; i++) {  // see DBoxShape
-    const int4 b = __ldg(reinterpret_cast<const int4*>(sc.box_shapes) + i);
-    if (shape_hit(sc, b.x, b.y, ray) && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax)) return true;
-  }
-  const WideRay w = make_wide_ray(ray, q);
-  uint2 stack[kWideStack];
-  int sp = 0;
-  uint2 ngroup = make_uint2(0u, 0x80000000u);
-  while (true) {
-    uint2 tgroup;
-    if (ngroup.y > 0x00ffffffu) {
-      const uint32_t hits = ngroup.y, imask = hits & 0xffu;
-      const int bit = 31 - __clz(hits);
-      ngroup.y &= ~(1u << bit);
-      if (ngroup.y > 0x00ffffffu) {
-        if (sp < kWideStack) stack[sp++] = ngroup;
-        else return any_ref_order(sc, ray);  // cannot happen for sane trees; stay exact if it does
-      }
-      const uint32_t slot = uint32_t(bit - 24) ^ (w.octinv4 & 7u);
-      const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
-      uint32_t child_base, prim_base, cmask;
-      const uint32_t hm = test_node8(sc.nodes8, ngroup.x + rel, w, ray.tmin, ray.tmax, child_base, prim_base, cmask);
-      ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
-      tgroup = make_uint2(prim_base, hm & 0x00ffffffu);
-    } else {
-      tgroup = ngroup;
-      ngroup = make_uint2(0u, 0u);
-    }
-    while (tgroup.y) {
-      const int i = __ffs(tgroup.y) - 1;
-      tgroup.y &= tgroup.y - 1;
-      const PrimRec r = load_prim(sc.wide_prims, tgroup.x + i);
-      bool ok;
-      if (r.prim >= 0) ok = tri_hit(ray, r.v0, r.v1, r.v2);
-      else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: done above
-      else ok = shape_hit(sc, -1 - r.prim, __float_as_int(r.v0.x), ray);
-      if (ok && leaf_gate(sc.leaves, r.leaf, q, ray.tmin, ray.tmax)) return true;
-    }
-    if (ngroup.y <= 0x00ffffffu) {
-      if (sp == 0) break;
-      ngroup = stack[--sp];
-    }
-  }
-  return false;
-}
-
-// Production entry points: accel 0.
-__device__ __forceinline__ bool closest_production(const DScene& sc, Ray& ray, Hit& h) {
-  return sc.order_dependent ? closest_ref_order(sc, ray, h) : closest_wide(sc, ray, h);
 }
 
 }  // namespace pb2

@@ -65,13 +65,23 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
           have = false; ambiguous = false; tie_t = -1.0f; win_leaf = -1;
           h.geom = h.prim = -1;
           active = true;
-          if (ANY && sc.n_box_shapes) {  // see DBoxShape
-            bool occ = false;
-            for (int i = 0; i < sc.n_box_shapes && !occ; i++) {
+          if (sc.n_box_shapes) {  // see DBoxShape and traverse.cuh (iii)
+            bool touched = false;
+            for (int i = 0; i < sc.n_box_shapes && !touched; i++) {
               const int4 b = __ldg(reinterpret_cast<const int4*>(sc.box_shapes) + i);
-              occ = shape_hit(sc, b.x, b.y, ray) && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax);
+              if (ANY) {
+                touched = shape_hit(sc, b.x, b.y, ray);
+              } else {
+                Ray r2 = ray;
+                touched = shape_intersect(sc, b.x, b.y, r2);
+              }
+              touched = touched && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax);
             }
-            if (occ) { io.store_any(idx, true); active = false; }
+            if (touched) {
+              if (ANY) io.store_any(idx, true);
+              else wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
+              active = false;
+            }
           }
         }
       }
@@ -96,7 +106,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
       const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
       uint32_t child_base, prim_base, cmask;
       const uint32_t hm = test_node8(sc.nodes8, ngroup.x + rel, w, ray.tmin, ANY ? ray.tmax : slack_of(ray.tmax),
-                                     child_base, prim_base, cmask);
+                                     ANY ? ray.tmax : tmax_in, child_base, prim_base, cmask);
       ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
       tgroup = make_uint2(prim_base, hm & 0x00ffffffu);
     } else {
@@ -119,6 +129,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         r2.tmax = next_up(ray.tmax);  // lets t == current best through so that ties are seen
         bool ok;
         if (r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
+        else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: rays that touch one never get here
         else ok = shape_intersect(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
         if (ok) {
           if (r2.tmax < ray.tmax) {

@@ -90,6 +90,8 @@ class Backend:
     def upload_tables(self, spp):
         if spp in self._tables_loaded:
             return
+        if spp not in sampler_tables():  # BlueSobolSampler::spp() is a power of two <= 256 (sampler.cpp:115-121)
+            raise A.PineB200Error(-1, f"spp must be BlueSobolSampler::spp(): a power of two <= 256, got {spp}")
         sob, scr, rnk = sampler_tables()[spp]
         A.check(self.L.pb2_upload_sampler_tables(self.h, spp, sob.ctypes.data, scr.ctypes.data,
                                                  rnk.ctypes.data))
@@ -116,6 +118,27 @@ class Backend:
         p = self._params(spp, depth, rows, samples, accel, flags)
         A.check(self.L.pb2_render(self.h, C.byref(p), film.ctypes.data))
         return film
+
+    def render_recorded(self, spp, depth, accel=0, samples=None):
+        """Test hook: render (one wave) and return (film, record) where record holds every ray the
+        render traced: closest rays with (geom, prim, t) and shadow rays with their occlusion."""
+        w, h = self.size
+        cap = w * h * spp * depth
+        rec = A.RayRecord()
+        bufs = {"closest_rays": np.zeros((cap, 8), np.float32), "closest_t": np.zeros(cap, np.float32),
+                "closest_geom": np.zeros(cap, np.int32), "closest_prim": np.zeros(cap, np.int32),
+                "shadow_rays": np.zeros((cap, 8), np.float32), "shadow_occluded": np.zeros(cap, np.uint8)}
+        rec.capacity = cap
+        for k, v in bufs.items():
+            setattr(rec, k, v.ctypes.data)
+        A.check(self.L.pb2_set_ray_record(self.h, C.byref(rec)))
+        try:
+            film = self.render(spp, depth, accel=accel, samples=samples)
+        finally:
+            A.check(self.L.pb2_set_ray_record(self.h, None))
+        nc, ns = int(rec.n_closest), int(rec.n_shadow)
+        out = {k: (v[:ns] if k.startswith("shadow") else v[:nc]) for k, v in bufs.items()}
+        return film, out
 
     def render_device(self, spp, depth, rows=None, samples=None, accel=0, stream=None, flags=0):
         """-> device pointer (int) of the float4 film owned by the context."""

@@ -106,6 +106,30 @@ def test_film_matches_reference_at_equal_spp(golden, backends, name):
     assert abs(e_gpu - e_ref) <= 0.02 * e_ref + 1e-6
 
 
+@pytest.mark.parametrize("name", SCENES)
+def test_every_ray_of_a_render_matches_the_oracle(backends, name):
+    """All closest-hit and shadow rays a production render actually traces (pb2_set_ray_record):
+    the results the render used equal, bit for bit, the oracle's reference-order walk (CPU
+    restatement, oracle/oracle_port.cpp) and the device's own reference-order walk."""
+    from oracle import port
+    B = backends(name)
+    S = pb.Scene()
+    common.build(S, name)
+    _, _, spp, depth = common.SMALL_SCENES[name]
+    film, rec = B.render_recorded(spp, depth, accel=0)
+    assert np.array_equal(u32(film), u32(B.render(spp, depth)))
+    assert len(rec["closest_t"]) >= film.shape[0] * film.shape[1] * spp and len(rec["shadow_occluded"]) > 0
+    P = port.PortScene(S)
+    want = P.trace_closest(rec["closest_rays"])
+    assert np.array_equal(rec["closest_geom"], want["geom"])
+    assert np.array_equal(rec["closest_prim"], want["prim"])
+    assert np.array_equal(u32(rec["closest_t"]), u32(want["t"]))
+    assert np.array_equal(rec["shadow_occluded"], P.trace_any(rec["shadow_rays"])["occluded"])
+    dev = B.trace_closest(rec["closest_rays"], accel=1)
+    assert np.array_equal(rec["closest_geom"], dev["geom"]) and np.array_equal(u32(rec["closest_t"]), u32(dev["t"]))
+    assert np.array_equal(rec["shadow_occluded"], B.trace_any(rec["shadow_rays"], accel=1))
+
+
 @pytest.mark.parametrize("name", ["c1_64", "mesh_48"])
 def test_pixel_means_within_three_sigma(golden, backends, name):
     """|mean_gpu - mean_ref| <= 3 sigma per pixel and channel, sigma = standard error of the mean from
