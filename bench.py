@@ -185,9 +185,8 @@ def run_gpu(args):
     B.upload_scene(S)
     upload_s = time.perf_counter() - t0
     c0 = B.counters()
-    if spp % world:
-        raise SystemExit(f"spp={spp} is not divisible by {world} ranks")
-    samples = (rank * spp // world, (rank + 1) * spp // world)
+    from pine_b200.multigpu import sample_shards
+    samples = sample_shards(spp, world)[rank]  # contiguous sample range of this rank
     stream = torch.cuda.current_stream().cuda_stream
     TIME = 2  # PB2_RENDER_TIME_KERNELS
 

@@ -148,6 +148,9 @@ typedef struct pb2_render_params {
 } pb2_render_params;
 #define PB2_RENDER_SORT_BY_MATERIAL 1 /* bucket the shade queue by BxDF kind */
 #define PB2_RENDER_TIME_KERNELS 2     /* fill pb2_counters.last_{trace,shadow,shade,other}_ms */
+#define PB2_RENDER_KEEP_FILM 4        /* do not clear the device film first: rows outside
+                                       * [row_begin,row_end) keep what earlier calls rendered
+                                       * (row-band sharding issues one call per band) */
 
 typedef struct pb2_counters {
   uint64_t closest_rays, shadow_rays, camera_samples, kernel_launches; /* cumulative */
@@ -184,6 +187,9 @@ int pb2_restage_scene(pb2_context* ctx, void* cuda_stream);
  * sobol[256*256], scramble[128*128*8], rank[128*128*8]. */
 int pb2_upload_sampler_tables(pb2_context* ctx, int spp_pow2, const uint8_t* sobol,
                               const uint8_t* scramble, const uint8_t* rank);
+/* Same, read from the blob oracle/extract_tables.cpp extracts from those sources (path NULL or "" =
+ * pine_b200/data/bluesobol_tables.bin beside the library); what a C++ caller without the arrays uses. */
+int pb2_load_sampler_tables_file(pb2_context* ctx, const char* path, int spp_pow2);
 /* Replaces: PathIntegrator::render's pixel loop (path.cpp:31-40). film_rgba: caller-owned HOST
  * buffer of width*height*4 floats, row-major p.x + p.y*width (array.h:51-55), pre-tonemap. */
 int pb2_render(pb2_context* ctx, const pb2_render_params* params, float* film_rgba_host);

@@ -32,6 +32,8 @@
 #include <pine/impl/accel/bvh.cpp>
 #include <pine/impl/integrator/path.cpp>
 
+#include "../integration/cuda_path_integrator.h"
+
 #include <chrono>
 #include <cstdint>
 #include <cstring>
@@ -193,6 +195,30 @@ double ref_render(void* h, int sampler_kind, int spp, int depth, float* film_rgb
   if (film_rgba) {
     auto& film = S.scene.camera.film();
     std::memcpy(film_rgba, film.data(), sizeof(float) * 4 * size_t(film.width()) * film.height());
+  }
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+// The drop-in: the SAME pine::Scene rendered by pine::CudaPathIntegrator (integration/), constructed
+// with PathIntegrator's own argument list. Returns wall seconds; stats = {closest rays, shadow rays,
+// kernel launches, device ms}. Aborts through SEVERE like the reference on unsupported content.
+double ref_render_cuda(void* h, int spp, int depth, int device, float* film_rgba, double* stats) {
+  auto& S = *(RefScene*)h;
+  auto integrator = CudaPathIntegrator(Accel(BVH()), Sampler(BlueSobolSampler(spp)),
+                                       LightSampler(UniformLightSampler()), depth);
+  integrator.set_device(device);
+  auto t0 = std::chrono::steady_clock::now();
+  Integrator& base = integrator;  // through the virtual interface, as the PRL binding calls it
+  base.render(S.scene);
+  auto t1 = std::chrono::steady_clock::now();
+  if (film_rgba) {
+    auto& film = S.scene.camera.film();
+    std::memcpy(film_rgba, film.data(), sizeof(float) * 4 * size_t(film.width()) * film.height());
+  }
+  if (stats) {
+    stats[0] = double(integrator.last_closest_rays());
+    stats[1] = double(integrator.last_shadow_rays());
+    stats[2] = double(integrator.kernel_launches());
+    stats[3] = integrator.last_render_ms();
   }
   return std::chrono::duration<double>(t1 - t0).count();
 }

@@ -116,7 +116,7 @@ MATERIAL_KINDS = {"emissive": 0, "diffuse": 1, "metal": 2, "glossy": 3, "glass":
 ABI_SYMBOLS = [
     "pb2_last_error", "pb2_device_count", "pb2_create", "pb2_destroy", "pb2_upload_scene",
     "pb2_restage_scene",
-    "pb2_upload_sampler_tables", "pb2_render", "pb2_render_device", "pb2_film_finalize",
+    "pb2_upload_sampler_tables", "pb2_load_sampler_tables_file", "pb2_render", "pb2_render_device", "pb2_film_finalize",
     "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler",
     "pb2_test_primary_rays", "pb2_get_counters", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
     "pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone", "pb2h_make_triangle",

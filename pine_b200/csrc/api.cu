@@ -1,6 +1,9 @@
 // api.cu -- context lifetime, sampler tables, and the traversal test hooks of include/pine_b200.h.
+#include <dlfcn.h>
+#include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "context.h"
 #include "kernels.cuh"
@@ -82,6 +85,47 @@ extern "C" int pb2_upload_sampler_tables(pb2_context* ctx, int spp_pow2, const u
   ctx->has_tables[k] = true;
   if (ctx->tables_spp == spp_pow2) ctx->tables_spp = 0;  // force re-upload
   return PB2_OK;
+}
+
+// Reads one spp variant from the table blob oracle/extract_tables.cpp writes ("PB2BLUE1", u32 count,
+// then per variant u32 spp, u32 pad, sobol[65536], scramble[131072], rank[131072]) and registers it.
+// path NULL/"" = pine_b200/data/bluesobol_tables.bin next to this library.
+extern "C" int pb2_load_sampler_tables_file(pb2_context* ctx, const char* path, int spp_pow2) {
+  if (!ctx) { set_error("null argument"); return PB2_E_INVALID; }
+  int k = log2_exact(spp_pow2);
+  if (k < 0) { set_error("sampler tables exist for spp in {1,2,4,...,256} only"); return PB2_E_INVALID; }
+  if (ctx->has_tables[k]) return PB2_OK;
+  std::string file = path ? path : "";
+  if (file.empty()) {
+    Dl_info info;
+    if (!dladdr(reinterpret_cast<const void*>(&pb2_load_sampler_tables_file), &info) || !info.dli_fname) {
+      set_error("cannot locate libpine_b200.so to find data/bluesobol_tables.bin");
+      return PB2_E_STATE;
+    }
+    file = info.dli_fname;
+    size_t slash = file.rfind('/');
+    file = (slash == std::string::npos ? std::string(".") : file.substr(0, slash)) + "/../data/bluesobol_tables.bin";
+  }
+  FILE* f = std::fopen(file.c_str(), "rb");
+  if (!f) { set_error("cannot open sampler table file " + file); return PB2_E_INVALID; }
+  char magic[8];
+  uint32_t n = 0, pad = 0;
+  bool ok = std::fread(magic, 1, 8, f) == 8 && std::memcmp(magic, "PB2BLUE1", 8) == 0 &&
+            std::fread(&n, 4, 1, f) == 1 && std::fread(&pad, 4, 1, f) == 1;
+  int rc = PB2_E_INVALID;
+  std::vector<uint8_t> buf(65536 + 2 * 131072);
+  for (uint32_t i = 0; ok && i < n; i++) {
+    uint32_t spp = 0;
+    if (std::fread(&spp, 4, 1, f) != 1 || std::fread(&pad, 4, 1, f) != 1 ||
+        std::fread(buf.data(), 1, buf.size(), f) != buf.size()) break;
+    if (int(spp) == spp_pow2) {
+      rc = pb2_upload_sampler_tables(ctx, spp_pow2, buf.data(), buf.data() + 65536, buf.data() + 65536 + 131072);
+      break;
+    }
+  }
+  std::fclose(f);
+  if (rc == PB2_E_INVALID) set_error("sampler table file " + file + " is malformed or lacks spp=" + std::to_string(spp_pow2));
+  return rc;
 }
 
 // Makes the tables of `spp` the active device tables.

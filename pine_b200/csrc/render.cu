@@ -504,7 +504,9 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   const int n_samples = p->sample_end - p->sample_begin;
 
   PB2_CUDA_CHECK(ctx->film.reserve(size_t(W) * H * 16));
-  PB2_CUDA_CHECK(cudaMemsetAsync(ctx->film.ptr, 0, size_t(W) * H * 16, st));
+  if (!(p->flags & PB2_RENDER_KEEP_FILM) || ctx->film_pixels != size_t(W) * H)
+    PB2_CUDA_CHECK(cudaMemsetAsync(ctx->film.ptr, 0, size_t(W) * H * 16, st));
+  ctx->film_pixels = size_t(W) * H;
   if (film_rgba_device) *film_rgba_device = ctx->film.as<float>();
   ctx->counters.last_render_ms = 0;
   if (P == 0 || n_samples == 0) { PB2_CUDA_CHECK(cudaStreamSynchronize(st)); return PB2_OK; }

@@ -1,0 +1,84 @@
+"""Multi-GPU sharding of one `PathIntegrator::render`: one process per GPU, the scene
+replicated, (pixel, sample) work split, ONE reduce(sum) of the float film over NCCL at the end.
+
+Every (pixel, sample) of path.cpp:31-40 is independent and every pixel has one writer, so there is
+no exchange step inside the render; the only collective is the final film reduction.
+
+  * mode "samples" (BASELINE.json's C5): rank r renders samples [r*spp/G, (r+1)*spp/G) of every
+    pixel; its film holds sum/spp over its samples and alpha = n/spp, so the rank films ADD to the
+    full film. Per-pixel RNG streams are re-seeded per rank with hash(p, first_sample) -- the
+    reference's own `start_pixel(p, sample_index)` argument (sampler.h:286-289); fp32 sum order
+    differs from one GPU, so 1-GPU and G-GPU films agree to rounding, not bit for bit.
+  * mode "rows": the film is cut into bands of `band` rows dealt round-robin to the ranks (fine
+    interleave against the light-facing-region imbalance); every rank renders all samples of its
+    bands, other pixels stay 0, so the same reduce(sum) assembles a film that is BIT-IDENTICAL to
+    the single-GPU render.
+
+The plan functions are pure (tested on CPU); `ShardedRenderer` drives a `Backend` and reduces with
+`torch.distributed` (NCCL on GPUs; the gloo tests substitute a CPU film model for the backend).
+"""
+from . import _abi as A
+
+PB2_RENDER_KEEP_FILM = 4
+
+
+def sample_shards(spp, world):
+    """[(begin, end)] per rank; contiguous, covering [0, spp), sizes differ by at most one."""
+    if spp <= 0 or world <= 0:
+        raise ValueError("spp and world must be positive")
+    base, extra = divmod(spp, world)
+    out, b = [], 0
+    for r in range(world):
+        n = base + (1 if r < extra else 0)
+        out.append((b, b + n))
+        b += n
+    return out
+
+
+def row_bands(height, world, rank, band=16):
+    """[(row_begin, row_end)] of the bands dealt to `rank`: band k goes to rank k % world."""
+    if band <= 0:
+        raise ValueError("band must be positive")
+    n_bands = (height + band - 1) // band
+    return [(k * band, min(height, (k + 1) * band)) for k in range(rank, n_bands, world)]
+
+
+class ShardedRenderer:
+    """Renders this rank's share on its Backend and reduces the film to rank `dst`."""
+
+    def __init__(self, backend, rank, world, mode="samples", band=16, group=None):
+        if mode not in ("samples", "rows"):
+            raise ValueError("mode must be 'samples' or 'rows'")
+        self.backend, self.rank, self.world, self.mode, self.band, self.group = backend, rank, world, mode, band, group
+
+    def plan(self, spp):
+        """[(rows, samples, flags)] render calls of this rank."""
+        w, h = self.backend.size
+        if self.mode == "samples":
+            s = sample_shards(spp, self.world)[self.rank]
+            return [((0, h), s, 0)] if s[1] > s[0] else []
+        bands = row_bands(h, self.world, self.rank, self.band)
+        return [(b, (0, spp), PB2_RENDER_KEEP_FILM if i else 0) for i, b in enumerate(bands)]
+
+    def _partial(self, spp, depth, stream=None):
+        """This rank's film as a torch tensor [h, w, 4] on its device (zeros where not rendered)."""
+        import torch
+        w, h = self.backend.size
+        ptr = None
+        for rows, samples, flags in self.plan(spp):
+            ptr = self.backend.render_device(spp, depth, rows=rows, samples=samples, stream=stream, flags=flags)
+        if ptr is None:  # nothing dealt to this rank (more ranks than bands/samples)
+            return torch.zeros((h, w, 4), dtype=torch.float32, device=f"cuda:{self.backend.device}")
+
+        class _P:
+            __cuda_array_interface__ = {"shape": (h, w, 4), "typestr": "<f4", "data": (ptr, False),
+                                        "version": 3, "strides": None}
+        return torch.as_tensor(_P(), device=f"cuda:{self.backend.device}")
+
+    def render(self, spp, depth, dst=0, stream=None):
+        """-> the full film tensor on rank `dst` (other ranks get their partial back)."""
+        film = self._partial(spp, depth, stream)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM, group=self.group)
+        return film
