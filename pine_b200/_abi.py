@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libpine_b200.so")
+LIB_PATH = os.environ.get("PINE_B200_LIB") or os.path.join(HERE, "lib", "libpine_b200.so")  # env: tuning variants
 INCLUDE_DIR = os.path.join(os.path.dirname(HERE), "include")
 
 PB2_OK, PB2_E_INVALID, PB2_E_UNSUPPORTED, PB2_E_CUDA, PB2_E_STATE = 0, -1, -2, -3, -4

@@ -117,7 +117,7 @@ __device__ __forceinline__ bool bxdf_is_delta(const Bxdf& b) {
 }
 
 // psl::lerp(t, a, b) used by SampleWm: see pmath.h plerp (vecmath.h:873 / psl math.h:119)
-__device__ inline bool bxdf_sample(const DScene& sc, const Bxdf& b, BlueSampler& smp, BsdfSample& bs) {
+__device__ __forceinline__ bool bxdf_sample(const DScene& sc, const Bxdf& b, BlueSampler& smp, BsdfSample& bs) {
   const V3 wi = b.wi;
   bs.is_delta = false;
   bs.pdf = 0;
@@ -243,7 +243,7 @@ __device__ inline bool bxdf_sample(const DScene& sc, const Bxdf& b, BlueSampler&
   return false;
 }
 
-__device__ inline V3 bxdf_f(const Bxdf& b, V3 wo) {
+__device__ __forceinline__ V3 bxdf_f(const Bxdf& b, V3 wo) {
   const V3 wi = b.wi;
   const float alpha = sqr(b.roughness);
   TRDist d{alpha, alpha};
@@ -293,7 +293,7 @@ __device__ inline V3 bxdf_f(const Bxdf& b, V3 wo) {
   return V3();
 }
 
-__device__ inline float bxdf_pdf(const Bxdf& b, V3 wo) {
+__device__ __forceinline__ float bxdf_pdf(const Bxdf& b, V3 wo) {
   const V3 wi = b.wi;
   const float alpha = sqr(b.roughness);
   TRDist d{alpha, alpha};

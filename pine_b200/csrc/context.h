@@ -105,6 +105,7 @@ struct pb2_context {
   int tables_spp = 0;
   pb2::SamplerTables tables[9];  // index = log2(spp)
   bool has_tables[9] = {};
+  unsigned material_kinds = 0;        // bit k: some geometry uses pb2_material_kind k
   bool needs_rng_in_shading = false;  // Uber / Subsurface present (they draw randf(), material.cpp:9-28)
   int n_pixels = 0;
 

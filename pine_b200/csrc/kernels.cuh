@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
 #include "device_scene.h"
 
 struct pb2_context;
@@ -21,7 +23,17 @@ void launch_trace_any(const DScene& sc, const float* rays, size_t n, int accel, 
 
 constexpr int kNumSMs = 148;  // B200
 constexpr int kTraceBlock = 128;
-constexpr int kTraceBlocksPerSM = 6;  // persistent traversal grid = kNumSMs * kTraceBlocksPerSM
-inline int persistent_grid() { return kNumSMs * kTraceBlocksPerSM; }
+#ifndef PB2_TRACE_MINBLOCKS
+#define PB2_TRACE_MINBLOCKS 8  // __launch_bounds__ min blocks per SM of the persistent traversal kernels
+#endif
+constexpr int kTraceBlocksPerSM = PB2_TRACE_MINBLOCKS;  // persistent traversal grid = kNumSMs * this
+inline int persistent_grid() {
+  static const int per_sm = [] {
+    const char* v = std::getenv("PB2_TRACE_BLOCKS");  // tuning knob: resident blocks per SM
+    const int n = v ? std::atoi(v) : kTraceBlocksPerSM;
+    return n > 0 ? n : kTraceBlocksPerSM;
+  }();
+  return kNumSMs * per_sm;
+}
 
 }  // namespace pb2

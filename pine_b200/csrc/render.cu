@@ -47,6 +47,8 @@ struct WaveView {
                           // depth {closest cursor, closest fallbacks, shadow cursor, shadow fallbacks}
   int* fb_list;           // fallback list shared by the traversal kernels (used one at a time)
   uint8_t* occ;           // NULL unless a ray record is being taken
+  int* lists;             // shade lists: [list][n_slots] queue indices, one list per shading class
+  int list_of_class[8];   // class (0 = terminal, k = pb2_material_kind k) -> list number, -1 = absent
   int n_slots;            // capacity of this wave
   int pixels;             // pixels per sample layer in this wave
   int pixel0;             // first pixel (linear index in the row range) of this wave
@@ -57,7 +59,7 @@ struct WaveView {
 };
 
 struct WavefrontBuffers {
-  DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, rng, lacc, counts, fb_list, occ;
+  DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, rng, lacc, counts, fb_list, occ, lists;
   std::vector<int> host_counts;
   std::vector<cudaEvent_t> events;  // PB2_RENDER_TIME_KERNELS: one event between consecutive launches
   ~WavefrontBuffers() { for (cudaEvent_t e : events) cudaEventDestroy(e); }
@@ -173,7 +175,7 @@ __device__ __forceinline__ TraceIO trace_io(const WaveView& w, int depth) {
 __device__ __forceinline__ ShadowIO shadow_io(const WaveView& w, int depth) {
   return ShadowIO{w.sh_o, w.sh_d, w.vtx + size_t(depth) * w.n_slots * 2, w.occ};
 }
-__global__ void __launch_bounds__(kTraceBlock) k_trace(DScene sc, WaveView w, int depth) {
+__global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_trace(DScene sc, WaveView w, int depth) {
   wide_persistent<false>(sc, w.counts[depth], wave_queue(w, depth, 0), trace_io(w, depth));
 }
 __global__ void __launch_bounds__(kTraceBlock) k_trace_fallback(DScene sc, WaveView w, int depth) {
@@ -182,7 +184,7 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_fallback(DScene sc, WaveV
 __global__ void __launch_bounds__(kTraceBlock) k_trace_ref(DScene sc, WaveView w, int depth) {
   ref_order_all<false>(sc, w.counts[depth], trace_io(w, depth));
 }
-__global__ void __launch_bounds__(kTraceBlock) k_shadow(DScene sc, WaveView w, int depth) {
+__global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_shadow(DScene sc, WaveView w, int depth) {
   wide_persistent<true>(sc, w.counts[w.max_depth + 1 + depth], wave_queue(w, depth, 1), shadow_io(w, depth));
 }
 __global__ void __launch_bounds__(kTraceBlock) k_shadow_fallback(DScene sc, WaveView w, int depth) {
@@ -198,31 +200,29 @@ __device__ __forceinline__ bool with_probability(float prob, Rng& g) {  // sampl
   if (prob == 1) return true;
   return rng_nextf(g) < prob;
 }
-__device__ inline Bxdf material_bxdf(const DScene& sc, const pb2_material& m, V3 wi_world, V3 n,
-                                     float min_roughness, bool diffused, BlueSampler& smp, Rng& g) {
+template <int MAT>
+__device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_material& m, V3 wi_world, V3 n,
+                                              float min_roughness, bool diffused, BlueSampler& smp, Rng& g) {
   Bxdf b;
   b.albedo = V3(m.color[0], m.color[1], m.color[2]);
   b.roughness = m.roughness;
   b.ior = m.ior;
   b.sigma_s = V3(m.sigma_s[0], m.sigma_s[1], m.sigma_s[2]);
   b.kind = BX_DIFFUSE;
-  switch (m.kind) {
-    case PB2_MAT_DIFFUSE: b.kind = BX_DIFFUSE; break;
-    case PB2_MAT_METAL: b.kind = BX_CONDUCTOR; b.roughness = pmax(m.roughness, min_roughness); break;
-    case PB2_MAT_GLOSSY: b.kind = BX_DIFF_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); break;
-    case PB2_MAT_GLASS: b.kind = BX_REFR_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); break;
-    case PB2_MAT_UBER:
-      if (with_probability(m.metallic, g)) b.kind = BX_CONDUCTOR;
-      else if (with_probability(m.transmission, g)) b.kind = BX_REFR_DIELECTRIC;
-      else b.kind = BX_DIFF_DIELECTRIC;
-      break;
-    case PB2_MAT_SUBSURFACE: {
-      b.ior = 1.4f;  // SubsurfaceMaterial::ior (material.h:103)
-      float fr = FrDielectric(dot(wi_world, n), b.ior);
-      if (blue_get1d(sc, smp) < fr) { b.kind = BX_REFRACTIVE; b.roughness = pmax(m.roughness, min_roughness); }
-      else if (diffused) b.kind = BX_DIFFUSE;
-      else b.kind = BX_BSSRDF;
-    } break;
+  if (MAT == PB2_MAT_METAL) { b.kind = BX_CONDUCTOR; b.roughness = pmax(m.roughness, min_roughness); }
+  if (MAT == PB2_MAT_GLOSSY) { b.kind = BX_DIFF_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); }
+  if (MAT == PB2_MAT_GLASS) { b.kind = BX_REFR_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); }
+  if (MAT == PB2_MAT_UBER) {
+    if (with_probability(m.metallic, g)) b.kind = BX_CONDUCTOR;
+    else if (with_probability(m.transmission, g)) b.kind = BX_REFR_DIELECTRIC;
+    else b.kind = BX_DIFF_DIELECTRIC;
+  }
+  if (MAT == PB2_MAT_SUBSURFACE) {
+    b.ior = 1.4f;  // SubsurfaceMaterial::ior (material.h:103)
+    float fr = FrDielectric(dot(wi_world, n), b.ior);
+    if (blue_get1d(sc, smp) < fr) { b.kind = BX_REFRACTIVE; b.roughness = pmax(m.roughness, min_roughness); }
+    else if (diffused) b.kind = BX_DIFFUSE;
+    else b.kind = BX_BSSRDF;
   }
   return b;
 }
@@ -286,17 +286,89 @@ __device__ __forceinline__ void store_vertex(const WaveView& w, int depth, int s
   v[1] = make_float4(f.x, f.y, f.z, __int_as_float(beta_code));
 }
 
-__global__ void __launch_bounds__(128) k_shade(DScene sc, WaveView w, int depth) {
+// The shade queue is bucketed by shading class first (k_classify): class 0 = the path ends at this
+// vertex (miss, emitter, or depth cut: path.cpp:56-66,89), class k = pb2_material_kind k. Each class
+// then runs its own kernel, compiled with only that material's BxDF code: one kernel for all
+// materials was 315 KB of SASS running at 8.5 of 32 lanes and stalled on instruction fetch
+// (profiles/r1), because neighbouring rays hit different materials.
+__device__ __forceinline__ int* list_count(const WaveView& w, int depth, int cls) {
+  return w.counts + 6 * (w.max_depth + 1) + 8 * depth + cls;
+}
+__global__ void __launch_bounds__(256) k_classify(DScene sc, WaveView w, int depth) {
   const int n = w.counts[depth];
+  const unsigned lane = threadIdx.x & 31u;
+  PB2_WARP_LOOP(i, n) {
+    int cls = -1;
+    if (i < n) {
+      const int geom = __float_as_int(w.hit[i].y);
+      cls = 0;
+      if (geom >= 0 && depth + 1 < w.max_depth) {  // Vertex::length == depth on this queue
+        const int kind = sc.materials[sc.geoms[geom].material].kind;
+        if (kind != PB2_MAT_EMISSIVE) cls = kind;
+      }
+    }
+    const unsigned peers = __match_any_sync(0xffffffffu, cls);
+    const int leader = __ffs(peers) - 1;
+    int base = 0;
+    if (cls >= 0 && int(lane) == leader) base = atomicAdd(list_count(w, depth, cls), __popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (cls >= 0)
+      w.lists[size_t(w.list_of_class[cls]) * w.n_slots + base + __popc(peers & ((1u << lane) - 1u))] = i;
+  }
+}
+
+// class 0: emitted radiance seen by this vertex, or nothing (path.cpp:56-66)
+__global__ void __launch_bounds__(256) k_shade_terminal(DScene sc, WaveView w, int depth) {
+  const int n = *list_count(w, depth, 0);
+  const int cur = depth & 1;
+  const int* list = w.lists + size_t(w.list_of_class[0]) * w.n_slots;
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+    const int i = list[j];
+    const float4 b = w.ray_d[cur][i], hrec = w.hit[i];
+    const int slot = __float_as_int(b.w);
+    const int geom = __float_as_int(hrec.y);
+    V3 X(0.0f);
+    if (geom >= 0) {
+      const DGeom g = sc.geoms[geom];
+      const pb2_material m = sc.materials[g.material];
+      if (m.kind == PB2_MAT_EMISSIVE) {
+        const float4 a = w.ray_o[cur][i];
+        const V3 ro(a.x, a.y, a.z), rd(b.x, b.y, b.z);
+        const V3 wi = -rd;
+        const float t = hrec.x;
+        Surf it;
+        surface_info(sc, geom, __float_as_int(hrec.z), ro + t * rd, it);
+        // Lo += Tr * le; light_pdf = light_sampler.pdf(ray, it) unless the previous vertex was delta
+        if (!(dot(wi, it.n) < 0.0f)) X = V3(1.0f) * V3(m.color[0], m.color[1], m.color[2]);
+        const bool pv_delta = (w.pv_flags[slot] >> 16) & 1;
+        if (!pv_delta && depth > 0) {
+          float light_pdf = shape_pdf(sc, geom, ro, rd, t, it.n) / float(sc.n_lights);
+          float bs_pdf = w.pv_pdf[slot];
+          float mis = balance_heuristic(bs_pdf, light_pdf);
+          float4* v = w.vtx + (size_t(depth - 1) * w.n_slots + slot) * 2;
+          v[0].w = v[0].w * mis;  // s = cosine / bs.pdf * mis
+        }
+      }
+    }
+    w.term[slot] = make_float4(X.x, X.y, X.z, __int_as_float(depth));
+  }
+}
+
+// class MAT: NEE + BSDF sample at a surface vertex (path.cpp:74-120)
+template <int MAT>
+__global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int depth) {
+  const int n = *list_count(w, depth, MAT);
   const int cur = depth & 1, nxt = cur ^ 1;
   int* next_count = w.counts + depth + 1;
   int* shadow_count = w.counts + w.max_depth + 1 + depth;
-  PB2_WARP_LOOP(i, n) {
-    const bool valid = i < n;
+  const int* list = w.lists + size_t(w.list_of_class[MAT]) * w.n_slots;
+  PB2_WARP_LOOP(j, n) {
+    const bool valid = j < n;
     bool emit_next = false, emit_shadow = false;
     Ray next_ray, shadow_ray;
     int slot = 0;
     if (valid) {
+      const int i = list[j];
       float4 a = w.ray_o[cur][i], b = w.ray_d[cur][i], hrec = w.hit[i];
       V3 ro(a.x, a.y, a.z), rd(b.x, b.y, b.z);
       slot = __float_as_int(b.w);
@@ -304,97 +376,76 @@ __global__ void __launch_bounds__(128) k_shade(DScene sc, WaveView w, int depth)
       const int geom = __float_as_int(hrec.y), prim = __float_as_int(hrec.z);
       const int flags = w.pv_flags[slot];
       const int pv_length = flags & 0xff, pv_diffuse = (flags >> 8) & 0xff;
-      const bool pv_delta = (flags >> 16) & 1;
       const V3 wi = -rd;
-      // terminal radiance of this path (if it ends here) and number of vertex records so far
-      V3 X(0.0f);
-      bool terminated = true;
-      if (geom >= 0) {
-        Surf it;
-        surface_info(sc, geom, prim, ro + t * rd, it);
-        const DGeom g = sc.geoms[geom];
-        const pb2_material m = sc.materials[g.material];
-        if (m.kind == PB2_MAT_EMISSIVE) {
-          // Lo += Tr * le; light_pdf = light_sampler.pdf(ray, it) unless the previous vertex was delta
-          if (!(dot(wi, it.n) < 0.0f)) X = V3(1.0f) * V3(m.color[0], m.color[1], m.color[2]);
-          if (!pv_delta && depth > 0) {
-            float light_pdf = shape_pdf(sc, geom, ro, rd, t, it.n) / float(sc.n_lights);
-            float bs_pdf = w.pv_pdf[slot];
-            float mis = balance_heuristic(bs_pdf, light_pdf);
-            float4* v = w.vtx + (size_t(depth - 1) * w.n_slots + slot) * 2;
-            v[0].w = v[0].w * mis;  // s = cosine / bs.pdf * mis
+      Surf it;
+      surface_info(sc, geom, prim, ro + t * rd, it);
+      const DGeom g = sc.geoms[geom];
+      const pb2_material m = sc.materials[g.material];
+      int pix = w.pixel0 + slot % w.pixels;
+      int px = pix % w.width, py = w.row_begin + pix / w.width;
+      BlueSampler smp{px, py, w.sample0 + slot / w.pixels, w.dim[slot]};
+      Rng g_rng;
+      constexpr bool uses_rng = MAT == PB2_MAT_UBER || MAT == PB2_MAT_SUBSURFACE;
+      if (uses_rng) g_rng = load_rng(w.rng, pix);
+      const bool diffused = pv_diffuse > 0;
+      Bxdf bx = material_bxdf<MAT>(sc, m, wi, it.n, diffused ? 0.6f : 0.0f, diffused, smp, g_rng);
+      M3 l2w = coordinate_system(it.n);
+      M3 w2l = transpose(l2w);
+      bx.wi = w2l * wi;
+      int beta_code = 0;
+      if constexpr (MAT == PB2_MAT_SUBSURFACE) {
+        if (bx.kind == BX_BSSRDF) {
+          V3 beta, wi2;
+          if (bssrdf_walk(sc, bx, geom, wi, it, smp, g_rng, beta, wi2)) {
+            beta_code = beta.x != 0 ? 1 : (beta.y != 0 ? 2 : 3);
+            l2w = coordinate_system(it.n);
+            w2l = transpose(l2w);
+            bx.wi = w2l * wi2;
           }
-        } else if (pv_length + 1 < w.max_depth) {
-          terminated = false;
-          int pix = w.pixel0 + slot % w.pixels;
-          int px = pix % w.width, py = w.row_begin + pix / w.width;
-          BlueSampler smp{px, py, w.sample0 + slot / w.pixels, w.dim[slot]};
-          Rng g_rng;
-          const bool uses_rng = m.kind == PB2_MAT_UBER || m.kind == PB2_MAT_SUBSURFACE;
-          if (uses_rng) g_rng = load_rng(w.rng, pix);
-          const bool diffused = pv_diffuse > 0;
-          Bxdf bx = material_bxdf(sc, m, wi, it.n, diffused ? 0.6f : 0.0f, diffused, smp, g_rng);
-          M3 l2w = coordinate_system(it.n);
-          M3 w2l = transpose(l2w);
-          bx.wi = w2l * wi;
-          int beta_code = 0;
-          bool alive = true;
-          if (bx.kind == BX_BSSRDF) {
-            V3 beta, wi2;
-            if (bssrdf_walk(sc, bx, geom, wi, it, smp, g_rng, beta, wi2)) {
-              beta_code = beta.x != 0 ? 1 : (beta.y != 0 ? 2 : 3);
-              l2w = coordinate_system(it.n);
-              w2l = transpose(l2w);
-              bx.wi = w2l * wi2;
-            }
-          }
-          if (uses_rng) store_rng(w.rng, pix, g_rng);
-          // next-event estimation (path.cpp:98-113); draws get2d then get1d (g++ evaluates the
-          // arguments of light_sampler.sample(p, get1d(), get2d()) right to left, lightsampler.h:27)
-          V3 nee(0.0f);
-          if (!bxdf_is_delta(bx)) {
-            V2 u2 = blue_get2d(sc, smp);
-            float u1 = blue_get1d(sc, smp);
-            if (sc.n_lights > 0) {
-              u1 *= sc.n_lights;
-              int index = int(u1);
-              int lgeom = sc.lights[index];
-              ShapeSample ss;
-              if (shape_sample(sc, lgeom, it.p, u2, u1 - index, ss)) {
-                const pb2_material lm = sc.materials[sc.geoms[lgeom].material];
-                V3 le = dot(-ss.w, ss.n) < 0.0f ? V3(0.0f) : V3(lm.color[0], lm.color[1], lm.color[2]);
-                if (!is_zero(le)) {
-                  float ls_pdf = ss.pdf / sc.n_lights;
-                  float cosine = absdot(ss.w, it.n);
-                  V3 wo = w2l * ss.w;
-                  V3 f = bxdf_f(bx, wo);
-                  float mis = balance_heuristic(ls_pdf, bxdf_pdf(bx, wo));
-                  nee = le * V3(1.0f) * cosine * f / ls_pdf * mis;
-                  shadow_ray = spawn_ray(it.p, it.n, ss.w, ss.distance);
-                  emit_shadow = true;
-                }
-              }
-            }
-          }
-          BsdfSample bs;
-          if (bxdf_sample(sc, bx, smp, bs)) {
-            V3 wo_world = l2w * bs.wo;
-            float cosine = absdot(wo_world, it.n);
-            store_vertex(w, depth, slot, nee, cosine / bs.pdf * 1.0f, bs.f, beta_code);
-            next_ray = spawn_ray(it.p, it.n, wo_world);
-            emit_next = true;
-            w.pv_pdf[slot] = bs.pdf;
-            w.pv_flags[slot] = (pv_length + 1) | ((pv_diffuse + (bs.is_delta ? 0 : 1)) << 8) | (int(bs.is_delta) << 16);
-          } else {
-            store_vertex(w, depth, slot, nee, 0.0f, V3(0.0f), beta_code);
-            alive = false;
-          }
-          w.dim[slot] = smp.dim;
-          w.term[slot] = make_float4(0, 0, 0, __int_as_float(depth + 1));
-          (void)alive;
         }
       }
-      if (terminated) w.term[slot] = make_float4(X.x, X.y, X.z, __int_as_float(depth));
+      if (uses_rng) store_rng(w.rng, pix, g_rng);
+      // next-event estimation (path.cpp:98-113); draws get2d then get1d (g++ evaluates the
+      // arguments of light_sampler.sample(p, get1d(), get2d()) right to left, lightsampler.h:27)
+      V3 nee(0.0f);
+      if (!bxdf_is_delta(bx)) {
+        V2 u2 = blue_get2d(sc, smp);
+        float u1 = blue_get1d(sc, smp);
+        if (sc.n_lights > 0) {
+          u1 *= sc.n_lights;
+          int index = int(u1);
+          int lgeom = sc.lights[index];
+          ShapeSample ss;
+          if (shape_sample(sc, lgeom, it.p, u2, u1 - index, ss)) {
+            const pb2_material lm = sc.materials[sc.geoms[lgeom].material];
+            V3 le = dot(-ss.w, ss.n) < 0.0f ? V3(0.0f) : V3(lm.color[0], lm.color[1], lm.color[2]);
+            if (!is_zero(le)) {
+              float ls_pdf = ss.pdf / sc.n_lights;
+              float cosine = absdot(ss.w, it.n);
+              V3 wo = w2l * ss.w;
+              V3 f = bxdf_f(bx, wo);
+              float mis = balance_heuristic(ls_pdf, bxdf_pdf(bx, wo));
+              nee = le * V3(1.0f) * cosine * f / ls_pdf * mis;
+              shadow_ray = spawn_ray(it.p, it.n, ss.w, ss.distance);
+              emit_shadow = true;
+            }
+          }
+        }
+      }
+      BsdfSample bs;
+      if (bxdf_sample(sc, bx, smp, bs)) {
+        V3 wo_world = l2w * bs.wo;
+        float cosine = absdot(wo_world, it.n);
+        store_vertex(w, depth, slot, nee, cosine / bs.pdf * 1.0f, bs.f, beta_code);
+        next_ray = spawn_ray(it.p, it.n, wo_world);
+        emit_next = true;
+        w.pv_pdf[slot] = bs.pdf;
+        w.pv_flags[slot] = (pv_length + 1) | ((pv_diffuse + (bs.is_delta ? 0 : 1)) << 8) | (int(bs.is_delta) << 16);
+      } else {
+        store_vertex(w, depth, slot, nee, 0.0f, V3(0.0f), beta_code);
+      }
+      w.dim[slot] = smp.dim;
+      w.term[slot] = make_float4(0, 0, 0, __int_as_float(depth + 1));
     }
     int pos = warp_compact(emit_next, next_count);
     if (emit_next) {
@@ -540,7 +591,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   const int n_pixel_waves = int((P + pixels_per_wave - 1) / pixels_per_wave);
   const int n_sample_waves = (n_samples + s_batch - 1) / s_batch;
   const int n_waves = n_pixel_waves * n_sample_waves;
-  const int cstride = 6 * (D + 1);
+  const int cstride = 14 * (D + 1);  // + 8 shade-list counters per depth
   PB2_CUDA_CHECK(B.fb_list.reserve(size_t(n_slots) * 4));
   PB2_CUDA_CHECK(B.counts.reserve(size_t(n_waves) * cstride * 4));
   PB2_CUDA_CHECK(cudaMemsetAsync(B.counts.ptr, 0, size_t(n_waves) * cstride * 4, st));
@@ -551,6 +602,14 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   }
 
   WaveView w{};
+  // shade lists: class 0 always, plus one per material kind some geometry uses
+  int n_lists = 0;
+  for (int c = 0; c < 8; c++) w.list_of_class[c] = -1;
+  w.list_of_class[0] = n_lists++;
+  for (int k = 1; k < 8; k++)
+    if (ctx->material_kinds & (1u << k)) w.list_of_class[k] = n_lists++;
+  PB2_CUDA_CHECK(B.lists.reserve(size_t(n_lists) * n_slots * 4));
+  w.lists = B.lists.as<int>();
   w.occ = rec ? B.occ.as<uint8_t>() : nullptr;
   for (int k = 0; k < 2; k++) { w.ray_o[k] = B.ray_o[k].as<float4>(); w.ray_d[k] = B.ray_d[k].as<float4>(); }
   w.hit = B.hit.as<float4>(); w.sh_o = B.sh_o.as<float4>(); w.sh_d = B.sh_d.as<float4>();
@@ -640,8 +699,20 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
         }
         mark(0);
         if (rec && (rc = record(false, depth))) return rc;
-        k_shade<<<sm_grid(live, 128, 16), 128, 0, st>>>(sc, w, depth);
-        launches++; mark(2);
+        k_classify<<<sm_grid(live, 256, 8), 256, 0, st>>>(sc, w, depth);
+        k_shade_terminal<<<sm_grid(live, 256, 8), 256, 0, st>>>(sc, w, depth);
+        launches += 2;
+        if (depth + 1 < D) {
+          const int sg = sm_grid(live, 128, 16);
+          const unsigned mk = ctx->material_kinds;
+          if (mk & (1u << PB2_MAT_DIFFUSE)) { k_shade_mat<PB2_MAT_DIFFUSE><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
+          if (mk & (1u << PB2_MAT_METAL)) { k_shade_mat<PB2_MAT_METAL><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
+          if (mk & (1u << PB2_MAT_GLOSSY)) { k_shade_mat<PB2_MAT_GLOSSY><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
+          if (mk & (1u << PB2_MAT_GLASS)) { k_shade_mat<PB2_MAT_GLASS><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
+          if (mk & (1u << PB2_MAT_UBER)) { k_shade_mat<PB2_MAT_UBER><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
+          if (mk & (1u << PB2_MAT_SUBSURFACE)) { k_shade_mat<PB2_MAT_SUBSURFACE><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
+        }
+        mark(2);
         if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
           if (any_wide_ok) {
             k_shadow<<<pgrid, kTraceBlock, 0, st>>>(sc, w, depth);

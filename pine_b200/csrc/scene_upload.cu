@@ -57,6 +57,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
 
   std::vector<DGeom> geoms(sd->n_geometries);
   ctx->needs_rng_in_shading = false;
+  ctx->material_kinds = 0;
   for (uint32_t i = 0; i < sd->n_geometries; i++) {
     const pb2_geometry& g = sd->geometries[i];
     if (g.shape_kind < 0 || g.shape_kind > PB2_SHAPE_MESH) {
@@ -75,6 +76,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
       return PB2_E_UNSUPPORTED;
     }
     if (m.kind == PB2_MAT_UBER || m.kind == PB2_MAT_SUBSURFACE) ctx->needs_rng_in_shading = true;
+    ctx->material_kinds |= 1u << m.kind;
     geoms[i] = DGeom{g.shape_kind, g.shape_index, g.material, -1};
   }
   std::vector<int32_t> lights(sd->light_geometries, sd->light_geometries + sd->n_lights);

@@ -43,7 +43,7 @@ struct HookIO {
 };
 
 template <bool ANY>
-__global__ void __launch_bounds__(kTraceBlock) k_hook_wide(DScene sc, int n, WideQueue wq, HookIO io) {
+__global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_hook_wide(DScene sc, int n, WideQueue wq, HookIO io) {
   wide_persistent<ANY>(sc, n, wq, io);
 }
 template <bool ANY>

@@ -26,6 +26,16 @@ struct WideQueue {
   int* fb_list;   // queue indices that need the reference-order walk
 };
 
+// Scheduling inside a warp (measured on B200, see DESIGN.md "what did not work"). One iteration =
+// at most one wide-node test per lane, then primitive tests. After a node test only ~3 of 32 lanes
+// of an incoherent warp own primitives, so those lanes test ONE primitive and go back to walking
+// with the rest (a lane's remaining primitives wait in `tgroup`); when at least half the warp owns
+// primitives (coherent rays, small scenes) every lane drains its whole group in a tight loop.
+// Making lanes WAIT until a batch of primitive owners has formed was tried and lost 7% (fewer
+// walking lanes per node test); `prefetch.global.L1` of the next primitive record gained 1.6% on
+// the 10 M-triangle scene and cost 2x on scenes that live in L1, so neither is here.
+// The order in which a ray's primitives are tested does not matter for the result (ties are
+// detected and sent to the fallback, see traverse.cuh).
 template <bool ANY, class IO>
 __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQueue wq, const IO& io) {
   const unsigned lane = threadIdx.x & 31u;
@@ -36,7 +46,8 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
   Ray ray;
   Octant q;
   WideRay w;
-  uint2 ngroup = make_uint2(0u, 0u);
+  uint2 ngroup = make_uint2(0u, 0u);  // invariant while walking: has a node bit (y > 0x00ffffff)
+  uint2 tgroup = make_uint2(0u, 0u);  // primitives waiting to be tested (y = 24-bit mask)
   bool have = false, ambiguous = false;
   float tie_t = -1.0f, tmax_in = 0.0f;
   int win_leaf = -1;
@@ -61,6 +72,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
           w = make_wide_ray(ray, q);
           tmax_in = ray.tmax;
           ngroup = make_uint2(0u, 0x80000000u);
+          tgroup = make_uint2(0u, 0u);
           sp = 0;
           have = false; ambiguous = false; tie_t = -1.0f; win_leaf = -1;
           h.geom = h.prim = -1;
@@ -90,11 +102,11 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
       if (drained) break;
       continue;
     }
-    if (!active) continue;
 
-    // ---- one step ----
-    uint2 tgroup;
-    if (ngroup.y > 0x00ffffffu) {
+    bool done = false;
+    // ---- node step: every lane that has no primitives left to test ----
+    const bool walking = active && tgroup.y == 0u;
+    if (walking) {
       const uint32_t hits = ngroup.y, imask = hits & 0xffu;
       const int bit = 31 - __clz(hits);
       ngroup.y &= ~(1u << bit);
@@ -109,41 +121,48 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
                                      ANY ? ray.tmax : tmax_in, child_base, prim_base, cmask);
       ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
       tgroup = make_uint2(prim_base, hm & 0x00ffffffu);
-    } else {
-      tgroup = ngroup;
-      ngroup = make_uint2(0u, 0u);
-    }
-    bool done = ambiguous;
-    while (tgroup.y && !done) {
-      const int i = __ffs(tgroup.y) - 1;
-      tgroup.y &= tgroup.y - 1;
-      const PrimRec r = load_prim(sc.wide_prims, tgroup.x + i);
-      if (ANY) {
-        bool ok;
-        if (r.prim >= 0) ok = tri_hit(ray, r.v0, r.v1, r.v2);
-        else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: tested at refill
-        else ok = shape_hit(sc, -1 - r.prim, __float_as_int(r.v0.x), ray);
-        if (ok && leaf_gate(sc.leaves, r.leaf, q, ray.tmin, ray.tmax)) { have = true; done = true; }
-      } else {
-        Ray r2 = ray;
-        r2.tmax = next_up(ray.tmax);  // lets t == current best through so that ties are seen
-        bool ok;
-        if (r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
-        else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: rays that touch one never get here
-        else ok = shape_intersect(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
-        if (ok) {
-          if (r2.tmax < ray.tmax) {
-            ray.tmax = r2.tmax; h.geom = r.geom; h.prim = r.prim >= 0 ? r.prim : 0; win_leaf = r.leaf; have = true;
-          } else if (r2.tmax == ray.tmax) {
-            if (have) tie_t = r2.tmax;
-            else { ambiguous = true; done = true; }
-          }
-        }
+      if (ambiguous) {
+        done = true;
+      } else if (tgroup.y == 0u && ngroup.y <= 0x00ffffffu) {
+        if (sp == 0) done = true;
+        else ngroup = stack[--sp];
       }
     }
-    if (!done && ngroup.y <= 0x00ffffffu) {
-      if (sp == 0) done = true;
-      else ngroup = stack[--sp];
+    // ---- primitive step ----
+    const bool owns = active && !done && tgroup.y != 0u;
+    const bool tight = __popc(__ballot_sync(0xffffffffu, owns)) >= 16;
+    if (owns) {
+      do {
+        const int i = __ffs(tgroup.y) - 1;
+        tgroup.y &= tgroup.y - 1;
+        const PrimRec r = load_prim(sc.wide_prims, tgroup.x + i);
+        if (ANY) {
+          bool ok;
+          if (r.prim >= 0) ok = tri_hit(ray, r.v0, r.v1, r.v2);
+          else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: tested at refill
+          else ok = shape_hit(sc, -1 - r.prim, __float_as_int(r.v0.x), ray);
+          if (ok && leaf_gate(sc.leaves, r.leaf, q, ray.tmin, ray.tmax)) { have = true; done = true; }
+        } else {
+          Ray r2 = ray;
+          r2.tmax = next_up(ray.tmax);  // lets t == current best through so that ties are seen
+          bool ok;
+          if (r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
+          else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: rays that touch one never get here
+          else ok = shape_intersect(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
+          if (ok) {
+            if (r2.tmax < ray.tmax) {
+              ray.tmax = r2.tmax; h.geom = r.geom; h.prim = r.prim >= 0 ? r.prim : 0; win_leaf = r.leaf; have = true;
+            } else if (r2.tmax == ray.tmax) {
+              if (have) tie_t = r2.tmax;
+              else { ambiguous = true; done = true; }
+            }
+          }
+        }
+      } while (tight && tgroup.y != 0u && !done);
+      if (!done && tgroup.y == 0u && ngroup.y <= 0x00ffffffu) {  // back to walking: restore the invariant
+        if (sp == 0) done = true;
+        else ngroup = stack[--sp];
+      }
     }
     if (done) {
       if (ANY) {
@@ -158,6 +177,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         else io.store_closest(sc, idx, ray, have, h);
       }
       active = false;
+      tgroup.y = 0u;
     }
   }
 }
