@@ -166,6 +166,8 @@ typedef struct pb2_counters {
   double upload_ms;       /* host wall time of the last host->device staging of the scene */
   uint64_t scene_bytes;   /* bytes that staging copies */
   uint32_t bvh2_nodes, wide_nodes, n_primitives, build_threads;
+  /* rays of the last render the wide walk could not certify and re-traced in reference order */
+  uint64_t last_closest_fallbacks, last_shadow_fallbacks;
 } pb2_counters;
 
 typedef struct pb2_context pb2_context;
@@ -229,6 +231,9 @@ int pb2_test_sampler(pb2_context* ctx, int spp, int px, int py, int sample_index
                      float* out_rand, const char* pattern, int n_samples, float* out_draws);
 int pb2_test_primary_rays(pb2_context* ctx, int sample_index, float* rays_host);
 int pb2_get_counters(pb2_context* ctx, pb2_counters* out);
+/* Debug hook (meaningful in -DPB2_COUNT tuning builds only; zeros otherwise): wide-walk node and
+ * primitive tests since the last call, see pine_b200/csrc/api.cu. */
+int pb2_debug_walk_stats(pb2_context* ctx, uint64_t* out10);
 /* Dump of the host-built reference-order binary tree (which=-1 top level, k = k-th mesh tree) in
  * the layout of oracle/ref_harness.cpp:ref_bvh_nodes, to pin the builder node for node. */
 int pb2_bvh_info(pb2_context* ctx, int which, int32_t* n_nodes, int32_t* root,

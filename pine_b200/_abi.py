@@ -104,7 +104,8 @@ class Counters(C.Structure):
                 ("bvh_build_ms", C.c_double), ("upload_ms", C.c_double),
                 ("scene_bytes", C.c_uint64), ("bvh2_nodes", C.c_uint32),
                 ("wide_nodes", C.c_uint32), ("n_primitives", C.c_uint32),
-                ("build_threads", C.c_uint32)]
+                ("build_threads", C.c_uint32), ("last_closest_fallbacks", C.c_uint64),
+                ("last_shadow_fallbacks", C.c_uint64)]
 
 
 SHAPE_KINDS = {"aabb": 0, "obb": 1, "sphere": 2, "triangle": 3, "cone": 4, "rect": 5, "disk": 6,
@@ -118,7 +119,7 @@ ABI_SYMBOLS = [
     "pb2_restage_scene",
     "pb2_upload_sampler_tables", "pb2_load_sampler_tables_file", "pb2_render", "pb2_render_device", "pb2_film_finalize",
     "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler",
-    "pb2_test_primary_rays", "pb2_get_counters", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
+    "pb2_test_primary_rays", "pb2_get_counters", "pb2_debug_walk_stats", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
     "pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone", "pb2h_make_triangle",
     "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_round_spp",
 ]

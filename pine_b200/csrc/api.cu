@@ -221,6 +221,19 @@ extern "C" int pb2_set_ray_record(pb2_context* ctx, pb2_ray_record* rec) {
   return PB2_OK;
 }
 
+// Debug hook of -DPB2_COUNT builds (scripts/gpu_variants.sh): wide-walk work counters since the last
+// call: {closest node tests, closest primitive tests, any-hit node tests, any-hit primitive tests,
+// closest rays, any-hit rays, closest fallbacks by reason: box shape touched, tie/stack during the walk,
+// tie with the winner, winner's leaf gate failed} = 10 values. In the product build the kernels do not count and this returns zeros.
+extern "C" int pb2_debug_walk_stats(pb2_context* ctx, uint64_t* out10) {
+  if (!ctx || !out10) { set_error("null argument"); return PB2_E_INVALID; }
+  for (int i = 0; i < 10; i++) out10[i] = 0;
+  if (!ctx->walk_stats.ptr) return PB2_OK;
+  PB2_CUDA_CHECK(cudaMemcpy(out10, ctx->walk_stats.ptr, 80, cudaMemcpyDeviceToHost));
+  PB2_CUDA_CHECK(cudaMemset(ctx->walk_stats.ptr, 0, 80));
+  return PB2_OK;
+}
+
 extern "C" int pb2_get_counters(pb2_context* ctx, pb2_counters* out) {
   if (!ctx || !out) { set_error("null argument"); return PB2_E_INVALID; }
   *out = ctx->counters;

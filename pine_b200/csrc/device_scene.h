@@ -130,6 +130,8 @@ struct DScene {
   const uint8_t* scramble;
   const uint8_t* rank;
   pb2_camera camera;
+  unsigned long long* walk_stats;  // PB2_COUNT builds only: {closest nodes, closest prims, any nodes, any prims,
+                                   // closest rays, any rays}; NULL otherwise
 };
 
 constexpr int kMaxBoxShapes = 16;

@@ -23,6 +23,7 @@ void launch_trace_any(const DScene& sc, const float* rays, size_t n, int accel, 
 
 constexpr int kNumSMs = 148;  // B200
 constexpr int kTraceBlock = 128;
+constexpr int kFallbackBlocksPerSM = 6;  // reference-order re-trace: one ray per thread, latency bound
 #ifndef PB2_TRACE_MINBLOCKS
 #define PB2_TRACE_MINBLOCKS 8  // __launch_bounds__ min blocks per SM of the persistent traversal kernels
 #endif

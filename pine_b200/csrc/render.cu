@@ -691,7 +691,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       for (int depth = 0; depth < D; depth++) {
         if (closest_wide_ok) {
           k_trace<<<pgrid, kTraceBlock, 0, st>>>(sc, w, depth);
-          k_trace_fallback<<<kNumSMs, kTraceBlock, 0, st>>>(sc, w, depth);
+          k_trace_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, w, depth);
           launches += 2;
         } else {
           k_trace_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, st>>>(sc, w, depth);
@@ -716,7 +716,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
         if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
           if (any_wide_ok) {
             k_shadow<<<pgrid, kTraceBlock, 0, st>>>(sc, w, depth);
-            k_shadow_fallback<<<kNumSMs, kTraceBlock, 0, st>>>(sc, w, depth);
+            k_shadow_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, w, depth);
             launches += 2;
           } else {
             k_shadow_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, st>>>(sc, w, depth);
@@ -756,12 +756,16 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   ctx->counters.last_shade_ms = cls_ms[2];
   ctx->counters.last_other_ms = cls_ms[3];
   ctx->counters.last_trace_launches = trace_launches;
-  uint64_t closest = 0, shadow = 0;
+  uint64_t closest = 0, shadow = 0, fb_closest = 0, fb_shadow = 0;
   for (int wv = 0; wv < n_waves; wv++)
     for (int k = 0; k <= D; k++) {
       closest += uint64_t(B.host_counts[size_t(wv) * cstride + k]);
       shadow += uint64_t(B.host_counts[size_t(wv) * cstride + D + 1 + k]);
+      fb_closest += uint64_t(B.host_counts[size_t(wv) * cstride + 2 * (D + 1) + 4 * k + 1]);
+      fb_shadow += uint64_t(B.host_counts[size_t(wv) * cstride + 2 * (D + 1) + 4 * k + 3]);
     }
+  ctx->counters.last_closest_fallbacks = fb_closest;
+  ctx->counters.last_shadow_fallbacks = fb_shadow;
   ctx->counters.closest_rays += closest;
   ctx->counters.shadow_rays += shadow;
   ctx->counters.last_closest_rays = closest;

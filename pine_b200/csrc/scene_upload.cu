@@ -264,6 +264,11 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   int rc = pb2_restage_scene(ctx, nullptr);
   if (rc) return rc;
   PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+#ifdef PB2_COUNT
+  PB2_CUDA_CHECK(ctx->walk_stats.reserve(80));
+  PB2_CUDA_CHECK(cudaMemset(ctx->walk_stats.ptr, 0, 80));
+  ctx->scene.walk_stats = ctx->walk_stats.as<unsigned long long>();
+#endif
   ctx->scene_ready = true;
   return PB2_OK;
 }

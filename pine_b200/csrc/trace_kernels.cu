@@ -68,7 +68,7 @@ static void launch_hook(const DScene& sc, int n, int accel, const HookIO& io, in
   cudaMemsetAsync(scratch, 0, 8, st);
   WideQueue wq{scratch, scratch + 1, scratch + 2};
   k_hook_wide<ANY><<<persistent_grid(), kTraceBlock, 0, st>>>(sc, n, wq, io);
-  k_hook_fallback<ANY><<<kNumSMs, kTraceBlock, 0, st>>>(sc, wq, io);
+  k_hook_fallback<ANY><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, wq, io);
 }
 
 void launch_trace_closest(const DScene& sc, const float* rays, size_t n, int accel, int32_t* geom,

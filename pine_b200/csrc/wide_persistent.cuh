@@ -49,10 +49,13 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
   uint2 ngroup = make_uint2(0u, 0u);  // invariant while walking: has a node bit (y > 0x00ffffff)
   uint2 tgroup = make_uint2(0u, 0u);  // primitives waiting to be tested (y = 24-bit mask)
   bool have = false, ambiguous = false;
-  float tie_t = -1.0f, tmax_in = 0.0f;
+  float tie_t = -1.0f, tmax_in = 0.0f, t2 = kFloatMax;
   int win_leaf = -1;
   Hit h;
   h.geom = h.prim = -1;
+#ifdef PB2_COUNT
+  unsigned long long c_nodes = 0, c_prims = 0, c_rays = 0;
+#endif
 
   while (true) {
     // ---- refill idle lanes ----
@@ -74,7 +77,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
           ngroup = make_uint2(0u, 0x80000000u);
           tgroup = make_uint2(0u, 0u);
           sp = 0;
-          have = false; ambiguous = false; tie_t = -1.0f; win_leaf = -1;
+          have = false; ambiguous = false; tie_t = -1.0f; win_leaf = -1; t2 = kFloatMax;
           h.geom = h.prim = -1;
           active = true;
           if (sc.n_box_shapes) {  // see DBoxShape and traverse.cuh (iii)
@@ -92,6 +95,9 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
             if (touched) {
               if (ANY) io.store_any(idx, true);
               else wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
+#ifdef PB2_COUNT
+              if (!ANY && sc.walk_stats) atomicAdd(sc.walk_stats + 6, 1ull);
+#endif
               active = false;
             }
           }
@@ -117,6 +123,9 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
       const uint32_t slot = uint32_t(bit - 24) ^ (w.octinv4 & 7u);
       const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
       uint32_t child_base, prim_base, cmask;
+#ifdef PB2_COUNT
+      c_nodes++;
+#endif
       const uint32_t hm = test_node8(sc.nodes8, ngroup.x + rel, w, ray.tmin, ANY ? ray.tmax : slack_of(ray.tmax),
                                      ANY ? ray.tmax : tmax_in, child_base, prim_base, cmask);
       ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
@@ -130,12 +139,18 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
     }
     // ---- primitive step ----
     const bool owns = active && !done && tgroup.y != 0u;
-    const bool tight = __popc(__ballot_sync(0xffffffffu, owns)) >= 16;
+#ifndef PB2_TIGHT_LANES
+#define PB2_TIGHT_LANES 16
+#endif
+    const bool tight = __popc(__ballot_sync(0xffffffffu, owns)) >= PB2_TIGHT_LANES;
     if (owns) {
       do {
         const int i = __ffs(tgroup.y) - 1;
         tgroup.y &= tgroup.y - 1;
         const PrimRec r = load_prim(sc.wide_prims, tgroup.x + i);
+#ifdef PB2_COUNT
+        c_prims++;
+#endif
         if (ANY) {
           bool ok;
           if (r.prim >= 0) ok = tri_hit(ray, r.v0, r.v1, r.v2);
@@ -143,18 +158,24 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
           else ok = shape_hit(sc, -1 - r.prim, __float_as_int(r.v0.x), ray);
           if (ok && leaf_gate(sc.leaves, r.leaf, q, ray.tmin, ray.tmax)) { have = true; done = true; }
         } else {
+          // Accept candidates up to slack_of(best): t == best exposes ties, and every candidate a
+          // little behind the best is remembered in t2 (second-smallest t seen), which the
+          // certificate at the end needs.
           Ray r2 = ray;
-          r2.tmax = next_up(ray.tmax);  // lets t == current best through so that ties are seen
+          r2.tmax = slack_of(ray.tmax);
           bool ok;
           if (r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
           else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: rays that touch one never get here
           else ok = shape_intersect(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
           if (ok) {
             if (r2.tmax < ray.tmax) {
+              if (have) t2 = pmin(t2, ray.tmax);
               ray.tmax = r2.tmax; h.geom = r.geom; h.prim = r.prim >= 0 ? r.prim : 0; win_leaf = r.leaf; have = true;
             } else if (r2.tmax == ray.tmax) {
               if (have) tie_t = r2.tmax;
               else { ambiguous = true; done = true; }
+            } else if (have) {
+              t2 = pmin(t2, r2.tmax);
             }
           }
         }
@@ -169,17 +190,40 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
         else io.store_any(idx, have);
       } else {
+#ifdef PB2_COUNT
+        if (ambiguous && sc.walk_stats) atomicAdd(sc.walk_stats + 7, 1ull);
+#endif
         if (have && !ambiguous) {
           if (tie_t == ray.tmax) ambiguous = true;
-          else if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, ray.tmax)) ambiguous = true;
+          else if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, ray.tmax)) {
+            // The exact leaf box can come out a few ulps BEHIND the hit it contains (flat boxes of
+            // Rects and axis-aligned triangles: two different float expressions for one distance).
+            // The reference still reaches the leaf if its tmax at that moment is large enough, and
+            // that tmax is tmax_in or the t of another primitive hit before: >= U (traverse.cuh (ii')).
+            const float U = pmin(pmin(tmax_in, t2), half_slack_of(ray.tmax));
+            if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, U)) ambiguous = true;
+          }
+#ifdef PB2_COUNT
+          if (ambiguous && sc.walk_stats) atomicAdd(sc.walk_stats + (tie_t == ray.tmax ? 8 : 9), 1ull);
+#endif
         }
         if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
         else io.store_closest(sc, idx, ray, have, h);
       }
       active = false;
       tgroup.y = 0u;
+#ifdef PB2_COUNT
+      c_rays++;
+#endif
     }
   }
+#ifdef PB2_COUNT
+  if (sc.walk_stats) {
+    atomicAdd(sc.walk_stats + (ANY ? 2 : 0), c_nodes);
+    atomicAdd(sc.walk_stats + (ANY ? 3 : 1), c_prims);
+    atomicAdd(sc.walk_stats + (ANY ? 5 : 4), c_rays);
+  }
+#endif
 }
 
 // Reference-order re-trace of the rays the wide walk could not certify.
