@@ -112,6 +112,7 @@ struct pb2_context {
   // scratch for trace hooks / render
   pb2::DBuf rays, out_geom, out_prim, out_t, out_surf, out_occ, trace_scratch;
   pb2::DBuf film, film_accum, walk_stats;
+  bool l2_window_set = false;  // an access-policy window is installed on the render stream
   size_t film_pixels = 0;  // pixels the film buffer was last cleared for (PB2_RENDER_KEEP_FILM)
   pb2::WavefrontBuffers* wf = nullptr;
 

@@ -675,6 +675,33 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
     have += uint64_t(n);
     return PB2_OK;
   };
+  // L2 persistence window over the top of the wide BVH (nodes8 is breadth first, so its prefix is the
+  // top levels): node fetches that hit keep their lines, everything else in the window's stream
+  // (ray queues, hit records, vertex records) is marked streaming. PB2_L2_PERSIST_MB = 0 turns it off.
+  {
+    static const int persist_mb = env_int("PB2_L2_PERSIST_MB", 0);
+    size_t bytes = std::min(size_t(persist_mb) << 20, ctx->nodes8.cap);
+    cudaStreamAttrValue attr{};
+    if (bytes && sc.wide_ready) {
+      int max_window = 0, max_persist = 0;
+      cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, ctx->device);
+      cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, ctx->device);
+      bytes = std::min(bytes, std::min(size_t(max_window), size_t(max_persist)));
+      if (bytes) {
+        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes);
+        attr.accessPolicyWindow.base_ptr = const_cast<DNode8*>(sc.nodes8);
+        attr.accessPolicyWindow.num_bytes = bytes;
+        attr.accessPolicyWindow.hitRatio = 1.0f;
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+      }
+    }
+    if (bytes || ctx->l2_window_set) {
+      cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &attr);
+      ctx->l2_window_set = bytes != 0;
+      cudaGetLastError();  // best effort: a device without the feature just ignores it
+    }
+  }
   PB2_CUDA_CHECK(cudaEventRecord(ctx->ev0, st));
   mark(-1);
   int wave = 0;

@@ -34,7 +34,7 @@ if [[ $STEPS == *ncu* ]]; then
       $CMD > $O/${TAG}_ncu_launches.log 2>&1
   echo "ncu launches rc=$?"
   $CMD > $O/${TAG}_plain_c5s.log 2>&1 &&
-  ncu --set full --clock-control none --import-source on -k regex:'k_trace$|k_shadow$|k_shade$' -s 6 -c 6 \
+  ncu --set full --clock-control none --import-source on -k regex:'k_trace$|k_shadow$|k_shade_mat|k_classify|k_shade_terminal' -s 14 -c 7 \
       -f -o $O/${TAG}_prof_c5s $CMD > $O/${TAG}_ncu_full.log 2>&1
   echo "ncu full rc=$?"
 fi
