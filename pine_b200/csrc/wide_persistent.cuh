@@ -18,7 +18,10 @@
 
 namespace pb2 {
 
-constexpr int kRefillThreshold = 8;  // refill a warp when at least this many lanes are idle
+#ifndef PB2_REFILL
+#define PB2_REFILL 8
+#endif
+constexpr int kRefillThreshold = PB2_REFILL;  // refill a warp when at least this many lanes are idle
 
 struct WideQueue {
   int* next;      // next unclaimed queue index (zero before the launch)

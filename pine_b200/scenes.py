@@ -166,5 +166,33 @@ def cbox_readme_noboxes(B, size=(640, 640)):
     return {"spp": 16, "depth": 4}
 
 
-SCENES = {"cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
+def materials_room(B, size=(96, 96)):
+    """Parity scene for the material kinds the named configs never assign: Glass, Uber and
+    Subsurface (on a mesh, where the reference's BSSRDF walk is well defined) next to Diffuse,
+    Metal and Glossy, inside the cbox-indirect room."""
+    white = B.add_material("diffuse", (0.9, 0.9, 0.9))
+    red = B.add_material("diffuse", (0.9, 0.1, 0.05))
+    glass = B.add_material("glass", (0.95, 0.95, 1.0), roughness=0.0, ior=1.5)
+    frosted = B.add_material("glass", (0.9, 1.0, 0.9), roughness=0.3, ior=1.4)
+    uber = B.add_material("uber", (0.8, 0.6, 0.2), roughness=0.25, metallic=0.4, transmission=0.3, ior=1.45)
+    skin = B.add_material("subsurface", (0.9, 0.7, 0.6), roughness=0.1, sigma_s=(20.0, 30.0, 40.0))
+    metal = B.add_material("metal", (0.9, 0.9, 0.9), roughness=0.15)
+    glossy = B.add_material("glossy", (0.3, 0.5, 0.8), roughness=0.1)
+    B.add_rect((0, 0, 1), (2, 0, 0), (0, 0, 2), white)
+    B.add_rect((0, 2, 1), (2, 0, 0), (0, 0, 2), white)
+    B.add_rect((0, 1, 2), (2, 0, 0), (0, 2, 0), glossy)
+    B.add_rect((-1, 1, 1), (0, 0, 2), (0, 2, 0), red)
+    B.add_rect((1, 1, 1), (0, 0, 2), (0, 2, 0), metal)
+    B.add_sphere((-0.5, 0.35, 0.7), 0.35, glass)
+    B.add_sphere((0.5, 0.3, 0.5), 0.3, uber)
+    B.add_sphere((0.0, 0.25, 1.3), 0.25, frosted)
+    v, f = icosphere(2)
+    B.add_mesh((v * np.float32(0.3) + np.array([0.1, 1.0, 0.9], np.float32)).astype(np.float32), f, skin)
+    light = B.add_material("emissive", (60.0, 50.0, 40.0))
+    B.add_rect((0, 1.95, 1), (0.6, 0, 0), (0, 0, 0.6), light)
+    B.set_camera(size, (0, 1, -3.5), (0, 1, 0), 0.28)
+    return {"spp": 16, "depth": 6}
+
+
+SCENES = {"materials_room": materials_room, "cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
           "mesh_field": mesh_field}
