@@ -88,11 +88,17 @@ def _worker(rank, world, port, mode, out_path):
 @pytest.mark.parametrize("mode", ["samples", "rows"])
 def test_two_ranks_over_gloo_assemble_the_full_film(tmp_path, mode):
     import torch.multiprocessing as mp
-    with socket.socket() as s:
-        s.bind(("127.0.0.1", 0))
-        port = s.getsockname()[1]
     out = str(tmp_path / f"film_{mode}.npy")
-    mp.spawn(_worker, args=(2, port, mode, out), nprocs=2, join=True)
+    for attempt in range(3):  # the free port found here can be taken before the ranks bind it
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            port = s.getsockname()[1]
+        try:
+            mp.spawn(_worker, args=(2, port, mode, out), nprocs=2, join=True)
+            break
+        except Exception:
+            if attempt == 2:
+                raise
     got = np.load(out)
     full = _model_film(40, 50, 16, (0, 50), (0, 16)).numpy()
     assert (got[..., 3] == 1).all()
