@@ -1,0 +1,138 @@
+"""pine_b200/prl.py: the PRL-subset loader that lets Pine's scene FILES drive the backend.
+CPU tests: grammar, binary32 arithmetic rules, error behaviour, and (where /root/reference is
+mounted) that the reference's own scripts produce scene descriptions byte-identical to the builder
+functions the benchmarks use. The GPU test renders a script and the equivalent builder scene."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import pine_b200 as pb
+from pine_b200 import _abi as A
+from pine_b200 import prl, scenes
+
+REFERENCE = "/root/reference"
+needs_reference_tree = pytest.mark.skipif(not os.path.isdir(os.path.join(REFERENCE, "scenes")),
+                                          reason="reference checkout not mounted (GPU box)")
+
+
+def desc_bytes(scene):
+    """Every array of the pb2_scene_desc a Scene hands to pb2_upload_scene, as bytes."""
+    d, keep = scene.desc()
+    out = {}
+    for name, typ in (("geometries", A.Geometry), ("materials", A.Material), ("rects", A.Rect),
+                      ("obbs", A.Obb), ("cones", A.Cone), ("spheres", A.Sphere), ("disks", A.Disk)):
+        n = getattr(d, "n_" + name)
+        p = getattr(d, name)
+        out[name] = bytes((C.c_char * (n * C.sizeof(typ))).from_address(C.addressof(p.contents))) if n else b""
+    out["lights"] = [d.light_geometries[i] for i in range(d.n_lights)]
+    out["camera"] = bytes(d.camera)
+    return out
+
+
+SCRIPT = """
+# a small room, written the way Pine's scene files are
+scene := Scene();
+size := [16, 8] * 4;
+scene.add("white", Diffuse([0.9, 0.9, 0.9]));
+scene.add("mirror", Metal([1, 1, 1], 0.0));
+scene.add(Rect([0, 0, 1], [2, 0, 0], [0, 0, 2]), "white");
+scene.add(Rect([0, 1, 2], [2, 0, 0], [0, 2, 0], true), "mirror");
+for x in -0.5 ~ 0.5 ~ 0.5 {
+    scene.add(Cone([x, 0, 1], Y, 0.1, 0.3), "white");
+}
+scene.add(Sphere([0, 0.5, 1.2], 0.25), Glossy([1, 1, 1] / 4.0, 0.05));
+scene.add(Box(AABB([0, 0, 0], [1, 1, 1]), translate([0.3, 0.0, 0.6]) * rotate_y(0.4) * scale([0.2, 0.4, 0.2])), "white");
+scene.add(Rect([0.0, 1.9, 1], [0.3, 0, 0], [0, 0, 0.3]), Emissive(60 * [1.0, 0.64, 0.185]));
+scene.set(ThinLenCamera(Film(size, ACES()), [0, 1, -4], [0, 1, 0], 0.25));
+PathIntegrator(BlueSampler(4), 3).render(scene);
+scene.camera.film().save("out/room.png");
+"""
+
+
+def build_by_hand(B):
+    white = B.add_material("diffuse", (0.9, 0.9, 0.9))
+    mirror = B.add_material("metal", (1, 1, 1), roughness=0.0)
+    B.add_rect((0, 0, 1), (2, 0, 0), (0, 0, 2), white)
+    B.add_rect((0, 1, 2), (2, 0, 0), (0, 2, 0), mirror, flip=True)
+    for x in (-0.5, 0.0, 0.5):
+        B.add_cone((x, 0, 1), (0, 1, 0), 0.1, 0.3, white)
+    g = B.add_material("glossy", (0.25, 0.25, 0.25), roughness=0.05)
+    B.add_sphere((0, 0.5, 1.2), 0.25, g)
+    m = pb.mat4.mul(pb.mat4.mul(pb.mat4.translate((0.3, 0.0, 0.6)), pb.mat4.rotate_y(0.4)), pb.mat4.scale((0.2, 0.4, 0.2)))
+    B.add_box((0, 0, 0), (1, 1, 1), m, white)
+    e = B.add_material("emissive", tuple(np.float32(60) * np.float32(c) for c in (1.0, 0.64, 0.185)))
+    B.add_rect((0.0, 1.9, 1), (0.3, 0, 0), (0, 0, 0.3), e)
+    B.set_camera((64, 32), (0, 1, -4), (0, 1, 0), 0.25, tonemapper="aces")
+
+
+def test_script_equals_builder_calls():
+    renders, saves = [], []
+    sp, = prl.load(SCRIPT, pb.Scene, on_render=lambda s, spp, d: renders.append((spp, d)),
+                   on_save=lambda s, p: saves.append(p))
+    assert renders == [(4, 3)] and saves == ["out/room.png"]
+    assert sp.config == {"spp": 4, "depth": 3, "save": "out/room.png"}
+    S = pb.Scene()
+    build_by_hand(S)
+    assert desc_bytes(sp.target) == desc_bytes(S)
+
+
+def test_arithmetic_follows_the_jit_types():
+    ev = lambda src: prl.Interpreter(pb.Scene).eval(prl.Parser(src + ";").statement()[1])
+    assert ev("[256, 256] * 4") == [1024, 1024] and all(isinstance(v, int) for v in ev("[256, 256] * 4"))
+    assert ev("7 / 2") == 3 and ev("-7 / 2") == -3                      # integer division truncates
+    v = ev("600 * [1.0, 0.64, 0.185]")
+    assert [type(x) for x in v] == [np.float32] * 3
+    assert v[1] == np.float32(600) * np.float32(0.64)                   # binary32, not double
+    assert ev("1 + 2 * 3 - 4 / 2") == 5 and ev("(1 + 2) * 3") == 9
+    # the inclusive float loop accumulates in binary32: -1 + 20 * 0.1f overshoots 1, so 20 values
+    it = prl.Interpreter(pb.Scene)
+    it.run("n := 0; for x in -1.0 ~ 0.1 ~ 1.0 { n := n + 1; }")
+    assert it.env["n"] == 20
+    it.run("k := 0; for i in 0 ~ 1 ~ 3 { k := k + i; }")
+    assert it.env["k"] == 6
+
+
+@pytest.mark.parametrize("src, msg", [
+    ("scene := Scene(); scene.add(Rect([0,0,0],[1,0,0],[0,1,0]), \"nope\");", "unknown material"),
+    ("x := foo(1);", "unknown name"),
+    ("scene := Scene(); scene.add(Plane([0,0,0],[0,1,0]), Diffuse([1,1,1]));", "unknown name"),
+    ("x := [1, 2] + [1, 2, 3];", "size mismatch"),
+    ("x := 1 $ 2;", "unexpected character"),
+    ("x := (1 + 2;", "expected"),
+    ("scene := Scene(); y := scene.camera;", "before scene.set"),
+])
+def test_errors_are_loud(src, msg):
+    with pytest.raises(prl.PrlError, match=msg):
+        prl.load(src, pb.Scene)
+
+
+@needs_reference_tree
+@pytest.mark.parametrize("source, builder, kw, want", [
+    ("README.md", "cbox_readme", dict(size=(640, 640)), {"spp": 16, "depth": 4}),
+    ("scenes/cbox.pine", "cbox_file", dict(size=(1024, 1024)), {"spp": 256, "depth": 8}),
+    ("scenes/cbox-indirect.pine", "cbox_indirect", dict(size=(720, 360)), {"spp": 64, "depth": 5}),
+])
+def test_reference_scene_files_load_byte_identically(source, builder, kw, want):
+    text = open(os.path.join(REFERENCE, source)).read()
+    if source.endswith(".md"):
+        text = re.search(r"```\n(scene := Scene\(\);.*?)```", text, re.S).group(1)
+    sp, = prl.load(text, pb.Scene)
+    assert {k: sp.config[k] for k in ("spp", "depth")} == want
+    S = pb.Scene()
+    scenes.SCENES[builder](S, **kw)
+    assert desc_bytes(sp.target) == desc_bytes(S)
+
+
+@pytest.mark.gpu
+def test_script_renders_like_the_builder_scene(tmp_path):
+    path = tmp_path / "room.pine"
+    path.write_text(SCRIPT.replace("out/room.png", str(tmp_path / "room.png")))
+    sp, = prl.run_file(str(path))
+    S = pb.Scene()
+    build_by_hand(S)
+    film = pb.PathIntegrator(pb.BlueSampler(4), 3).render(S)
+    assert np.array_equal(sp.target.camera.film().pixels.view(np.uint32), film.view(np.uint32))
+    assert (tmp_path / "room.png").stat().st_size > 100
