@@ -221,15 +221,19 @@ __device__ __forceinline__ bool leaf_gate(const DLeaf* leaves, int leaf, const O
 // delta = 2^-21 * (|origin * inv| + 255 |a| + |ood|), which bounds the difference of the two
 // expressions (at most ~6 roundings of magnitude <= that sum), so near planes come out no larger
 // and far planes no smaller than the reference's value for any box inside the quantised one.
+// (q enters the fma as 2^15 + q with the bias folded into the constant, see byte_biased.)
 struct WideRay {
   V3 inv, ood;
   uint32_t octinv4;  // (7 ^ octant) replicated into 4 bytes
   uint32_t neg;      // bit k: d[k] < 0
 };
-__device__ __forceinline__ float byte_f(uint32_t w, int k) {  // byte k of w as a float, exact
-  // one PRMT builds the bits of 2^23 + byte (0x4B0000bb); subtracting 2^23 is exact
-  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u | uint32_t(k))) - 8388608.0f;
+// Byte k of w as the float 2^15 + byte (bits 0x4700bb00), built by ONE PRMT. The bias is folded into
+// the per-node constants (b - 2^15 a), so a plane distance costs PRMT + FMA instead of
+// PRMT + FADD + FMA: 48 instructions fewer per wide-node test.
+__device__ __forceinline__ float byte_biased(uint32_t w, int k) {
+  return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7604u | (uint32_t(k) << 4)));
 }
+constexpr float kByteBias = 32768.0f;
 
 struct PrimRec {
   V3 v0, v1, v2;
@@ -267,7 +271,13 @@ __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx
   const float dy = (fabsf(uy) + 255.0f * fabsf(ay) + fabsf(w.ood.y)) * 4.76837158203125e-7f;
   const float dz = (fabsf(uz) + 255.0f * fabsf(az) + fabsf(w.ood.z)) * 4.76837158203125e-7f;
   const float bx = ux - w.ood.x, by = uy - w.ood.y, bz = uz - w.ood.z;
-  const float bnx = bx - dx, bfx = bx + dx, bny = by - dy, bfy = by + dy, bnz = bz - dz, bfz = bz + dz;
+  // fma(2^15 + q, a, (b -/+ delta) - 2^15 a) == q a + b -/+ delta up to ONE more rounding, of a value
+  // no larger than |b| + delta + 2^15 |a|: delta grows by 2^-23 * 2^15 |a| (0.4% of a quantisation step)
+  const float sx = kByteBias * ax, sy = kByteBias * ay, sz = kByteBias * az;  // exact (power of two)
+  const float ex = dx + fabsf(sx) * 1.1920928955078125e-7f, ey = dy + fabsf(sy) * 1.1920928955078125e-7f,
+              ez = dz + fabsf(sz) * 1.1920928955078125e-7f;
+  const float bnx = (bx - ex) - sx, bfx = (bx + ex) - sx, bny = (by - ey) - sy, bfy = (by + ey) - sy,
+              bnz = (bz - ez) - sz, bfz = (bz + ez) - sz;
   // qlo: x = n2.xy, y = n2.zw, z = n3.xy; qhi: x = n3.zw, y = n4.xy, z = n4.zw. near = lo unless d < 0
   const bool nx = w.neg & 1, ny = w.neg & 2, nz = w.neg & 4;
   uint32_t hitmask = 0;
@@ -285,9 +295,9 @@ __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx
     const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-      const float tnx = __fmaf_rn(byte_f(qnx, k), ax, bnx), tfx = __fmaf_rn(byte_f(qfx, k), ax, bfx);
-      const float tny = __fmaf_rn(byte_f(qny, k), ay, bny), tfy = __fmaf_rn(byte_f(qfy, k), ay, bfy);
-      const float tnz = __fmaf_rn(byte_f(qnz, k), az, bnz), tfz = __fmaf_rn(byte_f(qfz, k), az, bfz);
+      const float tnx = __fmaf_rn(byte_biased(qnx, k), ax, bnx), tfx = __fmaf_rn(byte_biased(qfx, k), ax, bfx);
+      const float tny = __fmaf_rn(byte_biased(qny, k), ay, bny), tfy = __fmaf_rn(byte_biased(qfy, k), ay, bfy);
+      const float tnz = __fmaf_rn(byte_biased(qnz, k), az, bnz), tfz = __fmaf_rn(byte_biased(qfz, k), az, bfz);
       const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
       const float tf = fminf(fminf(tfx, tfy), fminf(tfz, lim));
       if (tn <= tf) hitmask |= ((child_bits4 >> (8 * k)) & 0xffu) << ((bit_index4 >> (8 * k)) & 0xffu);
