@@ -231,7 +231,9 @@ struct WideRay {
 // the per-node constants (b - 2^15 a), so a plane distance costs PRMT + FMA instead of
 // PRMT + FADD + FMA: 48 instructions fewer per wide-node test.
 __device__ __forceinline__ float byte_biased(uint32_t w, int k) {
-  return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7604u | (uint32_t(k) << 4)));
+  // constant first: SASS PRMT takes ONE immediate, and it must be the selector (4 different ones per
+  // word) rather than the constant, or every PRMT is preceded by a MOV of its selector
+  return __uint_as_float(__byte_perm(0x47000000u, w, 0x3140u + (uint32_t(k) << 4)));
 }
 constexpr float kByteBias = 32768.0f;
 
@@ -267,15 +269,14 @@ __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx
   prim_base = n1.y & ~kNoCullBit;
   if (n1.y & kNoCullBit) lim = lim_nocull;
   const float ux = ox * w.inv.x, uy = oy * w.inv.y, uz = oz * w.inv.z;
-  const float dx = (fabsf(ux) + 255.0f * fabsf(ax) + fabsf(w.ood.x)) * 4.76837158203125e-7f;
-  const float dy = (fabsf(uy) + 255.0f * fabsf(ay) + fabsf(w.ood.y)) * 4.76837158203125e-7f;
-  const float dz = (fabsf(uz) + 255.0f * fabsf(az) + fabsf(w.ood.z)) * 4.76837158203125e-7f;
-  const float bx = ux - w.ood.x, by = uy - w.ood.y, bz = uz - w.ood.z;
   // fma(2^15 + q, a, (b -/+ delta) - 2^15 a) == q a + b -/+ delta up to ONE more rounding, of a value
-  // no larger than |b| + delta + 2^15 |a|: delta grows by 2^-23 * 2^15 |a| (0.4% of a quantisation step)
+  // no larger than |b| + delta + 2^15 |a|, so delta grows by 2^-23 * 2^15 |a| = 2^-21 * 2^13 |a|
+  // (0.4% of a quantisation step): 255 |a| + 8192 |a| below.
+  const float ex = (fabsf(ux) + 8447.0f * fabsf(ax) + fabsf(w.ood.x)) * 4.76837158203125e-7f;
+  const float ey = (fabsf(uy) + 8447.0f * fabsf(ay) + fabsf(w.ood.y)) * 4.76837158203125e-7f;
+  const float ez = (fabsf(uz) + 8447.0f * fabsf(az) + fabsf(w.ood.z)) * 4.76837158203125e-7f;
+  const float bx = ux - w.ood.x, by = uy - w.ood.y, bz = uz - w.ood.z;
   const float sx = kByteBias * ax, sy = kByteBias * ay, sz = kByteBias * az;  // exact (power of two)
-  const float ex = dx + fabsf(sx) * 1.1920928955078125e-7f, ey = dy + fabsf(sy) * 1.1920928955078125e-7f,
-              ez = dz + fabsf(sz) * 1.1920928955078125e-7f;
   const float bnx = (bx - ex) - sx, bfx = (bx + ex) - sx, bny = (by - ey) - sy, bfy = (by + ey) - sy,
               bnz = (bz - ez) - sz, bfz = (bz + ez) - sz;
   // qlo: x = n2.xy, y = n2.zw, z = n3.xy; qhi: x = n3.zw, y = n4.xy, z = n4.zw. near = lo unless d < 0
