@@ -426,8 +426,12 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
               V3 f = bxdf_f(bx, wo);
               float mis = balance_heuristic(ls_pdf, bxdf_pdf(bx, wo));
               nee = le * V3(1.0f) * cosine * f / ls_pdf * mis;
-              shadow_ray = spawn_ray(it.p, it.n, ss.w, ss.distance);
-              emit_shadow = true;
+              // a light sample the BxDF gives no weight (below the surface of an opaque lobe) adds
+              // nothing whether or not it is occluded: no shadow ray for it
+              if (!is_zero(nee)) {
+                shadow_ray = spawn_ray(it.p, it.n, ss.w, ss.distance);
+                emit_shadow = true;
+              }
             }
           }
         }
