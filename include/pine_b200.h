@@ -145,7 +145,18 @@ typedef struct pb2_render_params {
   int32_t sample_begin, sample_end;
   int32_t accel; /* 0 = wide BVH (production), 1 = reference-order binary BVH (verification) */
   int32_t flags; /* PB2_RENDER_* */
+  /* Which alternative of pine::Sampler (sampler.h:203) drives get1d/get2d; 0 keeps the meaning above.
+   * PB2_SAMPLER_SOBOL: SobolSampler(spp) (sampler.h:83-164, sampler.cpp:82-113), any spp in
+   * [1, 65536], streams bit-identical to the reference's. PB2_SAMPLER_UNIFORM: UniformSampler(spp,
+   * sampler_seed) (sampler.h:13-39) -- the reference draws from one RNG per worker thread, so its
+   * stream depends on the thread schedule; here every (pixel, sample, dimension) has its own
+   * counter-based draw from the same generator (rng.h:97-144): statistically equivalent only. */
+  int32_t sampler;
+  int32_t sampler_seed;
 } pb2_render_params;
+#define PB2_SAMPLER_BLUE 0
+#define PB2_SAMPLER_SOBOL 1
+#define PB2_SAMPLER_UNIFORM 2
 #define PB2_RENDER_SORT_BY_MATERIAL 1 /* bucket the shade queue by BxDF kind */
 #define PB2_RENDER_TIME_KERNELS 2     /* fill pb2_counters.last_{trace,shadow,shade,other}_ms */
 #define PB2_RENDER_KEEP_FILM 4        /* do not clear the device film first: rows outside
@@ -229,6 +240,10 @@ typedef struct pb2_ray_record {
 int pb2_set_ray_record(pb2_context* ctx, pb2_ray_record* rec);
 int pb2_test_sampler(pb2_context* ctx, int spp, int px, int py, int sample_index, int n_rand,
                      float* out_rand, const char* pattern, int n_samples, float* out_draws);
+/* get1d/get2d draws of any sampler kind: Sampler::init(film size of the uploaded scene),
+ * start_pixel((px, py), sample_index), then per sample the pattern of '1'/'2' draws. */
+int pb2_test_sampler_kind(pb2_context* ctx, int sampler, int spp, int sampler_seed, int px, int py,
+                          int sample_index, const char* pattern, int n_samples, float* out_draws);
 int pb2_test_primary_rays(pb2_context* ctx, int sample_index, float* rays_host);
 int pb2_get_counters(pb2_context* ctx, pb2_counters* out);
 /* Debug hook (meaningful in -DPB2_COUNT tuning builds only; zeros otherwise): wide-walk node and

@@ -32,6 +32,12 @@ void pb2h_make_camera(int w, int h, int tonemapper, const float* from, const flo
 void pb2h_mat4(int op, const float* a, float* out_colmajor);
 void pb2h_mat4_mul(const float* a, const float* b, float* out_colmajor);
 int pb2h_round_spp(int spp);
+/* Host evaluation of the device draw functions of SobolSampler (sampler.h:83-164, sampler.cpp:82-113)
+ * and UniformSampler (the same __host__ __device__ code the kernels inline; test hook, no GPU):
+ * init({width, height}), start_pixel((px, py), sample_index), then n_samples x the pattern of
+ * '1' (get1d) / '2' (get2d) draws. sampler = PB2_SAMPLER_SOBOL or PB2_SAMPLER_UNIFORM. */
+int pb2h_sampler_draws(int sampler, int spp, int sampler_seed, int width, int height, int px, int py,
+                       int sample_index, const char* pattern, int n_samples, float* out_draws);
 #ifdef __cplusplus
 }
 #endif

@@ -219,8 +219,8 @@ CudaPathIntegrator::CudaPathIntegrator(Accel, Sampler sampler, LightSampler, int
     : sampler_(MOVE(sampler)), max_path_length_(max_path_length) {
   if (max_path_length <= 0)  // path.cpp:12-13
     SEVERE("`PathIntegrator` expect `max_path_length` to be positive, get", max_path_length);
-  if (!sampler_.is<BlueSobolSampler>())
-    SEVERE("[CudaPathIntegrator]only BlueSampler (BlueSobolSampler) runs on the CUDA path");
+  if (!sampler_.is<BlueSobolSampler>() && !sampler_.is<SobolSampler>() && !sampler_.is<UniformSampler>())
+    SEVERE("[CudaPathIntegrator]only BlueSampler, SobolSampler and UniformSampler run on the CUDA path");
 }
 CudaPathIntegrator::CudaPathIntegrator(Sampler sampler, int max_path_length)
     : CudaPathIntegrator(Accel(), MOVE(sampler), LightSampler(UniformLightSampler()), max_path_length) {}
@@ -239,14 +239,20 @@ void CudaPathIntegrator::render(Scene& scene) {
   Flat flat;
   flatten(scene, flat);
   check(pb2_upload_scene(ctx_, &flat.desc), "pb2_upload_scene");
-  const char* tables = std::getenv("PINE_B200_TABLES");
-  check(pb2_load_sampler_tables_file(ctx_, tables ? tables : "", spp), "pb2_load_sampler_tables_file");
+  const int kind = sampler_.is<SobolSampler>()     ? PB2_SAMPLER_SOBOL
+                   : sampler_.is<UniformSampler>() ? PB2_SAMPLER_UNIFORM
+                                                   : PB2_SAMPLER_BLUE;
+  if (kind == PB2_SAMPLER_BLUE) {
+    const char* tables = std::getenv("PINE_B200_TABLES");
+    check(pb2_load_sampler_tables_file(ctx_, tables ? tables : "", spp), "pb2_load_sampler_tables_file");
+  }
   set_progress(0);
   pb2_render_params p{};
   p.spp = spp;
   p.max_path_length = max_path_length_;
   p.row_begin = 0; p.row_end = flat.desc.camera.height;
   p.sample_begin = 0; p.sample_end = spp;
+  p.sampler = kind;  // UniformSampler keeps its seed private (sampler.h:36-38): the CUDA stream uses seed 0
   auto& film = scene.camera.film();
   // Film::pixels is Array2d<vec4>, row-major p.x + p.y*w (array.h:51-55): the ABI's film layout
   check(pb2_render(ctx_, &p, &film.data()[0][0]), "pb2_render");

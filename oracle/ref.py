@@ -276,6 +276,16 @@ def sampler_stream(spp, px, py, sample_index, n_rand, pattern, n_samples):
     return r[:n_rand], d[:width * n_samples].reshape(n_samples, width)
 
 
+def sampler_stream_kind(sampler, spp, size, px, py, sample_index, pattern, n_samples):
+    """get1d/get2d draws of Sampler(<sampler>(spp)) after init(size), start_pixel((px, py), sample_index)."""
+    width = sum(1 if c == "1" else 2 for c in pattern)
+    d = np.zeros(max(width * n_samples, 1), np.float32)
+    kind = {"blue": 0, "sobol": 1, "uniform": 2}[sampler]
+    lib().ref_sampler_stream_kind(kind, spp, size[0], size[1], px, py, sample_index, pattern.encode(),
+                                  n_samples, _fp(d))
+    return d[:width * n_samples].reshape(n_samples, width)
+
+
 def spawn_rays(p_n_wo_dist):
     a = _f(p_n_wo_dist).reshape(-1, 10)
     rays = np.zeros((len(a), 8), np.float32)

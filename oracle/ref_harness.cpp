@@ -407,6 +407,26 @@ void ref_sampler_stream(int spp, int px, int py, int sample_index, int n_rand, f
       }
     }
 }
+// The same stream for the other Sampler alternatives (sampler_kind as in ref_render): init(film
+// size) matters for SobolSampler (nbase4_digits, sampler.cpp:82-85).
+void ref_sampler_stream_kind(int sampler_kind, int spp, int width, int height, int px, int py,
+                             int sample_index, const char* pattern, int n_samples, float* out_draws) {
+  Sampler sampler = sampler_kind == 0   ? Sampler(BlueSobolSampler(spp))
+                    : sampler_kind == 1 ? Sampler(SobolSampler(spp))
+                                        : Sampler(UniformSampler(spp));
+  sampler.init(vec2i(width, height));
+  sampler.start_pixel(vec2i(px, py), sample_index);
+  for (int s = 0; s < n_samples; s++, sampler.start_next_sample())
+    for (const char* c = pattern; *c; c++) {
+      if (*c == '1') {
+        *out_draws++ = sampler.get1d();
+      } else {
+        auto u = sampler.get2d();
+        *out_draws++ = u.x;
+        *out_draws++ = u.y;
+      }
+    }
+}
 uint64_t ref_hash_pixel(int px, int py, int sample_index) { return hash(vec2i(px, py), sample_index); }
 void ref_rng_u64(uint64_t seed, int n, uint64_t* out) {
   RNG rng(seed);

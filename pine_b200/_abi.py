@@ -84,7 +84,11 @@ class SceneDesc(C.Structure):
 class RenderParams(C.Structure):
     _fields_ = [("spp", C.c_int32), ("max_path_length", C.c_int32), ("row_begin", C.c_int32),
                 ("row_end", C.c_int32), ("sample_begin", C.c_int32), ("sample_end", C.c_int32),
-                ("accel", C.c_int32), ("flags", C.c_int32)]
+                ("accel", C.c_int32), ("flags", C.c_int32), ("sampler", C.c_int32),
+                ("sampler_seed", C.c_int32)]
+
+
+SAMPLER_BLUE, SAMPLER_SOBOL, SAMPLER_UNIFORM = 0, 1, 2
 
 
 class RayRecord(C.Structure):
@@ -118,10 +122,10 @@ ABI_SYMBOLS = [
     "pb2_last_error", "pb2_device_count", "pb2_create", "pb2_destroy", "pb2_upload_scene",
     "pb2_restage_scene",
     "pb2_upload_sampler_tables", "pb2_load_sampler_tables_file", "pb2_render", "pb2_render_device", "pb2_film_finalize",
-    "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler",
+    "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler", "pb2_test_sampler_kind",
     "pb2_test_primary_rays", "pb2_get_counters", "pb2_debug_walk_stats", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
     "pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone", "pb2h_make_triangle",
-    "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_round_spp",
+    "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_round_spp", "pb2h_sampler_draws",
 ]
 
 _lib = None
@@ -158,6 +162,8 @@ def lib():
         L.pb2_trace_any.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
         L.pb2_trace_closest_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int,
                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pb2_test_sampler_kind.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                            C.c_char_p, C.c_int, C.c_void_p]
         L.pb2_test_sampler.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_void_p, C.c_char_p, C.c_int, C.c_void_p]
         L.pb2_test_primary_rays.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -177,6 +183,7 @@ def lib():
                                        C.c_float, C.POINTER(Camera)]
         L.pb2h_mat4.argtypes = [C.c_int, fp, fp]
         L.pb2h_mat4_mul.argtypes = [fp, fp, fp]
+        L.pb2h_sampler_draws.argtypes = [C.c_int] * 8 + [C.c_char_p, C.c_int, C.c_void_p]
         for name in ("pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone",
                      "pb2h_make_triangle", "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul"):
             getattr(L, name).restype = None

@@ -117,14 +117,15 @@ __device__ __forceinline__ bool bxdf_is_delta(const Bxdf& b) {
 }
 
 // psl::lerp(t, a, b) used by SampleWm: see pmath.h plerp (vecmath.h:873 / psl math.h:119)
-__device__ __forceinline__ bool bxdf_sample(const DScene& sc, const Bxdf& b, BlueSampler& smp, BsdfSample& bs) {
+template <class Smp>
+__device__ __forceinline__ bool bxdf_sample(const DScene& sc, const Bxdf& b, Smp& smp, BsdfSample& bs) {
   const V3 wi = b.wi;
   bs.is_delta = false;
   bs.pdf = 0;
   const float alpha = sqr(b.roughness);
   switch (b.kind) {
     case BX_DIFFUSE: {
-      V3 wo = cosine_weighted_hemisphere(blue_get2d(sc, smp));
+      V3 wo = cosine_weighted_hemisphere(smp_get2d(sc, smp));
       if (CosTheta(wi) < 0) wo = -wo;
       bs.wo = wo;
       bs.pdf = AbsCosTheta(wo) / kPi;
@@ -132,7 +133,7 @@ __device__ __forceinline__ bool bxdf_sample(const DScene& sc, const Bxdf& b, Blu
       return true;
     }
     case BX_BSSRDF: {
-      V3 wo = cosine_weighted_hemisphere(blue_get2d(sc, smp));
+      V3 wo = cosine_weighted_hemisphere(smp_get2d(sc, smp));
       if (CosTheta(wi) > 0) wo = -wo;
       bs.wo = wo;
       bs.pdf = AbsCosTheta(wo) / kPi;
@@ -148,7 +149,7 @@ __device__ __forceinline__ bool bxdf_sample(const DScene& sc, const Bxdf& b, Blu
         return true;
       }
       TRDist d{alpha, alpha};
-      V3 wm = d.SampleWm(wi, blue_get2d(sc, smp));
+      V3 wm = d.SampleWm(wi, smp_get2d(sc, smp));
       V3 wo = Reflect(wi, wm);
       if (!SameHemisphere(wi, wo)) return false;
       V3 fr = FrSchlick(b.albedo, absdot(wi, wm));
@@ -166,7 +167,7 @@ __device__ __forceinline__ bool bxdf_sample(const DScene& sc, const Bxdf& b, Blu
         return true;
       }
       TRDist d{alpha, alpha};
-      V3 wm = d.SampleWm(wi, blue_get2d(sc, smp));
+      V3 wm = d.SampleWm(wi, smp_get2d(sc, smp));
       V3 wo = Reflect(wi, wm);
       if (!SameHemisphere(wi, wo)) return false;
       bs.wo = wo;
@@ -177,7 +178,7 @@ __device__ __forceinline__ bool bxdf_sample(const DScene& sc, const Bxdf& b, Blu
     case BX_REFR_DIELECTRIC: {
       float fr = FrDielectric(CosTheta(wi), b.ior);
       if (alpha < 1e-4f) {
-        if (blue_get1d(sc, smp) < fr) {
+        if (smp_get1d(sc, smp) < fr) {
           bs.wo = Reflect(wi);
           bs.f = b.albedo * (fr / AbsCosTheta(bs.wo));
           bs.pdf = fr;
@@ -191,8 +192,8 @@ __device__ __forceinline__ bool bxdf_sample(const DScene& sc, const Bxdf& b, Blu
         return true;
       }
       TRDist d{alpha, alpha};
-      V3 wm = d.SampleWm(wi, blue_get2d(sc, smp));
-      if (blue_get1d(sc, smp) < fr) {
+      V3 wm = d.SampleWm(wi, smp_get2d(sc, smp));
+      if (smp_get1d(sc, smp) < fr) {
         V3 wo = Reflect(wi, wm);
         if (!SameHemisphere(wi, wo)) return false;
         bs.wo = wo;
@@ -212,28 +213,28 @@ __device__ __forceinline__ bool bxdf_sample(const DScene& sc, const Bxdf& b, Blu
     case BX_DIFF_DIELECTRIC: {
       float fr = FrDielectric(CosTheta(wi), b.ior);
       if (alpha < 1e-4f) {
-        if (blue_get1d(sc, smp) < fr) {
+        if (smp_get1d(sc, smp) < fr) {
           bs.wo = Reflect(wi);
           bs.f = V3(fr);
           bs.pdf = fr * AbsCosTheta(bs.wo);
           bs.is_delta = true;
         } else {
-          bs.wo = cosine_weighted_hemisphere(blue_get2d(sc, smp));
+          bs.wo = cosine_weighted_hemisphere(smp_get2d(sc, smp));
           bs.f = b.albedo * ((1 - fr) / kPi);
           bs.pdf = (1 - fr) * AbsCosTheta(bs.wo) / kPi;
         }
         return true;
       }
       TRDist d{alpha, alpha};
-      V3 wm = d.SampleWm(wi, blue_get2d(sc, smp));
-      if (blue_get1d(sc, smp) < fr) {
+      V3 wm = d.SampleWm(wi, smp_get2d(sc, smp));
+      if (smp_get1d(sc, smp) < fr) {
         V3 wo = Reflect(wi, wm);
         if (!SameHemisphere(wi, wo)) return false;
         bs.wo = wo;
         bs.f = V3(fr * d.D_G(wi, wm, wo) / (4 * CosTheta(wi) * CosTheta(wo)));
         bs.pdf = fr * d.pdf(wi, wm) / (4 * absdot(wi, wm));
       } else {
-        bs.wo = cosine_weighted_hemisphere(blue_get2d(sc, smp));
+        bs.wo = cosine_weighted_hemisphere(smp_get2d(sc, smp));
         bs.f = b.albedo * ((1 - fr) / kPi);
         bs.pdf = AbsCosTheta(bs.wo) * (1 - fr) / kPi;
       }

@@ -129,6 +129,9 @@ struct DScene {
   const uint8_t* sobol;
   const uint8_t* scramble;
   const uint8_t* rank;
+  // sampler of the current render (PB2_SAMPLER_*); SobolSampler::log2_spp / nbase4_digits (sampler.h:128-130,
+  // sampler.cpp:82-85)
+  int sampler_kind, sampler_seed, log2_spp, nbase4_digits;
   pb2_camera camera;
   unsigned long long* walk_stats;  // PB2_COUNT builds only: {closest nodes, closest prims, any nodes, any prims,
                                    // closest rays, any rays}; NULL otherwise

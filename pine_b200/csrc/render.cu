@@ -200,9 +200,9 @@ __device__ __forceinline__ bool with_probability(float prob, Rng& g) {  // sampl
   if (prob == 1) return true;
   return rng_nextf(g) < prob;
 }
-template <int MAT>
+template <int MAT, class Smp>
 __device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_material& m, V3 wi_world, V3 n,
-                                              float min_roughness, bool diffused, BlueSampler& smp, Rng& g) {
+                                              float min_roughness, bool diffused, Smp& smp, Rng& g) {
   Bxdf b;
   b.albedo = V3(m.color[0], m.color[1], m.color[2]);
   b.roughness = m.roughness;
@@ -220,7 +220,7 @@ __device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_materi
   if (MAT == PB2_MAT_SUBSURFACE) {
     b.ior = 1.4f;  // SubsurfaceMaterial::ior (material.h:103)
     float fr = FrDielectric(dot(wi_world, n), b.ior);
-    if (blue_get1d(sc, smp) < fr) { b.kind = BX_REFRACTIVE; b.roughness = pmax(m.roughness, min_roughness); }
+    if (smp_get1d(sc, smp) < fr) { b.kind = BX_REFRACTIVE; b.roughness = pmax(m.roughness, min_roughness); }
     else if (diffused) b.kind = BX_DIFFUSE;
     else b.kind = BX_BSSRDF;
   }
@@ -229,8 +229,9 @@ __device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_materi
 
 // BSSRDF::sample_p (bxdf.cpp:329-357): random walk inside the hit shape only. For analytic shapes
 // the reference's Shape::intersect leaves the exit interaction untouched (p = n = 0); reproduced.
+template <class Smp>
 __device__ inline bool bssrdf_walk(const DScene& sc, const Bxdf& b, int geom, V3 wi_world, Surf& it,
-                                   BlueSampler& smp, Rng& g, V3& beta, V3& wi_out) {
+                                   Smp& smp, Rng& g, V3& beta, V3& wi_out) {
   V3 p = it.p;
   V3 w = -wi_world;
   if (!Refract(wi_world, it.n, b.ior, w)) return false;
@@ -266,7 +267,7 @@ __device__ inline bool bssrdf_walk(const DScene& sc, const Bxdf& b, int geom, V3
       hit = shape_intersect(sc, gm.kind, gm.index, ray);
     }
     if (!hit) return false;
-    float t = -logf(1 - blue_get1d(sc, smp)) * sigma_t_inv;
+    float t = -logf(1 - smp_get1d(sc, smp)) * sigma_t_inv;
     if (ray.tmax < t) {
       wi_out = -w;
       it.p = exit_it.p;
@@ -274,7 +275,7 @@ __device__ inline bool bssrdf_walk(const DScene& sc, const Bxdf& b, int geom, V3
       return true;
     }
     p = ray.o + t * ray.d;
-    w = uniform_sphere(blue_get2d(sc, smp));
+    w = uniform_sphere(smp_get2d(sc, smp));
   }
   return false;
 }
@@ -355,7 +356,7 @@ __global__ void __launch_bounds__(256) k_shade_terminal(DScene sc, WaveView w, i
 }
 
 // class MAT: NEE + BSDF sample at a surface vertex (path.cpp:74-120)
-template <int MAT>
+template <int MAT, bool GENERIC_SAMPLER>
 __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int depth) {
   const int n = *list_count(w, depth, MAT);
   const int cur = depth & 1, nxt = cur ^ 1;
@@ -383,7 +384,7 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
       const pb2_material m = sc.materials[g.material];
       int pix = w.pixel0 + slot % w.pixels;
       int px = pix % w.width, py = w.row_begin + pix / w.width;
-      BlueSampler smp{px, py, w.sample0 + slot / w.pixels, w.dim[slot]};
+      PixelSamplerT<GENERIC_SAMPLER> smp{px, py, w.sample0 + slot / w.pixels, w.dim[slot]};
       Rng g_rng;
       constexpr bool uses_rng = MAT == PB2_MAT_UBER || MAT == PB2_MAT_SUBSURFACE;
       if (uses_rng) g_rng = load_rng(w.rng, pix);
@@ -409,8 +410,8 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
       // arguments of light_sampler.sample(p, get1d(), get2d()) right to left, lightsampler.h:27)
       V3 nee(0.0f);
       if (!bxdf_is_delta(bx)) {
-        V2 u2 = blue_get2d(sc, smp);
-        float u1 = blue_get1d(sc, smp);
+        V2 u2 = smp_get2d(sc, smp);
+        float u1 = smp_get1d(sc, smp);
         if (sc.n_lights > 0) {
           u1 *= sc.n_lights;
           int index = int(u1);
@@ -519,6 +520,25 @@ int sm_grid(int work_items, int block, int max_waves_per_sm) {
   return int(g > 0 ? g : kNumSMs);
 }
 
+int floor_log2(int v) {  // psl::log2i == hsb (psl/math.h:81,262)
+  int r = 0;
+  while (v > 1) { v >>= 1; r++; }
+  return r;
+}
+// Binds the sampler of the next render to the device scene: table set for BlueSobolSampler,
+// log2_spp / nbase4_digits for SobolSampler (sampler.h:128-130, SobolSampler::init sampler.cpp:82-85).
+int select_sampler(pb2_context* ctx, int kind, int spp, int seed) {
+  DScene& sc = ctx->scene;
+  sc.sampler_kind = kind;
+  sc.sampler_seed = seed;
+  sc.log2_spp = floor_log2(spp);
+  int res = std::max(sc.camera.width, sc.camera.height), pow2 = 1;
+  while (pow2 < res) pow2 <<= 1;  // psl::roundup2
+  sc.nbase4_digits = floor_log2(pow2) + (sc.log2_spp + 1) / 2;
+  if (kind == PB2_SAMPLER_BLUE) return activate_tables(ctx, spp);
+  return PB2_OK;
+}
+
 int check_params(pb2_context* ctx, const pb2_render_params* p) {
   if (!ctx || !p) { set_error("null argument"); return PB2_E_INVALID; }
   if (ctx->device < 0) { set_error("host-only context: no CUDA device, and there is no CPU fallback"); return PB2_E_CUDA; }
@@ -529,9 +549,20 @@ int check_params(pb2_context* ctx, const pb2_render_params* p) {
   }
   if (p->max_path_length > 250) { set_error("max_path_length > 250 is not supported"); return PB2_E_UNSUPPORTED; }
   const int h = ctx->scene.camera.height;
-  if (p->spp <= 0 || p->spp > 256 || (p->spp & (p->spp - 1))) {
-    set_error("spp must be BlueSobolSampler::spp(): a power of two <= 256");
-    return PB2_E_INVALID;
+  if (p->sampler == PB2_SAMPLER_BLUE) {
+    if (p->spp <= 0 || p->spp > 256 || (p->spp & (p->spp - 1))) {
+      set_error("spp must be BlueSobolSampler::spp(): a power of two <= 256");
+      return PB2_E_INVALID;
+    }
+  } else if (p->sampler == PB2_SAMPLER_SOBOL || p->sampler == PB2_SAMPLER_UNIFORM) {
+    if (p->spp <= 0) {  // sampler.h:16-17
+      set_error("`UniformSampler` should have positive samples per pixel");
+      return PB2_E_INVALID;
+    }
+    if (p->spp > 65536) { set_error("spp > 65536 is not supported"); return PB2_E_UNSUPPORTED; }
+  } else {
+    set_error("unknown sampler kind " + std::to_string(p->sampler) + " (HaltonSampler is not supported)");
+    return PB2_E_UNSUPPORTED;
   }
   if (p->row_begin < 0 || p->row_end > h || p->row_begin > p->row_end || p->sample_begin < 0 ||
       p->sample_end > p->spp || p->sample_begin > p->sample_end) {
@@ -548,7 +579,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   int rc = check_params(ctx, p);
   if (rc) return rc;
   PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
-  rc = activate_tables(ctx, p->spp);
+  rc = select_sampler(ctx, p->sampler, p->spp, p->sampler_seed);
   if (rc) return rc;
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
   const DScene& sc = ctx->scene;
@@ -736,12 +767,16 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
         if (depth + 1 < D) {
           const int sg = sm_grid(live, 128, 16);
           const unsigned mk = ctx->material_kinds;
-          if (mk & (1u << PB2_MAT_DIFFUSE)) { k_shade_mat<PB2_MAT_DIFFUSE><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
-          if (mk & (1u << PB2_MAT_METAL)) { k_shade_mat<PB2_MAT_METAL><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
-          if (mk & (1u << PB2_MAT_GLOSSY)) { k_shade_mat<PB2_MAT_GLOSSY><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
-          if (mk & (1u << PB2_MAT_GLASS)) { k_shade_mat<PB2_MAT_GLASS><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
-          if (mk & (1u << PB2_MAT_UBER)) { k_shade_mat<PB2_MAT_UBER><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
-          if (mk & (1u << PB2_MAT_SUBSURFACE)) { k_shade_mat<PB2_MAT_SUBSURFACE><<<sg, 128, 0, st>>>(sc, w, depth); launches++; }
+          const bool blue = sc.sampler_kind == PB2_SAMPLER_BLUE;
+#define PB2_SHADE(MAT)                                                      \
+  if (mk & (1u << MAT)) {                                                   \
+    if (blue) k_shade_mat<MAT, false><<<sg, 128, 0, st>>>(sc, w, depth);    \
+    else k_shade_mat<MAT, true><<<sg, 128, 0, st>>>(sc, w, depth);          \
+    launches++;                                                             \
+  }
+          PB2_SHADE(PB2_MAT_DIFFUSE) PB2_SHADE(PB2_MAT_METAL) PB2_SHADE(PB2_MAT_GLOSSY)
+          PB2_SHADE(PB2_MAT_GLASS) PB2_SHADE(PB2_MAT_UBER) PB2_SHADE(PB2_MAT_SUBSURFACE)
+#undef PB2_SHADE
         }
         mark(2);
         if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
@@ -852,13 +887,13 @@ __global__ void k_test_sampler(DScene sc, int px, int py, int sample_index, int 
   if (blockIdx.x || threadIdx.x) return;
   Rng g = rng_seed(murmur_pixel(px, py, sample_index));
   for (int i = 0; i < n_rand; i++) out_rand[i] = rng_nextf(g);
-  BlueSampler s{px, py, sample_index, 0};
+  PixelSampler s{px, py, sample_index, 0};
   for (int k = 0; k < n_samples; k++) {
     for (int c = 0; c < n_pattern; c++) {
       if (pattern[c] == '1') {
-        *out_draws++ = blue_get1d(sc, s);
+        *out_draws++ = smp_get1d(sc, s);
       } else {
-        V2 u = blue_get2d(sc, s);
+        V2 u = smp_get2d(sc, s);
         *out_draws++ = u.x;
         *out_draws++ = u.y;
       }
@@ -909,7 +944,7 @@ extern "C" int pb2_test_sampler(pb2_context* ctx, int spp, int px, int py, int s
                                 float* out_rand, const char* pattern, int n_samples, float* out_draws) {
   if (!ctx || ctx->device < 0) { set_error("no CUDA device, and there is no CPU fallback"); return PB2_E_CUDA; }
   PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
-  int rc = activate_tables(ctx, spp);
+  int rc = select_sampler(ctx, PB2_SAMPLER_BLUE, spp, 0);
   if (rc) return rc;
   int n_pattern = int(strlen(pattern)), width = 0;
   for (int i = 0; i < n_pattern; i++) width += pattern[i] == '1' ? 1 : 2;
@@ -926,6 +961,63 @@ extern "C" int pb2_test_sampler(pb2_context* ctx, int spp, int px, int py, int s
   if (n_rand) PB2_CUDA_CHECK(cudaMemcpy(out_rand, d_rand.ptr, size_t(n_rand) * 4, cudaMemcpyDeviceToHost));
   if (width * n_samples)
     PB2_CUDA_CHECK(cudaMemcpy(out_draws, d_draws.ptr, size_t(width) * n_samples * 4, cudaMemcpyDeviceToHost));
+  return PB2_OK;
+}
+
+extern "C" int pb2_test_sampler_kind(pb2_context* ctx, int sampler, int spp, int sampler_seed, int px, int py,
+                                     int sample_index, const char* pattern, int n_samples, float* out_draws) {
+  if (!ctx || ctx->device < 0) { set_error("no CUDA device, and there is no CPU fallback"); return PB2_E_CUDA; }
+  if (!ctx->scene_ready) { set_error("pb2_upload_scene has not succeeded on this context"); return PB2_E_STATE; }
+  pb2_render_params chk{};
+  chk.spp = spp; chk.max_path_length = 1; chk.row_end = ctx->scene.camera.height; chk.sample_end = spp;
+  chk.sampler = sampler;
+  int rc = check_params(ctx, &chk);
+  if (rc) return rc;
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  rc = select_sampler(ctx, sampler, spp, sampler_seed);
+  if (rc) return rc;
+  int n_pattern = int(strlen(pattern)), width = 0;
+  for (int i = 0; i < n_pattern; i++) width += pattern[i] == '1' ? 1 : 2;
+  DBuf d_rand, d_draws, d_pat;
+  PB2_CUDA_CHECK(d_rand.reserve(4));
+  PB2_CUDA_CHECK(d_draws.reserve(size_t(width) * n_samples * 4 + 4));
+  PB2_CUDA_CHECK(d_pat.reserve(n_pattern + 1));
+  PB2_CUDA_CHECK(cudaMemcpy(d_pat.ptr, pattern, n_pattern, cudaMemcpyHostToDevice));
+  k_test_sampler<<<1, 1, 0, ctx->stream>>>(ctx->scene, px, py, sample_index, 0, d_rand.as<float>(),
+                                           d_pat.as<char>(), n_pattern, n_samples, d_draws.as<float>());
+  ctx->counters.kernel_launches++;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  if (width * n_samples)
+    PB2_CUDA_CHECK(cudaMemcpy(out_draws, d_draws.ptr, size_t(width) * n_samples * 4, cudaMemcpyDeviceToHost));
+  return PB2_OK;
+}
+
+// Host evaluation of the SobolSampler / UniformSampler draw functions above (the same __host__ __device__
+// code the kernels inline): lets the CPU test-suite pin their integer arithmetic against the reference.
+extern "C" int pb2h_sampler_draws(int sampler, int spp, int sampler_seed, int width, int height, int px, int py,
+                                  int sample_index, const char* pattern, int n_samples, float* out_draws) {
+  if (sampler != PB2_SAMPLER_SOBOL && sampler != PB2_SAMPLER_UNIFORM) {
+    set_error("pb2h_sampler_draws: SobolSampler and UniformSampler only (BlueSampler reads device tables)");
+    return PB2_E_UNSUPPORTED;
+  }
+  if (spp <= 0 || !pattern || !out_draws) { set_error("invalid argument"); return PB2_E_INVALID; }
+  const int log2_spp = floor_log2(spp);
+  int pow2 = 1;
+  while (pow2 < std::max(width, height)) pow2 <<= 1;
+  const int nb4 = floor_log2(pow2) + (log2_spp + 1) / 2;
+  for (int k = 0; k < n_samples; k++) {
+    PixelSampler s{px, py, sample_index + k, 0};
+    for (const char* c = pattern; *c; c++) {
+      if (sampler == PB2_SAMPLER_SOBOL) {
+        if (*c == '1') { *out_draws++ = sobol_get1d(s, log2_spp, nb4); }
+        else { V2 u = sobol_get2d(s, log2_spp, nb4); *out_draws++ = u.x; *out_draws++ = u.y; }
+      } else {
+        const int n = *c == '1' ? 1 : 2;
+        for (int i = 0; i < n; i++) *out_draws++ = uniform_dim(s, sampler_seed, s.dim++);
+      }
+    }
+  }
   return PB2_OK;
 }
 

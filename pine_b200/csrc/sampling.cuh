@@ -53,11 +53,19 @@ __host__ __device__ __forceinline__ float rng_nextf(Rng& g) {
   return pmin(float(uint32_t(u ^ (u >> 32))) * 0x1p-32f, kOneMinusEpsilon);
 }
 
-// ---- BlueSobolSampler ---------------------------------------------------------------------------------
-struct BlueSampler {
+// ---- samplers: state of pine::Sampler's active alternative for one (pixel, sample) ------------------------
+// GENERIC = false compiles the BlueSobolSampler draws only (the sampler of every named configuration: its
+// shade kernels carry no dispatch); GENERIC = true dispatches on DScene::sampler_kind.
+template <bool GENERIC>
+struct PixelSamplerT {
   int px, py, index, dim;
 };
-__device__ __forceinline__ float blue_dim(const DScene& sc, const BlueSampler& s, int dim) {
+using PixelSampler = PixelSamplerT<true>;
+using BlueOnlySampler = PixelSamplerT<false>;
+
+// BlueSobolSampler (sampler.h:166-201, bluenoise_<N>spp.cpp:14-34)
+template <bool G>
+__device__ __forceinline__ float blue_dim(const DScene& sc, const PixelSamplerT<G>& s, int dim) {
   int pi = s.px & 127, pj = s.py & 127;
   int si = s.index & 255, sd = dim & 255;
   int tile = (pi + pj * 128) * 8;
@@ -66,11 +74,134 @@ __device__ __forceinline__ float blue_dim(const DScene& sc, const BlueSampler& s
   value ^= int(__ldg(sc.scramble + (sd % 8) + tile));
   return (0.5f + value) / 256.0f;
 }
-__device__ __forceinline__ float blue_get1d(const DScene& sc, BlueSampler& s) {
+
+// SobolSampler (sampler.h:83-164, sampler.cpp:82-113, lowdiscrepancy.h:73-80): all integer until the
+// final scale, so the draws are the reference's bit for bit.
+__host__ __device__ __forceinline__ uint64_t mix_bits(uint64_t v) {  // rng.h:81-88
+  v ^= (v >> 31); v *= 0x7fb5d329728ea185ull;
+  v ^= (v >> 27); v *= 0x81dadef4bc2dd44dull;
+  v ^= (v >> 33);
+  return v;
+}
+__host__ __device__ __forceinline__ uint64_t murmur_int(int v) {  // hash(int): 4 tail bytes, seed 0 (rng.h:9-65)
+  const uint64_t m = 0xc6a4a7935bd1e995ull;
+  const int r = 47;
+  uint64_t h = 0 ^ (4ull * m);
+  h ^= uint64_t(uint32_t(v));
+  h *= m;
+  h ^= h >> r; h *= m; h ^= h >> r;
+  return h;
+}
+__host__ __device__ __forceinline__ uint64_t spread_bits_64x2(uint64_t x) {  // left_shift_64x2 (vecmath.h)
+  x &= 0xffffffffull;
+  x = (x ^ (x << 16)) & 0x0000ffff0000ffffull;
+  x = (x ^ (x << 8)) & 0x00ff00ff00ff00ffull;
+  x = (x ^ (x << 4)) & 0x0f0f0f0f0f0f0f0full;
+  x = (x ^ (x << 2)) & 0x3333333333333333ull;
+  x = (x ^ (x << 1)) & 0x5555555555555555ull;
+  return x;
+}
+__host__ __device__ __forceinline__ uint32_t reverse_bits32(uint32_t x) {
+#ifdef __CUDA_ARCH__
+  return __brev(x);
+#else
+  x = (x & 0x55555555u) << 1 | (x & 0xaaaaaaaau) >> 1;
+  x = (x & 0x33333333u) << 2 | (x & 0xccccccccu) >> 2;
+  x = (x & 0x0f0f0f0fu) << 4 | (x & 0xf0f0f0f0u) >> 4;
+  x = (x & 0x00ff00ffu) << 8 | (x & 0xff00ff00u) >> 8;
+  return (x << 16) | (x >> 16);
+#endif
+}
+__host__ __device__ __forceinline__ uint32_t fast_owen(uint32_t v, uint32_t seed) {  // sampler.h:97-110
+  v = reverse_bits32(v);
+  v ^= v * 0x3d20adeau;
+  v += seed;
+  v *= (seed >> 16) | 1u;
+  v ^= v * 0x05526c56u;
+  v ^= v * 0x53a22864u;
+  return reverse_bits32(v);
+}
+// SobolMatrices32 restricted to the two dimensions the sampler uses (sobolmatrices.cpp:40-58): dimension
+// 0 is the bit reversal of the low 32 bits (rows >= 32 are zero), dimension 1 the Pascal-triangle
+// matrix v[i] = v[i-1] ^ (v[i-1] >> 1) from 0x80000000 (which repeats with period 32, as the table does).
+__host__ __device__ __forceinline__ uint32_t sobol_dim0(uint64_t a) { return reverse_bits32(uint32_t(a)); }
+__host__ __device__ __forceinline__ uint32_t sobol_dim1(uint64_t a) {
+  uint32_t v = 0, col = 0x80000000u;
+  for (; a != 0; a >>= 1, col ^= col >> 1)
+    if (a & 1) v ^= col;
+  return v;
+}
+__host__ __device__ __forceinline__ uint64_t sobol_sample_index(uint64_t sobol_index, int dimension, int log2_spp,
+                                                              int nbase4_digits) {  // sampler.cpp:87-113
+  // the 24 permutations of {0,1,2,3} in the reference's order, 2 bits per image, digit 0 lowest
+  const uint8_t perms[24] = {0xE4, 0xB4, 0xD8, 0x78, 0x6C, 0x9C, 0xE1, 0xB1, 0xC9, 0x39, 0x2D, 0x8D,
+                             0xC6, 0x36, 0xD2, 0x72, 0x4E, 0x1E, 0x27, 0x87, 0x1B, 0x4B, 0x63, 0x93};
+  uint64_t si = 0;
+  const bool only_power_of_2 = log2_spp & 1;
+  const int last_digit = only_power_of_2 ? 1 : 0;
+  for (int i = nbase4_digits - 1; i >= last_digit; --i) {
+    const int digit_shift = 2 * i - (only_power_of_2 ? 1 : 0);
+    int digit = int(sobol_index >> digit_shift) & 3;
+    const uint64_t higher_digits = sobol_index >> (digit_shift + 2);
+    const int p = int((mix_bits(higher_digits ^ uint64_t(0x55555555u * uint32_t(dimension))) >> 24) % 24);
+    digit = (perms[p] >> (2 * digit)) & 3;
+    si |= uint64_t(digit) << digit_shift;
+  }
+  if (only_power_of_2) {
+    const int digit = int(sobol_index & 1);
+    si |= uint64_t(digit ^ int(mix_bits((sobol_index >> 1) ^ uint64_t(0x55555555u * uint32_t(dimension))) & 1));
+  }
+  return si;
+}
+__host__ __device__ __forceinline__ float sobol_to_float(uint32_t v) { return pmin(float(v) * 0x1p-32f, kOneMinusEpsilon); }
+__host__ __device__ __forceinline__ uint64_t sobol_index_of(const PixelSampler& s, int log2_spp) {  // sampler.h:135-142
+  const uint64_t morton = (spread_bits_64x2(uint32_t(s.py)) << 1) | spread_bits_64x2(uint32_t(s.px));
+  // start_pixel(p, 0) then `sobol_index++` per sample (path.cpp:32-34): a sum, which carries into the
+  // Morton bits when spp is not a power of two, exactly as the reference's does
+  return (morton << log2_spp) + uint64_t(int64_t(s.index));
+}
+
+// SobolSampler::get1d / get2d (sampler.h:143-160): the dimension advances before the Owen seed is hashed
+__host__ __device__ __forceinline__ float sobol_get1d(PixelSampler& s, int log2_spp, int nbase4_digits) {
+  const uint64_t si = sobol_sample_index(sobol_index_of(s, log2_spp), s.dim, log2_spp, nbase4_digits);
+  s.dim += 1;
+  const uint64_t u = murmur_int(s.dim);
+  return sobol_to_float(fast_owen(sobol_dim0(si), uint32_t(u)));
+}
+__host__ __device__ __forceinline__ V2 sobol_get2d(PixelSampler& s, int log2_spp, int nbase4_digits) {
+  const uint64_t si = sobol_sample_index(sobol_index_of(s, log2_spp), s.dim, log2_spp, nbase4_digits);
+  s.dim += 2;
+  const uint64_t u = murmur_int(s.dim);
+  return V2(sobol_to_float(fast_owen(sobol_dim0(si), uint32_t(u))),
+            sobol_to_float(fast_owen(sobol_dim1(si), uint32_t(u >> 32))));
+}
+
+// UniformSampler: a draw per (pixel, sample, dimension) from the reference's generator
+__host__ __device__ __forceinline__ float uniform_dim(const PixelSampler& s, int seed, int dim) {
+  uint64_t key = murmur_pixel(s.px, s.py, s.index) ^ mix_bits(uint64_t(uint32_t(dim)) * 0x9E3779B97f4A7C15ull + uint64_t(uint32_t(seed)) + 1ull);
+  Rng g = rng_seed(key);
+  return rng_nextf(g);
+}
+
+template <bool G>
+__device__ __forceinline__ float smp_get1d(const DScene& sc, PixelSamplerT<G>& s) {
+  if constexpr (G) {
+    if (sc.sampler_kind == PB2_SAMPLER_SOBOL) return sobol_get1d(s, sc.log2_spp, sc.nbase4_digits);
+    if (sc.sampler_kind == PB2_SAMPLER_UNIFORM) return uniform_dim(s, sc.sampler_seed, s.dim++);
+  }
   if (s.dim >= 256) s.dim = 2;
   return blue_dim(sc, s, s.dim++);
 }
-__device__ __forceinline__ V2 blue_get2d(const DScene& sc, BlueSampler& s) {
+template <bool G>
+__device__ __forceinline__ V2 smp_get2d(const DScene& sc, PixelSamplerT<G>& s) {
+  if constexpr (G) {
+    if (sc.sampler_kind == PB2_SAMPLER_SOBOL) return sobol_get2d(s, sc.log2_spp, sc.nbase4_digits);
+    if (sc.sampler_kind == PB2_SAMPLER_UNIFORM) {
+      const int d = s.dim;
+      s.dim += 2;
+      return V2(uniform_dim(s, sc.sampler_seed, d), uniform_dim(s, sc.sampler_seed, d + 1));
+    }
+  }
   if (s.dim + 1 >= 256) s.dim = 2;
   int d = s.dim;
   s.dim += 2;

@@ -60,6 +60,54 @@ class BlueSampler:
         return self.samples_per_pixel
 
 
+class SobolSampler:
+    """pine::SobolSampler (sampler.h:83-164): Owen-scrambled (0,2)-sequence over a Morton-ordered pixel
+    index; any positive spp. Draws are bit-identical to the reference's."""
+    kind = A.SAMPLER_SOBOL
+
+    def __init__(self, samples_per_pixel):
+        if samples_per_pixel <= 0:
+            raise ValueError("samples per pixel must be positive")
+        self.samples_per_pixel = int(samples_per_pixel)
+        self.seed = 0
+
+    def spp(self):
+        return self.samples_per_pixel
+
+
+class UniformSampler:
+    """pine::UniformSampler (sampler.h:13-39): independent uniform draws. The reference shares one RNG
+    per worker thread; here each (pixel, sample, dimension) has its own draw (include/pine_b200.h)."""
+    kind = A.SAMPLER_UNIFORM
+
+    def __init__(self, samples_per_pixel, seed=0):
+        if samples_per_pixel <= 0:
+            raise ValueError("`UniformSampler` should have positive samples per pixel")
+        self.samples_per_pixel = int(samples_per_pixel)
+        self.seed = int(seed)
+
+    def spp(self):
+        return self.samples_per_pixel
+
+
+def _sampler_of(spp_or_sampler):
+    """(spp, kind, seed) of a sampler object, or of BlueSampler's already-rounded spp given as an int."""
+    if isinstance(spp_or_sampler, (int, np.integer)):
+        return int(spp_or_sampler), A.SAMPLER_BLUE, 0
+    return spp_or_sampler.spp(), getattr(spp_or_sampler, "kind", A.SAMPLER_BLUE), getattr(spp_or_sampler, "seed", 0)
+
+
+def host_sampler_draws(sampler, size, px, py, sample_index, pattern, n_samples):
+    """Draws of a SobolSampler / UniformSampler object evaluated by the library's host build of the device
+    draw functions (pb2h_sampler_draws; test hook, no GPU, no film)."""
+    spp, kind, seed = _sampler_of(sampler)
+    width = sum(1 if c == "1" else 2 for c in pattern)
+    d = np.zeros(max(width * n_samples, 1), np.float32)
+    A.check(A.lib().pb2h_sampler_draws(kind, spp, seed, size[0], size[1], px, py, sample_index,
+                                       pattern.encode(), n_samples, d.ctypes.data))
+    return d[:width * n_samples].reshape(n_samples, width)
+
+
 class Backend:
     """One pb2_context (one GPU). `device=-1` makes a host-only context (BVH builder inspection)."""
 
@@ -98,8 +146,13 @@ class Backend:
         self._tables_loaded.add(spp)
 
     def _params(self, spp, depth, rows=None, samples=None, accel=0, flags=0):
+        """`spp`: an int (BlueSampler's spp) or a sampler object (BlueSampler/SobolSampler/UniformSampler)."""
+        spp, kind, seed = _sampler_of(spp)
+        if kind == A.SAMPLER_BLUE:
+            self.upload_tables(spp)
         p = A.RenderParams()
         p.spp, p.max_path_length = spp, depth
+        p.sampler, p.sampler_seed = kind, seed
         p.row_begin, p.row_end = rows if rows else (0, self.size[1])
         p.sample_begin, p.sample_end = samples if samples else (0, spp)
         p.accel, p.flags = accel, flags
@@ -112,7 +165,6 @@ class Backend:
     def render(self, spp, depth, rows=None, samples=None, accel=0, out=None, flags=0):
         """-> film float32 [h, w, 4] in host memory (pre-tonemap). `out` may be any writable
         C-contiguous float32 buffer object of that size (e.g. a pinned torch tensor's numpy view)."""
-        self.upload_tables(spp)
         w, h = self.size
         film = out if out is not None else np.empty((h, w, 4), np.float32)
         p = self._params(spp, depth, rows, samples, accel, flags)
@@ -142,7 +194,6 @@ class Backend:
 
     def render_device(self, spp, depth, rows=None, samples=None, accel=0, stream=None, flags=0):
         """-> device pointer (int) of the float4 film owned by the context."""
-        self.upload_tables(spp)
         p = self._params(spp, depth, rows, samples, accel, flags)
         ptr = C.c_void_p()
         A.check(self.L.pb2_render_device(self.h, C.byref(p), stream, C.byref(ptr)))
@@ -186,6 +237,17 @@ class Backend:
                                         pattern.encode(), n_samples, d.ctypes.data))
         return r[:n_rand], d[:width * n_samples].reshape(n_samples, width)
 
+    def test_sampler_kind(self, sampler, px, py, sample_index, pattern, n_samples):
+        """get1d/get2d draws of `sampler` (an object of this module) for the uploaded scene's film size."""
+        spp, kind, seed = _sampler_of(sampler)
+        if kind == A.SAMPLER_BLUE:
+            self.upload_tables(spp)
+        width = sum(1 if c == "1" else 2 for c in pattern)
+        d = np.zeros(max(width * n_samples, 1), np.float32)
+        A.check(self.L.pb2_test_sampler_kind(self.h, kind, spp, seed, px, py, sample_index, pattern.encode(),
+                                             n_samples, d.ctypes.data))
+        return d[:width * n_samples].reshape(n_samples, width)
+
     def primary_rays(self, si=0):
         w, h = self.size
         rays = np.empty((w * h, 8), np.float32)
@@ -227,7 +289,7 @@ class PathIntegrator:
         if self.backend is None:
             self.backend = Backend(self.device)
         self.backend.upload_scene(scene)
-        film = self.backend.render(self.sampler.spp(), self.max_path_length, accel=self.accel)
+        film = self.backend.render(self.sampler, self.max_path_length, accel=self.accel)
         scene.camera.film().pixels = film
         scene._backend = self.backend
         return film

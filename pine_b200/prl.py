@@ -9,7 +9,7 @@ this is not it. It interprets exactly the grammar those files use:
 and binds the names the scripts call to the builder interface of `pine_b200.Scene` /
 `oracle.ref.RefScene` (program_context.cpp / *_context functions register the same names):
   Scene, Rect, Box, AABB, Cone, Sphere, Disk, Triangle, Diffuse, Metal, Glossy, Glass, Subsurface,
-  Emissive, translate, rotate_x/y/z, scale, ThinLenCamera, Film, Uncharted2, ACES, BlueSampler,
+  Emissive, translate, rotate_x/y/z, scale, ThinLenCamera, Film, Uncharted2, ACES, BlueSampler, SobolSampler, UniformSampler,
   PathIntegrator, X/Y/Z.
 Arithmetic follows the JIT's types: int stays int, anything with a float is binary32, the inclusive
 float loop `a ~ s ~ b` accumulates in binary32 (jit.cpp:1534-1541), matrices multiply through the
@@ -183,8 +183,18 @@ class _Camera:
 
 
 class _Sampler:
-    def __init__(self, spp):
-        self.spp = int(spp)
+    name = "BlueSampler"
+
+    def __init__(self, spp, seed=0):
+        self.spp, self.seed = int(spp), int(seed)
+
+
+class _SobolSampler(_Sampler):
+    name = "SobolSampler"
+
+
+class _UniformSampler(_Sampler):
+    name = "UniformSampler"
 
 
 def _f32(v):
@@ -287,6 +297,9 @@ class _Integrator:
 
     def render(self, scene):
         scene.config = {"spp": self.sampler.spp, "depth": self.depth}
+        if self.sampler.name != "BlueSampler":
+            scene.config["sampler"] = self.sampler.name
+            scene.config["sampler_seed"] = self.sampler.seed
         if scene.on_render:
             scene.on_render(scene, self.sampler.spp, self.depth)
 
@@ -322,7 +335,8 @@ def _globals(make_scene):
         "rotate_z": lambda r: mat4.rotate_z(float(_f32(r))),
         "Film": lambda size, tm="uncharted2": _Film(size, tm),
         "Uncharted2": lambda: "uncharted2", "ACES": lambda: "aces",
-        "ThinLenCamera": _Camera, "BlueSampler": _Sampler, "PathIntegrator": _Integrator,
+        "ThinLenCamera": _Camera, "BlueSampler": _Sampler, "SobolSampler": _SobolSampler,
+        "UniformSampler": _UniformSampler, "PathIntegrator": _Integrator,
         "X": [1, 0, 0], "Y": [0, 1, 0], "Z": [0, 0, 1],
     }
 
@@ -413,7 +427,11 @@ def run_file(path, device=0):
     films = {}
 
     def on_render(sp, spp, depth):
-        integ = I.PathIntegrator(I.BlueSampler(spp), depth, device=device)
+        kind = sp.config.get("sampler", "BlueSampler")
+        sampler = (I.SobolSampler(spp) if kind == "SobolSampler" else
+                   I.UniformSampler(spp, sp.config.get("sampler_seed", 0)) if kind == "UniformSampler" else
+                   I.BlueSampler(spp))
+        integ = I.PathIntegrator(sampler, depth, device=device)
         films[id(sp)] = integ.render(sp.target)
 
     def on_save(sp, out):

@@ -53,6 +53,23 @@ def kats():
     np.savez_compressed(os.path.join(OUT, "kats.npz"), **out)
 
 
+SOBOL_CASES = [(1, (64, 64)), (3, (640, 640)), (16, (640, 640)), (100, (1024, 768)), (256, (720, 360)),
+               (4096, (3840, 2160))]
+SOBOL_PIXELS = [(0, 0), (37, 411), (639, 12), (3839, 2159)]
+
+
+def sobol_kats():
+    """SobolSampler(spp) after init(size), start_pixel(p, 0): 6 samples of the draw pattern 21221, plus a
+    70-draw sample (dimension > 128), for power-of-two, odd-log2 and non-power-of-two spp."""
+    out = {"cases": np.array([(s, w, h) for s, (w, h) in SOBOL_CASES], np.int32),
+           "pixels": np.array(SOBOL_PIXELS, np.int32)}
+    for spp, size in SOBOL_CASES:
+        for i, (px, py) in enumerate(SOBOL_PIXELS):
+            out[f"draws_{spp}_{i}"] = ref.sampler_stream_kind("sobol", spp, size, px, py, 0, "21221", min(6, spp))
+        out[f"long_{spp}"] = ref.sampler_stream_kind("sobol", spp, size, 5, 7, 0, "2" * 60 + "1" * 10, 1)
+    np.savez_compressed(os.path.join(OUT, "sobol_kats.npz"), **out)
+
+
 def scene(name):
     fn, kw, spp, depth = common.SMALL_SCENES[name]
     R = ref.RefScene()
@@ -105,6 +122,7 @@ if __name__ == "__main__":
     if not ref.available():
         raise SystemExit("oracle/_ref/libpine_ref.so missing: make -C oracle ref")
     kats()
+    sobol_kats()
     camera_lens()
     for name in common.SMALL_SCENES:
         scene(name)
