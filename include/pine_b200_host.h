@@ -20,7 +20,9 @@ enum pb2h_mat_op {
   PB2H_ROTATE_Y = 3,  /* a = {rad}           vecmath.h:1144 */
   PB2H_ROTATE_Z = 4,  /* a = {rad}           vecmath.h:1126 */
   PB2H_INVERSE = 5,   /* a = m[16]           vecmath.cpp:104 */
-  PB2H_LOOK_AT = 6    /* a = from[3], to[3]  vecmath.h:1172 */
+  PB2H_LOOK_AT = 6,   /* a = from[3], to[3]  vecmath.h:1172 */
+  PB2H_QUAT = 7,      /* a = {w, x, y, z}    q2m, fileio.cpp:127-144 */
+  PB2H_TRANSPOSE = 8  /* a = m[16] */
 };
 void pb2h_make_rect(const float* pos, const float* ex, const float* ey, int flip, pb2_rect* out);
 void pb2h_make_obb(const float* lo, const float* hi, const float* m_colmajor, pb2_obb* out);
@@ -31,6 +33,10 @@ void pb2h_make_camera(int w, int h, int tonemapper, const float* from, const flo
                       float len_radius, float focus, pb2_camera* out);
 void pb2h_mat4(int op, const float* a, float* out_colmajor);
 void pb2h_mat4_mul(const float* a, const float* b, float* out_colmajor);
+/* Mesh::apply(m) (geometry.cpp:652-658) in place: points by m, normals by transpose(inverse(mat3(m))),
+ * renormalised. Used by the glTF loader (scene_from_gltf, fileio.cpp:146-327). */
+void pb2h_mesh_apply(const float* m_colmajor, float* vertices, size_t n_vertices, float* normals,
+                     size_t n_normals);
 int pb2h_round_spp(int spp);
 /* Host evaluation of the device draw functions of SobolSampler (sampler.h:83-164, sampler.cpp:82-113)
  * and UniformSampler (the same __host__ __device__ code the kernels inline; test hook, no GPU):

@@ -143,8 +143,15 @@ class RefScene:
                               0 if tonemapper == "uncharted2" else 1, _fp(a), _fp(b),
                               C.c_float(fov), C.c_float(len_radius), C.c_float(focus))
 
-    def load_gltf(self, path):
-        return self.L.ref_load_gltf(self.h, path.encode())
+    def load_gltf(self, path, has_camera=False):
+        """scene_from_gltf(scene, path) (fileio.cpp:146-327); `has_camera`: the file carries a camera node,
+        so the film size is read back from the scene it set."""
+        n = self.L.ref_load_gltf(self.h, path.encode())
+        if has_camera:
+            wh = (C.c_int * 2)()
+            self.L.ref_camera_size(self.h, wh)
+            self.size = (int(wh[0]), int(wh[1]))
+        return n
 
     # ---- reference operations ----
     def render(self, spp, depth, sampler="blue"):

@@ -174,6 +174,12 @@ void ref_set_camera(void* h, int w, int hgt, int tonemapper, const float* from, 
   S.scene.set_camera(ThinLenCamera(Film(vec2i(w, hgt), tm), v3(from), v3(to), fov, len_radius,
                                    focus));
 }
+// Film size of the scene's camera (a glTF camera node sets it inside scene_from_gltf, fileio.cpp:308-321)
+void ref_camera_size(void* h, int* wh) {
+  auto size = ((RefScene*)h)->scene.camera.film().size();
+  wh[0] = size.x;
+  wh[1] = size.y;
+}
 int ref_num_geometries(void* h) { return int(((RefScene*)h)->scene.geometries.size()); }
 int ref_num_lights(void* h) { return int(((RefScene*)h)->scene.lights.size()); }
 int ref_num_threads() { return n_threads(); }

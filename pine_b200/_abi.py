@@ -125,7 +125,7 @@ ABI_SYMBOLS = [
     "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler", "pb2_test_sampler_kind",
     "pb2_test_primary_rays", "pb2_get_counters", "pb2_debug_walk_stats", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
     "pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone", "pb2h_make_triangle",
-    "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_round_spp", "pb2h_sampler_draws",
+    "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_mesh_apply", "pb2h_round_spp", "pb2h_sampler_draws",
 ]
 
 _lib = None
@@ -183,6 +183,7 @@ def lib():
                                        C.c_float, C.POINTER(Camera)]
         L.pb2h_mat4.argtypes = [C.c_int, fp, fp]
         L.pb2h_mat4_mul.argtypes = [fp, fp, fp]
+        L.pb2h_mesh_apply.argtypes = [fp, fp, C.c_size_t, fp, C.c_size_t]
         L.pb2h_sampler_draws.argtypes = [C.c_int] * 8 + [C.c_char_p, C.c_int, C.c_void_p]
         for name in ("pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone",
                      "pb2h_make_triangle", "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul"):

@@ -36,10 +36,19 @@ void pb2h_mat4(int op, const float* a, float* out_colmajor) {
     case PB2H_ROTATE_Z: m = m4_rotate_z(a[0]); break;
     case PB2H_INVERSE: m = m4_inverse(ld_m4(a)); break;
     case PB2H_LOOK_AT: m = m4_look_at(ld3(a), ld3(a + 3)); break;
+    case PB2H_QUAT: m = m4_from_quat(a[0], a[1], a[2], a[3]); break;
+    case PB2H_TRANSPOSE: m = m4_transpose(ld_m4(a)); break;
   }
   st_m4(out_colmajor, m);
 }
 void pb2h_mat4_mul(const float* a, const float* b, float* out) { st_m4(out, m4_mul(ld_m4(a), ld_m4(b))); }
+void pb2h_mesh_apply(const float* m_colmajor, float* vertices, size_t n_vertices, float* normals,
+                     size_t n_normals) {  // Mesh::apply (geometry.cpp:652-658)
+  const M4 m = ld_m4(m_colmajor);
+  for (size_t i = 0; i < n_vertices; i++) st3(vertices + 3 * i, mul_point(m, ld3(vertices + 3 * i)));
+  const M3 m3 = transpose(m3_inverse(upper3(m)));
+  for (size_t i = 0; i < n_normals; i++) st3(normals + 3 * i, normalize(m3 * ld3(normals + 3 * i)));
+}
 int pb2h_round_spp(int spp) {  // BlueSobolSampler ctor (sampler.cpp:115-121): clamp 256, roundup2
   if (spp > 256) spp = 256;
   if (spp < 1) return 0;

@@ -51,6 +51,40 @@ inline M4 m4_mul(const M4& a, const M4& b) {
     }
   return ret;
 }
+// q2m(a, b, c, d) of the glTF loader: unit quaternion (w = a, x = b, y = c, z = d) to a rotation matrix
+// (fileio.cpp:127-144); every sum is evaluated left to right in binary32.
+inline M4 m4_from_quat(float a, float b, float c, float d) {
+  return m4_rows(a * a + b * b - c * c - d * d, 2 * b * c - 2 * a * d, 2 * b * d + 2 * a * c, 0,
+                 2 * b * c + 2 * a * d, a * a - b * b + c * c - d * d, 2 * c * d - 2 * a * b, 0,
+                 2 * b * d - 2 * a * c, 2 * c * d + 2 * a * b, a * a - b * b - c * c + d * d, 0,
+                 0, 0, 0, 1);
+}
+inline M4 m4_transpose(const M4& m) {
+  M4 r;
+  for (int c = 0; c < 4; c++)
+    for (int k = 0; k < 4; k++) r[c][k] = m[k][c];
+  return r;
+}
+// inverse(mat3) (vecmath.cpp:81-103): adjugate entry by entry, then every entry divided by det
+inline M3 m3_inverse(const M3& m) {
+  M3 r;
+  float det = m[0][0] * (m[1][1] * m[2][2] - m[2][1] * m[1][2]) +
+              m[1][0] * (m[2][1] * m[0][2] - m[0][1] * m[2][2]) +
+              m[2][0] * (m[0][1] * m[1][2] - m[1][1] * m[0][2]);
+  if (det == 0) return r;
+  r[0][0] = m[1][1] * m[2][2] - m[2][1] * m[1][2];
+  r[0][1] = m[2][1] * m[0][2] - m[0][1] * m[2][2];
+  r[0][2] = m[0][1] * m[1][2] - m[1][1] * m[0][2];
+  r[1][0] = m[1][2] * m[2][0] - m[2][2] * m[1][0];
+  r[1][1] = m[2][2] * m[0][0] - m[0][2] * m[2][0];
+  r[1][2] = m[0][2] * m[1][0] - m[1][2] * m[0][0];
+  r[2][0] = m[1][0] * m[2][1] - m[2][0] * m[1][1];
+  r[2][1] = m[2][0] * m[0][1] - m[0][0] * m[2][1];
+  r[2][2] = m[0][0] * m[1][1] - m[1][0] * m[0][1];
+  for (int c = 0; c < 3; c++)
+    for (int k = 0; k < 3; k++) r[c][k] /= det;
+  return r;
+}
 // Cofactor inverse with the reference's index pattern and summation order (vecmath.cpp:104-131).
 inline M4 m4_inverse(const M4& m) {
   M4 r;

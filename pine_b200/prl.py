@@ -245,6 +245,7 @@ class SceneProxy:
     def __init__(self, target, on_render=None, on_save=None):
         self.target, self.on_render, self.on_save = target, on_render, on_save
         self.named, self.camera, self.config = {}, None, {}
+        self.search_dirs = []
 
     def _material(self, m):
         if isinstance(m, str):
@@ -279,6 +280,25 @@ class SceneProxy:
             self.target.add_triangle(_vec(p[0]), _vec(p[1]), _vec(p[2]), mat)
         else:
             raise PrlError(f"shape {k} is not supported by the CUDA path")
+
+    def load(self, filename, m=None):
+        """scene.load("file.glb"[, mat4]) (fileio.cpp:584-589): scene_from_gltf into this scene. The name is
+        tried as given (the reference resolves it against the working directory), then against the
+        script's directory and its parent."""
+        import os
+        if not isinstance(filename, str):
+            raise PrlError("scene.load expects a file name")
+        tried = [filename] + [os.path.join(d, filename) for d in self.search_dirs]
+        path = next((t for t in tried if os.path.isfile(t)), None)
+        if path is None:
+            raise PrlError(f"scene.load: no such file {filename!r}")
+        if hasattr(self.target, "load_gltf"):  # oracle.ref.RefScene: the reference's own loader
+            if m is not None:
+                raise PrlError("scene.load with a transform is not wired to the reference harness")
+            self.target.load_gltf(path)
+        else:
+            from . import gltf
+            gltf.scene_from_gltf(self.target, path, m)
 
     def set(self, cam):
         if not isinstance(cam, _Camera):
@@ -344,9 +364,11 @@ def _globals(make_scene):
 class Interpreter:
     def __init__(self, target_factory, on_render=None, on_save=None):
         self.scenes = []
+        self.search_dirs = []
 
         def make_scene():
             s = SceneProxy(target_factory(), on_render, on_save)
+            s.search_dirs = self.search_dirs
             self.scenes.append(s)
             return s
         self.env = _globals(make_scene)
@@ -413,10 +435,13 @@ class _CameraHandle:
         return _FilmHandle(self.scene)
 
 
-def load(text, target_factory, on_render=None, on_save=None):
+def load(text, target_factory, on_render=None, on_save=None, search_dirs=()):
     """Run a script against builders made by `target_factory()`; -> list of SceneProxy (each with
-    .target, .config = {"spp", "depth", "save"} as the script asked)."""
-    return Interpreter(target_factory, on_render, on_save).run(text)
+    .target, .config = {"spp", "depth", "save"} as the script asked). `search_dirs`: where scene.load
+    looks for a file it cannot find relative to the working directory."""
+    it = Interpreter(target_factory, on_render, on_save)
+    it.search_dirs = list(search_dirs)
+    return it.run(text)
 
 
 def run_file(path, device=0):
@@ -436,5 +461,7 @@ def run_file(path, device=0):
 
     def on_save(sp, out):
         I.save_film(sp.target.camera.film(), out, scene=sp.target)
+    import os
+    here = os.path.dirname(os.path.abspath(path))
     with open(path) as f:
-        return load(f.read(), Scene, on_render, on_save)
+        return load(f.read(), Scene, on_render, on_save, search_dirs=(here, os.path.dirname(here)))

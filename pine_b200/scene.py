@@ -236,6 +236,11 @@ class Scene:
               "mesh": lambda: self.add_mesh(*s.args, mat, **s.kw)}[s.kind]
         return fn()
 
+    def load(self, filename, m=None):
+        """scene.load("file.glb"[, mat4]) (fileio.cpp:584-589)"""
+        from .gltf import scene_from_gltf
+        return scene_from_gltf(self, filename, m)
+
     def set(self, camera):
         self.camera = camera
         f = camera.film()

@@ -46,6 +46,16 @@ def shadow_from(sec, seed):
     return sh
 
 
+def ray_fan(origin, n, seed):
+    """n rays {o, d, tmin = 0, tmax} in uniformly random directions from one point."""
+    rng = np.random.RandomState(seed)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, :3], rays[:, 3:6], rays[:, 7] = origin, d, 3.0e38
+    return rays
+
+
 def relmse(a, b, eps=1e-2):
     a, b = a[..., :3].astype(np.float64), b[..., :3].astype(np.float64)
     return float(((a - b) ** 2 / (b ** 2 + eps)).mean())

@@ -70,6 +70,28 @@ def sobol_kats():
     np.savez_compressed(os.path.join(OUT, "sobol_kats.npz"), **out)
 
 
+def gltf_kats():
+    """scene_from_gltf (fileio.cpp:146-327) on tests/golden/room_like.glb (written by tests/gltf_fixture.py):
+    camera rays, closest hits of the camera rays and of a spherical ray fan from inside the room, the film
+    at 4 spp and a SobolSampler(256) film, all from the reference's own loader + integrator."""
+    path = os.path.join(OUT, "room_like.glb")
+    R = ref.RefScene()
+    out = {"n_geometries": np.array([R.load_gltf(path, has_camera=True)], np.int32),
+           "size": np.array(R.size, np.int32)}
+    rays = R.primary_rays(0)
+    out["primary0"] = rays
+    fan = common.ray_fan((0.05, 1.2, 0.1), 20000, 5)
+    out["fan"] = fan
+    for tag, r in (("p", rays), ("f", fan)):
+        h = R.trace_closest(r, surf=True)
+        for k in ("geom", "prim", "t", "surf"):
+            out[f"{tag}_{k}"] = h[k]
+    out["geometry_aabbs"] = R.geometry_aabbs()
+    out["film"], _ = R.render(4, 5)
+    out["film_sobol256"], _ = R.render(256, 5, sampler="sobol")
+    np.savez_compressed(os.path.join(OUT, "room_like.npz"), **out)
+
+
 def scene(name):
     fn, kw, spp, depth = common.SMALL_SCENES[name]
     R = ref.RefScene()
@@ -123,6 +145,7 @@ if __name__ == "__main__":
         raise SystemExit("oracle/_ref/libpine_ref.so missing: make -C oracle ref")
     kats()
     sobol_kats()
+    gltf_kats()
     camera_lens()
     for name in common.SMALL_SCENES:
         scene(name)
