@@ -98,7 +98,23 @@ typedef struct pb2_material {
   float color[3]; /* albedo, or emitted radiance for EMISSIVE */
   float roughness, ior, metallic, transmission;
   float sigma_s[3];
+  /* UBER only: image nodes of a glTF material (scene_from_gltf, fileio.cpp:285-292). 1-BASED index into
+   * pb2_scene_desc.textures, 0 = none (a zero-initialised material has no textures).
+   * color_texture: albedo = NodeImage(NodeUV(), image) (node.cpp:20-23) replaces `color`;
+   * roughness_texture: roughness = NodeComponent(NodeImage(...), 1), metallic_texture: metallic =
+   * NodeComponent(NodeImage(...), 2) (node.h:181-193) replace `roughness` / `metallic`. */
+  int32_t color_texture, roughness_texture, metallic_texture;
 } pb2_material;
+
+/* pine::Image holding Array2d<vec4u8> (image.h:11; what tinygltf hands scene_from_gltf): row-major
+ * texel (x, y) at rgba[4 * (x + y * width)], row 0 first. A lookup is NEAREST with wrap:
+ * texel = min(int(size * fract(uv)), size - 1), value = pow(byte / 255, 2.2) per channel
+ * (Image::operator[], image.cpp:7-18) -- evaluated through a 256-entry table the HOST fills with its own
+ * powf, so albedo bits equal the reference's on the same machine. */
+typedef struct pb2_texture {
+  const uint8_t* rgba;
+  int32_t width, height;
+} pb2_texture;
 
 /* One entry of Scene::geometries (scene.h:37), in the scene's order: geometry index == position. */
 typedef struct pb2_geometry {
@@ -131,6 +147,7 @@ typedef struct pb2_scene_desc {
    * (scene.cpp:19-20 adds one per Emissive geometry). Delta and environment lights: unsupported. */
   const int32_t* light_geometries; uint32_t n_lights;
   pb2_camera camera;
+  const pb2_texture* textures;     uint32_t n_textures; /* may be NULL / 0 */
 } pb2_scene_desc;
 
 typedef struct pb2_render_params {

@@ -55,7 +55,13 @@ class Mesh(C.Structure):
 
 class Material(C.Structure):
     _fields_ = [("kind", C.c_int32), ("color", f3), ("roughness", C.c_float), ("ior", C.c_float),
-                ("metallic", C.c_float), ("transmission", C.c_float), ("sigma_s", f3)]
+                ("metallic", C.c_float), ("transmission", C.c_float), ("sigma_s", f3),
+                ("color_texture", C.c_int32), ("roughness_texture", C.c_int32),
+                ("metallic_texture", C.c_int32)]  # 1-based, 0 = none
+
+
+class Texture(C.Structure):
+    _fields_ = [("rgba", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32)]
 
 
 class Geometry(C.Structure):
@@ -78,7 +84,7 @@ class SceneDesc(C.Structure):
                 _arr("cones", Cone) + _arr("rects", Rect) + _arr("disks", Disk) +
                 _arr("meshes", Mesh) +
                 [("light_geometries", C.POINTER(C.c_int32)), ("n_lights", C.c_uint32),
-                 ("camera", Camera)])
+                 ("camera", Camera)] + _arr("textures", Texture))
 
 
 class RenderParams(C.Structure):

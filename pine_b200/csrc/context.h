@@ -67,6 +67,9 @@ struct HostScene {
   std::vector<float> verts, normals, uvs;
   std::vector<uint32_t> tris;
   std::vector<pb2_material> materials;
+  std::vector<uint32_t> texels;
+  std::vector<DTexture> textures;
+  std::vector<float> srgb_lut;
   std::vector<pb2_aabb> aabbs;
   std::vector<pb2_obb> obbs;
   std::vector<pb2_sphere> spheres;
@@ -100,7 +103,7 @@ struct pb2_context {
   pb2::DScene scene{};  // device pointers
   pb2::DBuf nodes2, nodes8, leaves, wide_prims, box_shapes, leaf_prims, top_prims, meshes, geoms, materials, lights;
   pb2::DBuf aabbs, obbs, spheres, triangles, cones, rects, disks;
-  pb2::DBuf verts, tris, normals, uvs;
+  pb2::DBuf verts, tris, normals, uvs, texels, textures, srgb_lut;
   pb2::DBuf tab_sobol, tab_scramble, tab_rank;
   int tables_spp = 0;
   pb2::SamplerTables tables[9];  // index = log2(spp)

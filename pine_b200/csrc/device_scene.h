@@ -93,6 +93,11 @@ struct DBoxShape {
   int32_t kind, index, gate, geom;
 };
 
+struct DTexture {
+  uint32_t offset;  // first texel in DScene::texels
+  int32_t width, height;
+};
+
 struct DScene {
   const DNode2* nodes2;
   const DNode8* nodes8;
@@ -125,6 +130,11 @@ struct DScene {
   const uint32_t* tris;
   const float* normals;
   const float* uvs;
+  // image nodes of Uber materials (pb2_texture): texel pool, per-texture {offset, w, h}, and the host-made
+  // table byte -> pow(byte / 255, 2.2) (Image::operator[], image.cpp:7-18)
+  const uint32_t* texels;  // r | g << 8 | b << 16 | a << 24
+  const DTexture* textures;
+  const float* srgb_lut;
   // sampler tables for the active spp variant
   const uint8_t* sobol;
   const uint8_t* scramble;

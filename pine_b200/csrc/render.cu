@@ -200,12 +200,27 @@ __device__ __forceinline__ bool with_probability(float prob, Rng& g) {  // sampl
   if (prob == 1) return true;
   return rng_nextf(g) < prob;
 }
+// NodeImage(NodeUV(), image)(ctx) (node.cpp:20-23, image.cpp:7-18): nearest texel with wrap, gamma-decoded
+__device__ __forceinline__ V3 image_node(const DScene& sc, int texture1, V2 uv) {
+  const DTexture t = sc.textures[texture1 - 1];
+  const float fx = uv.x - floorf(uv.x), fy = uv.y - floorf(uv.y);  // psl::fract (psl/math.h:151-154)
+  const int x = min(int(float(t.width) * fx), t.width - 1), y = min(int(float(t.height) * fy), t.height - 1);
+  const uint32_t c = __ldg(sc.texels + t.offset + size_t(x) + size_t(y) * size_t(t.width));
+  return V3(__ldg(sc.srgb_lut + (c & 0xffu)), __ldg(sc.srgb_lut + ((c >> 8) & 0xffu)),
+            __ldg(sc.srgb_lut + ((c >> 16) & 0xffu)));
+}
 template <int MAT, class Smp>
-__device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_material& m, V3 wi_world, V3 n,
+__device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_material& m, V3 wi_world, V3 n, V2 uv,
                                               float min_roughness, bool diffused, Smp& smp, Rng& g) {
   Bxdf b;
   b.albedo = V3(m.color[0], m.color[1], m.color[2]);
   b.roughness = m.roughness;
+  float metallic = m.metallic;
+  if (MAT == PB2_MAT_UBER) {
+    if (m.color_texture) b.albedo = image_node(sc, m.color_texture, uv);
+    if (m.roughness_texture) b.roughness = image_node(sc, m.roughness_texture, uv).y;
+    if (m.metallic_texture) metallic = image_node(sc, m.metallic_texture, uv).z;
+  }
   b.ior = m.ior;
   b.sigma_s = V3(m.sigma_s[0], m.sigma_s[1], m.sigma_s[2]);
   b.kind = BX_DIFFUSE;
@@ -213,7 +228,7 @@ __device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_materi
   if (MAT == PB2_MAT_GLOSSY) { b.kind = BX_DIFF_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); }
   if (MAT == PB2_MAT_GLASS) { b.kind = BX_REFR_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); }
   if (MAT == PB2_MAT_UBER) {
-    if (with_probability(m.metallic, g)) b.kind = BX_CONDUCTOR;
+    if (with_probability(metallic, g)) b.kind = BX_CONDUCTOR;
     else if (with_probability(m.transmission, g)) b.kind = BX_REFR_DIELECTRIC;
     else b.kind = BX_DIFF_DIELECTRIC;
   }
@@ -389,7 +404,7 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
       constexpr bool uses_rng = MAT == PB2_MAT_UBER || MAT == PB2_MAT_SUBSURFACE;
       if (uses_rng) g_rng = load_rng(w.rng, pix);
       const bool diffused = pv_diffuse > 0;
-      Bxdf bx = material_bxdf<MAT>(sc, m, wi, it.n, diffused ? 0.6f : 0.0f, diffused, smp, g_rng);
+      Bxdf bx = material_bxdf<MAT>(sc, m, wi, it.n, it.uv, diffused ? 0.6f : 0.0f, diffused, smp, g_rng);
       M3 l2w = coordinate_system(it.n);
       M3 w2l = transpose(l2w);
       bx.wi = w2l * wi;

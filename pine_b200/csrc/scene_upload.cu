@@ -52,8 +52,26 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   }
   const uint32_t counts[8] = {sd->n_aabbs, sd->n_obbs, sd->n_spheres, sd->n_triangles,
                               sd->n_cones, sd->n_rects, sd->n_disks, sd->n_meshes};
-  for (uint32_t i = 0; i < sd->n_materials; i++)
-    if (!valid_material(sd->materials[i])) { set_error("unknown material kind"); return PB2_E_UNSUPPORTED; }
+  for (uint32_t i = 0; i < sd->n_materials; i++) {
+    const pb2_material& m = sd->materials[i];
+    if (!valid_material(m)) { set_error("unknown material kind"); return PB2_E_UNSUPPORTED; }
+    const int32_t tex[3] = {m.color_texture, m.roughness_texture, m.metallic_texture};
+    bool tex_ok = true;
+    for (int32_t t : tex) tex_ok = tex_ok && t >= 0 && uint32_t(t) <= sd->n_textures;
+    if (!tex_ok) {
+      set_error("material " + std::to_string(i) + ": texture index out of range");
+      return PB2_E_INVALID;
+    }
+    if ((tex[0] || tex[1] || tex[2]) && m.kind != PB2_MAT_UBER) {
+      set_error("material " + std::to_string(i) + ": image nodes are supported on Uber materials only");
+      return PB2_E_UNSUPPORTED;
+    }
+  }
+  for (uint32_t i = 0; i < sd->n_textures; i++)
+    if (!sd->textures[i].rgba || sd->textures[i].width <= 0 || sd->textures[i].height <= 0) {
+      set_error("texture " + std::to_string(i) + ": empty image");
+      return PB2_E_INVALID;
+    }
 
   std::vector<DGeom> geoms(sd->n_geometries);
   ctx->needs_rng_in_shading = false;
@@ -96,6 +114,19 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   H.geoms = std::move(geoms);
   H.lights = std::move(lights);
   H.materials.assign(sd->materials, sd->materials + sd->n_materials);
+  for (uint32_t i = 0; i < sd->n_textures; i++) {
+    const pb2_texture& t = sd->textures[i];
+    const size_t n = size_t(t.width) * size_t(t.height);
+    if (H.texels.size() + n > 0xffffffffull) { set_error("more than 2^32 texels"); return PB2_E_UNSUPPORTED; }
+    H.textures.push_back(DTexture{uint32_t(H.texels.size()), t.width, t.height});
+    const size_t at = H.texels.size();
+    H.texels.resize(at + n);
+    memcpy(H.texels.data() + at, t.rgba, n * 4);
+  }
+  H.srgb_lut.resize(256);
+  // inverse_gamma_correction(value / 255.0f) = pow(v, 2.2f) (color.h:13-18) with the host's powf, as the
+  // reference evaluates it per lookup
+  for (int v = 0; v < 256; v++) H.srgb_lut[v] = powf(float(v) / 255.0f, 2.2f);
   H.aabbs.assign(sd->aabbs, sd->aabbs + sd->n_aabbs);
   H.obbs.assign(sd->obbs, sd->obbs + sd->n_obbs);
   H.spheres.assign(sd->spheres, sd->spheres + sd->n_spheres);
@@ -256,6 +287,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   ITEM(wide_prims, lay.wide_prims); ITEM(box_shapes, lay.box_shapes); ITEM(leaf_prims, lay.leaf_prims);
   ITEM(top_prims, H.top_prims); ITEM(meshes, H.meshes); ITEM(geoms, H.geoms); ITEM(lights, H.lights);
   ITEM(verts, H.verts); ITEM(tris, H.tris); ITEM(normals, H.normals); ITEM(uvs, H.uvs);
+  ITEM(texels, H.texels); ITEM(textures, H.textures); ITEM(srgb_lut, H.srgb_lut);
   ITEM(materials, H.materials); ITEM(aabbs, H.aabbs); ITEM(obbs, H.obbs); ITEM(spheres, H.spheres);
   ITEM(triangles, H.triangles); ITEM(cones, H.cones); ITEM(rects, H.rects); ITEM(disks, H.disks);
 #undef ITEM
@@ -302,6 +334,8 @@ extern "C" int pb2_restage_scene(pb2_context* ctx, void* cuda_stream) {
   s.disks = ctx->disks.as<pb2_disk>();
   s.verts = ctx->verts.as<float>(); s.tris = ctx->tris.as<uint32_t>();
   s.normals = ctx->normals.as<float>(); s.uvs = ctx->uvs.as<float>();
+  s.texels = ctx->texels.as<uint32_t>(); s.textures = ctx->textures.as<DTexture>();
+  s.srgb_lut = ctx->srgb_lut.as<float>();
   ctx->counters.upload_ms =
       std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   return PB2_OK;

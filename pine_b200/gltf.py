@@ -16,9 +16,16 @@ helpers, so vertices, normals and the camera are bit-identical -- tests/test_glt
     material gets Uber(1, 1, 0, 0, 1.45);
   * every node with a camera sets `ThinLenCamera(Film(int(640 * aspect), 640), T, T + R * (0,0,-1),
     yfov / 2)` from the node's OWN translation / rotation (fileio.cpp:308-321).
-Not supported (error, never a silent fallback): `baseColorTexture` / `metallicRoughnessTexture`
-(`NodeImage` material graphs), sparse accessors, non-triangle modes, external (non-embedded) buffers
-other than a sibling file.
+  * `baseColorTexture` becomes the albedo image node `NodeImage(NodeUV(), image)`, and
+    `metallicRoughnessTexture` supplies roughness (component 1; unless the JSON also gives a
+    roughnessFactor, which the reference applies afterwards) and metallic (component 2)
+    (fileio.cpp:276-292): the 8-bit image goes to the device as a texture (pb2_texture) and is looked up
+    there exactly as node.cpp:20-23 / image.cpp:7-18 do (nearest texel, wrap, pow(v / 255, 2.2)). As in
+    the reference the factors are NOT multiplied in, texCoord sets other than 0, samplers and
+    KHR_texture_transform are ignored. Images are decoded with Pillow: PNG is lossless, so texels equal
+    the reference's stb_image decode; JPEG decoders may differ by one level in a few texels.
+Not supported (error, never a silent fallback): 16-bit or float images, sparse accessors, non-triangle
+modes.
 """
 import base64
 import json
@@ -116,8 +123,30 @@ def _node_transform(node, transform):
     return transform
 
 
-def _material(doc, index):
-    """-> ("uber" | "emissive", kwargs for add_material)"""
+def _image(doc, buffers, index, base_dir):
+    """-> uint8 [h, w, 4] of images[index] (tinygltf expands every image to 4 components)."""
+    import io
+    from PIL import Image
+    img = doc["images"][index]
+    if "bufferView" in img:
+        view = doc["bufferViews"][img["bufferView"]]
+        start = view.get("byteOffset", 0)
+        raw = bytes(buffers[view["buffer"]][start:start + view["byteLength"]])
+    elif img.get("uri", "").startswith("data:"):
+        raw = base64.b64decode(img["uri"].split(",", 1)[1])
+    elif "uri" in img and base_dir is not None:
+        with open(os.path.join(base_dir, img["uri"]), "rb") as f:
+            raw = f.read()
+    else:
+        raise GltfError(f"image {index} has no readable source")
+    im = Image.open(io.BytesIO(raw))
+    if im.mode in ("I;16", "I;16B", "I", "F"):
+        raise GltfError(f"image {index}: only 8-bit images are supported (fileio.cpp:152)")
+    return np.ascontiguousarray(np.asarray(im.convert("RGBA"), np.uint8))
+
+
+def _material(doc, index, texture_of=None):
+    """-> ("uber" | "emissive", kwargs for add_material). `texture_of(texture index)` -> scene texture."""
     color, rough, metal, trans, ior = (1.0, 1.0, 1.0), 1.0, 0.0, 0.0, 1.45
     emission_color, emission_strength = (1.0, 1.0, 1.0), 0.0
     if index is not None and index >= 0:
@@ -130,10 +159,22 @@ def _material(doc, index):
         if "KHR_materials_emissive_strength" in ext:
             emission_strength = ext["KHR_materials_emissive_strength"].get("emissiveStrength", 0.0)
         pbr = mat.get("pbrMetallicRoughness", {})
-        for tex in ("baseColorTexture", "metallicRoughnessTexture"):
-            if tex in pbr:
-                raise GltfError(f"material `{mat.get('name', index)}` uses {tex}: image-node materials "
-                                "(NodeImage, fileio.cpp:285-292) are not supported on the CUDA path")
+        textures = {}
+        for key in ("baseColorTexture", "metallicRoughnessTexture"):
+            if key in pbr:
+                if texture_of is None:
+                    raise GltfError(f"material `{mat.get('name', index)}` uses {key} but the scene builder "
+                                    "has no add_texture")
+                slot = texture_of(pbr[key]["index"])
+                if key == "baseColorTexture":
+                    textures["color_texture"] = slot
+                else:
+                    # the reference applies the parsed keys in std::map order (fileio.cpp:276-292):
+                    # metallicFactor < metallicRoughnessTexture < roughnessFactor, so an explicit
+                    # roughnessFactor overrides the texture's roughness while metallic stays textured
+                    textures["metallic_texture"] = slot
+                    if "roughnessFactor" not in pbr:
+                        textures["roughness_texture"] = slot
         color = tuple(pbr.get("baseColorFactor", [1.0, 1.0, 1.0, 1.0])[:3])
         metal = pbr.get("metallicFactor", 1.0)
         rough = pbr.get("roughnessFactor", 1.0)
@@ -142,8 +183,11 @@ def _material(doc, index):
     emission = tuple(f(c) * f(emission_strength) for c in emission_color)
     if any(e != 0 for e in emission):
         return "emissive", dict(color=emission)
-    return "uber", dict(color=tuple(f(c) for c in color), roughness=float(f(rough)), metallic=float(f(metal)),
-                        transmission=float(f(trans)), ior=float(f(ior)))
+    kw = dict(color=tuple(f(c) for c in color), roughness=float(f(rough)), metallic=float(f(metal)),
+              transmission=float(f(trans)), ior=float(f(ior)))
+    if index is not None and index >= 0:
+        kw.update(textures)
+    return "uber", kw
 
 
 def scene_from_gltf(scene, source, transform=None):
@@ -158,6 +202,16 @@ def scene_from_gltf(scene, source, transform=None):
     transform = np.eye(4, dtype=np.float32) if transform is None else _f(transform).reshape(4, 4)
     added = 0
     nodes = doc.get("nodes", [])
+    image_slots = {}
+
+    def texture_of(tex_index):  # textures[i].source -> one scene texture per image
+        texs = doc.get("textures", [])
+        src = texs[tex_index].get("source") if 0 <= tex_index < len(texs) else None
+        if src is None or not 0 <= src < len(doc.get("images", [])):
+            raise GltfError(f"texture {tex_index} has no source image")
+        if src not in image_slots:
+            image_slots[src] = scene.add_texture(_image(doc, buffers, src, base_dir))
+        return image_slots[src]
 
     def process(node, tr):
         nonlocal added
@@ -193,7 +247,8 @@ def scene_from_gltf(scene, source, transform=None):
                 n_norm = 0 if normals is None else len(normals)
                 A.lib().pb2h_mesh_apply(_fp(_col(tr)), _fp(verts), len(verts),
                                         _fp(normals) if n_norm else None, n_norm)
-                kind, kw = _material(doc, prim.get("material", -1))
+                kind, kw = _material(doc, prim.get("material", -1),
+                                     texture_of if hasattr(scene, "add_texture") else None)
                 mat = scene.add_material(kind, **kw)
                 scene.add_mesh(verts, idx, mat, normals=normals, uvs=uvs)
                 added += 1

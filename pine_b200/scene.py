@@ -128,14 +128,30 @@ class Scene:
         self.geometries = []         # (shape_kind, shape_index, material)
         self.shapes = {k: [] for k in A.SHAPE_KINDS}
         self.mesh_data = []          # keeps numpy arrays alive
+        self.textures = []           # uint8 [h, w, 4] arrays (pine::Image of vec4u8)
         self.camera = None
         self._cam = None             # A.Camera
         self.size = None
 
     # ---- builder interface (shared with oracle.ref.RefScene) ----
+    def add_texture(self, rgba):
+        """An 8-bit image (uint8 [h, w, 3 or 4], row 0 first) for Uber materials' image nodes -> index."""
+        a = np.asarray(rgba)
+        if a.dtype != np.uint8 or a.ndim != 3 or a.shape[2] not in (3, 4) or a.size == 0:
+            raise ValueError("texture must be a non-empty uint8 [h, w, 3|4] array")
+        if a.shape[2] == 3:
+            a = np.concatenate([a, np.full(a.shape[:2] + (1,), 255, np.uint8)], axis=2)
+        self.textures.append(np.ascontiguousarray(a))
+        return len(self.textures) - 1
+
     def add_material(self, kind, color, roughness=0.0, ior=1.4, metallic=0.0, transmission=0.0,
-                     sigma_s=(0.0, 0.0, 0.0)):
+                     sigma_s=(0.0, 0.0, 0.0), color_texture=None, roughness_texture=None, metallic_texture=None):
+        """`*_texture`: indices from add_texture (Uber only): NodeImage(NodeUV(), image) as albedo, its
+        component 1 as roughness, its component 2 as metallic (fileio.cpp:285-292)."""
         m = A.Material()
+        m.color_texture = 0 if color_texture is None else int(color_texture) + 1
+        m.roughness_texture = 0 if roughness_texture is None else int(roughness_texture) + 1
+        m.metallic_texture = 0 if metallic_texture is None else int(metallic_texture) + 1
         m.kind = A.MATERIAL_KINDS[kind]
         m.color = A.f3(*[float(c) for c in color])
         m.roughness, m.ior, m.metallic, m.transmission = roughness, ior, metallic, transmission
@@ -280,6 +296,12 @@ class Scene:
         put("rects", A.Rect, self.shapes["rect"])
         put("disks", A.Disk, self.shapes["disk"])
         put("meshes", A.Mesh, self.shapes["mesh"])
+        texs = []
+        for a in self.textures:
+            t = A.Texture()
+            t.rgba, t.width, t.height = a.ctypes.data, a.shape[1], a.shape[0]
+            texs.append(t)
+        put("textures", A.Texture, texs)
         ls = self.lights()
         larr = (C.c_int32 * max(len(ls), 1))(*ls)
         keep.append(larr)

@@ -95,6 +95,27 @@ class GlbWriter:
                 struct.pack("<I4s", len(binc), b"BIN\0") + binc)
 
 
+def png(pixels):
+    """uint8 [h, w, 3|4] -> PNG bytes (8-bit, filter 0 / Sub alternating so a decoder's unfilter is exercised)."""
+    import zlib
+    a = np.ascontiguousarray(pixels, np.uint8)
+    h, w, c = a.shape
+    rows = bytearray()
+    for y in range(h):
+        row = a[y].reshape(-1)
+        if y % 2:
+            prev = np.concatenate([np.zeros(c, np.uint8), row[:-c]])
+            rows += b"\x01" + ((row.astype(np.int16) - prev) & 255).astype(np.uint8).tobytes()
+        else:
+            rows += b"\x00" + row.tobytes()
+
+    def chunk(kind, data):
+        body = kind + data
+        return struct.pack(">I", len(data)) + body + struct.pack(">I", zlib.crc32(body) & 0xffffffff)
+    ihdr = struct.pack(">IIBBBBB", w, h, 8, 2 if c == 3 else 6, 0, 0, 0)
+    return b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", ihdr) + chunk(b"IDAT", zlib.compress(bytes(rows), 9)) + chunk(b"IEND", b"")
+
+
 def box(lo, hi):
     lo, hi = np.asarray(lo, np.float32), np.asarray(hi, np.float32)
     verts, normals, idx = [], [], []
@@ -177,8 +198,65 @@ def room_like():
     return w.tobytes()
 
 
+def room_textured():
+    """Image-node materials (fileio.cpp:285-292): a floor with a base-colour PNG (RGB, 37 x 23), a wall
+    whose metallic/roughness come from an RGBA PNG (metallic texels are 0 or 255 only, so the Uber lobe
+    choice stays deterministic: with_probability(0 | 1), sampler.h:317-324), a ball that uses both images
+    plus an explicit roughnessFactor (which the reference lets override the texture), and a mesh without
+    TEXCOORD_0 (uv falls back to the triangle's own parametrisation). No camera node: the test sets one."""
+    from pine_b200 import scenes
+    rng = np.random.RandomState(7)
+    w = GlbWriter()
+    w.doc["images"], w.doc["textures"], w.doc["samplers"] = [], [], [{}]
+
+    def image(pixels):
+        raw = png(pixels)
+        w.doc["images"].append({"bufferView": w.view(raw), "mimeType": "image/png"})
+        w.doc["textures"].append({"source": len(w.doc["images"]) - 1, "sampler": 0})
+        return len(w.doc["textures"]) - 1
+    color = rng.randint(30, 256, size=(23, 37, 3)).astype(np.uint8)
+    mr = rng.randint(0, 256, size=(16, 16, 4)).astype(np.uint8)
+    mr[..., 2] = np.where(rng.rand(16, 16) < 0.4, 255, 0)
+    t_color, t_mr = image(color), image(mr)
+    floor = w.material(name="floor", pbrMetallicRoughness={"baseColorTexture": {"index": t_color},
+                                                           "baseColorFactor": [0.1, 0.1, 0.1, 1],
+                                                           "metallicFactor": 0, "roughnessFactor": 0.8})
+    wall = w.material(name="wall", pbrMetallicRoughness={"baseColorFactor": [0.8, 0.75, 0.7, 1], "metallicFactor": 0.5,
+                                                         "metallicRoughnessTexture": {"index": t_mr}})
+    ball = w.material(name="ball", pbrMetallicRoughness={"baseColorTexture": {"index": t_color},
+                                                         "metallicRoughnessTexture": {"index": t_mr},
+                                                         "roughnessFactor": 0.35})
+    plain = w.material(name="no uvs", pbrMetallicRoughness={"baseColorTexture": {"index": t_color},
+                                                            "metallicFactor": 0, "roughnessFactor": 0.9})
+    lamp = w.material(name="lamp", emissiveFactor=[1.0, 0.9, 0.8],
+                      extensions={"KHR_materials_emissive_strength": {"emissiveStrength": 40.0}})
+    quad = np.array([[-1, 0, -1], [1, 0, -1], [1, 0, 1], [-1, 0, 1]], np.float32)
+    quad_uv = np.array([[0, 0], [3, 0], [3, 2], [0, 2]], np.float32)  # repeats: exercises fract()
+    qi = [[0, 2, 1], [0, 3, 2]]
+    up = np.tile(np.float32([0, 1, 0]), (4, 1))
+    w.node(root=True, name="floor", mesh=w.mesh([w.primitive(quad, qi, floor, normals=up, uvs=quad_uv)]),
+           scale=[2.0, 1.0, 2.0])
+    w.node(root=True, name="wall", mesh=w.mesh([w.primitive(quad, qi, wall, normals=up, uvs=quad_uv * 0.5 - 0.75)]),
+           translation=[0.0, 1.5, -2.0], rotation=[0.7071067811865476, 0.0, 0.0, 0.7071067811865476],
+           scale=[2.0, 1.0, 1.5])
+    sv, si = scenes.icosphere(3)
+    sv, si = np.asarray(sv, np.float32), np.asarray(si, np.uint32)
+    uv = np.stack([np.arctan2(sv[:, 2], sv[:, 0]) / (2 * np.pi) + 0.5, np.arccos(np.clip(sv[:, 1], -1, 1)) / np.pi], 1)
+    w.node(root=True, name="ball", mesh=w.mesh([w.primitive(sv, si, ball, normals=sv, uvs=uv.astype(np.float32),
+                                                            index_type=np.uint32)]),
+           translation=[-0.7, 0.6, -0.3], scale=[0.6, 0.6, 0.6])
+    bv, bi, bn = box((-0.4, 0.0, -0.4), (0.4, 0.8, 0.4))
+    w.node(root=True, name="box without uvs", mesh=w.mesh([w.primitive(bv, bi, plain, normals=bn)]),
+           translation=[0.9, 0.0, 0.4], rotation=[0.0, 0.25881904510252074, 0.0, 0.9659258262890683])
+    down = np.array([[-0.5, 0, -0.5], [0.5, 0, -0.5], [0.5, 0, 0.5], [-0.5, 0, 0.5]], np.float32)
+    w.node(root=True, name="lamp", mesh=w.mesh([w.primitive(down, [[0, 1, 2], [0, 2, 3]], lamp)]),
+           translation=[0.0, 2.6, 0.0])
+    return w.tobytes()
+
+
 if __name__ == "__main__":
-    out = os.path.join(ROOT, "tests", "golden", "room_like.glb")
-    with open(out, "wb") as f:
-        f.write(room_like())
-    print(out, os.path.getsize(out), "bytes")
+    for name, make in (("room_like", room_like), ("room_textured", room_textured)):
+        out = os.path.join(ROOT, "tests", "golden", name + ".glb")
+        with open(out, "wb") as f:
+            f.write(make())
+        print(out, os.path.getsize(out), "bytes")

@@ -92,6 +92,22 @@ def gltf_kats():
     np.savez_compressed(os.path.join(OUT, "room_like.npz"), **out)
 
 
+TEXTURED_CAMERA = dict(size=(96, 64), frm=(0.3, 1.6, 3.6), to=(0.0, 0.8, 0.0), fov=0.45)
+
+
+def gltf_textured_kats():
+    """tests/golden/room_textured.glb (image-node materials, fileio.cpp:285-292) through the reference's loader
+    (tinygltf + stb_image decode the embedded PNGs): films at 8 spp (BlueSampler) and 256 spp (SobolSampler)."""
+    R = ref.RefScene()
+    R.load_gltf(os.path.join(OUT, "room_textured.glb"))
+    R.set_camera(**TEXTURED_CAMERA)
+    out = {}
+    out["film"], _ = R.render(8, 4)
+    out["film_depth2"], _ = R.render(8, 2)
+    out["film_sobol256"], _ = R.render(256, 4, sampler="sobol")
+    np.savez_compressed(os.path.join(OUT, "room_textured.npz"), **out)
+
+
 def scene(name):
     fn, kw, spp, depth = common.SMALL_SCENES[name]
     R = ref.RefScene()
@@ -146,6 +162,7 @@ if __name__ == "__main__":
     kats()
     sobol_kats()
     gltf_kats()
+    gltf_textured_kats()
     camera_lens()
     for name in common.SMALL_SCENES:
         scene(name)

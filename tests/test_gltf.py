@@ -21,6 +21,7 @@ from pine_b200 import _abi as A
 from pine_b200 import gltf
 
 GLB = os.path.join(common.GOLDEN, "room_like.glb")
+GLB_TEXTURED = os.path.join(common.GOLDEN, "room_textured.glb")
 REF_CBOX = "/root/reference/scenes/cbox.glb"
 
 
@@ -35,6 +36,28 @@ def test_fixture_is_what_the_writer_writes():
     import gltf_fixture
     with open(GLB, "rb") as f:
         assert f.read() == gltf_fixture.room_like()
+    with open(GLB_TEXTURED, "rb") as f:
+        assert f.read() == gltf_fixture.room_textured()
+
+
+def test_image_node_materials_load():
+    # fileio.cpp:276-292: baseColorTexture -> albedo image; metallicRoughnessTexture -> roughness (unless a
+    # roughnessFactor is given, applied after it in std::map order) and metallic
+    S = pb.Scene()
+    assert gltf.scene_from_gltf(S, GLB_TEXTURED) == 5
+    assert [t.shape for t in S.textures] == [(23, 37, 4), (16, 16, 4)]  # one texture per image, RGBA
+    rng = np.random.RandomState(7)
+    color = rng.randint(30, 256, size=(23, 37, 3)).astype(np.uint8)
+    assert np.array_equal(S.textures[0][..., :3], color) and (S.textures[0][..., 3] == 255).all()
+    assert set(np.unique(S.textures[1][..., 2])) == {0, 255}
+    slots = [(m.color_texture, m.roughness_texture, m.metallic_texture) for m in S.materials]
+    assert slots == [(1, 0, 0), (0, 2, 2), (1, 0, 2), (1, 0, 0), (0, 0, 0)]
+    assert np.float32(S.materials[2].roughness) == np.float32(0.35)
+    S.set_camera((8, 8), (0, 1, 4), (0, 1, 0), 0.4)
+    d, keep = S.desc()
+    assert d.n_textures == 2 and d.textures[0].width == 37 and d.textures[0].height == 23
+    with pytest.raises(ValueError):
+        S.add_texture(np.zeros((4, 4), np.uint8))
 
 
 def test_geometries_materials_and_camera(golden, loaded):
@@ -121,10 +144,10 @@ def test_global_transform_and_load_scene(loaded):
 
 
 def test_unsupported_content_is_an_error():
-    def textured(doc):
+    def dangling_texture(doc):
         doc["materials"][0]["pbrMetallicRoughness"]["baseColorTexture"] = {"index": 0}
-    with pytest.raises(gltf.GltfError, match="baseColorTexture"):
-        gltf.scene_from_gltf(pb.Scene(), _rewrite(textured))
+    with pytest.raises(gltf.GltfError, match="no source image"):
+        gltf.scene_from_gltf(pb.Scene(), _rewrite(dangling_texture))
 
     def lines(doc):
         doc["meshes"][0]["primitives"][0]["mode"] = 1

@@ -67,3 +67,31 @@ def test_glb_through_path_integrator_and_prl(tmp_path, golden):
     script.write_text(f'scene := Scene();\nscene.load("{GLB}");\nPathIntegrator(BlueSampler(4), 5).render(scene);\n')
     sp, = prl.run_file(str(script))
     assert np.array_equal(u32(sp.target.camera.film().pixels), u32(film))
+
+
+def test_textured_glb_film_matches_the_reference(golden):
+    """Image-node Uber materials: texel addressing (fract / wrap / nearest), gamma decode and the
+    roughnessFactor-overrides-texture quirk all show in the film; the fixture keeps every lobe choice
+    deterministic (metallic texels 0 or 255), so the equal-spp tolerance of the plain scenes applies."""
+    from pine_b200 import _abi as A
+    g = golden("room_textured")
+    S = pb.load_scene(os.path.join(common.GOLDEN, "room_textured.glb"))
+    S.set_camera((96, 64), (0.3, 1.6, 3.6), (0.0, 0.8, 0.0), 0.45)
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    for depth, key in ((2, "film_depth2"), (4, "film")):
+        film = B.render(8, depth)
+        assert np.isfinite(film).all()
+        assert relmse(film, g[key]) <= 1e-4, (depth, relmse(film, g[key]))
+    assert relmse(B.render(pb.SobolSampler(256), 4), g["film_sobol256"]) <= 1e-4
+    # texture indices are validated, and only Uber materials may carry image nodes
+    S.materials[0].color_texture = 9
+    with pytest.raises(pb.PineB200Error) as e:
+        B.upload_scene(S)
+    assert e.value.code == A.PB2_E_INVALID
+    S.materials[0].color_texture = 1
+    S.materials[0].kind = A.MATERIAL_KINDS["diffuse"]
+    with pytest.raises(pb.PineB200Error) as e:
+        B.upload_scene(S)
+    assert e.value.code == A.PB2_E_UNSUPPORTED
+    B.close()
