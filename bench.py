@@ -295,6 +295,9 @@ def run_gpu(args):
         roof["achieved"] = b_ray * rank0_closest / trace_s / 1e9
         roof["frac"] = roof["achieved"] / peak
         roof["bytes_per_ray"] = b_ray
+        # the algorithmic bytes one launch stands for, to read `traffic` (ncu DRAM bytes per launch) against
+        roof["algorithmic_bytes_per_launch"] = b_ray * rank0_closest / max(kt["trace_launches"] / n_k, 1)
+        roof["traffic_unit"] = "bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/b_ray.json ncu_source)"
     else:
         roof["achieved"], roof["frac"] = None, None
     roof["launches_per_step"] = kt["trace_launches"] / n_k
