@@ -132,6 +132,24 @@ typedef struct pb2_camera { /* pine::ThinLenCamera, camera.h:10-27 */
   int32_t tonemapper;    /* 0 Uncharted2, 1 ACES (film.h:9-24); used by pb2_film_finalize only */
 } pb2_camera;
 
+/* One entry of UniformLightSampler::lights (lightsampler.cpp:6-10): Scene::lights in insertion order
+ * (scene.cpp:19-20,29-31) followed by the environment light, if any. */
+enum pb2_light_kind {
+  PB2_LIGHT_AREA = 0,        /* AreaLight(geometry), light.cpp:55-69 */
+  PB2_LIGHT_POINT = 1,       /* PointLight(position, color), light.cpp:11-17 */
+  PB2_LIGHT_SPOT = 2,        /* SpotLight: direction normalised, cosines precomputed, light.cpp:18-45 */
+  PB2_LIGHT_DIRECTIONAL = 3, /* DirectionalLight(normalize(direction), color), light.cpp:46-53 */
+  PB2_LIGHT_SKY = 4          /* Sky(sun_color) as the environment light, light.cpp:71-84; must come last */
+};
+typedef struct pb2_light {
+  int32_t kind;
+  int32_t geometry;   /* AREA: index into geometries (must be Emissive); otherwise -1 */
+  float position[3];  /* POINT, SPOT */
+  float direction[3]; /* SPOT, DIRECTIONAL: unit vector */
+  float color[3];     /* POINT, SPOT, DIRECTIONAL: radiant colour; SKY: sun_color */
+  float falloff_cos, cutoff_cos; /* SPOT */
+} pb2_light;
+
 typedef struct pb2_scene_desc {
   const pb2_geometry* geometries; uint32_t n_geometries;
   const pb2_material* materials;  uint32_t n_materials;
@@ -144,10 +162,13 @@ typedef struct pb2_scene_desc {
   const pb2_disk* disks;          uint32_t n_disks;
   const pb2_mesh* meshes;         uint32_t n_meshes;
   /* Scene::lights (scene.h:39): geometry index of every AreaLight, in scene order
-   * (scene.cpp:19-20 adds one per Emissive geometry). Delta and environment lights: unsupported. */
+   * (scene.cpp:19-20 adds one per Emissive geometry). Delta lights and Sky: see light_records. */
   const int32_t* light_geometries; uint32_t n_lights;
   pb2_camera camera;
   const pb2_texture* textures;     uint32_t n_textures; /* may be NULL / 0 */
+  /* The full light list. NULL: area lights only, taken from light_geometries. Non-NULL: supersedes
+   * light_geometries (whose entries must then equal the AREA records' geometries, or n_lights = 0). */
+  const pb2_light* light_records;  uint32_t n_light_records;
 } pb2_scene_desc;
 
 typedef struct pb2_render_params {

@@ -37,6 +37,7 @@ void pb2h_mat4_mul(const float* a, const float* b, float* out_colmajor);
  * renormalised. Used by the glTF loader (scene_from_gltf, fileio.cpp:146-327). */
 void pb2h_mesh_apply(const float* m_colmajor, float* vertices, size_t n_vertices, float* normals,
                      size_t n_normals);
+float pb2h_cosf(float x); /* the host libm's cosf, as SpotLight's constructor uses (light.cpp:23-24) */
 int pb2h_round_spp(int spp);
 /* Host evaluation of the device draw functions of SobolSampler (sampler.h:83-164, sampler.cpp:82-113)
  * and UniformSampler (the same __host__ __device__ code the kernels inline; test hook, no GPU):

@@ -143,6 +143,23 @@ class RefScene:
                               0 if tonemapper == "uncharted2" else 1, _fp(a), _fp(b),
                               C.c_float(fov), C.c_float(len_radius), C.c_float(focus))
 
+    def add_point_light(self, position, color):
+        a, b = _f(position), _f(color)
+        self.L.ref_add_point_light(self.h, _fp(a), _fp(b))
+
+    def add_directional_light(self, direction, color):
+        a, b = _f(direction), _f(color)
+        self.L.ref_add_directional_light(self.h, _fp(a), _fp(b))
+
+    def add_spot_light(self, position, direction, color, falloff_radian, cutoff_additional_radian=0.0):
+        a, b, c = _f(position), _f(direction), _f(color)
+        self.L.ref_add_spot_light(self.h, _fp(a), _fp(b), _fp(c), C.c_float(falloff_radian),
+                                  C.c_float(cutoff_additional_radian))
+
+    def set_sky(self, sun_color):
+        a = _f(sun_color)
+        self.L.ref_set_sky(self.h, _fp(a))
+
     def load_gltf(self, path, has_camera=False):
         """scene_from_gltf(scene, path) (fileio.cpp:146-327); `has_camera`: the file carries a camera node,
         so the film size is read back from the scene it set."""

@@ -174,6 +174,19 @@ void ref_set_camera(void* h, int w, int hgt, int tonemapper, const float* from, 
   S.scene.set_camera(ThinLenCamera(Film(vec2i(w, hgt), tm), v3(from), v3(to), fov, len_radius,
                                    focus));
 }
+// Scene::add_light / set_env_light (scene.cpp:29-31,44-46) for the non-area lights (light.h:21-66)
+void ref_add_point_light(void* h, const float* position, const float* color) {
+  ((RefScene*)h)->scene.add_light(PointLight(v3(position), v3(color)));
+}
+void ref_add_directional_light(void* h, const float* direction, const float* color) {
+  ((RefScene*)h)->scene.add_light(DirectionalLight(v3(direction), v3(color)));
+}
+void ref_add_spot_light(void* h, const float* position, const float* direction, const float* color,
+                        float falloff_radian, float cutoff_additional_radian) {
+  ((RefScene*)h)->scene.add_light(
+      SpotLight(v3(position), v3(direction), v3(color), falloff_radian, cutoff_additional_radian));
+}
+void ref_set_sky(void* h, const float* sun_color) { ((RefScene*)h)->scene.set_env_light(Sky(v3(sun_color))); }
 // Film size of the scene's camera (a glTF camera node sets it inside scene_from_gltf, fileio.cpp:308-321)
 void ref_camera_size(void* h, int* wh) {
   auto size = ((RefScene*)h)->scene.camera.film().size();

@@ -78,13 +78,21 @@ def _arr(name, typ):
     return [(name, C.POINTER(typ)), ("n_" + name, C.c_uint32)]
 
 
+class Light(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("geometry", C.c_int32), ("position", f3), ("direction", f3),
+                ("color", f3), ("falloff_cos", C.c_float), ("cutoff_cos", C.c_float)]
+
+
+LIGHT_KINDS = {"area": 0, "point": 1, "spot": 2, "directional": 3, "sky": 4}
+
+
 class SceneDesc(C.Structure):
     _fields_ = (_arr("geometries", Geometry) + _arr("materials", Material) + _arr("aabbs", Aabb) +
                 _arr("obbs", Obb) + _arr("spheres", Sphere) + _arr("triangles", Triangle) +
                 _arr("cones", Cone) + _arr("rects", Rect) + _arr("disks", Disk) +
                 _arr("meshes", Mesh) +
                 [("light_geometries", C.POINTER(C.c_int32)), ("n_lights", C.c_uint32),
-                 ("camera", Camera)] + _arr("textures", Texture))
+                 ("camera", Camera)] + _arr("textures", Texture) + _arr("light_records", Light))
 
 
 class RenderParams(C.Structure):
@@ -131,7 +139,7 @@ ABI_SYMBOLS = [
     "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler", "pb2_test_sampler_kind",
     "pb2_test_primary_rays", "pb2_get_counters", "pb2_debug_walk_stats", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
     "pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone", "pb2h_make_triangle",
-    "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_mesh_apply", "pb2h_round_spp", "pb2h_sampler_draws",
+    "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_mesh_apply", "pb2h_cosf", "pb2h_round_spp", "pb2h_sampler_draws",
 ]
 
 _lib = None
@@ -189,6 +197,8 @@ def lib():
                                        C.c_float, C.POINTER(Camera)]
         L.pb2h_mat4.argtypes = [C.c_int, fp, fp]
         L.pb2h_mat4_mul.argtypes = [fp, fp, fp]
+        L.pb2h_cosf.restype = C.c_float
+        L.pb2h_cosf.argtypes = [C.c_float]
         L.pb2h_mesh_apply.argtypes = [fp, fp, C.c_size_t, fp, C.c_size_t]
         L.pb2h_sampler_draws.argtypes = [C.c_int] * 8 + [C.c_char_p, C.c_int, C.c_void_p]
         for name in ("pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone",

@@ -64,6 +64,7 @@ struct HostScene {
   std::vector<DMesh> meshes;
   std::vector<DGeom> geoms;
   std::vector<int32_t> lights;
+  std::vector<pb2_light> light_recs;
   std::vector<float> verts, normals, uvs;
   std::vector<uint32_t> tris;
   std::vector<pb2_material> materials;
@@ -101,13 +102,14 @@ struct pb2_context {
 
   pb2::HostScene host;
   pb2::DScene scene{};  // device pointers
-  pb2::DBuf nodes2, nodes8, leaves, wide_prims, box_shapes, leaf_prims, top_prims, meshes, geoms, materials, lights;
+  pb2::DBuf nodes2, nodes8, leaves, wide_prims, box_shapes, leaf_prims, top_prims, meshes, geoms, materials, lights, light_recs;
   pb2::DBuf aabbs, obbs, spheres, triangles, cones, rects, disks;
   pb2::DBuf verts, tris, normals, uvs, texels, textures, srgb_lut;
   pb2::DBuf tab_sobol, tab_scramble, tab_rank;
   int tables_spp = 0;
   pb2::SamplerTables tables[9];  // index = log2(spp)
   bool has_tables[9] = {};
+  bool only_area_lights = true;       // no delta light, no environment light: the specialised shade kernels apply
   unsigned material_kinds = 0;        // bit k: some geometry uses pb2_material_kind k
   bool needs_rng_in_shading = false;  // Uber / Subsurface present (they draw randf(), material.cpp:9-28)
   int n_pixels = 0;

@@ -115,8 +115,11 @@ struct DScene {
   const DMesh* meshes;
   const DGeom* geoms;
   const pb2_material* materials;
-  const int32_t* lights;  // geometry index per light
+  const int32_t* lights;  // geometry index per light (-1: not an area light, see light_recs)
+  const pb2_light* light_recs;  // UniformLightSampler::lights, same order
   int32_t n_lights, n_geoms;
+  int32_t env_kind;       // 0, or PB2_LIGHT_SKY: Scene::env_light
+  float env_color[3];     // Sky::sun_color
   // per-kind shape arrays (members of the reference structs, include/pine_b200.h)
   const pb2_aabb* aabbs;
   const pb2_obb* obbs;

@@ -2,6 +2,8 @@
 // bindings; declared in include/pine_b200_host.h. Pure host code, no CUDA.
 #include "../../include/pine_b200_host.h"
 
+#include <math.h>
+
 #include "host_shapes.h"
 
 using namespace pb2;
@@ -49,6 +51,7 @@ void pb2h_mesh_apply(const float* m_colmajor, float* vertices, size_t n_vertices
   const M3 m3 = transpose(m3_inverse(upper3(m)));
   for (size_t i = 0; i < n_normals; i++) st3(normals + 3 * i, normalize(m3 * ld3(normals + 3 * i)));
 }
+float pb2h_cosf(float x) { return cosf(x); }  // psl::cos (SpotLight ctor, light.cpp:23-24)
 int pb2h_round_spp(int spp) {  // BlueSobolSampler ctor (sampler.cpp:115-121): clamp 256, roundup2
   if (spp > 256) spp = 256;
   if (spp < 1) return 0;

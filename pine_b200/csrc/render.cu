@@ -194,6 +194,13 @@ __global__ void __launch_bounds__(kTraceBlock) k_shadow_ref(DScene sc, WaveView 
   ref_order_all<true>(sc, w.counts[w.max_depth + 1 + depth], shadow_io(w, depth));
 }
 
+// sky_color(direction) (color.cpp:100-103): sqr(lerp(d.y / 2 + 0.7, warm, cool)), lerp = a (1 - t) + b t
+__device__ __forceinline__ V3 sky_color(V3 d) {
+  const float t = d.y / 2 + 0.7f;
+  const V3 c = V3(1.0f, 0.8f, 0.6f) * (1.0f - t) + V3(0.6f, 0.8f, 1.0f) * t;
+  return c * c;
+}
+
 // ---- material -> BxDF (material.h:30-121, material.cpp:9-28) -------------------------------------------------
 __device__ __forceinline__ bool with_probability(float prob, Rng& g) {  // sampler.h:317-324
   if (prob == 0) return false;
@@ -344,6 +351,16 @@ __global__ void __launch_bounds__(256) k_shade_terminal(DScene sc, WaveView w, i
     const int slot = __float_as_int(b.w);
     const int geom = __float_as_int(hrec.y);
     V3 X(0.0f);
+    if (geom < 0 && sc.env_kind) {
+      // Lo += Tr * env_light->color(ray.d); light_pdf = env_light->pdf(ray.d) unless pv.is_delta (path.cpp:76-81)
+      X = V3(1.0f) * (V3(sc.env_color[0], sc.env_color[1], sc.env_color[2]) * sky_color(V3(b.x, b.y, b.z)));
+      const bool pv_delta = (w.pv_flags[slot] >> 16) & 1;
+      if (!pv_delta && depth > 0) {
+        const float mis = balance_heuristic(w.pv_pdf[slot], 1 / (4 * kPi));
+        float4* v = w.vtx + (size_t(depth - 1) * w.n_slots + slot) * 2;
+        v[0].w = v[0].w * mis;
+      }
+    }
     if (geom >= 0) {
       const DGeom g = sc.geoms[geom];
       const pb2_material m = sc.materials[g.material];
@@ -371,7 +388,7 @@ __global__ void __launch_bounds__(256) k_shade_terminal(DScene sc, WaveView w, i
 }
 
 // class MAT: NEE + BSDF sample at a surface vertex (path.cpp:74-120)
-template <int MAT, bool GENERIC_SAMPLER>
+template <int MAT, bool GENERIC>
 __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int depth) {
   const int n = *list_count(w, depth, MAT);
   const int cur = depth & 1, nxt = cur ^ 1;
@@ -399,7 +416,7 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
       const pb2_material m = sc.materials[g.material];
       int pix = w.pixel0 + slot % w.pixels;
       int px = pix % w.width, py = w.row_begin + pix / w.width;
-      PixelSamplerT<GENERIC_SAMPLER> smp{px, py, w.sample0 + slot / w.pixels, w.dim[slot]};
+      PixelSamplerT<GENERIC> smp{px, py, w.sample0 + slot / w.pixels, w.dim[slot]};
       Rng g_rng;
       constexpr bool uses_rng = MAT == PB2_MAT_UBER || MAT == PB2_MAT_SUBSURFACE;
       if (uses_rng) g_rng = load_rng(w.rng, pix);
@@ -431,21 +448,62 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
           u1 *= sc.n_lights;
           int index = int(u1);
           int lgeom = sc.lights[index];
-          ShapeSample ss;
-          if (shape_sample(sc, lgeom, it.p, u2, u1 - index, ss)) {
-            const pb2_material lm = sc.materials[sc.geoms[lgeom].material];
-            V3 le = dot(-ss.w, ss.n) < 0.0f ? V3(0.0f) : V3(lm.color[0], lm.color[1], lm.color[2]);
-            if (!is_zero(le)) {
-              float ls_pdf = ss.pdf / sc.n_lights;
-              float cosine = absdot(ss.w, it.n);
-              V3 wo = w2l * ss.w;
-              V3 f = bxdf_f(bx, wo);
-              float mis = balance_heuristic(ls_pdf, bxdf_pdf(bx, wo));
-              nee = le * V3(1.0f) * cosine * f / ls_pdf * mis;
-              // a light sample the BxDF gives no weight (below the surface of an opaque lobe) adds
-              // nothing whether or not it is occluded: no shadow ray for it
+          if (!GENERIC || lgeom >= 0) {  // AreaLight::sample (light.cpp:55-69)
+            ShapeSample ss;
+            if (shape_sample(sc, lgeom, it.p, u2, u1 - index, ss)) {
+              const pb2_material lm = sc.materials[sc.geoms[lgeom].material];
+              V3 le = dot(-ss.w, ss.n) < 0.0f ? V3(0.0f) : V3(lm.color[0], lm.color[1], lm.color[2]);
+              if (!is_zero(le)) {
+                float ls_pdf = ss.pdf / sc.n_lights;
+                float cosine = absdot(ss.w, it.n);
+                V3 wo = w2l * ss.w;
+                V3 f = bxdf_f(bx, wo);
+                float mis = balance_heuristic(ls_pdf, bxdf_pdf(bx, wo));
+                nee = le * V3(1.0f) * cosine * f / ls_pdf * mis;
+                // a light sample the BxDF gives no weight (below the surface of an opaque lobe) adds
+                // nothing whether or not it is occluded: no shadow ray for it
+                if (!is_zero(nee)) {
+                  shadow_ray = spawn_ray(it.p, it.n, ss.w, ss.distance);
+                  emit_shadow = true;
+                }
+              }
+            }
+          } else {
+            // PointLight / SpotLight / DirectionalLight / Sky ::sample (light.cpp:11-53,71-84)
+            const pb2_light L = sc.light_recs[index];
+            V3 lwo, le;
+            float ldist, lpdf;
+            bool ok = true;
+            if (L.kind == PB2_LIGHT_DIRECTIONAL) {
+              ldist = 1e+10f;
+              lwo = V3(L.direction[0], L.direction[1], L.direction[2]);
+              lpdf = 1.0f;
+              le = V3(L.color[0], L.color[1], L.color[2]);
+            } else if (L.kind == PB2_LIGHT_SKY) {
+              lwo = uniform_sphere(u2);
+              lpdf = 1 / (4 * kPi);
+              ldist = kFloatMax;
+              le = V3(L.color[0], L.color[1], L.color[2]) * sky_color(lwo);
+            } else {
+              lwo = normalize(V3(L.position[0], L.position[1], L.position[2]) - it.p, ldist);
+              le = V3(L.color[0], L.color[1], L.color[2]);
+              if (L.kind == PB2_LIGHT_SPOT) {
+                const float c = -dot(lwo, V3(L.direction[0], L.direction[1], L.direction[2]));
+                if (c > L.falloff_cos) {}
+                else if (c > L.cutoff_cos) le = le * (c - L.cutoff_cos) / (L.falloff_cos - L.cutoff_cos);
+                else ok = false;
+              }
+              lpdf = sqr(ldist);
+            }
+            if (ok) {
+              const float ls_pdf = lpdf / sc.n_lights;
+              const float cosine = absdot(lwo, it.n);
+              const V3 wo = w2l * lwo;
+              const V3 f = bxdf_f(bx, wo);
+              if (L.kind != PB2_LIGHT_SKY) nee = le * V3(1.0f) * cosine * f / ls_pdf;  // is_delta: no MIS (path.cpp:104-106)
+              else nee = le * V3(1.0f) * cosine * f / ls_pdf * balance_heuristic(ls_pdf, bxdf_pdf(bx, wo));
               if (!is_zero(nee)) {
-                shadow_ray = spawn_ray(it.p, it.n, ss.w, ss.distance);
+                shadow_ray = spawn_ray(it.p, it.n, lwo, ldist);
                 emit_shadow = true;
               }
             }
@@ -782,7 +840,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
         if (depth + 1 < D) {
           const int sg = sm_grid(live, 128, 16);
           const unsigned mk = ctx->material_kinds;
-          const bool blue = sc.sampler_kind == PB2_SAMPLER_BLUE;
+          const bool blue = sc.sampler_kind == PB2_SAMPLER_BLUE && ctx->only_area_lights;
 #define PB2_SHADE(MAT)                                                      \
   if (mk & (1u << MAT)) {                                                   \
     if (blue) k_shade_mat<MAT, false><<<sg, 128, 0, st>>>(sc, w, depth);    \

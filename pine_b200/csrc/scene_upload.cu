@@ -97,15 +97,43 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     ctx->material_kinds |= 1u << m.kind;
     geoms[i] = DGeom{g.shape_kind, g.shape_index, g.material, -1};
   }
-  std::vector<int32_t> lights(sd->light_geometries, sd->light_geometries + sd->n_lights);
-  for (uint32_t l = 0; l < sd->n_lights; l++) {
-    if (lights[l] < 0 || uint32_t(lights[l]) >= sd->n_geometries) { set_error("light index out of range"); return PB2_E_INVALID; }
-    if (sd->materials[sd->geometries[lights[l]].material].kind != PB2_MAT_EMISSIVE) {
+  // UniformLightSampler::lights: light_records when given, else one AreaLight per light_geometries entry
+  std::vector<pb2_light> light_recs;
+  if (sd->light_records) {
+    light_recs.assign(sd->light_records, sd->light_records + sd->n_light_records);
+  } else {
+    for (uint32_t l = 0; l < sd->n_lights; l++) {
+      pb2_light r{};
+      r.kind = PB2_LIGHT_AREA;
+      r.geometry = sd->light_geometries[l];
+      light_recs.push_back(r);
+    }
+  }
+  std::vector<int32_t> lights(light_recs.size(), -1);
+  bool only_area = true;
+  int32_t env_kind = 0;
+  float env_color[3] = {0, 0, 0};
+  for (size_t l = 0; l < light_recs.size(); l++) {
+    const pb2_light& r = light_recs[l];
+    if (r.kind < PB2_LIGHT_AREA || r.kind > PB2_LIGHT_SKY) { set_error("unknown light kind"); return PB2_E_UNSUPPORTED; }
+    if (r.kind != PB2_LIGHT_AREA) {
+      only_area = false;
+      if (r.kind == PB2_LIGHT_SKY) {
+        if (l + 1 != light_recs.size()) { set_error("the environment light must be the last light record"); return PB2_E_INVALID; }
+        env_kind = PB2_LIGHT_SKY;
+        for (int k = 0; k < 3; k++) env_color[k] = r.color[k];
+      }
+      continue;
+    }
+    if (r.geometry < 0 || uint32_t(r.geometry) >= sd->n_geometries) { set_error("light index out of range"); return PB2_E_INVALID; }
+    if (sd->materials[sd->geometries[r.geometry].material].kind != PB2_MAT_EMISSIVE) {
       set_error("light geometry is not emissive");
       return PB2_E_INVALID;
     }
-    geoms[lights[l]].light = int32_t(l);
+    lights[l] = r.geometry;
+    geoms[r.geometry].light = int32_t(l);
   }
+  ctx->only_area_lights = only_area;
 
   // ---- host copies (kept, pinned, for re-staging) ----
   HostScene& H = ctx->host;
@@ -113,6 +141,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   H = HostScene();
   H.geoms = std::move(geoms);
   H.lights = std::move(lights);
+  H.light_recs = std::move(light_recs);
   H.materials.assign(sd->materials, sd->materials + sd->n_materials);
   for (uint32_t i = 0; i < sd->n_textures; i++) {
     const pb2_texture& t = sd->textures[i];
@@ -263,7 +292,9 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
       std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   DScene& s = ctx->scene;
   s.top = top_tree;
-  s.n_lights = int32_t(sd->n_lights); s.n_geoms = int32_t(sd->n_geometries);
+  s.n_lights = int32_t(H.lights.size()); s.env_kind = env_kind;
+  for (int k = 0; k < 3; k++) s.env_color[k] = env_color[k];
+  s.n_geoms = int32_t(sd->n_geometries);
   s.wide_ready = lay.nodes8.empty() ? 0 : 1;
   s.n_box_shapes = int32_t(lay.box_shapes.size());
   s.order_dependent = order_dependent ? 1 : 0;
@@ -285,7 +316,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
 #define ITEM(buf, vec) item(ctx->buf, (vec).data(), (vec).size() * sizeof((vec)[0]))
   ITEM(nodes2, lay.nodes2); ITEM(nodes8, lay.nodes8); ITEM(leaves, lay.leaves);
   ITEM(wide_prims, lay.wide_prims); ITEM(box_shapes, lay.box_shapes); ITEM(leaf_prims, lay.leaf_prims);
-  ITEM(top_prims, H.top_prims); ITEM(meshes, H.meshes); ITEM(geoms, H.geoms); ITEM(lights, H.lights);
+  ITEM(top_prims, H.top_prims); ITEM(meshes, H.meshes); ITEM(geoms, H.geoms); ITEM(lights, H.lights); ITEM(light_recs, H.light_recs);
   ITEM(verts, H.verts); ITEM(tris, H.tris); ITEM(normals, H.normals); ITEM(uvs, H.uvs);
   ITEM(texels, H.texels); ITEM(textures, H.textures); ITEM(srgb_lut, H.srgb_lut);
   ITEM(materials, H.materials); ITEM(aabbs, H.aabbs); ITEM(obbs, H.obbs); ITEM(spheres, H.spheres);
@@ -328,6 +359,7 @@ extern "C" int pb2_restage_scene(pb2_context* ctx, void* cuda_stream) {
   s.top_prims = ctx->top_prims.as<DTopPrim>(); s.meshes = ctx->meshes.as<DMesh>();
   s.geoms = ctx->geoms.as<DGeom>(); s.materials = ctx->materials.as<pb2_material>();
   s.lights = ctx->lights.as<int32_t>();
+  s.light_recs = ctx->light_recs.as<pb2_light>();
   s.aabbs = ctx->aabbs.as<pb2_aabb>(); s.obbs = ctx->obbs.as<pb2_obb>();
   s.spheres = ctx->spheres.as<pb2_sphere>(); s.triangles = ctx->triangles.as<pb2_triangle>();
   s.cones = ctx->cones.as<pb2_cone>(); s.rects = ctx->rects.as<pb2_rect>();

@@ -129,6 +129,8 @@ class Scene:
         self.shapes = {k: [] for k in A.SHAPE_KINDS}
         self.mesh_data = []          # keeps numpy arrays alive
         self.textures = []           # uint8 [h, w, 4] arrays (pine::Image of vec4u8)
+        self.extra_lights = []       # (position in Scene::lights order = n geometries added before, A.Light)
+        self.env_light = None        # A.Light of kind "sky"
         self.camera = None
         self._cam = None             # A.Camera
         self.size = None
@@ -218,6 +220,64 @@ class Scene:
         m.n_vertices, m.n_triangles = len(v), len(i)
         return self._add("mesh", m, mat)
 
+    # ---- lights other than Emissive geometry (light.h:21-66; Scene::add_light / set_env_light) ----
+    def _light(self, kind, position=(0, 0, 0), direction=(0, 0, 0), color=(0, 0, 0), falloff_cos=0.0,
+               cutoff_cos=0.0):
+        l = A.Light()
+        l.kind, l.geometry = A.LIGHT_KINDS[kind], -1
+        l.position = A.f3(*[float(np.float32(c)) for c in position])
+        l.direction = A.f3(*[float(np.float32(c)) for c in direction])
+        l.color = A.f3(*[float(np.float32(c)) for c in color])
+        l.falloff_cos, l.cutoff_cos = falloff_cos, cutoff_cos
+        return l
+
+    @staticmethod
+    def _unit(v):  # normalize(vec3) (vecmath.h): v / sqrt(x*x + y*y + z*z) in binary32, zero stays zero
+        v = _f(v)
+        n = np.sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2], dtype=np.float32)
+        return v if n == 0 else (v / n).astype(np.float32)
+
+    def add_point_light(self, position, color):
+        self.extra_lights.append((len(self.geometries), self._light("point", position=position, color=color)))
+
+    def add_directional_light(self, direction, color):
+        self.extra_lights.append((len(self.geometries),
+                                  self._light("directional", direction=self._unit(direction), color=color)))
+
+    def add_spot_light(self, position, direction, color, falloff_radian, cutoff_additional_radian=0.0):
+        f, c = np.float32(falloff_radian), np.float32(cutoff_additional_radian)
+        if f <= 0 or f > np.float32(np.pi * 2):
+            raise ValueError("`SpotLight` invalid falloff angle")  # light.cpp:26-29
+        if c < 0 or f + c > np.float32(np.pi * 2):
+            raise ValueError("`SpotLight` invalid cutoff angle")   # light.cpp:30-33
+        import math
+        fc = A.lib().pb2h_cosf(float(f))
+        cc = A.lib().pb2h_cosf(float(np.float32(f + c)))
+        self.extra_lights.append((len(self.geometries),
+                                  self._light("spot", position, self._unit(direction), color, fc, cc)))
+
+    def set_sky(self, sun_color):
+        """scene.set(Sky(sun_color)): the environment light (light.cpp:71-84)"""
+        self.env_light = self._light("sky", color=sun_color)
+
+    def light_records(self):
+        """UniformLightSampler::lights (lightsampler.cpp:6-10): Scene::lights in insertion order -- an AreaLight
+        per Emissive geometry at the point it was added, the explicit lights where they were added -- then
+        the environment light."""
+        emissive = A.MATERIAL_KINDS["emissive"]
+        out, extra = [], list(self.extra_lights)
+        for g, (_, _, m) in enumerate(self.geometries):
+            while extra and extra[0][0] <= g:
+                out.append(extra.pop(0)[1])
+            if self.materials[m].kind == emissive:
+                l = A.Light()
+                l.kind, l.geometry = A.LIGHT_KINDS["area"], g
+                out.append(l)
+        out += [l for _, l in extra]
+        if self.env_light is not None:
+            out.append(self.env_light)
+        return out
+
     def set_camera(self, size, frm, to, fov, len_radius=0.0, focus=1.0, tonemapper="uncharted2"):
         self.size = (int(size[0]), int(size[1]))
         cam = A.Camera()
@@ -302,6 +362,8 @@ class Scene:
             t.rgba, t.width, t.height = a.ctypes.data, a.shape[1], a.shape[0]
             texs.append(t)
         put("textures", A.Texture, texs)
+        if self.extra_lights or self.env_light is not None:
+            put("light_records", A.Light, self.light_records())
         ls = self.lights()
         larr = (C.c_int32 * max(len(ls), 1))(*ls)
         keep.append(larr)

@@ -194,5 +194,34 @@ def materials_room(B, size=(96, 96)):
     return {"spp": 16, "depth": 6}
 
 
-SCENES = {"materials_room": materials_room, "cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
+def lights_yard(B, size=(96, 64), sky=True, delta=True, area=True):
+    """Parity scene for the lights the named configs never use (light.h:21-66): an open yard (ground, one
+    wall, a sphere, a cone, a box) lit by a DirectionalLight, a PointLight, a SpotLight (with a cutoff band),
+    a small Emissive rect ADDED BETWEEN them (Scene::lights keeps insertion order, scene.cpp:19-31) and
+    a Sky environment light (rays that leave the scene see it, light.cpp:71-84)."""
+    ground = B.add_material("diffuse", (0.6, 0.6, 0.55))
+    wall = B.add_material("glossy", (0.7, 0.3, 0.25), roughness=0.2)
+    ball = B.add_material("metal", (0.9, 0.85, 0.6), roughness=0.25)
+    cone = B.add_material("diffuse", (0.2, 0.5, 0.8))
+    B.add_rect((0, 0, 0), (8, 0, 0), (0, 0, 8), ground)
+    if delta:
+        B.add_directional_light((1.0, 2.0, -1.5), (2.5, 2.4, 2.2))
+    B.add_rect((0, 1, 2), (4, 0, 0), (0, 2, 0), wall)
+    B.add_sphere((-0.9, 0.5, 0.3), 0.5, ball)
+    if area:
+        lamp = B.add_material("emissive", (30.0, 24.0, 16.0))
+        B.add_rect((1.6, 1.8, 0.6), (0.5, 0, 0), (0, 0, 0.5), lamp)
+    if delta:
+        B.add_point_light((-1.5, 1.2, -0.8), (3.0, 4.0, 6.0))
+    B.add_cone((0.6, 0.0, 0.2), (0, 1, 0), 0.35, 0.9, cone)
+    B.add_box((0, 0, 0), (1, 1, 1), mat4.mul(mat4.translate((1.4, 0.0, -0.9)), mat4.mul(mat4.rotate_y(0.5), mat4.scale((0.5, 0.7, 0.5)))), ground)
+    if delta:
+        B.add_spot_light((0.0, 2.6, -1.2), (0.1, -1.0, 0.45), (40.0, 40.0, 36.0), 0.35, 0.2)
+    if sky:
+        B.set_sky((0.9, 1.0, 1.2))
+    B.set_camera(size, (0.4, 1.5, -4.5), (0.1, 0.7, 0), 0.3)
+    return {"spp": 16, "depth": 5}
+
+
+SCENES = {"materials_room": materials_room, "lights_yard": lights_yard, "cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
           "mesh_field": mesh_field}

@@ -108,6 +108,27 @@ def gltf_textured_kats():
     np.savez_compressed(os.path.join(OUT, "room_textured.npz"), **out)
 
 
+LIGHT_VARIANTS = {"all": {}, "no_sky": dict(sky=False), "sky_only": dict(delta=False, area=False),
+                  "delta_only": dict(sky=False, area=False), "area_sky": dict(delta=False)}
+
+
+def lights_kats():
+    """scenes.lights_yard (Directional / Point / Spot lights, an Emissive rect between them, Sky) rendered by the
+    reference: BlueSampler(16) films of every light subset, plus a SobolSampler(1024) film of the full scene."""
+    from pine_b200 import scenes
+    out = {}
+    for name, kw in LIGHT_VARIANTS.items():
+        R = ref.RefScene()
+        cfg = scenes.lights_yard(R, **kw)
+        out["film_" + name], _ = R.render(cfg["spp"], cfg["depth"])
+        out["n_lights_" + name] = np.array([R.L.ref_num_lights(R.h)], np.int32)
+    R = ref.RefScene()
+    cfg = scenes.lights_yard(R)
+    out["film_depth1"], _ = R.render(4, 1)
+    out["film_sobol1024"], _ = R.render(1024, cfg["depth"], sampler="sobol")
+    np.savez_compressed(os.path.join(OUT, "lights_yard.npz"), **out)
+
+
 def scene(name):
     fn, kw, spp, depth = common.SMALL_SCENES[name]
     R = ref.RefScene()
@@ -163,6 +184,7 @@ if __name__ == "__main__":
     sobol_kats()
     gltf_kats()
     gltf_textured_kats()
+    lights_kats()
     camera_lens()
     for name in common.SMALL_SCENES:
         scene(name)
