@@ -9,7 +9,7 @@ this is not it. It interprets exactly the grammar those files use:
 and binds the names the scripts call to the builder interface of `pine_b200.Scene` /
 `oracle.ref.RefScene` (program_context.cpp / *_context functions register the same names):
   Scene, Rect, Box, AABB, Cone, Sphere, Disk, Triangle, Diffuse, Metal, Glossy, Glass, Subsurface,
-  Emissive, translate, rotate_x/y/z, scale, ThinLenCamera, Film, Uncharted2, ACES, BlueSampler, SobolSampler, UniformSampler,
+  Emissive, PointLight, SpotLight, DirectionalLight, Sky, translate, rotate_x/y/z, scale, ThinLenCamera, Film, Uncharted2, ACES, BlueSampler, SobolSampler, UniformSampler,
   PathIntegrator, X/Y/Z.
 Arithmetic follows the JIT's types: int stays int, anything with a float is binary32, the inclusive
 float loop `a ~ s ~ b` accumulates in binary32 (jit.cpp:1534-1541), matrices multiply through the
@@ -182,6 +182,11 @@ class _Camera:
         return self.film_
 
 
+class _Light:
+    def __init__(self, kind, *a):
+        self.kind, self.a = kind, a
+
+
 class _Sampler:
     name = "BlueSampler"
 
@@ -256,7 +261,18 @@ class SceneProxy:
             raise PrlError("expected a material or a material name")
         return self.target.add_material(m.kind, m.color, **m.kw)
 
-    def add(self, a, b):
+    def add(self, a, b=None):
+        if isinstance(a, _Light) and b is None:  # scene.add(Light) (scene.cpp:29-31)
+            if a.kind == "point":
+                self.target.add_point_light(_vec(a.a[0]), _vec(a.a[1]))
+            elif a.kind == "directional":
+                self.target.add_directional_light(_vec(a.a[0]), _vec(a.a[1]))
+            elif a.kind == "spot":
+                self.target.add_spot_light(_vec(a.a[0]), _vec(a.a[1]), _vec(a.a[2]), float(_f32(a.a[3])),
+                                           float(_f32(a.a[4])) if len(a.a) > 4 else 0.0)
+            else:
+                raise PrlError("scene.add: an environment light is set with scene.set(...)")
+            return
         if isinstance(a, str):  # scene.add("name", Material)
             self.named[a] = self._material(b)
             return
@@ -301,6 +317,9 @@ class SceneProxy:
             gltf.scene_from_gltf(self.target, path, m)
 
     def set(self, cam):
+        if isinstance(cam, _Light) and cam.kind == "sky":  # scene.set(Sky(sun_color)) (scene.cpp:44-46)
+            self.target.set_sky(_vec(cam.a[0]))
+            return
         if not isinstance(cam, _Camera):
             raise PrlError("scene.set expects a camera")
         self.camera = cam
@@ -355,6 +374,9 @@ def _globals(make_scene):
         "rotate_z": lambda r: mat4.rotate_z(float(_f32(r))),
         "Film": lambda size, tm="uncharted2": _Film(size, tm),
         "Uncharted2": lambda: "uncharted2", "ACES": lambda: "aces",
+        "PointLight": lambda p, c: _Light("point", p, c),
+        "DirectionalLight": lambda d, c: _Light("directional", d, c),
+        "SpotLight": lambda *a: _Light("spot", *a), "Sky": lambda c: _Light("sky", c),
         "ThinLenCamera": _Camera, "BlueSampler": _Sampler, "SobolSampler": _SobolSampler,
         "UniformSampler": _UniformSampler, "PathIntegrator": _Integrator,
         "X": [1, 0, 0], "Y": [0, 1, 0], "Z": [0, 0, 1],

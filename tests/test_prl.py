@@ -136,3 +136,31 @@ def test_script_renders_like_the_builder_scene(tmp_path):
     film = pb.PathIntegrator(pb.BlueSampler(4), 3).render(S)
     assert np.array_equal(sp.target.camera.film().pixels.view(np.uint32), film.view(np.uint32))
     assert (tmp_path / "room.png").stat().st_size > 100
+
+
+def test_lights_and_sky_from_a_script():
+    # scene.add(PointLight | SpotLight | DirectionalLight) and scene.set(Sky) (light.cpp:174-185, scene.cpp:29-46)
+    src = """
+scene := Scene();
+scene.add(Rect([0, 0, 0], [8, 0, 0], [0, 0, 8]), Diffuse([0.6, 0.6, 0.55]));
+scene.add(DirectionalLight([1.0, 2.0, -1.5], [2.5, 2.4, 2.2]));
+scene.add(Rect([1.6, 1.8, 0.6], [0.5, 0, 0], [0, 0, 0.5]), Emissive([30, 24, 16]));
+scene.add(PointLight([-1.5, 1.2, -0.8], [3, 4, 6]));
+scene.add(SpotLight([0.0, 2.6, -1.2], [0.1, -1.0, 0.45], [40, 40, 36], 0.35, 0.2));
+scene.set(Sky([0.9, 1.0, 1.2]));
+scene.set(ThinLenCamera(Film([32, 16], Uncharted2()), [0.4, 1.5, -4.5], [0.1, 0.7, 0], 0.3));
+"""
+    sp, = prl.load(src, pb.Scene)
+    S = pb.Scene()
+    S.add_rect((0, 0, 0), (8, 0, 0), (0, 0, 8), S.add_material("diffuse", (0.6, 0.6, 0.55)))
+    S.add_directional_light((1.0, 2.0, -1.5), (2.5, 2.4, 2.2))
+    S.add_rect((1.6, 1.8, 0.6), (0.5, 0, 0), (0, 0, 0.5), S.add_material("emissive", (30, 24, 16)))
+    S.add_point_light((-1.5, 1.2, -0.8), (3, 4, 6))
+    S.add_spot_light((0.0, 2.6, -1.2), (0.1, -1.0, 0.45), (40, 40, 36), 0.35, 0.2)
+    S.set_sky((0.9, 1.0, 1.2))
+    a, b = sp.target.light_records(), S.light_records()
+    assert [l.kind for l in a] == [A.LIGHT_KINDS[k] for k in ("directional", "area", "point", "spot", "sky")]
+    assert [bytes(l) for l in a] == [bytes(l) for l in b]
+    d = np.array(list(a[0].direction), np.float32)
+    assert abs(float(np.linalg.norm(d)) - 1) < 1e-6  # DirectionalLight normalises (light.h:42)
+    assert np.float32(a[3].falloff_cos) == np.float32(np.cos(np.float32(0.35)))
