@@ -118,6 +118,7 @@ struct Flat {
   std::vector<pb2_disk> disks;
   std::vector<pb2_mesh> meshes;
   std::vector<int32_t> lights;
+  std::vector<pb2_light> light_records;
   pb2_scene_desc desc{};
 };
 
@@ -130,8 +131,8 @@ int32_t push(std::vector<T>& v, const S& s) {
 void flatten(Scene& scene, Flat& f) {
   if (scene.mediums.size())
     SEVERE("[CudaPathIntegrator]participating media are not supported by the CUDA path");
-  if (scene.env_light)
-    SEVERE("[CudaPathIntegrator]environment lights are not supported by the CUDA path");
+  if (scene.env_light && !scene.env_light->is<Sky>())
+    SEVERE("[CudaPathIntegrator]only the Sky environment light is supported by the CUDA path");
   if (scene.instancings.size())  // pine::BVH ignores them too (bvh.cpp:453-495)
     SEVERE("[CudaPathIntegrator]Scene::instancings are not supported: add flattened Mesh geometries");
   for (size_t gi = 0; gi < scene.geometries.size(); gi++) {
@@ -171,16 +172,46 @@ void flatten(Scene& scene, Flat& f) {
     }
     f.geometries.push_back(rec);
   }
-  // Scene::lights (scene.h:39): AreaLights were added per Emissive geometry in order (scene.cpp:19-20)
+  // UniformLightSampler::lights (lightsampler.cpp:6-10): Scene::lights in order (AreaLights were added per
+  // Emissive geometry, scene.cpp:19-20; the others by Scene::add_light), then the environment light
+  bool only_area = !scene.env_light;
   for (const Light& l : scene.lights) {
-    if (!l.is<AreaLight>())
-      SEVERE("[CudaPathIntegrator]only AreaLight is supported by the CUDA path");
-    const Geometry* lg = l.as<AreaLight>().geometry.get();
-    int32_t gi = -1;
-    for (size_t i = 0; i < scene.geometries.size(); i++)
-      if (scene.geometries[i].get() == lg) gi = int32_t(i);
-    if (gi < 0) SEVERE("[CudaPathIntegrator]AreaLight over a geometry that is not in Scene::geometries");
-    f.lights.push_back(gi);
+    pb2_light r{};
+    r.geometry = -1;
+    if (l.is<AreaLight>()) {
+      const Geometry* lg = l.as<AreaLight>().geometry.get();
+      for (size_t i = 0; i < scene.geometries.size(); i++)
+        if (scene.geometries[i].get() == lg) r.geometry = int32_t(i);
+      if (r.geometry < 0) SEVERE("[CudaPathIntegrator]AreaLight over a geometry that is not in Scene::geometries");
+      r.kind = PB2_LIGHT_AREA;
+      f.lights.push_back(r.geometry);
+    } else if (l.is<PointLight>()) {
+      r.kind = PB2_LIGHT_POINT;
+      put3(r.position, l.as<PointLight>().position);
+      put3(r.color, l.as<PointLight>().color);
+    } else if (l.is<SpotLight>()) {
+      auto& x = l.as<SpotLight>();
+      r.kind = PB2_LIGHT_SPOT;
+      put3(r.position, x.position); put3(r.direction, x.direction); put3(r.color, x.color);
+      r.falloff_cos = x.falloff_cos; r.cutoff_cos = x.cutoff_cos;
+    } else if (l.is<DirectionalLight>()) {
+      r.kind = PB2_LIGHT_DIRECTIONAL;
+      put3(r.direction, l.as<DirectionalLight>().direction);
+      put3(r.color, l.as<DirectionalLight>().color);
+    } else {
+      SEVERE("[CudaPathIntegrator]Atmosphere / ImageSky lights are not supported by the CUDA path");
+    }
+    only_area = only_area && r.kind == PB2_LIGHT_AREA;
+    f.light_records.push_back(r);
+  }
+  if (scene.env_light) {
+    // Sky's only data member is `vec3 sun_color` (light.h:57-66, private): read it by value
+    static_assert(sizeof(Sky) == 3 * sizeof(float), "Sky is expected to hold sun_color only");
+    pb2_light r{};
+    r.kind = PB2_LIGHT_SKY;
+    r.geometry = -1;
+    std::memcpy(r.color, &scene.env_light->as<Sky>(), sizeof(r.color));
+    f.light_records.push_back(r);
   }
   if (!scene.camera.is<ThinLenCamera>()) SEVERE("[CudaPathIntegrator]unsupported camera");
   auto& cam = scene.camera.as<ThinLenCamera>();
@@ -207,6 +238,7 @@ void flatten(Scene& scene, Flat& f) {
   d.disks = f.disks.data();           d.n_disks = uint32_t(f.disks.size());
   d.meshes = f.meshes.data();         d.n_meshes = uint32_t(f.meshes.size());
   d.light_geometries = f.lights.data(); d.n_lights = uint32_t(f.lights.size());
+  if (!only_area) { d.light_records = f.light_records.data(); d.n_light_records = uint32_t(f.light_records.size()); }
 }
 
 void check(int rc, const char* what) {

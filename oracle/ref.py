@@ -43,6 +43,8 @@ def lib():
         if hasattr(L, "ref_render_cuda"):
             L.ref_render_cuda.restype = C.c_double
             L.ref_render_cuda.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+            L.ref_render_cuda_kind.restype = C.c_double
+            L.ref_render_cuda_kind.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.ref_bounded_prepare.restype = C.c_double
         L.ref_bounded_prepare.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.ref_bounded_render_rows.restype = C.c_double
@@ -180,13 +182,14 @@ class RefScene:
         secs = self.L.ref_render(self.h, kind, spp, depth, film.ctypes.data_as(C.c_void_p))
         return film, secs
 
-    def render_cuda(self, spp, depth, device=0):
+    def render_cuda(self, spp, depth, device=0, sampler="blue"):
         """The drop-in test: THIS pine::Scene through pine::CudaPathIntegrator (integration/) ->
         (film, seconds, stats). The product library does the work; the harness only hosts the scene."""
         w, h = self.size
         film = np.zeros((h, w, 4), np.float32)
         stats = np.zeros(4, np.float64)
-        secs = lib().ref_render_cuda(self.h, spp, depth, device, film.ctypes.data, stats.ctypes.data)
+        kind = {"blue": 0, "sobol": 1, "uniform": 2}[sampler]
+        secs = lib().ref_render_cuda_kind(self.h, kind, spp, depth, device, film.ctypes.data, stats.ctypes.data)
         return film, secs, {"closest_rays": int(stats[0]), "shadow_rays": int(stats[1]),
                             "kernel_launches": int(stats[2]), "render_ms": float(stats[3])}
 

@@ -220,10 +220,13 @@ double ref_render(void* h, int sampler_kind, int spp, int depth, float* film_rgb
 // The drop-in: the SAME pine::Scene rendered by pine::CudaPathIntegrator (integration/), constructed
 // with PathIntegrator's own argument list. Returns wall seconds; stats = {closest rays, shadow rays,
 // kernel launches, device ms}. Aborts through SEVERE like the reference on unsupported content.
-double ref_render_cuda(void* h, int spp, int depth, int device, float* film_rgba, double* stats) {
+double ref_render_cuda_kind(void* h, int sampler_kind, int spp, int depth, int device, float* film_rgba,
+                            double* stats) {
   auto& S = *(RefScene*)h;
-  auto integrator = CudaPathIntegrator(Accel(BVH()), Sampler(BlueSobolSampler(spp)),
-                                       LightSampler(UniformLightSampler()), depth);
+  auto sampler = sampler_kind == 0   ? Sampler(BlueSobolSampler(spp))
+                 : sampler_kind == 1 ? Sampler(SobolSampler(spp))
+                                     : Sampler(UniformSampler(spp));
+  auto integrator = CudaPathIntegrator(Accel(BVH()), sampler, LightSampler(UniformLightSampler()), depth);
   integrator.set_device(device);
   auto t0 = std::chrono::steady_clock::now();
   Integrator& base = integrator;  // through the virtual interface, as the PRL binding calls it
@@ -240,6 +243,9 @@ double ref_render_cuda(void* h, int spp, int depth, int device, float* film_rgba
     stats[3] = integrator.last_render_ms();
   }
   return std::chrono::duration<double>(t1 - t0).count();
+}
+double ref_render_cuda(void* h, int spp, int depth, int device, float* film_rgba, double* stats) {
+  return ref_render_cuda_kind(h, 0, spp, depth, device, film_rgba, stats);
 }
 // Bounded-sample variant for timing (see BoundedPath): prepare once (returns the seconds the
 // prologue took, dominated by BVH::build), then render row subsets. BlueSobolSampler only.

@@ -33,6 +33,13 @@ if [[ $STEPS == *ncu* ]]; then
   ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches_c5s.csv \
       $CMD > $O/${TAG}_ncu_launches.log 2>&1
   echo "ncu launches rc=$?"
+  python scripts/launch_shares.py $O/${TAG}_launches_c5s.csv > $O/${TAG}_launch_shares_c5s.txt
+  # the default bench command (C5): one whole render = 32 waves x ~51 launches
+  CMD5="python bench.py --steps 1 --warmup 1 --no-cpu-baseline"
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 1700 --csv --log-file $O/${TAG}_launches_c5.csv \
+      $CMD5 > $O/${TAG}_ncu_launches_c5.log 2>&1
+  echo "ncu launches c5 rc=$?"
+  python scripts/launch_shares.py $O/${TAG}_launches_c5.csv > $O/${TAG}_launch_shares_c5.txt; tail -2 $O/${TAG}_launch_shares_c5.txt
   $CMD > $O/${TAG}_plain_c5s.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:'k_trace$|k_shadow$|k_shade_mat|k_classify|k_shade_terminal' -s 14 -c 7 \
       -f -o $O/${TAG}_prof_c5s $CMD > $O/${TAG}_ncu_full.log 2>&1
