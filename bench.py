@@ -251,8 +251,12 @@ def run_gpu(args):
     host_film = torch.empty((h, w, 4), dtype=torch.float32).pin_memory() if rank == 0 else None
     scene_bytes = c0["scene_bytes"] + 65536 + 2 * 131072
 
+    from pine_b200.multigpu import restage_sharded
+
     def e2e_step():
-        B.restage(stream)
+        # N = 1: the whole scene from pinned host memory. N > 1: each rank pulls 1/N of the large arrays
+        # through PCIe and the replicas are completed by in-place all-gathers over NVLink
+        restage_sharded(B, rank, world, stream)
         ptr = step()
         if rank == 0:
             src = film_t if world > 1 else torch.as_tensor(_DevicePtr(ptr, (h, w, 4)), device=dev)
@@ -326,7 +330,7 @@ def run_gpu(args):
                    "upload_scene_s": upload_s, "film_sum_rgb": film_sum},
         "e2e": {"value": e2e_value, "unit": "Msamples/s", "ms_per_step": e2e_ms_per_step,
                 "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(w * h * 16),
-                "what": "pb2_restage_scene (scene, BVH and sampler tables from pinned host memory) + "
+                "what": ("pb2_restage_scene" if world == 1 else f"pb2_restage_scene_part (1/{world} of the replica per rank through PCIe, all-gathered over NVLink)") + " (scene, BVH and sampler tables from pinned host memory) + "
                         "render + film to pinned host memory, every step; host BVH build not repeated"},
         "gpu_launches": int(launches),
         "clocks": clock_info,

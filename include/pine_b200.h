@@ -234,6 +234,19 @@ int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* scene);
  * context's stream). What pb2_upload_scene does after the host build; exposed so that a caller
  * (bench.py's end-to-end leg) can put the host->device transfer inside a timed region. */
 int pb2_restage_scene(pb2_context* ctx, void* cuda_stream);
+/* Staging for REPLICAS on one NVLink domain (one context per GPU, same scene on each): instead of every GPU
+ * pulling the whole scene through PCIe, part `part` of `n_parts` copies only its 1/n_parts slice of every large
+ * array (>= 1 MiB) from pinned host memory -- small arrays and the sampler tables whole -- and the caller
+ * all-gathers each large array IN PLACE over NVLink (NCCL: sendbuf = device_ptr + part * part_bytes, recvbuf =
+ * device_ptr, count = part_bytes; pine_b200/multigpu.py restage_sharded). `arrays` receives the large arrays
+ * (each padded to n_parts * part_bytes); at most max_arrays, the count in *n_arrays. */
+typedef struct pb2_device_array {
+  void* device_ptr;
+  uint64_t bytes;      /* n_parts * part_bytes (allocation, >= the array's own size) */
+  uint64_t part_bytes; /* multiple of 256 */
+} pb2_device_array;
+int pb2_restage_scene_part(pb2_context* ctx, void* cuda_stream, int part, int n_parts,
+                           pb2_device_array* arrays, int max_arrays, int* n_arrays);
 /* The Heitz et al. tables Pine links in (src/contrib/bluesobol/bluenoise_<spp>spp.cpp:2-12), as u8:
  * sobol[256*256], scramble[128*128*8], rank[128*128*8]. */
 int pb2_upload_sampler_tables(pb2_context* ctx, int spp_pow2, const uint8_t* sobol,

@@ -78,6 +78,10 @@ def _arr(name, typ):
     return [(name, C.POINTER(typ)), ("n_" + name, C.c_uint32)]
 
 
+class DeviceArray(C.Structure):
+    _fields_ = [("device_ptr", C.c_void_p), ("bytes", C.c_uint64), ("part_bytes", C.c_uint64)]
+
+
 class Light(C.Structure):
     _fields_ = [("kind", C.c_int32), ("geometry", C.c_int32), ("position", f3), ("direction", f3),
                 ("color", f3), ("falloff_cos", C.c_float), ("cutoff_cos", C.c_float)]
@@ -134,7 +138,7 @@ MATERIAL_KINDS = {"emissive": 0, "diffuse": 1, "metal": 2, "glossy": 3, "glass":
 # every symbol include/*.h declares (tests check the built library exports all of them)
 ABI_SYMBOLS = [
     "pb2_last_error", "pb2_device_count", "pb2_create", "pb2_destroy", "pb2_upload_scene",
-    "pb2_restage_scene",
+    "pb2_restage_scene", "pb2_restage_scene_part",
     "pb2_upload_sampler_tables", "pb2_load_sampler_tables_file", "pb2_render", "pb2_render_device", "pb2_film_finalize",
     "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler", "pb2_test_sampler_kind",
     "pb2_test_primary_rays", "pb2_get_counters", "pb2_debug_walk_stats", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
@@ -165,6 +169,8 @@ def lib():
         L.pb2_destroy.restype = None
         L.pb2_upload_scene.argtypes = [C.c_void_p, C.POINTER(SceneDesc)]
         L.pb2_restage_scene.argtypes = [C.c_void_p, C.c_void_p]
+        L.pb2_restage_scene_part.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int,
+                                             C.c_void_p]
         L.pb2_upload_sampler_tables.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                                 C.c_void_p]
         L.pb2_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p]

@@ -336,15 +336,39 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   return PB2_OK;
 }
 
-extern "C" int pb2_restage_scene(pb2_context* ctx, void* cuda_stream) {
+namespace {
+// Copies the staging list (whole, or part `part` of `n_parts` of every array >= kShardMinBytes) and rebinds the
+// device pointers of ctx->scene.
+constexpr size_t kShardMinBytes = size_t(1) << 20;
+int restage(pb2_context* ctx, void* cuda_stream, int part, int n_parts, pb2_device_array* arrays, int max_arrays,
+            int* n_arrays) {
   if (!ctx || !ctx->host_scene_ready || ctx->device < 0) { set_error("no host scene / no device"); return PB2_E_STATE; }
+  if (n_parts < 1 || part < 0 || part >= n_parts) { set_error("part out of range"); return PB2_E_INVALID; }
   PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
   auto t0 = std::chrono::steady_clock::now();
+  int n_out = 0;
   for (const HostScene::Item& it : ctx->host.items) {
-    PB2_CUDA_CHECK(it.dst->reserve(it.bytes));
-    if (it.bytes) PB2_CUDA_CHECK(cudaMemcpyAsync(it.dst->ptr, it.src, it.bytes, cudaMemcpyHostToDevice, st));
+    if (n_parts == 1 || it.bytes < kShardMinBytes) {
+      PB2_CUDA_CHECK(it.dst->reserve(it.bytes));
+      if (it.bytes) PB2_CUDA_CHECK(cudaMemcpyAsync(it.dst->ptr, it.src, it.bytes, cudaMemcpyHostToDevice, st));
+      continue;
+    }
+    const size_t part_bytes = ((it.bytes + size_t(n_parts) - 1) / size_t(n_parts) + 255) / 256 * 256;
+    PB2_CUDA_CHECK(it.dst->reserve(part_bytes * size_t(n_parts)));
+    const size_t off = part_bytes * size_t(part);
+    if (off < it.bytes) {
+      const size_t len = std::min(part_bytes, it.bytes - off);
+      PB2_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(it.dst->ptr) + off, static_cast<const char*>(it.src) + off, len,
+                                     cudaMemcpyHostToDevice, st));
+    }
+    if (arrays) {
+      if (n_out >= max_arrays) { set_error("pb2_restage_scene_part: max_arrays too small"); return PB2_E_INVALID; }
+      arrays[n_out] = pb2_device_array{it.dst->ptr, uint64_t(part_bytes) * uint64_t(n_parts), uint64_t(part_bytes)};
+    }
+    n_out++;
   }
+  if (n_arrays) *n_arrays = n_out;
   if (ctx->tables_spp) {  // the active sampler tables travel with the scene
     int k = 0;
     while ((1 << k) != ctx->tables_spp) k++;
@@ -371,6 +395,15 @@ extern "C" int pb2_restage_scene(pb2_context* ctx, void* cuda_stream) {
   ctx->counters.upload_ms =
       std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   return PB2_OK;
+}
+}  // namespace
+
+extern "C" int pb2_restage_scene(pb2_context* ctx, void* cuda_stream) {
+  return restage(ctx, cuda_stream, 0, 1, nullptr, 0, nullptr);
+}
+extern "C" int pb2_restage_scene_part(pb2_context* ctx, void* cuda_stream, int part, int n_parts,
+                                      pb2_device_array* arrays, int max_arrays, int* n_arrays) {
+  return restage(ctx, cuda_stream, part, n_parts, arrays, max_arrays, n_arrays);
 }
 
 extern "C" int pb2_bvh_info(pb2_context* ctx, int which, int32_t* n_nodes, int32_t* root,

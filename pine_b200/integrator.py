@@ -162,6 +162,15 @@ class Backend:
         """Copy the built scene host->device again (asynchronously on `stream`)."""
         A.check(self.L.pb2_restage_scene(self.h, stream))
 
+    def restage_part(self, part, n_parts, stream=None):
+        """Copy only slice `part` of `n_parts` of every large scene array host->device (small ones whole);
+        -> [(device pointer, padded bytes, part bytes)] of the large arrays, for an in-place all-gather
+        (multigpu.restage_sharded)."""
+        arr = (A.DeviceArray * 64)()
+        n = C.c_int(0)
+        A.check(self.L.pb2_restage_scene_part(self.h, stream, part, n_parts, arr, 64, C.byref(n)))
+        return [(int(arr[i].device_ptr), int(arr[i].bytes), int(arr[i].part_bytes)) for i in range(n.value)]
+
     def render(self, spp, depth, rows=None, samples=None, accel=0, out=None, flags=0):
         """-> film float32 [h, w, 4] in host memory (pre-tonemap). `out` may be any writable
         C-contiguous float32 buffer object of that size (e.g. a pinned torch tensor's numpy view)."""

@@ -82,3 +82,25 @@ class ShardedRenderer:
             import torch.distributed as dist
             dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM, group=self.group)
         return film
+
+
+def restage_sharded(backend, rank, world, stream=None, group=None):
+    """Re-stage a scene that every rank of one NVLink domain holds a replica of: each rank pulls 1/world of
+    every large array through PCIe from its pinned host copy (pb2_restage_scene_part) and the slices are
+    all-gathered in place over NVLink / NVSwitch -- world x less host traffic per GPU than world full copies,
+    which is what bounds the end-to-end step at 8 GPUs (1.43 GB per replica on C5). Collectives run on
+    torch's current stream; `stream` must be that stream (or None with a synchronised context stream)."""
+    arrays = backend.restage_part(rank, world, stream)
+    if world == 1:
+        return 0
+    import torch
+    import torch.distributed as dist
+    moved = 0
+    for ptr, nbytes, part in arrays:
+        class _P:
+            __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                        "version": 3, "strides": None}
+        full = torch.as_tensor(_P(), device=f"cuda:{backend.device}")
+        dist.all_gather_into_tensor(full, full[rank * part:(rank + 1) * part], group=group)
+        moved += nbytes
+    return moved

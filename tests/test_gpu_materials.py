@@ -89,3 +89,28 @@ def test_sharded_plans_on_one_gpu(world):
             ratio = got[..., :3].astype(np.float64).sum() / full[..., :3].astype(np.float64).sum()
             assert abs(ratio - 1) < 0.1, ratio
     B.close()
+
+
+def test_sharded_restaging_rebuilds_the_replica():
+    """pb2_restage_scene_part: the slices of all parts together are the whole scene (here copied one after the
+    other into ONE context; across GPUs multigpu.restage_sharded all-gathers them over NVLink), so the render
+    after it equals the render after a full upload bit for bit."""
+    S = pb.Scene()
+    cfg = scenes.mesh_field(S, n_instances=40, subdiv=4, size=(96, 54), spp=4, depth=4, with_shapes=True)
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    want = B.render(4, 4)
+    for n_parts in (2, 3, 8):
+        seen = None
+        for part in range(n_parts):
+            arrays = B.restage_part(part, n_parts)
+            assert arrays and all(b == n_parts * p and p % 256 == 0 for _, b, p in arrays)
+            assert seen is None or [a[1:] for a in arrays] == [a[1:] for a in seen]
+            seen = arrays
+        assert np.array_equal(u32(B.render(4, 4)), u32(want)), n_parts
+    from pine_b200.multigpu import restage_sharded
+    assert restage_sharded(B, 0, 1) == 0  # world 1: a plain full restage
+    assert np.array_equal(u32(B.render(4, 4)), u32(want))
+    with pytest.raises(pb.PineB200Error):
+        B.restage_part(2, 2)
+    B.close()
