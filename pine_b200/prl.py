@@ -31,7 +31,7 @@ _TOKEN = re.compile(r"""
   | (?P<num>\d+\.\d*(?:[eE][-+]?\d+)?|\.\d+(?:[eE][-+]?\d+)?|\d+[eE][-+]?\d+|\d+)
   | (?P<str>"[^"\n]*")
   | (?P<id>[A-Za-z_][A-Za-z_0-9]*)
-  | (?P<op>:=|[-+*/~.,;(){}\[\]])
+  | (?P<op>:=|[-+*/~.,;(){}\[\]=])
 """, re.X)
 
 
@@ -87,9 +87,9 @@ class Parser:
                 body.append(self.statement())
             self.take("}")
             return ("for", var, a, step, b, body)
-        if tok[0] == "id" and self.peek(1)[1] == ":=":
+        if tok[0] == "id" and self.peek(1)[1] in (":=", "="):  # `:=` declares, `=` assigns (minimal.pine)
             name = self.take()[1]
-            self.take(":=")
+            self.take()
             e = self.expr()
             self.take(";")
             return ("assign", name, e)
@@ -315,6 +315,15 @@ class SceneProxy:
         else:
             from . import gltf
             gltf.scene_from_gltf(self.target, path, m)
+
+    def quick_render(self, frm, to, filename):
+        """quick_render(scene, from, to, file) (program_context.cpp:120-124): 640x480 film, fov 0.5,
+        PathIntegrator(BlueSampler(4), 4), save."""
+        self.set(_Camera(_Film([640, 480]), frm, to, 0.5))
+        _Integrator(_Sampler(4), 4).render(self)
+        self.config["save"] = filename
+        if self.on_save:
+            self.on_save(self, filename)
 
     def set(self, cam):
         if isinstance(cam, _Light) and cam.kind == "sky":  # scene.set(Sky(sun_color)) (scene.cpp:44-46)

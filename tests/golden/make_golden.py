@@ -129,6 +129,17 @@ def lights_kats():
     np.savez_compressed(os.path.join(OUT, "lights_yard.npz"), **out)
 
 
+def minimal_kats():
+    """What `scenes/minimal.pine` asks for (a unit sphere, one DirectionalLight, quick_render =
+    640x480, fov 0.5, PathIntegrator(BlueSampler(4), 4), program_context.cpp:120-124) rendered by the reference."""
+    R = ref.RefScene()
+    R.add_sphere((0, 0, 0), 1.0, R.add_material("diffuse", (1, 1, 1)))
+    R.add_directional_light((1, 1, -1), (1, 1, 1))
+    R.set_camera((640, 480), (0, 0, -4), (0, 0, 0), 0.5)
+    film, _ = R.render(4, 4)
+    np.savez_compressed(os.path.join(OUT, "minimal.npz"), film=film.astype(np.float16), film_sum=np.array([film[..., :3].astype(np.float64).sum()]))
+
+
 def scene(name):
     fn, kw, spp, depth = common.SMALL_SCENES[name]
     R = ref.RefScene()
@@ -185,6 +196,7 @@ if __name__ == "__main__":
     gltf_kats()
     gltf_textured_kats()
     lights_kats()
+    minimal_kats()
     camera_lens()
     for name in common.SMALL_SCENES:
         scene(name)

@@ -12,6 +12,7 @@ import pytest
 import pine_b200 as pb
 from pine_b200 import _abi as A
 from pine_b200 import prl, scenes
+from common import relmse
 
 REFERENCE = "/root/reference"
 needs_reference_tree = pytest.mark.skipif(not os.path.isdir(os.path.join(REFERENCE, "scenes")),
@@ -164,3 +165,42 @@ scene.set(ThinLenCamera(Film([32, 16], Uncharted2()), [0.4, 1.5, -4.5], [0.1, 0.
     d = np.array(list(a[0].direction), np.float32)
     assert abs(float(np.linalg.norm(d)) - 1) < 1e-6  # DirectionalLight normalises (light.h:42)
     assert np.float32(a[3].falloff_cos) == np.float32(np.cos(np.float32(0.35)))
+
+
+MINIMAL = """
+scene = Scene();
+scene.add(Sphere([0, 0, 0], 1), Diffuse([1, 1, 1]));
+scene.add(DirectionalLight([1, 1, -1], [1, 1, 1]));
+scene.quick_render([0, 0, -4], [0, 0, 0], "images/minimal.png");
+"""
+
+
+def test_minimal_scene_with_quick_render():
+    # the shape of scenes/minimal.pine: `=` assignment, a delta light, quick_render (program_context.cpp:120-124)
+    saves = []
+    sp, = prl.load(MINIMAL, pb.Scene, on_save=lambda s, p: saves.append(p))
+    assert sp.config == {"spp": 4, "depth": 4, "save": "images/minimal.png"} and saves == ["images/minimal.png"]
+    assert sp.target.size == (640, 480) and len(sp.target.geometries) == 1
+    S = pb.Scene()
+    S.add_sphere((0, 0, 0), 1.0, S.add_material("diffuse", (1, 1, 1)))
+    S.add_directional_light((1, 1, -1), (1, 1, 1))
+    S.set_camera((640, 480), (0, 0, -4), (0, 0, 0), 0.5)
+    assert desc_bytes(sp.target) == desc_bytes(S)
+    assert [bytes(l) for l in sp.target.light_records()] == [bytes(l) for l in S.light_records()]
+    ref_file = "/root/reference/scenes/minimal.pine"
+    if os.path.isfile(ref_file):  # the reference's own file, where the checkout is present
+        sp2, = prl.load(open(ref_file).read(), pb.Scene)
+        assert desc_bytes(sp2.target) == desc_bytes(S) and sp2.config == sp.config
+
+
+@pytest.mark.gpu
+def test_minimal_scene_renders_like_the_reference(golden, tmp_path):
+    g = golden("minimal")
+    path = tmp_path / "minimal.pine"
+    path.write_text(MINIMAL.replace("images/minimal.png", str(tmp_path / "minimal.png")))
+    sp, = prl.run_file(str(path))
+    film = sp.target.camera.film().pixels
+    assert film.shape == (480, 640, 4)
+    assert abs(float(film[..., :3].astype(np.float64).sum()) / float(g["film_sum"][0]) - 1) < 1e-5
+    assert relmse(film, g["film"].astype(np.float32)) <= 1e-4  # the fixture is stored as float16
+    assert (tmp_path / "minimal.png").stat().st_size > 1000
