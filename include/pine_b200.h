@@ -188,13 +188,16 @@ typedef struct pb2_render_params {
    * [1, 65536], streams bit-identical to the reference's. PB2_SAMPLER_UNIFORM: UniformSampler(spp,
    * sampler_seed) (sampler.h:13-39) -- the reference draws from one RNG per worker thread, so its
    * stream depends on the thread schedule; here every (pixel, sample, dimension) has its own
-   * counter-based draw from the same generator (rng.h:97-144): statistically equivalent only. */
+   * counter-based draw from the same generator (rng.h:97-144): statistically equivalent only.
+   * PB2_SAMPLER_HALTON: HaltonSampler(spp), digit permutations from compute_radical_inverse_permutations
+   * (lowdiscrepancy.cpp:5-17) rebuilt on the host with the same generator; draws bit-identical. */
   int32_t sampler;
   int32_t sampler_seed;
 } pb2_render_params;
 #define PB2_SAMPLER_BLUE 0
 #define PB2_SAMPLER_SOBOL 1
 #define PB2_SAMPLER_UNIFORM 2
+#define PB2_SAMPLER_HALTON 3 /* HaltonSampler(spp) (sampler.h:40-81, sampler.cpp:20-81): bit-identical draws */
 #define PB2_RENDER_SORT_BY_MATERIAL 1 /* bucket the shade queue by BxDF kind */
 #define PB2_RENDER_TIME_KERNELS 2     /* fill pb2_counters.last_{trace,shadow,shade,other}_ms */
 #define PB2_RENDER_KEEP_FILM 4        /* do not clear the device film first: rows outside

@@ -251,8 +251,9 @@ CudaPathIntegrator::CudaPathIntegrator(Accel, Sampler sampler, LightSampler, int
     : sampler_(MOVE(sampler)), max_path_length_(max_path_length) {
   if (max_path_length <= 0)  // path.cpp:12-13
     SEVERE("`PathIntegrator` expect `max_path_length` to be positive, get", max_path_length);
-  if (!sampler_.is<BlueSobolSampler>() && !sampler_.is<SobolSampler>() && !sampler_.is<UniformSampler>())
-    SEVERE("[CudaPathIntegrator]only BlueSampler, SobolSampler and UniformSampler run on the CUDA path");
+  if (!sampler_.is<BlueSobolSampler>() && !sampler_.is<SobolSampler>() && !sampler_.is<UniformSampler>() &&
+      !sampler_.is<HaltonSampler>())
+    SEVERE("[CudaPathIntegrator]only BlueSampler, SobolSampler, HaltonSampler and UniformSampler run on the CUDA path");
 }
 CudaPathIntegrator::CudaPathIntegrator(Sampler sampler, int max_path_length)
     : CudaPathIntegrator(Accel(), MOVE(sampler), LightSampler(UniformLightSampler()), max_path_length) {}
@@ -273,6 +274,7 @@ void CudaPathIntegrator::render(Scene& scene) {
   check(pb2_upload_scene(ctx_, &flat.desc), "pb2_upload_scene");
   const int kind = sampler_.is<SobolSampler>()     ? PB2_SAMPLER_SOBOL
                    : sampler_.is<UniformSampler>() ? PB2_SAMPLER_UNIFORM
+                   : sampler_.is<HaltonSampler>()  ? PB2_SAMPLER_HALTON
                                                    : PB2_SAMPLER_BLUE;
   if (kind == PB2_SAMPLER_BLUE) {
     const char* tables = std::getenv("PINE_B200_TABLES");

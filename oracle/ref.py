@@ -178,7 +178,7 @@ class RefScene:
         -> (film float32 [h, w, 4] pre-tonemap, wall seconds incl. BVH build)."""
         w, h = self.size
         film = np.zeros((h, w, 4), np.float32)
-        kind = {"blue": 0, "sobol": 1, "uniform": 2}[sampler]
+        kind = {"blue": 0, "sobol": 1, "uniform": 2, "halton": 3}[sampler]
         secs = self.L.ref_render(self.h, kind, spp, depth, film.ctypes.data_as(C.c_void_p))
         return film, secs
 
@@ -188,7 +188,7 @@ class RefScene:
         w, h = self.size
         film = np.zeros((h, w, 4), np.float32)
         stats = np.zeros(4, np.float64)
-        kind = {"blue": 0, "sobol": 1, "uniform": 2}[sampler]
+        kind = {"blue": 0, "sobol": 1, "uniform": 2, "halton": 3}[sampler]
         secs = lib().ref_render_cuda_kind(self.h, kind, spp, depth, device, film.ctypes.data, stats.ctypes.data)
         return film, secs, {"closest_rays": int(stats[0]), "shadow_rays": int(stats[1]),
                             "kernel_launches": int(stats[2]), "render_ms": float(stats[3])}
@@ -307,7 +307,7 @@ def sampler_stream_kind(sampler, spp, size, px, py, sample_index, pattern, n_sam
     """get1d/get2d draws of Sampler(<sampler>(spp)) after init(size), start_pixel((px, py), sample_index)."""
     width = sum(1 if c == "1" else 2 for c in pattern)
     d = np.zeros(max(width * n_samples, 1), np.float32)
-    kind = {"blue": 0, "sobol": 1, "uniform": 2}[sampler]
+    kind = {"blue": 0, "sobol": 1, "uniform": 2, "halton": 3}[sampler]
     lib().ref_sampler_stream_kind(kind, spp, size[0], size[1], px, py, sample_index, pattern.encode(),
                                   n_samples, _fp(d))
     return d[:width * n_samples].reshape(n_samples, width)

@@ -205,7 +205,7 @@ double ref_render(void* h, int sampler_kind, int spp, int depth, float* film_rgb
   auto& S = *(RefScene*)h;
   auto sampler = sampler_kind == 0   ? Sampler(BlueSobolSampler(spp))
                  : sampler_kind == 1 ? Sampler(SobolSampler(spp))
-                                     : Sampler(UniformSampler(spp));
+                                     : sampler_kind == 3 ? Sampler(HaltonSampler(spp)) : Sampler(UniformSampler(spp));
   auto integrator = PathIntegrator(Accel(BVH()), MOVE(sampler), LightSampler(UniformLightSampler()),
                                    depth);
   auto t0 = std::chrono::steady_clock::now();
@@ -225,7 +225,7 @@ double ref_render_cuda_kind(void* h, int sampler_kind, int spp, int depth, int d
   auto& S = *(RefScene*)h;
   auto sampler = sampler_kind == 0   ? Sampler(BlueSobolSampler(spp))
                  : sampler_kind == 1 ? Sampler(SobolSampler(spp))
-                                     : Sampler(UniformSampler(spp));
+                                     : sampler_kind == 3 ? Sampler(HaltonSampler(spp)) : Sampler(UniformSampler(spp));
   auto integrator = CudaPathIntegrator(Accel(BVH()), sampler, LightSampler(UniformLightSampler()), depth);
   integrator.set_device(device);
   auto t0 = std::chrono::steady_clock::now();
@@ -438,7 +438,7 @@ void ref_sampler_stream_kind(int sampler_kind, int spp, int width, int height, i
                              int sample_index, const char* pattern, int n_samples, float* out_draws) {
   Sampler sampler = sampler_kind == 0   ? Sampler(BlueSobolSampler(spp))
                     : sampler_kind == 1 ? Sampler(SobolSampler(spp))
-                                        : Sampler(UniformSampler(spp));
+                                        : sampler_kind == 3 ? Sampler(HaltonSampler(spp)) : Sampler(UniformSampler(spp));
   sampler.init(vec2i(width, height));
   sampler.start_pixel(vec2i(px, py), sample_index);
   for (int s = 0; s < n_samples; s++, sampler.start_next_sample())

@@ -106,7 +106,7 @@ class RenderParams(C.Structure):
                 ("sampler_seed", C.c_int32)]
 
 
-SAMPLER_BLUE, SAMPLER_SOBOL, SAMPLER_UNIFORM = 0, 1, 2
+SAMPLER_BLUE, SAMPLER_SOBOL, SAMPLER_UNIFORM, SAMPLER_HALTON = 0, 1, 2, 3
 
 
 class RayRecord(C.Structure):

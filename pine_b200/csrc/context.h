@@ -106,6 +106,7 @@ struct pb2_context {
   pb2::DBuf aabbs, obbs, spheres, triangles, cones, rects, disks;
   pb2::DBuf verts, tris, normals, uvs, texels, textures, srgb_lut;
   pb2::DBuf tab_sobol, tab_scramble, tab_rank;
+  pb2::DBuf halton_primes, halton_sums, halton_perms;  // HaltonSampler tables, made on first use
   int tables_spp = 0;
   pb2::SamplerTables tables[9];  // index = log2(spp)
   bool has_tables[9] = {};

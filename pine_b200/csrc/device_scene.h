@@ -145,6 +145,11 @@ struct DScene {
   // sampler of the current render (PB2_SAMPLER_*); SobolSampler::log2_spp / nbase4_digits (sampler.h:128-130,
   // sampler.cpp:82-85)
   int sampler_kind, sampler_seed, log2_spp, nbase4_digits;
+  // HaltonSampler tables (sampling.cuh HaltonTables) and multInverse[0..1] (sampler.cpp:61-62)
+  const int32_t* halton_primes;
+  const int32_t* halton_sums;
+  const uint16_t* halton_perms;
+  int halton_inv0, halton_inv1;
   pb2_camera camera;
   unsigned long long* walk_stats;  // PB2_COUNT builds only: {closest nodes, closest prims, any nodes, any prims,
                                    // closest rays, any rays}; NULL otherwise

@@ -593,6 +593,57 @@ int sm_grid(int work_items, int block, int max_waves_per_sm) {
   return int(g > 0 ? g : kNumSMs);
 }
 
+// Host tables of HaltonSampler: the first 1000 primes and their running sums (primes.cpp), the digit
+// permutations compute_radical_inverse_permutations(RNG()) makes (lowdiscrepancy.cpp:5-17: identity
+// shuffled with `other = i + rng.next32u(count - i)`, lowdiscrepancy.h:53-60), and multInverse
+// (sampler.cpp:20-41,61-62).
+struct HaltonHost {
+  std::vector<int32_t> primes, sums;
+  std::vector<uint16_t> perms;
+  int inv0 = 0, inv1 = 0;
+};
+int64_t pmod(int64_t a, int64_t n) { int64_t r = a % n; return r < 0 ? r + n : r; }
+void extended_gcd(uint64_t a, uint64_t b, int64_t& gcd, int64_t& x, int64_t& y) {
+  const int d = int(a / b), r = int(a - uint64_t(d) * b);
+  if (r == 0) { gcd = int64_t(b); x = 0; y = 1; return; }
+  int64_t nx, ny;
+  extended_gcd(b, uint64_t(r), gcd, nx, ny);
+  x = ny;
+  y = nx - d * ny;
+}
+const HaltonHost& halton_host() {
+  static const HaltonHost H = [] {
+    HaltonHost h;
+    for (int n = 2; int(h.primes.size()) < kHaltonPrimes; n++) {
+      bool prime = true;
+      for (int d = 2; d * d <= n && prime; d++) prime = n % d != 0;
+      if (prime) h.primes.push_back(n);
+    }
+    int32_t sum = 0;
+    for (int p : h.primes) { h.sums.push_back(sum); sum += p; }
+    h.perms.resize(size_t(sum));
+    Rng g = rng_seed(0);
+    uint16_t* p = h.perms.data();
+    for (int i = 0; i < kHaltonPrimes; i++) {
+      const int count = h.primes[i];
+      for (int j = 0; j < count; j++) p[j] = uint16_t(j);
+      for (int j = 0; j < count; j++) {
+        const uint64_t u = rng_next(g);
+        const uint32_t other = uint32_t(j) + uint32_t(u ^ (u >> 32)) % uint32_t(count - j);
+        std::swap(p[j], p[other]);
+      }
+      p += count;
+    }
+    int64_t gcd, x, y;
+    extended_gcd(kHaltonScale2, kHaltonScale3, gcd, x, y);
+    h.inv0 = int(pmod(x, kHaltonScale3));
+    extended_gcd(kHaltonScale3, kHaltonScale2, gcd, x, y);
+    h.inv1 = int(pmod(x, kHaltonScale2));
+    return h;
+  }();
+  return H;
+}
+
 int floor_log2(int v) {  // psl::log2i == hsb (psl/math.h:81,262)
   int r = 0;
   while (v > 1) { v >>= 1; r++; }
@@ -609,6 +660,19 @@ int select_sampler(pb2_context* ctx, int kind, int spp, int seed) {
   while (pow2 < res) pow2 <<= 1;  // psl::roundup2
   sc.nbase4_digits = floor_log2(pow2) + (sc.log2_spp + 1) / 2;
   if (kind == PB2_SAMPLER_BLUE) return activate_tables(ctx, spp);
+  if (kind == PB2_SAMPLER_HALTON) {
+    const HaltonHost& H = halton_host();
+    if (!ctx->halton_perms.ptr) {
+      PB2_CUDA_CHECK(ctx->halton_primes.upload(H.primes));
+      PB2_CUDA_CHECK(ctx->halton_sums.upload(H.sums));
+      PB2_CUDA_CHECK(ctx->halton_perms.upload(H.perms));
+    }
+    sc.halton_primes = ctx->halton_primes.as<int32_t>();
+    sc.halton_sums = ctx->halton_sums.as<int32_t>();
+    sc.halton_perms = ctx->halton_perms.as<uint16_t>();
+    sc.halton_inv0 = H.inv0;
+    sc.halton_inv1 = H.inv1;
+  }
   return PB2_OK;
 }
 
@@ -627,14 +691,14 @@ int check_params(pb2_context* ctx, const pb2_render_params* p) {
       set_error("spp must be BlueSobolSampler::spp(): a power of two <= 256");
       return PB2_E_INVALID;
     }
-  } else if (p->sampler == PB2_SAMPLER_SOBOL || p->sampler == PB2_SAMPLER_UNIFORM) {
+  } else if (p->sampler == PB2_SAMPLER_SOBOL || p->sampler == PB2_SAMPLER_UNIFORM || p->sampler == PB2_SAMPLER_HALTON) {
     if (p->spp <= 0) {  // sampler.h:16-17
       set_error("`UniformSampler` should have positive samples per pixel");
       return PB2_E_INVALID;
     }
     if (p->spp > 65536) { set_error("spp > 65536 is not supported"); return PB2_E_UNSUPPORTED; }
   } else {
-    set_error("unknown sampler kind " + std::to_string(p->sampler) + " (HaltonSampler is not supported)");
+    set_error("unknown sampler kind " + std::to_string(p->sampler));
     return PB2_E_UNSUPPORTED;
   }
   if (p->row_begin < 0 || p->row_end > h || p->row_begin > p->row_end || p->sample_begin < 0 ||
@@ -1070,8 +1134,8 @@ extern "C" int pb2_test_sampler_kind(pb2_context* ctx, int sampler, int spp, int
 // code the kernels inline): lets the CPU test-suite pin their integer arithmetic against the reference.
 extern "C" int pb2h_sampler_draws(int sampler, int spp, int sampler_seed, int width, int height, int px, int py,
                                   int sample_index, const char* pattern, int n_samples, float* out_draws) {
-  if (sampler != PB2_SAMPLER_SOBOL && sampler != PB2_SAMPLER_UNIFORM) {
-    set_error("pb2h_sampler_draws: SobolSampler and UniformSampler only (BlueSampler reads device tables)");
+  if (sampler != PB2_SAMPLER_SOBOL && sampler != PB2_SAMPLER_UNIFORM && sampler != PB2_SAMPLER_HALTON) {
+    set_error("pb2h_sampler_draws: Sobol / Uniform / Halton samplers only (BlueSampler reads device tables)");
     return PB2_E_UNSUPPORTED;
   }
   if (spp <= 0 || !pattern || !out_draws) { set_error("invalid argument"); return PB2_E_INVALID; }
@@ -1085,6 +1149,11 @@ extern "C" int pb2h_sampler_draws(int sampler, int spp, int sampler_seed, int wi
       if (sampler == PB2_SAMPLER_SOBOL) {
         if (*c == '1') { *out_draws++ = sobol_get1d(s, log2_spp, nb4); }
         else { V2 u = sobol_get2d(s, log2_spp, nb4); *out_draws++ = u.x; *out_draws++ = u.y; }
+      } else if (sampler == PB2_SAMPLER_HALTON) {
+        const HaltonHost& H = halton_host();
+        const HaltonTables t{H.primes.data(), H.sums.data(), H.perms.data()};
+        if (*c == '1') { *out_draws++ = halton_get1d(t, s, H.inv0, H.inv1); }
+        else { V2 u = halton_get2d(t, s, H.inv0, H.inv1); *out_draws++ = u.x; *out_draws++ = u.y; }
       } else {
         const int n = *c == '1' ? 1 : 2;
         for (int i = 0; i < n; i++) *out_draws++ = uniform_dim(s, sampler_seed, s.dim++);

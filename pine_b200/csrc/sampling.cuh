@@ -183,11 +183,73 @@ __host__ __device__ __forceinline__ float uniform_dim(const PixelSampler& s, int
   return rng_nextf(g);
 }
 
+// HaltonSampler (sampler.h:40-81, sampler.cpp:20-81, lowdiscrepancy.h:26-51): the pixel's first index comes
+// from the inverse radical inverses of (x mod 128, y mod 128) in bases 2 and 3 combined by the Chinese
+// remainder theorem, samples are `stride` = 128 * 243 apart, dimension d >= 2 is the radical inverse in the
+// d-th prime with a fixed random digit permutation (tables made on the host, halton_tables below).
+struct HaltonTables {
+  const int32_t* primes;   // Primes[1000] (primes.cpp)
+  const int32_t* sums;     // PrimeSums[1000]: offset of each base's permutation
+  const uint16_t* perms;   // compute_radical_inverse_permutations(RNG()) (lowdiscrepancy.cpp:5-17)
+};
+constexpr int kHaltonPrimes = 1000;           // PrimeTablesize (primes.h:7)
+constexpr int kHaltonScale2 = 128, kHaltonScale3 = 243, kHaltonExp2 = 7, kHaltonExp3 = 5;
+constexpr int kHaltonStride = kHaltonScale2 * kHaltonScale3;
+__host__ __device__ __forceinline__ uint64_t inverse_radical_inverse(uint64_t inverse, int base, int n_digits) {
+  uint64_t index = 0;
+  for (int i = 0; i < n_digits; i++) {
+    const uint64_t digit = inverse % uint64_t(base);
+    inverse /= uint64_t(base);
+    index = index * uint64_t(base) + digit;
+  }
+  return index;
+}
+__host__ __device__ __forceinline__ uint64_t halton_index_of(const PixelSampler& s, int inv0, int inv1) {  // sampler.cpp:67-81
+  const int pmx = ((s.px % 128) + 128) % 128, pmy = ((s.py % 128) + 128) % 128;  // psl::mod
+  int64_t h = 0;
+  h += int64_t(inverse_radical_inverse(uint64_t(pmx), 2, kHaltonExp2) * uint64_t(kHaltonScale3) * uint64_t(inv1));
+  h += int64_t(inverse_radical_inverse(uint64_t(pmy), 3, kHaltonExp3) * uint64_t(kHaltonScale2) * uint64_t(inv0));
+  h %= kHaltonStride;
+  h += int64_t(s.index) * int64_t(kHaltonStride);
+  return uint64_t(h);
+}
+__host__ __device__ __forceinline__ float halton_dim(const HaltonTables& t, uint64_t a, int dim) {  // lowdiscrepancy.h:26-40
+  const int base = t.primes[dim];
+  const uint16_t* perm = t.perms + t.sums[dim];
+  const float inv_base = 1.0f / float(base);
+  float inv_base_n = 1.0f;
+  uint64_t reversed = 0;
+  while (a) {
+    const uint64_t next = a / uint64_t(base);
+    const uint64_t digit = a - next * uint64_t(base);
+    reversed = reversed * uint64_t(base) + perm[digit];
+    inv_base_n *= inv_base;
+    a = next;
+  }
+  const float series = float(int(perm[0])) / (float(base) + 1.0f);
+  return pmin((float(reversed) + series) * inv_base_n, kOneMinusEpsilon);
+}
+template <class S>
+__host__ __device__ __forceinline__ float halton_get1d(const HaltonTables& t, S& s, int inv0, int inv1) {
+  if (s.dim < 2 || s.dim >= kHaltonPrimes) s.dim = 2;  // start_pixel / start_next_sample set 2 (sampler.h:49-52)
+  return halton_dim(t, halton_index_of(PixelSampler{s.px, s.py, s.index, 0}, inv0, inv1), s.dim++);
+}
+template <class S>
+__host__ __device__ __forceinline__ V2 halton_get2d(const HaltonTables& t, S& s, int inv0, int inv1) {
+  if (s.dim < 2 || s.dim + 1 >= kHaltonPrimes) s.dim = 2;
+  const uint64_t a = halton_index_of(PixelSampler{s.px, s.py, s.index, 0}, inv0, inv1);
+  const int d = s.dim;
+  s.dim += 2;
+  return V2(halton_dim(t, a, d), halton_dim(t, a, d + 1));
+}
+
 template <bool G>
 __device__ __forceinline__ float smp_get1d(const DScene& sc, PixelSamplerT<G>& s) {
   if constexpr (G) {
     if (sc.sampler_kind == PB2_SAMPLER_SOBOL) return sobol_get1d(s, sc.log2_spp, sc.nbase4_digits);
     if (sc.sampler_kind == PB2_SAMPLER_UNIFORM) return uniform_dim(s, sc.sampler_seed, s.dim++);
+    if (sc.sampler_kind == PB2_SAMPLER_HALTON)
+      return halton_get1d(HaltonTables{sc.halton_primes, sc.halton_sums, sc.halton_perms}, s, sc.halton_inv0, sc.halton_inv1);
   }
   if (s.dim >= 256) s.dim = 2;
   return blue_dim(sc, s, s.dim++);
@@ -201,6 +263,8 @@ __device__ __forceinline__ V2 smp_get2d(const DScene& sc, PixelSamplerT<G>& s) {
       s.dim += 2;
       return V2(uniform_dim(s, sc.sampler_seed, d), uniform_dim(s, sc.sampler_seed, d + 1));
     }
+    if (sc.sampler_kind == PB2_SAMPLER_HALTON)
+      return halton_get2d(HaltonTables{sc.halton_primes, sc.halton_sums, sc.halton_perms}, s, sc.halton_inv0, sc.halton_inv1);
   }
   if (s.dim + 1 >= 256) s.dim = 2;
   int d = s.dim;

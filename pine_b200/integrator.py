@@ -75,6 +75,21 @@ class SobolSampler:
         return self.samples_per_pixel
 
 
+class HaltonSampler:
+    """pine::HaltonSampler (sampler.h:40-81): scrambled radical inverses over the first 1000 primes, the
+    pixel's index from the Chinese remainder theorem on (x mod 128, y mod 128). Draws bit-identical."""
+    kind = A.SAMPLER_HALTON
+
+    def __init__(self, samples_per_pixel):
+        if samples_per_pixel <= 0:
+            raise ValueError("`HaltonSampler` should have positive samples per pixel")  # sampler.cpp:45-46
+        self.samples_per_pixel = int(samples_per_pixel)
+        self.seed = 0
+
+    def spp(self):
+        return self.samples_per_pixel
+
+
 class UniformSampler:
     """pine::UniformSampler (sampler.h:13-39): independent uniform draws. The reference shares one RNG
     per worker thread; here each (pixel, sample, dimension) has its own draw (include/pine_b200.h)."""

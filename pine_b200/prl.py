@@ -202,6 +202,10 @@ class _UniformSampler(_Sampler):
     name = "UniformSampler"
 
 
+class _HaltonSampler(_Sampler):
+    name = "HaltonSampler"
+
+
 def _f32(v):
     return np.float32(v)
 
@@ -387,7 +391,7 @@ def _globals(make_scene):
         "DirectionalLight": lambda d, c: _Light("directional", d, c),
         "SpotLight": lambda *a: _Light("spot", *a), "Sky": lambda c: _Light("sky", c),
         "ThinLenCamera": _Camera, "BlueSampler": _Sampler, "SobolSampler": _SobolSampler,
-        "UniformSampler": _UniformSampler, "PathIntegrator": _Integrator,
+        "UniformSampler": _UniformSampler, "HaltonSampler": _HaltonSampler, "PathIntegrator": _Integrator,
         "X": [1, 0, 0], "Y": [0, 1, 0], "Z": [0, 0, 1],
     }
 
@@ -485,6 +489,7 @@ def run_file(path, device=0):
     def on_render(sp, spp, depth):
         kind = sp.config.get("sampler", "BlueSampler")
         sampler = (I.SobolSampler(spp) if kind == "SobolSampler" else
+                   I.HaltonSampler(spp) if kind == "HaltonSampler" else
                    I.UniformSampler(spp, sp.config.get("sampler_seed", 0)) if kind == "UniformSampler" else
                    I.BlueSampler(spp))
         integ = I.PathIntegrator(sampler, depth, device=device)

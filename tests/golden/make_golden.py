@@ -70,6 +70,20 @@ def sobol_kats():
     np.savez_compressed(os.path.join(OUT, "sobol_kats.npz"), **out)
 
 
+def halton_kats():
+    """HaltonSampler(spp) (sampler.h:40-81): 6 samples of the pattern 21221 at four pixels, a 1043-draw sample
+    (the dimension counter wraps at PrimeTablesize = 1000), and its film of the small README scene."""
+    out = {"pixels": np.array(SOBOL_PIXELS, np.int32), "spps": np.array([1, 4, 100, 4096], np.int32)}
+    for spp in (1, 4, 100, 4096):
+        for i, (px, py) in enumerate(SOBOL_PIXELS):
+            out[f"draws_{spp}_{i}"] = ref.sampler_stream_kind("halton", spp, (640, 640), px, py, 0, "21221", min(6, spp))
+    out["wrap"] = ref.sampler_stream_kind("halton", 4, (64, 64), 5, 7, 0, "2" * 520 + "1" * 3, 2)
+    R = ref.RefScene()
+    common.build(R, "c1_64")
+    out["film_c1_64_spp16"], _ = R.render(16, 4, sampler="halton")
+    np.savez_compressed(os.path.join(OUT, "halton_kats.npz"), **out)
+
+
 def gltf_kats():
     """scene_from_gltf (fileio.cpp:146-327) on tests/golden/room_like.glb (written by tests/gltf_fixture.py):
     camera rays, closest hits of the camera rays and of a spherical ray fan from inside the room, the film
@@ -193,6 +207,7 @@ if __name__ == "__main__":
         raise SystemExit("oracle/_ref/libpine_ref.so missing: make -C oracle ref")
     kats()
     sobol_kats()
+    halton_kats()
     gltf_kats()
     gltf_textured_kats()
     lights_kats()

@@ -74,6 +74,21 @@ def test_sobol_non_power_of_two_spp(golden):
     B.close()
 
 
+def test_halton_device_draws_and_film(golden):
+    k = golden("halton_kats")
+    B, _ = _backend("c1_64")
+    for spp in k["spps"]:
+        spp = int(spp)
+        for i, (px, py) in enumerate(k["pixels"]):
+            d = B.test_sampler_kind(pb.HaltonSampler(spp), int(px), int(py), 0, "21221", min(6, spp))
+            assert np.array_equal(u32(d), u32(k[f"draws_{spp}_{i}"])), (spp, i)
+    d = B.test_sampler_kind(pb.HaltonSampler(4), 5, 7, 0, "2" * 520 + "1" * 3, 2)
+    assert np.array_equal(u32(d), u32(k["wrap"]))
+    film = B.render(pb.HaltonSampler(16), 4)
+    assert relmse(film, k["film_c1_64_spp16"]) <= FILM_RELMSE_TOL
+    B.close()
+
+
 def test_uniform_sampler_converges_to_the_same_image(golden):
     g = golden("c1_64")
     B, _ = _backend("c1_64")
@@ -94,14 +109,14 @@ def test_sampler_argument_errors():
         B.render(pb.SobolSampler(1 << 20), 4)
     assert e.value.code == A.PB2_E_UNSUPPORTED
 
-    class Halton:
-        kind, seed = 3, 0
+    class Unknown:
+        kind, seed = 7, 0
 
         def spp(self):
             return 4
     with pytest.raises(pb.PineB200Error) as e:
-        B.render(Halton(), 4)
-    assert e.value.code == A.PB2_E_UNSUPPORTED and "Halton" in str(e.value)
+        B.render(Unknown(), 4)
+    assert e.value.code == A.PB2_E_UNSUPPORTED and "sampler kind" in str(e.value)
     with pytest.raises(ValueError):
         pb.UniformSampler(0)
     B.close()

@@ -85,6 +85,22 @@ def test_sobol_sampler_host_draws_match_live_reference():
             assert np.array_equal(u32(got), u32(want)), (spp, size, px, py)
 
 
+def test_halton_sampler_host_draws_match_reference_vectors(golden):
+    # HaltonSampler (sampler.h:40-81, sampler.cpp:20-81, lowdiscrepancy.h:26-60): primes, digit permutations
+    # (rebuilt with the reference's generator), CRT pixel offset and the dimension wrap at 1000
+    from pine_b200.integrator import host_sampler_draws
+    k = golden("halton_kats")
+    for spp in k["spps"]:
+        spp = int(spp)
+        for i, (px, py) in enumerate(k["pixels"]):
+            d = host_sampler_draws(pb.HaltonSampler(spp), (640, 640), int(px), int(py), 0, "21221", min(6, spp))
+            assert np.array_equal(u32(d), u32(k[f"draws_{spp}_{i}"])), (spp, i)
+    d = host_sampler_draws(pb.HaltonSampler(4), (64, 64), 5, 7, 0, "2" * 520 + "1" * 3, 2)
+    assert np.array_equal(u32(d), u32(k["wrap"]))
+    with pytest.raises(ValueError):
+        pb.HaltonSampler(0)
+
+
 def test_uniform_sampler_host_draws_are_uniform_and_keyed():
     # UniformSampler (sampler.h:13-39) is statistical parity only: check the counter-based stream's
     # moments, its range (nextf < 1, rng.h:140-143) and that pixel / sample / dimension / seed all key it
