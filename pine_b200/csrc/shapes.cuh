@@ -139,6 +139,22 @@ __device__ __forceinline__ bool disk_hit(const pb2_disk& s, const Ray& ray) {
 }
 
 // ---- Triangle (Moller-Trumbore with three divisions) -----------------------------------------------
+// The reference divides three times (t, u, v = ... / D) and rejects on t, u, v, u + v in that order; the outcome
+// is a pure AND of the four conditions, so they may be evaluated in any order. Most candidates fail the u / v
+// range, which can be decided WITHOUT dividing whenever the numerator is clearly outside [0, D]:
+//   * a / D rounds to a negative float iff a and D differ in sign and the quotient does not underflow to -0
+//     (|a| > |D| * 1e-30 guarantees that);
+//   * a / D rounds to more than 1 if |a| > |D| (1 + 2^-22) (the quotient then exceeds 1 + ulp);
+//   * for u, v in [0, 1], fl(u + v) differs from (a + b) / D by less than 2e-7, so (a + b) > |D| (1 + 2e-6)
+//     means u + v > 1.
+// These are certain rejections; everything else takes the reference's own divisions below, so accepted hits
+// and their t are the reference's bit for bit (the parity tests compare every ray of whole renders).
+__device__ __forceinline__ bool tri_clearly_missed(float D, float a, float b) {
+  const float s = D < 0.0f ? -1.0f : 1.0f;
+  const float Dp = fabsf(D), ap = a * s, bp = b * s;  // exact sign flips
+  const float lo = -(Dp * 1e-30f), hi = Dp * 1.000001f;
+  return ap < lo || bp < lo || ap > hi || bp > hi || ap + bp > Dp * 1.000002f;
+}
 __device__ __forceinline__ bool tri_intersect(Ray& ray, V3 v0, V3 v1, V3 v2) {
   V3 E1 = v1 - v0, E2 = v2 - v0;
   V3 T = ray.o - v0;
@@ -146,11 +162,13 @@ __device__ __forceinline__ bool tri_intersect(Ray& ray, V3 v0, V3 v1, V3 v2) {
   V3 Q = cross(T, E1);
   float D = dot(P, E1);
   if (D == 0.0f) return false;
+  const float a = dot(P, T), b = dot(Q, ray.d);
+  if (tri_clearly_missed(D, a, b)) return false;
   float t = dot(Q, E2) / D;
   if (t <= ray.tmin || t >= ray.tmax) return false;
-  float u = dot(P, T) / D;
+  float u = a / D;
   if (u < 0.0f || u > 1.0f) return false;
-  float v = dot(Q, ray.d) / D;
+  float v = b / D;
   if (v < 0.0f || v > 1.0f) return false;
   if (u + v > 1.0f) return false;
   ray.tmax = t;
@@ -163,11 +181,13 @@ __device__ __forceinline__ bool tri_hit(const Ray& ray, V3 v0, V3 v1, V3 v2) {
   V3 Q = cross(T, E1);
   float D = dot(P, E1);
   if (D == 0.0f) return false;
+  const float a = dot(P, T), b = dot(Q, ray.d);
+  if (tri_clearly_missed(D, a, b)) return false;
   float t = dot(Q, E2) / D;
   if (t < ray.tmin || t > ray.tmax) return false;
-  float u = dot(P, T) / D;
+  float u = a / D;
   if (u < 0.0f || u > 1.0f) return false;
-  float v = dot(Q, ray.d) / D;
+  float v = b / D;
   if (v < 0.0f || v > 1.0f) return false;
   return u + v < 1.0f;
 }
