@@ -419,8 +419,15 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
   int* next_count = w.counts + depth + 1;
   int* shadow_count = w.counts + w.max_depth + 1 + depth;
   const int* list = w.lists + size_t(w.list_of_class[MAT]) * w.n_slots;
-  PB2_WARP_LOOP(j, n) {
+  // Output positions: warps add their counts to shared counters, the block takes ONE range per queue from
+  // the global counters (k_classify's reasoning: one global atomic per warp and queue ran into the L2's
+  // same-address atomic rate). The loop is block-uniform so the barriers are safe.
+  __shared__ int s_count[2], s_base[2];
+  for (int tile = blockIdx.x * blockDim.x; tile < n; tile += gridDim.x * blockDim.x) {
+    const int j = tile + int(threadIdx.x);
     const bool valid = j < n;
+    if (threadIdx.x < 2) s_count[threadIdx.x] = 0;
+    __syncthreads();
     bool emit_next = false, emit_shadow = false;
     Ray next_ray, shadow_ray;
     int slot = 0;
@@ -549,16 +556,23 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
       w.dim[slot] = smp.dim;
       w.term[slot] = make_float4(0, 0, 0, __int_as_float(depth + 1));
     }
-    int pos = warp_compact(emit_next, next_count);
+    const int pos = warp_compact(emit_next, &s_count[0]);      // position inside the block's range
+    const int spos = warp_compact(emit_shadow, &s_count[1]);
+    __syncthreads();
+    if (threadIdx.x == 0 && s_count[0]) s_base[0] = atomicAdd(next_count, s_count[0]);
+    if (threadIdx.x == 32 && s_count[1]) s_base[1] = atomicAdd(shadow_count, s_count[1]);
+    __syncthreads();
     if (emit_next) {
-      w.ray_o[nxt][pos] = make_float4(next_ray.o.x, next_ray.o.y, next_ray.o.z, next_ray.tmax);
-      w.ray_d[nxt][pos] = make_float4(next_ray.d.x, next_ray.d.y, next_ray.d.z, __int_as_float(slot));
+      const int at = s_base[0] + pos;
+      w.ray_o[nxt][at] = make_float4(next_ray.o.x, next_ray.o.y, next_ray.o.z, next_ray.tmax);
+      w.ray_d[nxt][at] = make_float4(next_ray.d.x, next_ray.d.y, next_ray.d.z, __int_as_float(slot));
     }
-    int spos = warp_compact(emit_shadow, shadow_count);
     if (emit_shadow) {
-      w.sh_o[spos] = make_float4(shadow_ray.o.x, shadow_ray.o.y, shadow_ray.o.z, shadow_ray.tmax);
-      w.sh_d[spos] = make_float4(shadow_ray.d.x, shadow_ray.d.y, shadow_ray.d.z, __int_as_float(slot));
+      const int at = s_base[1] + spos;
+      w.sh_o[at] = make_float4(shadow_ray.o.x, shadow_ray.o.y, shadow_ray.o.z, shadow_ray.tmax);
+      w.sh_d[at] = make_float4(shadow_ray.d.x, shadow_ray.d.y, shadow_ray.d.z, __int_as_float(slot));
     }
+    __syncthreads();  // s_base / s_count are reused by the next tile
   }
 }
 
