@@ -16,7 +16,22 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_ref", "libpine_ref.so")
 
+SHIM_PATH = os.path.join(_HERE, "_ref", "libpine_shim.so")
 _lib = None
+_shim = None
+
+
+def shim():
+    """oracle/_ref/libpine_shim.so: pine::CudaPathIntegrator (integration/) + its C entry points. The only
+    library on the oracle side that links the product; loaded by the drop-in tests alone."""
+    global _shim
+    if _shim is None:
+        lib()  # libpine_ref.so first: the shim resolves Pine's classes from it
+        S = C.CDLL(SHIM_PATH)
+        S.ref_render_cuda_kind.restype = C.c_double
+        S.ref_render_cuda_kind.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        _shim = S
+    return _shim
 
 
 def available():
@@ -40,11 +55,8 @@ def lib():
         L.ref_render.restype = C.c_double
         L.ref_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.ref_accel_build.restype = C.c_double
-        if hasattr(L, "ref_render_cuda"):
-            L.ref_render_cuda.restype = C.c_double
-            L.ref_render_cuda.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
-            L.ref_render_cuda_kind.restype = C.c_double
-            L.ref_render_cuda_kind.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.ref_render_moments.restype = C.c_double
+        L.ref_render_moments.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_bounded_prepare.restype = C.c_double
         L.ref_bounded_prepare.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.ref_bounded_render_rows.restype = C.c_double
@@ -189,9 +201,20 @@ class RefScene:
         film = np.zeros((h, w, 4), np.float32)
         stats = np.zeros(4, np.float64)
         kind = {"blue": 0, "sobol": 1, "uniform": 2, "halton": 3}[sampler]
-        secs = lib().ref_render_cuda_kind(self.h, kind, spp, depth, device, film.ctypes.data, stats.ctypes.data)
+        secs = shim().ref_render_cuda_kind(self.h, kind, spp, depth, device, film.ctypes.data, stats.ctypes.data)
         return film, secs, {"closest_rays": int(stats[0]), "shadow_rays": int(stats[1]),
                             "kernel_launches": int(stats[2]), "render_ms": float(stats[3])}
+
+    def render_moments(self, spp, depth):
+        """BlueSampler render that also returns the per-pixel mean and the standard error of that mean, from
+        the reference's own per-sample radiances -> (film, mean [h, w, 3] f64, sigma_of_mean [h, w, 3] f64)."""
+        w, h = self.size
+        film = np.zeros((h, w, 4), np.float32)
+        s1, s2 = np.zeros((h, w, 3), np.float64), np.zeros((h, w, 3), np.float64)
+        self.L.ref_render_moments(self.h, spp, depth, film.ctypes.data, s1.ctypes.data, s2.ctypes.data)
+        mean = s1 / spp
+        var = np.maximum(s2 / spp - mean ** 2, 0.0) * (spp / max(spp - 1, 1))
+        return film, mean, np.sqrt(var / spp)
 
     def bounded_prepare(self, spp, depth):
         """RTIntegrator::render prologue (sampler clones, BVH::build, light list) of a

@@ -32,8 +32,6 @@
 #include <pine/impl/accel/bvh.cpp>
 #include <pine/impl/integrator/path.cpp>
 
-#include "../integration/cuda_path_integrator.h"
-
 #include <chrono>
 #include <cstdint>
 #include <cstring>
@@ -75,7 +73,28 @@ struct BoundedPath : PathIntegrator {
       film[p] = vec4(L / spp, 1.0f);
     });
   }
+  // The same loop over the whole film, also returning per pixel and channel the sum and the sum of squares
+  // of the spp per-sample radiances (what the 3-sigma test of SURVEY 8(c) T4 takes its sigma from).
+  void render_moments(Scene& scene, double* sum, double* sumsq) {
+    auto& film = scene.camera.film();
+    const int w = film.size().x;
+    parallel_for(film.size(), [&](vec2i p) {
+      Sampler& sampler = samplers[threadIdx].start_pixel(p, 0);
+      auto L = vec3(0.0f);
+      double* s1 = sum + 3 * (size_t(p.x) + size_t(p.y) * w);
+      double* s2 = sumsq + 3 * (size_t(p.x) + size_t(p.y) * w);
+      for (int k = 0; k < 3; k++) s1[k] = s2[k] = 0;
+      for (int si = 0; si < spp; si++, sampler.start_next_sample()) {
+        auto ray = scene.camera.gen_ray((p + sampler.rand2f()) / film.size(), sampler.rand2f());
+        auto Lo = radiance(scene, ray, sampler, Vertex::first_vertex()).Lo;
+        L += Lo;
+        for (int k = 0; k < 3; k++) { s1[k] += double(Lo[k]); s2[k] += double(Lo[k]) * double(Lo[k]); }
+      }
+      film[p] = vec4(L / spp, 1.0f);
+    });
+  }
 };
+}  // namespace
 struct RefScene {
   Scene scene;
   std::vector<psl::shared_ptr<Material>> materials;
@@ -84,6 +103,7 @@ struct RefScene {
   BoundedPath* bounded = nullptr;
   ~RefScene() { delete bounded; }
 };
+namespace {
 vec3 v3(const float* p) { return vec3(p[0], p[1], p[2]); }
 mat4 m4_rowmajor(const float* m) {
   return mat4(m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], m[8], m[9], m[10], m[11], m[12],
@@ -99,6 +119,8 @@ extern "C" {
 
 void* ref_scene_new() { return new RefScene(); }
 void ref_scene_free(void* h) { delete (RefScene*)h; }
+// the live pine::Scene of a handle, for oracle/shim_harness.cpp (the drop-in test lives in its own library)
+void* ref_scene_ptr(void* h) { return &((RefScene*)h)->scene; }
 
 // kind: 0 Emissive(color) 1 Diffuse(albedo) 2 Metal(albedo, rough) 3 Glossy(albedo, rough, ior)
 //       4 Glass(albedo, rough, ior) 5 Uber(albedo, rough, metallic, transmission, ior)
@@ -217,36 +239,6 @@ double ref_render(void* h, int sampler_kind, int spp, int depth, float* film_rgb
   }
   return std::chrono::duration<double>(t1 - t0).count();
 }
-// The drop-in: the SAME pine::Scene rendered by pine::CudaPathIntegrator (integration/), constructed
-// with PathIntegrator's own argument list. Returns wall seconds; stats = {closest rays, shadow rays,
-// kernel launches, device ms}. Aborts through SEVERE like the reference on unsupported content.
-double ref_render_cuda_kind(void* h, int sampler_kind, int spp, int depth, int device, float* film_rgba,
-                            double* stats) {
-  auto& S = *(RefScene*)h;
-  auto sampler = sampler_kind == 0   ? Sampler(BlueSobolSampler(spp))
-                 : sampler_kind == 1 ? Sampler(SobolSampler(spp))
-                                     : sampler_kind == 3 ? Sampler(HaltonSampler(spp)) : Sampler(UniformSampler(spp));
-  auto integrator = CudaPathIntegrator(Accel(BVH()), sampler, LightSampler(UniformLightSampler()), depth);
-  integrator.set_device(device);
-  auto t0 = std::chrono::steady_clock::now();
-  Integrator& base = integrator;  // through the virtual interface, as the PRL binding calls it
-  base.render(S.scene);
-  auto t1 = std::chrono::steady_clock::now();
-  if (film_rgba) {
-    auto& film = S.scene.camera.film();
-    std::memcpy(film_rgba, film.data(), sizeof(float) * 4 * size_t(film.width()) * film.height());
-  }
-  if (stats) {
-    stats[0] = double(integrator.last_closest_rays());
-    stats[1] = double(integrator.last_shadow_rays());
-    stats[2] = double(integrator.kernel_launches());
-    stats[3] = integrator.last_render_ms();
-  }
-  return std::chrono::duration<double>(t1 - t0).count();
-}
-double ref_render_cuda(void* h, int spp, int depth, int device, float* film_rgba, double* stats) {
-  return ref_render_cuda_kind(h, 0, spp, depth, device, film_rgba, stats);
-}
 // Bounded-sample variant for timing (see BoundedPath): prepare once (returns the seconds the
 // prologue took, dominated by BVH::build), then render row subsets. BlueSobolSampler only.
 double ref_bounded_prepare(void* h, int spp, int depth) {
@@ -263,6 +255,21 @@ double ref_bounded_render_rows(void* h, int row_begin, int row_end, int row_step
   if (!S.bounded) return -1.0;
   auto t0 = std::chrono::steady_clock::now();
   S.bounded->render_rows(S.scene, row_begin, row_end, row_step);
+  auto t1 = std::chrono::steady_clock::now();
+  if (film_rgba) {
+    auto& film = S.scene.camera.film();
+    std::memcpy(film_rgba, film.data(), sizeof(float) * 4 * size_t(film.width()) * film.height());
+  }
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+// Whole-film render that also reports the per-pixel moments of the per-sample radiance (sum, sumsq:
+// w*h*3 doubles each). BlueSobolSampler; film_rgba as ref_render.
+double ref_render_moments(void* h, int spp, int depth, float* film_rgba, double* sum, double* sumsq) {
+  auto& S = *(RefScene*)h;
+  BoundedPath path(Accel(BVH()), Sampler(BlueSobolSampler(spp)), LightSampler(UniformLightSampler()), depth);
+  auto t0 = std::chrono::steady_clock::now();
+  path.prepare(S.scene);
+  path.render_moments(S.scene, sum, sumsq);
   auto t1 = std::chrono::steady_clock::now();
   if (film_rgba) {
     auto& film = S.scene.camera.film();

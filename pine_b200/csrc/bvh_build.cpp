@@ -8,6 +8,11 @@
 // whatever the thread count.
 #include "bvh_build.h"
 
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#define PB2_BUILD_SSE 1
+#endif
+
 #include <atomic>
 #include <future>
 #include <thread>
@@ -38,49 +43,144 @@ struct Builder {
 
   // Decides the split of [first,last) (bvh.cpp:50-131). Returns nullptr for "make a leaf",
   // else the partition point, with the two child boxes filled in.
+  // The reference makes one pass over the primitives per axis and recomputes the bucket of every
+  // primitive in the partition pass; here ONE pass fills the buckets of all three axes and remembers
+  // each primitive's bucket (same float expressions per primitive and axis, and min/max and integer
+  // counts do not depend on the order they are accumulated in, so every number is the reference's).
+  std::vector<uint8_t> bucket_scratch;  // [3][count] of the range being split
   BuildPrim* choose_split(BuildPrim* first, BuildPrim* last, const Box3& bounds, Box3 (&child_box)[2]) {
     const int count = int(last - first);
     if (count == 1) return nullptr;
 
+#ifdef PB2_BUILD_SSE
+    // Same float operations as the scalar statement below, three axes per instruction (IEEE add / sub / mul /
+    // div are lane-wise identical; MINPS / MAXPS are `a < b ? a : b` / `a > b ? a : b`, i.e. pmin / pmax).
+    // A box is read as two unaligned 4-float loads: lower.xyz + upper.x and upper.xyz + index; lane 3 is junk
+    // and never leaves the registers.
+    const __m128 half = _mm_set1_ps(0.5f);
+    __m128 clo = _mm_set1_ps(kFloatMax), chi = _mm_set1_ps(-kFloatMax);
+    for (int i = 0; i < count; i++) {
+      const __m128 c = _mm_mul_ps(_mm_add_ps(_mm_loadu_ps(&first[i].box.lower.x), _mm_loadu_ps(&first[i].box.upper.x)), half);
+      clo = _mm_min_ps(clo, c);
+      chi = _mm_max_ps(chi, c);
+    }
+    Box3 cbounds;
+    {
+      float t[4];
+      _mm_storeu_ps(t, clo); cbounds.lower = V3(t[0], t[1], t[2]);
+      _mm_storeu_ps(t, chi); cbounds.upper = V3(t[0], t[1], t[2]);
+    }
+    const float parent_area = bounds.surface_area();
+    const bool live[3] = {!cbounds.degenerated(0), !cbounds.degenerated(1), !cbounds.degenerated(2)};
+    int n_in[3][kBuckets] = {};
+    unsigned occupied[3] = {0, 0, 0};  // bit b: bucket b of the axis is non-empty
+    __m128 in_lo[3][kBuckets], in_hi[3][kBuckets];  // valid where n_in != 0 (min / max with the empty box's
+                                                     // +-FLT_MAX returns the other operand, so "first touch
+                                                     // assigns" equals "extend from empty")
+    if (bucket_scratch.size() < size_t(count) * 3) bucket_scratch.resize(size_t(count) * 3);
+    uint8_t* bk = bucket_scratch.data();
+    // relative_position: dd > 0 ? o / dd : o -- dd > 0 on every live axis; dead axes get dd = 1 and are ignored
+    const __m128 dd_raw = _mm_sub_ps(chi, clo);
+    const __m128 dd = _mm_or_ps(_mm_and_ps(_mm_cmpgt_ps(dd_raw, _mm_setzero_ps()), dd_raw),
+                                _mm_andnot_ps(_mm_cmpgt_ps(dd_raw, _mm_setzero_ps()), _mm_set1_ps(1.0f)));
+    const __m128 nb = _mm_set1_ps(float(kBuckets));
+    for (int i = 0; i < count; i++) {
+      const __m128 lo = _mm_loadu_ps(&first[i].box.lower.x), hi = _mm_loadu_ps(&first[i].box.upper.x);
+      const __m128 c = _mm_mul_ps(_mm_add_ps(lo, hi), half);
+      const __m128i raw4 = _mm_cvttps_epi32(_mm_mul_ps(nb, _mm_div_ps(_mm_sub_ps(c, clo), dd)));
+      alignas(16) int raw[4];
+      _mm_store_si128(reinterpret_cast<__m128i*>(raw), raw4);
+      for (int axis = 0; axis < 3; axis++) {
+        if (!live[axis]) continue;
+        bk[size_t(axis) * count + i] = uint8_t(raw[axis]);  // 0..16
+        const int b = pmin(raw[axis], kBuckets - 1);
+        if (n_in[axis][b]++ == 0) {
+          occupied[axis] |= 1u << b;
+          in_lo[axis][b] = lo;
+          in_hi[axis][b] = hi;
+        } else {
+          in_lo[axis][b] = _mm_min_ps(in_lo[axis][b], lo);
+          in_hi[axis][b] = _mm_max_ps(in_hi[axis][b], hi);
+        }
+      }
+    }
+    struct RawBox { float lower[3], upper[3]; };
+    RawBox box_raw[3][kBuckets];  // uninitialised on purpose: only non-empty buckets are read below
+    Box3(&box_in)[3][kBuckets] = reinterpret_cast<Box3(&)[3][kBuckets]>(box_raw);
+    for (int a = 0; a < 3; a++)
+      for (unsigned m = occupied[a]; m; m &= m - 1) {
+        const int b = __builtin_ctz(m);
+        float t[4];
+        _mm_storeu_ps(t, in_lo[a][b]); box_in[a][b].lower = V3(t[0], t[1], t[2]);
+        _mm_storeu_ps(t, in_hi[a][b]); box_in[a][b].upper = V3(t[0], t[1], t[2]);
+      }
+#else
     Box3 cbounds;
     for (int i = 0; i < count; i++) cbounds.extend(first[i].box.centroid());
     const float parent_area = bounds.surface_area();
 
+    const bool live[3] = {!cbounds.degenerated(0), !cbounds.degenerated(1), !cbounds.degenerated(2)};
+    int n_in[3][kBuckets] = {};
+    unsigned occupied[3] = {0, 0, 0};
+    Box3 box_in[3][kBuckets];
+    if (bucket_scratch.size() < size_t(count) * 3) bucket_scratch.resize(size_t(count) * 3);
+    uint8_t* bk = bucket_scratch.data();
+    for (int i = 0; i < count; i++) {
+      const Box3& pb = first[i].box;
+      for (int axis = 0; axis < 3; axis++) {
+        if (!live[axis]) continue;
+        const int raw = int(kBuckets * cbounds.relative_position(pb.centroid(axis), axis));
+        bk[size_t(axis) * count + i] = uint8_t(raw);  // 0..16
+        const int b = pmin(raw, kBuckets - 1);
+        n_in[axis][b]++;
+        occupied[axis] |= 1u << b;
+        box_in[axis][b].extend(pb);
+      }
+    }
+
+#endif
+
     float best_cost = kFloatMax;
     int best_axis = -1, best_bucket = -1;
     for (int axis = 0; axis < 3; axis++) {
-      if (cbounds.degenerated(axis)) continue;
-      int n_in[kBuckets] = {};
-      Box3 box_in[kBuckets];
-      for (int i = 0; i < count; i++) {
-        int b = pmin(bucket_of(cbounds, first[i], axis), kBuckets - 1);
-        n_in[b]++;
-        box_in[b].extend(first[i].box);
+      if (!live[axis]) continue;
+      // cost[i] of the split after bucket i = 1 + (nL SA(L) + nR SA(R)) / SA(parent) (bvh.cpp:84-107). The
+      // reference evaluates all 15; an empty side gives 0 * inf = NaN there, which never compares below the
+      // running minimum, and between two consecutive non-empty buckets a < b both sides -- hence the cost --
+      // are the same for every i in [a, b), of which the strict `<` keeps the first. So only i = a non-empty
+      // bucket with another non-empty bucket after it can win: evaluate those, with the reference's operations.
+      float right[kBuckets];  // right[i]: n * area of buckets >= i, valid where bucket i is non-empty
+      {
+        Box3 sweep;
+        int n = 0;
+        for (unsigned m = occupied[axis] & ~1u; m;) {  // descending over the non-empty buckets >= 1
+          const int i = 31 - __builtin_clz(m);
+          m &= ~(1u << i);
+          sweep.extend(box_in[axis][i]);
+          n += n_in[axis][i];
+          right[i] = n * sweep.surface_area();
+        }
       }
-      float cost[kBuckets - 1] = {};
-      Box3 sweep;
-      int n = 0;
-      for (int i = 0; i < kBuckets - 1; i++) {  // left side of a split after bucket i
-        sweep.extend(box_in[i]);
-        n += n_in[i];
-        cost[i] += n * sweep.surface_area();
-      }
-      sweep = Box3();
-      n = 0;
-      for (int i = kBuckets - 1; i >= 1; i--) {  // right side
-        sweep.extend(box_in[i]);
-        n += n_in[i];
-        cost[i - 1] += n * sweep.surface_area();
-      }
-      for (int i = 0; i < kBuckets - 1; i++) cost[i] = 1.0f + cost[i] / parent_area;
-
       float axis_cost = kFloatMax;
       int axis_bucket = -1;
-      for (int i = 0; i < kBuckets - 1; i++)
-        if (cost[i] < axis_cost) {
-          axis_cost = cost[i];
-          axis_bucket = i;
+      {
+        Box3 sweep;
+        int n = 0;
+        for (unsigned m = occupied[axis]; m & (m - 1); m &= m - 1) {  // ascending, all but the last non-empty bucket
+          const int i = __builtin_ctz(m);
+          const int nxt = __builtin_ctz(m & (m - 1));
+          sweep.extend(box_in[axis][i]);
+          n += n_in[axis][i];
+          float c = 0.0f;
+          c += n * sweep.surface_area();
+          c += right[nxt];
+          c = 1.0f + c / parent_area;
+          if (c < axis_cost) {
+            axis_cost = c;
+            axis_bucket = i;
+          }
         }
+      }
       if (axis_cost < best_cost) {
         best_cost = axis_cost;
         best_axis = axis;
@@ -90,19 +190,36 @@ struct Builder {
 
     if (best_cost > float(count)) return nullptr;
 
-    // psl::partition (src/psl/algorithm.h:394-402): forward scan, swap matches to the front
-    BuildPrim* mid = first;
-    for (BuildPrim* it = first; it != last; ++it) {
-      int b = bucket_of(cbounds, *it, best_axis);
+    // psl::partition (src/psl/algorithm.h:394-402): forward scan, swap matches to the front. The
+    // remembered buckets travel with their primitives (only positions < it change before it is read).
+    uint8_t* bb = bk + size_t(best_axis) * count;
+    int mid_i = 0;
+    for (int i = 0; i < count; i++) {
+      int b = bb[i];
       if (b == kBuckets) b = kBuckets - 1;
       if (b <= best_bucket) {
-        std::swap(*mid, *it);
-        ++mid;
+        std::swap(first[mid_i], first[i]);
+        std::swap(bb[mid_i], bb[i]);
+        ++mid_i;
       }
     }
+    BuildPrim* mid = first + mid_i;
 
+#ifdef PB2_BUILD_SSE
+    for (int c = 0; c < 2; c++) {
+      __m128 lo = _mm_set1_ps(kFloatMax), hi = _mm_set1_ps(-kFloatMax);
+      for (BuildPrim* p = c ? mid : first; p != (c ? last : mid); ++p) {
+        lo = _mm_min_ps(lo, _mm_loadu_ps(&p->box.lower.x));
+        hi = _mm_max_ps(hi, _mm_loadu_ps(&p->box.upper.x));
+      }
+      float t[4];
+      _mm_storeu_ps(t, lo); child_box[c].lower = V3(t[0], t[1], t[2]);
+      _mm_storeu_ps(t, hi); child_box[c].upper = V3(t[0], t[1], t[2]);
+    }
+#else
     for (BuildPrim* p = first; p != mid; ++p) child_box[0].extend(p->box);
     for (BuildPrim* p = mid; p != last; ++p) child_box[1].extend(p->box);
+#endif
     return mid;
   }
 

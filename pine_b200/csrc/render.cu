@@ -45,7 +45,8 @@ struct WaveView {
   float4* lacc;           // running L
   int* counts;            // [0..D] live rays per depth, [D+1..2D+1] shadow rays per depth, then per
                           // depth {closest cursor, closest fallbacks, shadow cursor, shadow fallbacks}
-  int* fb_list;           // fallback list shared by the traversal kernels (used one at a time)
+  int* fb_list;           // fallback list of the closest-hit kernels
+  int* sfb_list;          // fallback list of the shadow kernels (they may run beside the next depth's closest hits)
   uint8_t* occ;           // NULL unless a ray record is being taken
   int* lists;             // shade lists: [list][n_slots] queue indices, one list per shading class
   int list_of_class[8];   // class (0 = terminal, k = pb2_material_kind k) -> list number, -1 = absent
@@ -58,11 +59,36 @@ struct WaveView {
   int accel;
 };
 
+// Wavefront state. A render is cut into waves; up to kMaxLanes waves over DISJOINT pixel ranges are in
+// flight at once, each on its own stream with its own queue set ("lane"), so that the drain tail of one
+// lane's persistent traversal launch, its few-ray reference-order re-trace and its memory-streaming shade
+// kernels are filled by the other lane's work instead of leaving SMs idle (pb2_render_device).
+constexpr int kMaxLanes = 4;
+constexpr int kDefaultLanes = 2;  // measured on B200: C5 +9%, C3 +7%, C1 +5% over one lane; see DESIGN.md for 3 and 4
+constexpr long kMinLaneSlots = 1L << 19;  // a lane must still fill the GPU: below this, one lane
+struct LaneBuffers {
+  DBuf ray_o[2], ray_d[2], hit, sh_o[2], sh_d[2], pv_pdf, pv_flags, dim, term, vtx, fb_list, sfb_list, occ, lists;
+  cudaStream_t stream = nullptr;  // lanes >= 1 only; lane 0 runs on the caller's stream
+  cudaStream_t side = nullptr;    // shadow rays of depth d, beside the closest-hit rays of depth d + 1
+  cudaEvent_t done = nullptr, shaded = nullptr, shadowed[2] = {nullptr, nullptr};
+};
 struct WavefrontBuffers {
-  DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, rng, lacc, counts, fb_list, occ, lists;
+  LaneBuffers lane[kMaxLanes];
+  DBuf rng, lacc, counts;           // per pixel of the row range / per wave: shared by the lanes
+  cudaEvent_t fork = nullptr;
   std::vector<int> host_counts;
   std::vector<cudaEvent_t> events;  // PB2_RENDER_TIME_KERNELS: one event between consecutive launches
-  ~WavefrontBuffers() { for (cudaEvent_t e : events) cudaEventDestroy(e); }
+  ~WavefrontBuffers() {
+    for (cudaEvent_t e : events) cudaEventDestroy(e);
+    for (LaneBuffers& l : lane) {
+      if (l.stream) cudaStreamDestroy(l.stream);
+      if (l.side) cudaStreamDestroy(l.side);
+      if (l.done) cudaEventDestroy(l.done);
+      if (l.shaded) cudaEventDestroy(l.shaded);
+      for (cudaEvent_t e : l.shadowed) if (e) cudaEventDestroy(e);
+    }
+    if (fork) cudaEventDestroy(fork);
+  }
 };
 
 void free_wavefront(pb2_context* ctx) {
@@ -167,7 +193,7 @@ struct ShadowIO {
 };
 __device__ __forceinline__ WideQueue wave_queue(const WaveView& w, int depth, int which) {
   int* c = w.counts + 2 * (w.max_depth + 1) + 4 * depth + 2 * which;
-  return WideQueue{c, c + 1, w.fb_list};
+  return WideQueue{c, c + 1, which ? w.sfb_list : w.fb_list};
 }
 __device__ __forceinline__ TraceIO trace_io(const WaveView& w, int depth) {
   return TraceIO{w.ray_o[depth & 1], w.ray_d[depth & 1], w.hit};
@@ -773,68 +799,100 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   if (P == 0 || n_samples == 0) { PB2_CUDA_CHECK(cudaStreamSynchronize(st)); return PB2_OK; }
 
   // ---- wave plan ----
-  const long max_slots = long(env_int("PB2_MAX_SLOTS", 1 << 24));
-  long pixels_per_wave = std::min(P, std::max(long(W), (max_slots / W) * W));
+  // A wave = rows_per_wave film rows x s_batch samples <= max_slots (pixel, sample) slots. Waves over the
+  // same rows run one after the other (they share the pixels' RNG streams and accumulators); waves over
+  // different rows are independent, and n_lanes of them are in flight at once (see WavefrontBuffers).
+  pb2_ray_record* rec = ctx->record;
+  const bool timed = (p->flags & PB2_RENDER_TIME_KERNELS) != 0;
+  const long max_slots = std::max(long(W), long(env_int("PB2_MAX_SLOTS", 1 << 24)));
+  int n_lanes = rec ? 1 : std::min(kMaxLanes, std::max(1, env_int("PB2_LANES", kDefaultLanes)));
+  if (P * n_samples < long(n_lanes) * env_int("PB2_MIN_LANE_SLOTS", int(kMinLaneSlots)) || rows < n_lanes) n_lanes = 1;
+  int n_pixel_waves = int((rows + max_slots / W - 1) / (max_slots / W));
+  n_pixel_waves = ((n_pixel_waves + n_lanes - 1) / n_lanes) * n_lanes;
+  const int rows_per_wave = (rows + n_pixel_waves - 1) / n_pixel_waves;
+  n_pixel_waves = (rows + rows_per_wave - 1) / rows_per_wave;
+  const long pixels_per_wave = long(rows_per_wave) * W;
   int s_batch = int(std::max(1L, std::min(long(n_samples), max_slots / pixels_per_wave)));
   if (ctx->needs_rng_in_shading) s_batch = 1;  // randf() draws in shading share the per-pixel RNG stream
   const long n_slots = pixels_per_wave * s_batch;
   const int n_vtx = std::max(D - 1, 1);
-
-  if (!ctx->wf) ctx->wf = new WavefrontBuffers();
-  WavefrontBuffers& B = *ctx->wf;
-  for (int k = 0; k < 2; k++) {
-    PB2_CUDA_CHECK(B.ray_o[k].reserve(n_slots * 16));
-    PB2_CUDA_CHECK(B.ray_d[k].reserve(n_slots * 16));
-  }
-  PB2_CUDA_CHECK(B.hit.reserve(n_slots * 16));
-  PB2_CUDA_CHECK(B.sh_o.reserve(n_slots * 16));
-  PB2_CUDA_CHECK(B.sh_d.reserve(n_slots * 16));
-  PB2_CUDA_CHECK(B.pv_pdf.reserve(n_slots * 4));
-  PB2_CUDA_CHECK(B.pv_flags.reserve(n_slots * 4));
-  PB2_CUDA_CHECK(B.dim.reserve(n_slots * 4));
-  PB2_CUDA_CHECK(B.term.reserve(n_slots * 16));
-  PB2_CUDA_CHECK(B.vtx.reserve(size_t(n_slots) * n_vtx * 32));
-  PB2_CUDA_CHECK(B.rng.reserve(size_t(P) * 16));
-  PB2_CUDA_CHECK(B.lacc.reserve(size_t(P) * 16));
-  PB2_CUDA_CHECK(cudaMemsetAsync(B.lacc.ptr, 0, size_t(P) * 16, st));
-
-  const int n_pixel_waves = int((P + pixels_per_wave - 1) / pixels_per_wave);
   const int n_sample_waves = (n_samples + s_batch - 1) / s_batch;
   const int n_waves = n_pixel_waves * n_sample_waves;
   const int cstride = 14 * (D + 1);  // + 8 shade-list counters per depth
-  PB2_CUDA_CHECK(B.fb_list.reserve(size_t(n_slots) * 4));
+  if (rec && n_waves != 1) { set_error("ray record: the render must fit one wave"); return PB2_E_INVALID; }
+
+  if (!ctx->wf) ctx->wf = new WavefrontBuffers();
+  WavefrontBuffers& B = *ctx->wf;
+  // shade lists: class 0 always, plus one per material kind some geometry uses
+  int n_lists = 0, list_of_class[8];
+  for (int c = 0; c < 8; c++) list_of_class[c] = -1;
+  list_of_class[0] = n_lists++;
+  for (int k = 1; k < 8; k++)
+    if (ctx->material_kinds & (1u << k)) list_of_class[k] = n_lists++;
+  PB2_CUDA_CHECK(B.rng.reserve(size_t(P) * 16));
+  PB2_CUDA_CHECK(B.lacc.reserve(size_t(P) * 16));
+  PB2_CUDA_CHECK(cudaMemsetAsync(B.lacc.ptr, 0, size_t(P) * 16, st));
   PB2_CUDA_CHECK(B.counts.reserve(size_t(n_waves) * cstride * 4));
   PB2_CUDA_CHECK(cudaMemsetAsync(B.counts.ptr, 0, size_t(n_waves) * cstride * 4, st));
-  pb2_ray_record* rec = ctx->record;
-  if (rec) {
-    if (n_waves != 1) { set_error("ray record: the render must fit one wave"); return PB2_E_INVALID; }
-    PB2_CUDA_CHECK(B.occ.reserve(size_t(n_slots)));
-  }
+  if (!B.fork) PB2_CUDA_CHECK(cudaEventCreateWithFlags(&B.fork, cudaEventDisableTiming));
 
-  WaveView w{};
-  // shade lists: class 0 always, plus one per material kind some geometry uses
-  int n_lists = 0;
-  for (int c = 0; c < 8; c++) w.list_of_class[c] = -1;
-  w.list_of_class[0] = n_lists++;
-  for (int k = 1; k < 8; k++)
-    if (ctx->material_kinds & (1u << k)) w.list_of_class[k] = n_lists++;
-  PB2_CUDA_CHECK(B.lists.reserve(size_t(n_lists) * n_slots * 4));
-  w.lists = B.lists.as<int>();
-  w.occ = rec ? B.occ.as<uint8_t>() : nullptr;
-  for (int k = 0; k < 2; k++) { w.ray_o[k] = B.ray_o[k].as<float4>(); w.ray_d[k] = B.ray_d[k].as<float4>(); }
-  w.hit = B.hit.as<float4>(); w.sh_o = B.sh_o.as<float4>(); w.sh_d = B.sh_d.as<float4>();
-  w.pv_pdf = B.pv_pdf.as<float>(); w.pv_flags = B.pv_flags.as<int>(); w.dim = B.dim.as<int>();
-  w.term = B.term.as<float4>(); w.vtx = B.vtx.as<float4>();
-  w.rng = B.rng.as<uint2>(); w.lacc = B.lacc.as<float4>(); w.fb_list = B.fb_list.as<int>();
   const bool ref_order = p->accel != 0 || !sc.wide_ready;
   const bool closest_wide_ok = !ref_order && !sc.order_dependent;
   const bool any_wide_ok = !ref_order && sc.n_box_shapes <= kMaxBoxShapes;
   const int pgrid = persistent_grid();
-  w.n_slots = int(n_slots); w.width = W; w.row_begin = p->row_begin; w.max_depth = D; w.accel = p->accel;
+  // PB2_SHADOW_ASYNC: the shadow rays of depth d run on a side stream of the lane, beside the closest-hit
+  // rays of depth d + 1 (both are written by the shade kernels of depth d and independent of each other);
+  // the shadow queue is double buffered, and the shade kernels of depth d + 2 wait for shadow(d).
+  const bool shadow_async = !rec && !timed && env_int("PB2_SHADOW_ASYNC", 0) != 0;
+
+  WaveView lane_view[kMaxLanes];
+  cudaStream_t lane_stream[kMaxLanes];
+  for (int l = 0; l < n_lanes; l++) {
+    LaneBuffers& L = B.lane[l];
+    for (int k = 0; k < 2; k++) {
+      PB2_CUDA_CHECK(L.ray_o[k].reserve(n_slots * 16));
+      PB2_CUDA_CHECK(L.ray_d[k].reserve(n_slots * 16));
+    }
+    PB2_CUDA_CHECK(L.hit.reserve(n_slots * 16));
+    for (int k = 0; k < (shadow_async ? 2 : 1); k++) {
+      PB2_CUDA_CHECK(L.sh_o[k].reserve(n_slots * 16));
+      PB2_CUDA_CHECK(L.sh_d[k].reserve(n_slots * 16));
+    }
+    PB2_CUDA_CHECK(L.pv_pdf.reserve(n_slots * 4));
+    PB2_CUDA_CHECK(L.pv_flags.reserve(n_slots * 4));
+    PB2_CUDA_CHECK(L.dim.reserve(n_slots * 4));
+    PB2_CUDA_CHECK(L.term.reserve(n_slots * 16));
+    PB2_CUDA_CHECK(L.vtx.reserve(size_t(n_slots) * n_vtx * 32));
+    PB2_CUDA_CHECK(L.fb_list.reserve(size_t(n_slots) * 4));
+    PB2_CUDA_CHECK(L.sfb_list.reserve(size_t(n_slots) * 4));
+    if (shadow_async) {
+      if (!L.side) PB2_CUDA_CHECK(cudaStreamCreateWithFlags(&L.side, cudaStreamNonBlocking));
+      if (!L.shaded) PB2_CUDA_CHECK(cudaEventCreateWithFlags(&L.shaded, cudaEventDisableTiming));
+      for (cudaEvent_t& e : L.shadowed) if (!e) PB2_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    PB2_CUDA_CHECK(L.lists.reserve(size_t(n_lists) * n_slots * 4));
+    if (rec) PB2_CUDA_CHECK(L.occ.reserve(size_t(n_slots)));
+    if (l > 0 && !L.stream) PB2_CUDA_CHECK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+    if (!L.done) PB2_CUDA_CHECK(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+    // the per-kernel timing pass keeps the wave plan but runs the lanes one after the other on the caller's
+    // stream, so that the event pairs around a launch measure that launch alone
+    lane_stream[l] = (l == 0 || timed) ? st : L.stream;
+    WaveView& w = lane_view[l];
+    w = WaveView{};
+    for (int c = 0; c < 8; c++) w.list_of_class[c] = list_of_class[c];
+    w.lists = L.lists.as<int>();
+    w.occ = rec ? L.occ.as<uint8_t>() : nullptr;
+    for (int k = 0; k < 2; k++) { w.ray_o[k] = L.ray_o[k].as<float4>(); w.ray_d[k] = L.ray_d[k].as<float4>(); }
+    w.hit = L.hit.as<float4>(); w.sh_o = L.sh_o[0].as<float4>(); w.sh_d = L.sh_d[0].as<float4>();
+    w.pv_pdf = L.pv_pdf.as<float>(); w.pv_flags = L.pv_flags.as<int>(); w.dim = L.dim.as<int>();
+    w.term = L.term.as<float4>(); w.vtx = L.vtx.as<float4>();
+    w.rng = B.rng.as<uint2>(); w.lacc = B.lacc.as<float4>(); w.fb_list = L.fb_list.as<int>();
+    w.sfb_list = L.sfb_list.as<int>();
+    w.n_slots = int(n_slots); w.width = W; w.row_begin = p->row_begin; w.max_depth = D; w.accel = p->accel;
+  }
 
   uint64_t launches = 0;
   // optional per-kernel timing: an event after every launch, classified on the host afterwards
-  const bool timed = (p->flags & PB2_RENDER_TIME_KERNELS) != 0;
   std::vector<int> ev_class;  // 0 trace, 1 shadow, 2 shade, 3 other
   size_t ev_used = 0;
   auto mark = [&](int cls) {
@@ -846,7 +904,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   // ray record (test hook): synchronous copies of the queues after the traversal kernels ran
   std::vector<float4> rec_a, rec_b, rec_c;
   std::vector<uint8_t> rec_occ;
-  auto record = [&](bool shadow, int depth) -> int {
+  auto record = [&](const WaveView& w, bool shadow, int depth) -> int {
     int n = 0;
     const int* cnt = w.counts + (shadow ? D + 1 + depth : depth);
     if (cudaStreamSynchronize(st) != cudaSuccess ||
@@ -907,70 +965,106 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       }
     }
     if (bytes || ctx->l2_window_set) {
-      cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &attr);
+      for (int l = 0; l < n_lanes; l++)
+        cudaStreamSetAttribute(lane_stream[l], cudaStreamAttributeAccessPolicyWindow, &attr);
       ctx->l2_window_set = bytes != 0;
       cudaGetLastError();  // best effort: a device without the feature just ignores it
     }
   }
   PB2_CUDA_CHECK(cudaEventRecord(ctx->ev0, st));
   mark(-1);
-  int wave = 0;
-  for (int pw = 0; pw < n_pixel_waves; pw++) {
+  // One wave on one lane: raygen, then per depth trace / classify / shade / shadow, then the unwind.
+  auto enqueue_wave = [&](int l, int pw, int sw) -> int {
+    WaveView& w = lane_view[l];
+    cudaStream_t ls = lane_stream[l];
     w.pixel0 = int(long(pw) * pixels_per_wave);
     w.pixels = int(std::min(pixels_per_wave, P - w.pixel0));
-    for (int sw = 0; sw < n_sample_waves; sw++, wave++) {
-      w.sample0 = p->sample_begin + sw * s_batch;
-      w.s_batch = std::min(s_batch, p->sample_end - w.sample0);
-      w.counts = B.counts.as<int>() + size_t(wave) * cstride;
-      const int live = w.pixels * w.s_batch;
-      k_raygen<<<sm_grid(w.pixels, 256, 8), 256, 0, st>>>(sc, w, p->sample_begin, sw == 0);
-      launches++; mark(3);
-      for (int depth = 0; depth < D; depth++) {
-        if (closest_wide_ok) {
-          k_trace<<<pgrid, kTraceBlock, 0, st>>>(sc, w, depth);
-          k_trace_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, w, depth);
-          launches += 2;
-        } else {
-          k_trace_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, st>>>(sc, w, depth);
-          launches++;
-        }
-        mark(0);
-        if (rec && (rc = record(false, depth))) return rc;
-        k_classify<<<sm_grid(live, 256, 8), 256, 0, st>>>(sc, w, depth);
-        k_shade_terminal<<<sm_grid(live, 256, 8), 256, 0, st>>>(sc, w, depth);
+    w.sample0 = p->sample_begin + sw * s_batch;
+    w.s_batch = std::min(s_batch, p->sample_end - w.sample0);
+    w.counts = B.counts.as<int>() + size_t(pw * n_sample_waves + sw) * cstride;
+    const int live = w.pixels * w.s_batch;
+    k_raygen<<<sm_grid(w.pixels, 256, 8), 256, 0, ls>>>(sc, w, p->sample_begin, sw == 0);
+    launches++; mark(3);
+    for (int depth = 0; depth < D; depth++) {
+      if (closest_wide_ok) {
+        k_trace<<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+        k_trace_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
         launches += 2;
-        if (depth + 1 < D) {
-          const int sg = sm_grid(live, 128, 16);
-          const unsigned mk = ctx->material_kinds;
-          const bool blue = sc.sampler_kind == PB2_SAMPLER_BLUE && ctx->only_area_lights;
+      } else {
+        k_trace_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ls>>>(sc, w, depth);
+        launches++;
+      }
+      mark(0);
+      if (rec) { int rc2 = record(w, false, depth); if (rc2) return rc2; }
+      k_classify<<<sm_grid(live, 256, 8), 256, 0, ls>>>(sc, w, depth);
+      k_shade_terminal<<<sm_grid(live, 256, 8), 256, 0, ls>>>(sc, w, depth);
+      launches += 2;
+      if (depth + 1 < D) {
+        if (shadow_async) {
+          LaneBuffers& L = B.lane[l];
+          if (depth >= 2) PB2_CUDA_CHECK(cudaStreamWaitEvent(ls, L.shadowed[depth & 1], 0));
+          w.sh_o = L.sh_o[depth & 1].as<float4>();
+          w.sh_d = L.sh_d[depth & 1].as<float4>();
+        }
+        const int sg = sm_grid(live, 128, 16);
+        const unsigned mk = ctx->material_kinds;
+        const bool blue = sc.sampler_kind == PB2_SAMPLER_BLUE && ctx->only_area_lights;
 #define PB2_SHADE(MAT)                                                      \
   if (mk & (1u << MAT)) {                                                   \
-    if (blue) k_shade_mat<MAT, false><<<sg, 128, 0, st>>>(sc, w, depth);    \
-    else k_shade_mat<MAT, true><<<sg, 128, 0, st>>>(sc, w, depth);          \
+    if (blue) k_shade_mat<MAT, false><<<sg, 128, 0, ls>>>(sc, w, depth);    \
+    else k_shade_mat<MAT, true><<<sg, 128, 0, ls>>>(sc, w, depth);          \
     launches++;                                                             \
   }
-          PB2_SHADE(PB2_MAT_DIFFUSE) PB2_SHADE(PB2_MAT_METAL) PB2_SHADE(PB2_MAT_GLOSSY)
-          PB2_SHADE(PB2_MAT_GLASS) PB2_SHADE(PB2_MAT_UBER) PB2_SHADE(PB2_MAT_SUBSURFACE)
+        PB2_SHADE(PB2_MAT_DIFFUSE) PB2_SHADE(PB2_MAT_METAL) PB2_SHADE(PB2_MAT_GLOSSY)
+        PB2_SHADE(PB2_MAT_GLASS) PB2_SHADE(PB2_MAT_UBER) PB2_SHADE(PB2_MAT_SUBSURFACE)
 #undef PB2_SHADE
-        }
-        mark(2);
-        if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
-          if (any_wide_ok) {
-            k_shadow<<<pgrid, kTraceBlock, 0, st>>>(sc, w, depth);
-            k_shadow_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, w, depth);
-            launches += 2;
-          } else {
-            k_shadow_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, st>>>(sc, w, depth);
-            launches++;
-          }
-          mark(1);
-          if (rec && (rc = record(true, depth))) return rc;
-        }
       }
-      k_fold_resolve<<<sm_grid(w.pixels, 256, 8), 256, 0, st>>>(w);
-      launches++; mark(3);
+      mark(2);
+      if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
+        cudaStream_t ss = ls;
+        if (shadow_async) {
+          ss = B.lane[l].side;
+          PB2_CUDA_CHECK(cudaEventRecord(B.lane[l].shaded, ls));
+          PB2_CUDA_CHECK(cudaStreamWaitEvent(ss, B.lane[l].shaded, 0));
+        }
+        if (any_wide_ok) {
+          k_shadow<<<pgrid, kTraceBlock, 0, ss>>>(sc, w, depth);
+          k_shadow_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ss>>>(sc, w, depth);
+          launches += 2;
+        } else {
+          k_shadow_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ss>>>(sc, w, depth);
+          launches++;
+        }
+        if (shadow_async) PB2_CUDA_CHECK(cudaEventRecord(B.lane[l].shadowed[depth & 1], ss));
+        mark(1);
+        if (rec) { int rc2 = record(w, true, depth); if (rc2) return rc2; }
+      }
     }
-  }
+    if (shadow_async)
+      for (int k = 0; k < 2 && k < D - 1; k++) PB2_CUDA_CHECK(cudaStreamWaitEvent(ls, B.lane[l].shadowed[k], 0));
+    k_fold_resolve<<<sm_grid(w.pixels, 256, 8), 256, 0, ls>>>(w);
+    launches++; mark(3);
+    return PB2_OK;
+  };
+  // fork: the lanes' own streams start after the clears above
+  bool forked = false;
+  for (int l = 1; l < n_lanes; l++)
+    if (lane_stream[l] != st) {
+      if (!forked) { PB2_CUDA_CHECK(cudaEventRecord(B.fork, st)); forked = true; }
+      PB2_CUDA_CHECK(cudaStreamWaitEvent(lane_stream[l], B.fork, 0));
+    }
+  // pixel wave pw belongs to lane pw % n_lanes; launches are interleaved wave by wave so that every
+  // lane's stream stays fed whatever the driver's launch-queue depth
+  for (int pw0 = 0; pw0 < n_pixel_waves; pw0 += n_lanes)
+    for (int sw = 0; sw < n_sample_waves; sw++)
+      for (int l = 0; l < n_lanes && pw0 + l < n_pixel_waves; l++)
+        if ((rc = enqueue_wave(l, pw0 + l, sw))) return rc;
+  // join
+  for (int l = 1; l < n_lanes; l++)
+    if (lane_stream[l] != st) {
+      PB2_CUDA_CHECK(cudaEventRecord(B.lane[l].done, lane_stream[l]));
+      PB2_CUDA_CHECK(cudaStreamWaitEvent(st, B.lane[l].done, 0));
+    }
   const float alpha = float(n_samples) / float(p->spp);
   k_film<<<sm_grid(int(P), 256, 8), 256, 0, st>>>(B.lacc.as<float4>(), ctx->film.as<float4>(), int(P),
                                                   p->row_begin * W, p->spp, alpha);

@@ -147,6 +147,84 @@ def mesh_field(B, n_instances=64, subdiv=3, seed=42, size=(640, 360), spp=16, de
     return {"spp": spp, "depth": depth}
 
 
+def tessellated_box(n):
+    """Unit cube [0,1]^3 with every face cut into n x n quads (2 triangles each): 12 n^2 triangles,
+    vertices shared inside a face only -> (verts f32 [6 (n+1)^2, 3], faces u32 [12 n^2, 3])."""
+    g = np.linspace(0.0, 1.0, n + 1, dtype=np.float32)
+    u, v = np.meshgrid(g, g, indexing="ij")
+    u, v = u.reshape(-1), v.reshape(-1)
+    zero, one = np.zeros_like(u), np.ones_like(u)
+    faces = [(zero, u, v, True), (one, u, v, False), (u, zero, v, False), (u, one, v, True),
+             (u, v, zero, True), (u, v, one, False)]
+    verts, tris = [], []
+    i, j = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    a = (i * (n + 1) + j).reshape(-1)
+    b, c, d = a + (n + 1), a + (n + 2), a + 1
+    for k, (x, y, z, flip) in enumerate(faces):
+        verts.append(np.stack([x, y, z], axis=1))
+        base = k * (n + 1) ** 2
+        q = np.concatenate([np.stack([a, b, c], 1), np.stack([a, c, d], 1)]) + base
+        tris.append(q[:, ::-1] if flip else q)
+    return np.concatenate(verts).astype(np.float32), np.concatenate(tris).astype(np.uint32)
+
+
+def room_proc(B, size=(1920, 1080), spp=64, depth=6, n_spheres=60, n_boxes=64, sphere_subdiv=5, box_tess=32,
+              seed=1234):
+    """C4 "room-proc" (stands in for the missing scenes/room.glb): a CLOSED 8 x 3 x 6 m box room
+    (six Rects), furniture = `n_spheres` icospheres (subdivision 5, 20 480 triangles each) and `n_boxes`
+    tessellated boxes (12 * 32^2 = 12 288 triangles each) ~ 2.0 M triangles on a jittered floor grid, some
+    raised on "table" slabs, Diffuse / Metal / Glossy mix, ONE 1 x 1 m Rect emitter under the ceiling; camera
+    inside the room. Every path stays inside, so a sample traces close to the 2 D - 1 = 11 rays the depth
+    allows: the indirect-heavy, memory-bound interior regime. Deterministic in `seed` (numpy RandomState; the
+    same arrays feed the reference and the CUDA path)."""
+    rng = np.random.RandomState(seed)
+    W, H, D = 8.0, 3.0, 6.0
+    wall = B.add_material("diffuse", (0.82, 0.8, 0.76))
+    floor = B.add_material("glossy", (0.45, 0.32, 0.2), roughness=0.25)
+    accent = B.add_material("diffuse", (0.7, 0.25, 0.2))
+    mats = [B.add_material("diffuse", (0.75, 0.75, 0.7)), B.add_material("diffuse", (0.25, 0.45, 0.7)),
+            B.add_material("metal", (0.9, 0.85, 0.7), roughness=0.2), B.add_material("glossy", (0.3, 0.6, 0.4), roughness=0.1),
+            B.add_material("metal", (0.95, 0.95, 0.95), roughness=0.05), B.add_material("glossy", (0.8, 0.75, 0.3), roughness=0.3)]
+    B.add_rect((W / 2, 0, D / 2), (W, 0, 0), (0, 0, D), floor)
+    B.add_rect((W / 2, H, D / 2), (W, 0, 0), (0, 0, D), wall)
+    B.add_rect((0, H / 2, D / 2), (0, 0, D), (0, H, 0), accent)
+    B.add_rect((W, H / 2, D / 2), (0, 0, D), (0, H, 0), wall)
+    B.add_rect((W / 2, H / 2, 0), (W, 0, 0), (0, H, 0), wall)
+    B.add_rect((W / 2, H / 2, D), (W, 0, 0), (0, H, 0), wall)
+    sv, sf = icosphere(sphere_subdiv)
+    bv, bf = tessellated_box(box_tess)
+    n_obj = n_spheres + n_boxes
+    gx = int(np.ceil(np.sqrt(n_obj * W / D)))
+    gz = int(np.ceil(n_obj / gx))
+    cells = [(ix, iz) for iz in range(gz) for ix in range(gx)]
+    order = rng.permutation(len(cells))[:n_obj]
+    kinds = np.array([0] * n_spheres + [1] * n_boxes)
+    rng.shuffle(kinds)
+    cw, cd = (W - 0.6) / gx, (D - 1.4) / gz
+    for k, ci in enumerate(order):
+        ix, iz = cells[ci]
+        cx = np.float32(0.3 + (ix + 0.5 + (rng.rand() - 0.5) * 0.4) * cw)
+        cz = np.float32(1.1 + (iz + 0.5 + (rng.rand() - 0.5) * 0.4) * cd)
+        lift = np.float32(0.0 if rng.rand() < 0.6 else 0.5 + 1.6 * rng.rand())  # some objects float / sit high
+        mat = mats[int(rng.randint(len(mats)))]
+        if kinds[k] == 0:
+            r = np.float32(0.12 + 0.12 * rng.rand())
+            c = np.array([cx, lift + r, cz], np.float32)
+            B.add_mesh((sv * r + c).astype(np.float32), sf, mat)
+        else:
+            sx, sy, sz = (np.float32(0.18 + 0.22 * rng.rand()), np.float32(0.08 + 0.5 * rng.rand()),
+                          np.float32(0.18 + 0.22 * rng.rand()))
+            ang = np.float32(rng.rand() * np.pi)
+            ca, sa = np.float32(np.cos(ang)), np.float32(np.sin(ang))
+            p = (bv - np.array([0.5, 0.0, 0.5], np.float32)) * np.array([sx, sy, sz], np.float32)
+            q = np.stack([ca * p[:, 0] + sa * p[:, 2], p[:, 1], -sa * p[:, 0] + ca * p[:, 2]], axis=1)
+            B.add_mesh((q + np.array([cx, lift, cz], np.float32)).astype(np.float32), bf, mat)
+    light = B.add_material("emissive", (90.0, 82.0, 70.0))
+    B.add_rect((W / 2, H - 0.01, D / 2 + 0.5), (1.0, 0, 0), (0, 0, 1.0), light)
+    B.set_camera(size, (W / 2, 1.6, 0.25), (W / 2, 1.0, D * 0.7), 0.55)
+    return {"spp": spp, "depth": depth}
+
+
 def cbox_readme_noboxes(B, size=(640, 640)):
     """The README scene without its two Box geometries: cones + rects only, i.e. a scene whose
     closest hits go through the wide tree although a Cone is unbounded below its base."""
@@ -224,4 +302,4 @@ def lights_yard(B, size=(96, 64), sky=True, delta=True, area=True):
 
 
 SCENES = {"materials_room": materials_room, "lights_yard": lights_yard, "cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
-          "mesh_field": mesh_field}
+          "mesh_field": mesh_field, "room_proc": room_proc}
