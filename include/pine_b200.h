@@ -193,6 +193,11 @@ typedef struct pb2_render_params {
    * (lowdiscrepancy.cpp:5-17) rebuilt on the host with the same generator; draws bit-identical. */
   int32_t sampler;
   int32_t sampler_seed;
+  /* Interleaved row bands (fine-grained tile sharding in ONE call): with row_parts > 1 the call renders, of
+   * the bands of row_band rows that [row_begin, row_end) is cut into, those whose index k has
+   * k % row_parts == row_part; all other rows are left alone (zero, or kept with PB2_RENDER_KEEP_FILM).
+   * row_parts <= 1 (a zero-initialised struct): every row of the range. */
+  int32_t row_band, row_parts, row_part;
 } pb2_render_params;
 #define PB2_SAMPLER_BLUE 0
 #define PB2_SAMPLER_SOBOL 1
@@ -309,6 +314,40 @@ int pb2_bvh_info(pb2_context* ctx, int which, int32_t* n_nodes, int32_t* root,
                  int32_t* n_leaf_prims);
 int pb2_bvh_nodes(pb2_context* ctx, int which, float* aabbs, int32_t* children,
                   int32_t* leaf_range, int32_t* leaf_prims);
+
+/* ---- every GPU of the box behind ONE integrator (BASELINE.json north_star; the reference interface stays
+ * `Integrator::render(Scene&)`, integrator.h:20-25, registered at program_context.cpp:76-81) -----------------
+ * A pb2_multi owns one pb2_context per device. One host thread calls in; the BVH is built once on the host,
+ * the scene is replicated (each GPU pulls 1/N of every large array through PCIe, the rest arrives by in-place
+ * ncclAllGather over NVLink), the (pixel, sample) work is sharded, and ONE ncclReduce(sum) of the float film
+ * brings the result to the first device. NCCL is loaded at run time (libnccl.so.2) and only when N > 1.
+ *   PB2_SHARD_SAMPLES: GPU i renders a contiguous share of [sample_begin, sample_end) of every pixel; per-pixel
+ *     RNG streams are re-seeded hash(p, first sample of the share) (sampler.h:286-289 takes a sample_index), so
+ *     the film equals the single-GPU film statistically, not bit for bit.
+ *   PB2_SHARD_ROWS: bands of PB2_SHARD_ROW_BAND film rows dealt round-robin; every pixel has one writer and
+ *     the other GPUs add zeros: BIT-IDENTICAL to the single-GPU film. */
+typedef struct pb2_multi pb2_multi;
+#define PB2_SHARD_SAMPLES 0
+#define PB2_SHARD_ROWS 1
+#define PB2_SHARD_ROW_BAND 16
+/* devices NULL or n_devices <= 0: every visible CUDA device. */
+int pb2_create_multi(const int* devices, int n_devices, pb2_multi** out);
+void pb2_destroy_multi(pb2_multi* m);
+int pb2_multi_size(pb2_multi* m);
+/* The i-th device's context (owned by m), for the single-device entry points above (test hooks, counters). */
+pb2_context* pb2_multi_context(pb2_multi* m, int i);
+int pb2_multi_upload_sampler_tables(pb2_multi* m, int spp_pow2, const uint8_t* sobol, const uint8_t* scramble,
+                                    const uint8_t* rank);
+int pb2_multi_load_sampler_tables_file(pb2_multi* m, const char* path, int spp_pow2);
+/* pb2_upload_scene for all devices: one host build, sharded staging + all-gather. */
+int pb2_multi_upload_scene(pb2_multi* m, const pb2_scene_desc* scene);
+/* Repeats only the staging (host -> devices), synchronously: the end-to-end timing leg. */
+int pb2_multi_restage_scene(pb2_multi* m);
+/* pb2_render over all devices; film_rgba_host as in pb2_render. Blocking. */
+int pb2_multi_render(pb2_multi* m, const pb2_render_params* params, int shard_mode, float* film_rgba_host);
+/* Counters summed over the devices (last_render_ms: the slowest device's); optional host wall times of the
+ * last film reduce and the last staging, in ms. */
+int pb2_multi_get_counters(pb2_multi* m, pb2_counters* out, double* reduce_ms, double* stage_ms);
 
 #ifdef __cplusplus
 }

@@ -21,7 +21,6 @@
 // The Heitz et al. tables the reference links in (src/contrib/bluesobol/bluenoise_<N>spp.cpp:2-12)
 // are file-static there; a maintainer exposes them with three accessor lines per file. Until then
 // the shim reads the same bytes from the blob oracle/extract_tables.cpp wrote from those sources.
-extern "C" int pb2_load_sampler_tables_file(pb2_context* ctx, const char* path, int spp_pow2);
 
 namespace pine {
 
@@ -258,27 +257,31 @@ CudaPathIntegrator::CudaPathIntegrator(Accel, Sampler sampler, LightSampler, int
 CudaPathIntegrator::CudaPathIntegrator(Sampler sampler, int max_path_length)
     : CudaPathIntegrator(Accel(), MOVE(sampler), LightSampler(UniformLightSampler()), max_path_length) {}
 CudaPathIntegrator::CudaPathIntegrator(CudaPathIntegrator&& o) noexcept
-    : sampler_(MOVE(o.sampler_)), max_path_length_(o.max_path_length_), device_(o.device_), ctx_(o.ctx_) {
-  o.ctx_ = nullptr;
+    : sampler_(MOVE(o.sampler_)), max_path_length_(o.max_path_length_), devices_(MOVE(o.devices_)),
+      shard_mode_(o.shard_mode_), n_devices_(o.n_devices_), multi_(o.multi_) {
+  o.multi_ = nullptr;
 }
 CudaPathIntegrator::~CudaPathIntegrator() {
-  if (ctx_) pb2_destroy(ctx_);
+  if (multi_) pb2_destroy_multi(multi_);
 }
 
 void CudaPathIntegrator::render(Scene& scene) {
   // RTIntegrator::render prologue (integrator.cpp:26-35): spp from the sampler, accel build, light list
   const int spp = sampler_.spp();
-  if (!ctx_) check(pb2_create(device_, &ctx_), "pb2_create");
+  if (!multi_) {
+    check(pb2_create_multi(devices_.size() ? &devices_[0] : nullptr, int(devices_.size()), &multi_), "pb2_create_multi");
+    n_devices_ = pb2_multi_size(multi_);
+  }
   Flat flat;
   flatten(scene, flat);
-  check(pb2_upload_scene(ctx_, &flat.desc), "pb2_upload_scene");
+  check(pb2_multi_upload_scene(multi_, &flat.desc), "pb2_multi_upload_scene");
   const int kind = sampler_.is<SobolSampler>()     ? PB2_SAMPLER_SOBOL
                    : sampler_.is<UniformSampler>() ? PB2_SAMPLER_UNIFORM
                    : sampler_.is<HaltonSampler>()  ? PB2_SAMPLER_HALTON
                                                    : PB2_SAMPLER_BLUE;
   if (kind == PB2_SAMPLER_BLUE) {
     const char* tables = std::getenv("PINE_B200_TABLES");
-    check(pb2_load_sampler_tables_file(ctx_, tables ? tables : "", spp), "pb2_load_sampler_tables_file");
+    check(pb2_multi_load_sampler_tables_file(multi_, tables ? tables : "", spp), "pb2_multi_load_sampler_tables_file");
   }
   set_progress(0);
   pb2_render_params p{};
@@ -289,10 +292,10 @@ void CudaPathIntegrator::render(Scene& scene) {
   p.sampler = kind;  // UniformSampler keeps its seed private (sampler.h:36-38): the CUDA stream uses seed 0
   auto& film = scene.camera.film();
   // Film::pixels is Array2d<vec4>, row-major p.x + p.y*w (array.h:51-55): the ABI's film layout
-  check(pb2_render(ctx_, &p, &film.data()[0][0]), "pb2_render");
+  check(pb2_multi_render(multi_, &p, shard_mode_, &film.data()[0][0]), "pb2_multi_render");
   set_progress(1);
   pb2_counters c{};
-  pb2_get_counters(ctx_, &c);
+  pb2_multi_get_counters(multi_, &c, nullptr, nullptr);
   last_closest_ = c.last_closest_rays;
   last_shadow_ = c.last_shadow_rays;
   launches_ = c.kernel_launches;

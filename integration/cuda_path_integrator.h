@@ -15,7 +15,7 @@
 #pragma once
 #include <pine/core/integrator.h>
 
-struct pb2_context;
+struct pb2_multi;
 
 namespace pine {
 
@@ -34,8 +34,17 @@ class CudaPathIntegrator : public Integrator {
 
   void render(Scene& scene) override;
 
-  // Which CUDA device to use (default 0) -- not part of the reference interface.
-  void set_device(int device) { device_ = device; }
+  // Which CUDA devices to use -- not part of the reference interface. Default: EVERY visible device (the scene
+  // is replicated, interleaved 16-row bands of the film are dealt to the GPUs and ONE ncclReduce assembles the
+  // film: bit-identical to a single-GPU render). set_device(d) pins the render to one device.
+  void set_device(int device) { set_devices(&device, 1); }
+  void set_devices(const int* devices, int n) {
+    devices_.clear();
+    for (int i = 0; i < n; i++) devices_.push_back(devices[i]);
+  }
+  // PB2_SHARD_ROWS (default, bit-identical to one GPU) or PB2_SHARD_SAMPLES (include/pine_b200.h).
+  void set_shard_mode(int mode) { shard_mode_ = mode; }
+  int n_devices() const { return n_devices_; }
   // Counters of the last render (rays traced, kernel launches, device ms); see pb2_counters.
   uint64_t last_closest_rays() const { return last_closest_; }
   uint64_t last_shadow_rays() const { return last_shadow_; }
@@ -45,8 +54,10 @@ class CudaPathIntegrator : public Integrator {
  private:
   Sampler sampler_;
   int max_path_length_;
-  int device_ = 0;
-  pb2_context* ctx_ = nullptr;
+  psl::vector<int> devices_;  // empty: all visible
+  int shard_mode_ = 1;        // PB2_SHARD_ROWS
+  int n_devices_ = 0;
+  pb2_multi* multi_ = nullptr;
   uint64_t last_closest_ = 0, last_shadow_ = 0, launches_ = 0;
   double last_ms_ = 0;
 };

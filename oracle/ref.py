@@ -55,6 +55,8 @@ def lib():
         L.ref_render.restype = C.c_double
         L.ref_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.ref_accel_build.restype = C.c_double
+        L.ref_render_sample_range.restype = C.c_double
+        L.ref_render_sample_range.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.ref_render_moments.restype = C.c_double
         L.ref_render_moments.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_bounded_prepare.restype = C.c_double
@@ -196,14 +198,23 @@ class RefScene:
 
     def render_cuda(self, spp, depth, device=0, sampler="blue"):
         """The drop-in test: THIS pine::Scene through pine::CudaPathIntegrator (integration/) ->
-        (film, seconds, stats). The product library does the work; the harness only hosts the scene."""
+        (film, seconds, stats). The product library does the work; the harness only hosts the scene.
+        device = -1: every visible GPU (the shim's default), else that one device."""
         w, h = self.size
         film = np.zeros((h, w, 4), np.float32)
-        stats = np.zeros(4, np.float64)
+        stats = np.zeros(5, np.float64)
         kind = {"blue": 0, "sobol": 1, "uniform": 2, "halton": 3}[sampler]
         secs = shim().ref_render_cuda_kind(self.h, kind, spp, depth, device, film.ctypes.data, stats.ctypes.data)
         return film, secs, {"closest_rays": int(stats[0]), "shadow_rays": int(stats[1]),
-                            "kernel_launches": int(stats[2]), "render_ms": float(stats[3])}
+                            "kernel_launches": int(stats[2]), "render_ms": float(stats[3]), "n_devices": int(stats[4])}
+
+    def render_sample_range(self, spp, depth, s0, s1):
+        """Samples [s0, s1) of a BlueSampler(spp) render with the sampler started at sample index s0: one
+        rank's film of a sample-sharded render (sum / spp, alpha = (s1 - s0) / spp)."""
+        w, h = self.size
+        film = np.zeros((h, w, 4), np.float32)
+        self.L.ref_render_sample_range(self.h, spp, depth, s0, s1, film.ctypes.data)
+        return film
 
     def render_moments(self, spp, depth):
         """BlueSampler render that also returns the per-pixel mean and the standard error of that mean, from

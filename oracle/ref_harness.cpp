@@ -73,6 +73,21 @@ struct BoundedPath : PathIntegrator {
       film[p] = vec4(L / spp, 1.0f);
     });
   }
+  // Samples [s0, s1) of every pixel, the sampler started at sample index s0 (Sampler::start_pixel(p, sample_index),
+  // sampler.h:286-290: RNG(hash(p, s0)), BlueSobol index = s0): what one rank of a sample-sharded render owns
+  // (SURVEY 8(e)). film[p] = (sum over the range / spp, (s1 - s0) / spp), so that the ranks' films ADD to a full one.
+  void render_sample_range(Scene& scene, int s0, int s1) {
+    auto& film = scene.camera.film();
+    parallel_for(film.size(), [&](vec2i p) {
+      Sampler& sampler = samplers[threadIdx].start_pixel(p, s0);
+      auto L = vec3(0.0f);
+      for (int si = s0; si < s1; si++, sampler.start_next_sample()) {
+        auto ray = scene.camera.gen_ray((p + sampler.rand2f()) / film.size(), sampler.rand2f());
+        L += radiance(scene, ray, sampler, Vertex::first_vertex()).Lo;
+      }
+      film[p] = vec4(L / spp, float(s1 - s0) / float(spp));
+    });
+  }
   // The same loop over the whole film, also returning per pixel and channel the sum and the sum of squares
   // of the spp per-sample radiances (what the 3-sigma test of SURVEY 8(c) T4 takes its sigma from).
   void render_moments(Scene& scene, double* sum, double* sumsq) {
@@ -260,6 +275,18 @@ double ref_bounded_render_rows(void* h, int row_begin, int row_end, int row_step
     auto& film = S.scene.camera.film();
     std::memcpy(film_rgba, film.data(), sizeof(float) * 4 * size_t(film.width()) * film.height());
   }
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+// One rank's share of a sample-sharded render (see BoundedPath::render_sample_range). BlueSobolSampler.
+double ref_render_sample_range(void* h, int spp, int depth, int s0, int s1, float* film_rgba) {
+  auto& S = *(RefScene*)h;
+  BoundedPath path(Accel(BVH()), Sampler(BlueSobolSampler(spp)), LightSampler(UniformLightSampler()), depth);
+  auto t0 = std::chrono::steady_clock::now();
+  path.prepare(S.scene);
+  path.render_sample_range(S.scene, s0, s1);
+  auto t1 = std::chrono::steady_clock::now();
+  auto& film = S.scene.camera.film();
+  std::memcpy(film_rgba, film.data(), sizeof(float) * 4 * size_t(film.width()) * film.height());
   return std::chrono::duration<double>(t1 - t0).count();
 }
 // Whole-film render that also reports the per-pixel moments of the per-sample radiance (sum, sumsq:

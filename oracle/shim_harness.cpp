@@ -23,7 +23,7 @@ void* ref_scene_ptr(void* h);  // oracle/ref_harness.cpp
 
 // The drop-in: the SAME pine::Scene rendered by pine::CudaPathIntegrator (integration/), constructed
 // with PathIntegrator's own argument list. Returns wall seconds; stats = {closest rays, shadow rays,
-// kernel launches, device ms}. Aborts through SEVERE like the reference on unsupported content.
+// kernel launches, device ms, GPUs used}; device < 0 = every visible GPU. Aborts through SEVERE like the reference on unsupported content.
 double ref_render_cuda_kind(void* h, int sampler_kind, int spp, int depth, int device, float* film_rgba,
                             double* stats) {
   Scene& scene = *(Scene*)ref_scene_ptr(h);
@@ -31,7 +31,7 @@ double ref_render_cuda_kind(void* h, int sampler_kind, int spp, int depth, int d
                  : sampler_kind == 1 ? Sampler(SobolSampler(spp))
                                      : sampler_kind == 3 ? Sampler(HaltonSampler(spp)) : Sampler(UniformSampler(spp));
   auto integrator = CudaPathIntegrator(Accel(BVH()), sampler, LightSampler(UniformLightSampler()), depth);
-  integrator.set_device(device);
+  if (device >= 0) integrator.set_device(device);  // device < 0: every visible GPU (the shim's default)
   auto t0 = std::chrono::steady_clock::now();
   Integrator& base = integrator;  // through the virtual interface, as the PRL binding calls it
   base.render(scene);
@@ -45,6 +45,7 @@ double ref_render_cuda_kind(void* h, int sampler_kind, int spp, int depth, int d
     stats[1] = double(integrator.last_shadow_rays());
     stats[2] = double(integrator.kernel_launches());
     stats[3] = integrator.last_render_ms();
+    stats[4] = double(integrator.n_devices());
   }
   return std::chrono::duration<double>(t1 - t0).count();
 }

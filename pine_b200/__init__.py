@@ -8,6 +8,6 @@ prl.py (loader for the PRL subset Pine's scene files use; `python -m pine_b200 s
 """
 from .scene import (ACES, AABB, Box, Cone, Diffuse, Disk, Emissive, Film, Glass, Glossy, Mesh, Metal,
                     Rect, Scene, Sphere, Subsurface, ThinLenCamera, Triangle, Uber, Uncharted2, mat4)
-from .integrator import Backend, BlueSampler, HaltonSampler, PathIntegrator, SobolSampler, UniformSampler
+from .integrator import Backend, MultiBackend, BlueSampler, HaltonSampler, PathIntegrator, SobolSampler, UniformSampler
 from ._abi import PineB200Error
 from .gltf import GltfError, load_scene, scene_from_gltf

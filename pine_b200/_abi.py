@@ -103,7 +103,8 @@ class RenderParams(C.Structure):
     _fields_ = [("spp", C.c_int32), ("max_path_length", C.c_int32), ("row_begin", C.c_int32),
                 ("row_end", C.c_int32), ("sample_begin", C.c_int32), ("sample_end", C.c_int32),
                 ("accel", C.c_int32), ("flags", C.c_int32), ("sampler", C.c_int32),
-                ("sampler_seed", C.c_int32)]
+                ("sampler_seed", C.c_int32), ("row_band", C.c_int32), ("row_parts", C.c_int32),
+                ("row_part", C.c_int32)]
 
 
 SAMPLER_BLUE, SAMPLER_SOBOL, SAMPLER_UNIFORM, SAMPLER_HALTON = 0, 1, 2, 3
@@ -144,7 +145,11 @@ ABI_SYMBOLS = [
     "pb2_test_primary_rays", "pb2_get_counters", "pb2_debug_walk_stats", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
     "pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone", "pb2h_make_triangle",
     "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_mesh_apply", "pb2h_cosf", "pb2h_round_spp", "pb2h_sampler_draws",
+    "pb2_create_multi", "pb2_destroy_multi", "pb2_multi_size", "pb2_multi_context", "pb2_multi_upload_sampler_tables",
+    "pb2_multi_load_sampler_tables_file", "pb2_multi_upload_scene", "pb2_multi_restage_scene", "pb2_multi_render",
+    "pb2_multi_get_counters",
 ]
+SHARD_SAMPLES, SHARD_ROWS = 0, 1
 
 _lib = None
 
@@ -193,6 +198,19 @@ def lib():
                                    C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         L.pb2_bvh_nodes.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_void_p]
+        L.pb2_create_multi.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.pb2_destroy_multi.argtypes = [C.c_void_p]
+        L.pb2_destroy_multi.restype = None
+        L.pb2_multi_size.argtypes = [C.c_void_p]
+        L.pb2_multi_context.argtypes = [C.c_void_p, C.c_int]
+        L.pb2_multi_context.restype = C.c_void_p
+        L.pb2_multi_upload_sampler_tables.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pb2_multi_load_sampler_tables_file.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        L.pb2_multi_upload_scene.argtypes = [C.c_void_p, C.POINTER(SceneDesc)]
+        L.pb2_multi_restage_scene.argtypes = [C.c_void_p]
+        L.pb2_multi_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_int, C.c_void_p]
+        L.pb2_multi_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters), C.POINTER(C.c_double),
+                                             C.POINTER(C.c_double)]
         fp = C.POINTER(C.c_float)
         L.pb2h_make_rect.argtypes = [fp, fp, fp, C.c_int, C.POINTER(Rect)]
         L.pb2h_make_obb.argtypes = [fp, fp, fp, C.POINTER(Obb)]

@@ -54,6 +54,9 @@ struct SamplerTables {
 };
 
 struct WavefrontBuffers;  // render.cu
+}  // namespace pb2
+struct pb2_context;
+namespace pb2 {
 
 // Host copy of everything pb2_upload_scene lays out for the device. The vectors stay alive (and
 // page-locked, cudaHostRegister) for as long as the scene is current, so that the host->device
@@ -78,8 +81,10 @@ struct HostScene {
   std::vector<pb2_cone> cones;
   std::vector<pb2_rect> rects;
   std::vector<pb2_disk> disks;
-  struct Item { DBuf* dst; const void* src; size_t bytes; };
-  std::vector<Item> items;          // staging list, in upload order
+  // staging list, in upload order. `dst` names the destination by member so that the same list stages the
+  // scene into ANY context: the replicas of a pb2_multi share the host scene their first context built.
+  struct Item { DBuf pb2_context::* dst; const void* src; size_t bytes; };
+  std::vector<Item> items;
   std::vector<void*> registered;    // ranges currently page-locked
   void unpin() {
     for (void* p : registered) cudaHostUnregister(p);
@@ -95,12 +100,14 @@ struct pb2_context {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
   bool scene_ready = false;       // device copy valid
   bool host_scene_ready = false;  // host trees valid (also on a host-only context, device = -1)
+  bool defer_staging = false;     // pb2_upload_scene stops after the host build (pb2_multi stages the replicas)
 
   // host copies kept for the dump API
   pb2::Tree2 top_tree;
   std::vector<pb2::Tree2> mesh_trees;
 
   pb2::HostScene host;
+  const pb2::HostScene* host_view = nullptr;  // whose staging list restage() copies: &host, or the scene's owner (pb2_multi)
   pb2::DScene scene{};  // device pointers
   pb2::DBuf nodes2, nodes8, leaves, wide_prims, box_shapes, leaf_prims, top_prims, meshes, geoms, materials, lights, light_recs;
   pb2::DBuf aabbs, obbs, spheres, triangles, cones, rects, disks;

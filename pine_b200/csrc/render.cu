@@ -45,8 +45,7 @@ struct WaveView {
   float4* lacc;           // running L
   int* counts;            // [0..D] live rays per depth, [D+1..2D+1] shadow rays per depth, then per
                           // depth {closest cursor, closest fallbacks, shadow cursor, shadow fallbacks}
-  int* fb_list;           // fallback list of the closest-hit kernels
-  int* sfb_list;          // fallback list of the shadow kernels (they may run beside the next depth's closest hits)
+  int* fb_list;           // fallback list shared by the traversal kernels (used one at a time)
   uint8_t* occ;           // NULL unless a ray record is being taken
   int* lists;             // shade lists: [list][n_slots] queue indices, one list per shading class
   int list_of_class[8];   // class (0 = terminal, k = pb2_material_kind k) -> list number, -1 = absent
@@ -54,6 +53,7 @@ struct WaveView {
   int pixels;             // pixels per sample layer in this wave
   int pixel0;             // first pixel (linear index in the row range) of this wave
   int width, row_begin;
+  int row_band, row_parts, row_part;  // interleaved row bands (pb2_render_params); row_parts <= 1: contiguous rows
   int s_batch, sample0;   // samples [sample0, sample0 + s_batch) of every pixel in the wave
   int max_depth;          // PathIntegrator::max_path_length
   int accel;
@@ -64,13 +64,13 @@ struct WaveView {
 // lane's persistent traversal launch, its few-ray reference-order re-trace and its memory-streaming shade
 // kernels are filled by the other lane's work instead of leaving SMs idle (pb2_render_device).
 constexpr int kMaxLanes = 4;
-constexpr int kDefaultLanes = 2;  // measured on B200: C5 +9%, C3 +7%, C1 +5% over one lane; see DESIGN.md for 3 and 4
+constexpr int kDefaultLanes = 4;  // measured on B200 (profiles/r2): C5 458 / 502 / 511 / 516 Msamples/s with 1 / 2 / 3 / 4
+                                  // lanes, C3 1123 / 1197 / - / 1213, C1 822 / 870 / - / 866
 constexpr long kMinLaneSlots = 1L << 19;  // a lane must still fill the GPU: below this, one lane
 struct LaneBuffers {
-  DBuf ray_o[2], ray_d[2], hit, sh_o[2], sh_d[2], pv_pdf, pv_flags, dim, term, vtx, fb_list, sfb_list, occ, lists;
+  DBuf ray_o[2], ray_d[2], hit, sh_o, sh_d, pv_pdf, pv_flags, dim, term, vtx, fb_list, occ, lists;
   cudaStream_t stream = nullptr;  // lanes >= 1 only; lane 0 runs on the caller's stream
-  cudaStream_t side = nullptr;    // shadow rays of depth d, beside the closest-hit rays of depth d + 1
-  cudaEvent_t done = nullptr, shaded = nullptr, shadowed[2] = {nullptr, nullptr};
+  cudaEvent_t done = nullptr;
 };
 struct WavefrontBuffers {
   LaneBuffers lane[kMaxLanes];
@@ -82,10 +82,7 @@ struct WavefrontBuffers {
     for (cudaEvent_t e : events) cudaEventDestroy(e);
     for (LaneBuffers& l : lane) {
       if (l.stream) cudaStreamDestroy(l.stream);
-      if (l.side) cudaStreamDestroy(l.side);
       if (l.done) cudaEventDestroy(l.done);
-      if (l.shaded) cudaEventDestroy(l.shaded);
-      for (cudaEvent_t e : l.shadowed) if (e) cudaEventDestroy(e);
     }
     if (fork) cudaEventDestroy(fork);
   }
@@ -97,6 +94,12 @@ void free_wavefront(pb2_context* ctx) {
 }
 
 // ---- helpers ------------------------------------------------------------------------------------------
+// Film row of the render's `local`-th row: contiguous from row_begin, or the bands of `band` rows this call owns
+// out of every `parts` (band k of the range belongs to part k % parts).
+__device__ __forceinline__ int film_row(int row_begin, int band, int parts, int part, int local) {
+  if (parts <= 1) return row_begin + local;
+  return row_begin + ((local / band) * parts + part) * band + local % band;
+}
 __device__ __forceinline__ int warp_compact(bool keep, int* counter) {
   unsigned mask = __ballot_sync(0xffffffffu, keep);
   int lane = threadIdx.x & 31;
@@ -127,7 +130,7 @@ __global__ void __launch_bounds__(256) k_raygen(DScene sc, WaveView w, int seed_
   PB2_WARP_LOOP(i, w.pixels) {
     if (i >= w.pixels) continue;
     int pix = w.pixel0 + i;  // linear in the row range
-    int px = pix % w.width, py = w.row_begin + pix / w.width;
+    int px = pix % w.width, py = film_row(w.row_begin, w.row_band, w.row_parts, w.row_part, pix / w.width);
     Rng g = first_wave_of_pixel ? rng_seed(murmur_pixel(px, py, seed_sample)) : load_rng(w.rng, pix);
     for (int s = 0; s < w.s_batch; s++) {
       // gen_ray((p + rand2f()) / size, rand2f()) (path.cpp:35): g++ evaluates the arguments right
@@ -193,7 +196,7 @@ struct ShadowIO {
 };
 __device__ __forceinline__ WideQueue wave_queue(const WaveView& w, int depth, int which) {
   int* c = w.counts + 2 * (w.max_depth + 1) + 4 * depth + 2 * which;
-  return WideQueue{c, c + 1, which ? w.sfb_list : w.fb_list};
+  return WideQueue{c, c + 1, w.fb_list};
 }
 __device__ __forceinline__ TraceIO trace_io(const WaveView& w, int depth) {
   return TraceIO{w.ray_o[depth & 1], w.ray_d[depth & 1], w.hit};
@@ -472,7 +475,7 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
       const DGeom g = sc.geoms[geom];
       const pb2_material m = sc.materials[g.material];
       int pix = w.pixel0 + slot % w.pixels;
-      int px = pix % w.width, py = w.row_begin + pix / w.width;
+      int px = pix % w.width, py = film_row(w.row_begin, w.row_band, w.row_parts, w.row_part, pix / w.width);
       PixelSamplerT<GENERIC> smp{px, py, w.sample0 + slot / w.pixels, w.dim[slot]};
       Rng g_rng;
       constexpr bool uses_rng = MAT == PB2_MAT_UBER || MAT == PB2_MAT_SUBSURFACE;
@@ -628,11 +631,12 @@ __global__ void __launch_bounds__(256) k_fold_resolve(WaveView w) {
   }
 }
 
-__global__ void __launch_bounds__(256) k_film(const float4* lacc, float4* film, int pixels, int pixel_offset,
-                                            int spp, float alpha) {
+__global__ void __launch_bounds__(256) k_film(const float4* lacc, float4* film, int pixels, int width, int row_begin,
+                                            int band, int parts, int part, int spp, float alpha) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < pixels; i += gridDim.x * blockDim.x) {
     float4 a = lacc[i];
-    film[pixel_offset + i] = make_float4(a.x / float(spp), a.y / float(spp), a.z / float(spp), alpha);
+    const int row = film_row(row_begin, band, parts, part, i / width);
+    film[size_t(row) * width + i % width] = make_float4(a.x / float(spp), a.y / float(spp), a.z / float(spp), alpha);
   }
 }
 
@@ -770,6 +774,10 @@ int check_params(pb2_context* ctx, const pb2_render_params* p) {
     set_error("row/sample range out of bounds");
     return PB2_E_INVALID;
   }
+  if (p->row_parts > 1 && (p->row_band <= 0 || p->row_part < 0 || p->row_part >= p->row_parts)) {
+    set_error("row_band must be positive and row_part in [0, row_parts)");
+    return PB2_E_INVALID;
+  }
   return PB2_OK;
 }
 
@@ -786,7 +794,12 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   const DScene& sc = ctx->scene;
   const int W = sc.camera.width, H = sc.camera.height;
   const int D = p->max_path_length;
-  const int rows = p->row_end - p->row_begin;
+  int rows = p->row_end - p->row_begin;
+  if (p->row_parts > 1) {  // the rows of the bands this call owns
+    int mine = 0;
+    for (int k = p->row_part; k * p->row_band < rows; k += p->row_parts) mine += std::min(p->row_band, rows - k * p->row_band);
+    rows = mine;
+  }
   const long P = long(rows) * W;
   const int n_samples = p->sample_end - p->sample_begin;
 
@@ -840,10 +853,6 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   const bool closest_wide_ok = !ref_order && !sc.order_dependent;
   const bool any_wide_ok = !ref_order && sc.n_box_shapes <= kMaxBoxShapes;
   const int pgrid = persistent_grid();
-  // PB2_SHADOW_ASYNC: the shadow rays of depth d run on a side stream of the lane, beside the closest-hit
-  // rays of depth d + 1 (both are written by the shade kernels of depth d and independent of each other);
-  // the shadow queue is double buffered, and the shade kernels of depth d + 2 wait for shadow(d).
-  const bool shadow_async = !rec && !timed && env_int("PB2_SHADOW_ASYNC", 0) != 0;
 
   WaveView lane_view[kMaxLanes];
   cudaStream_t lane_stream[kMaxLanes];
@@ -854,22 +863,14 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       PB2_CUDA_CHECK(L.ray_d[k].reserve(n_slots * 16));
     }
     PB2_CUDA_CHECK(L.hit.reserve(n_slots * 16));
-    for (int k = 0; k < (shadow_async ? 2 : 1); k++) {
-      PB2_CUDA_CHECK(L.sh_o[k].reserve(n_slots * 16));
-      PB2_CUDA_CHECK(L.sh_d[k].reserve(n_slots * 16));
-    }
+    PB2_CUDA_CHECK(L.sh_o.reserve(n_slots * 16));
+    PB2_CUDA_CHECK(L.sh_d.reserve(n_slots * 16));
     PB2_CUDA_CHECK(L.pv_pdf.reserve(n_slots * 4));
     PB2_CUDA_CHECK(L.pv_flags.reserve(n_slots * 4));
     PB2_CUDA_CHECK(L.dim.reserve(n_slots * 4));
     PB2_CUDA_CHECK(L.term.reserve(n_slots * 16));
     PB2_CUDA_CHECK(L.vtx.reserve(size_t(n_slots) * n_vtx * 32));
     PB2_CUDA_CHECK(L.fb_list.reserve(size_t(n_slots) * 4));
-    PB2_CUDA_CHECK(L.sfb_list.reserve(size_t(n_slots) * 4));
-    if (shadow_async) {
-      if (!L.side) PB2_CUDA_CHECK(cudaStreamCreateWithFlags(&L.side, cudaStreamNonBlocking));
-      if (!L.shaded) PB2_CUDA_CHECK(cudaEventCreateWithFlags(&L.shaded, cudaEventDisableTiming));
-      for (cudaEvent_t& e : L.shadowed) if (!e) PB2_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    }
     PB2_CUDA_CHECK(L.lists.reserve(size_t(n_lists) * n_slots * 4));
     if (rec) PB2_CUDA_CHECK(L.occ.reserve(size_t(n_slots)));
     if (l > 0 && !L.stream) PB2_CUDA_CHECK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
@@ -883,12 +884,12 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
     w.lists = L.lists.as<int>();
     w.occ = rec ? L.occ.as<uint8_t>() : nullptr;
     for (int k = 0; k < 2; k++) { w.ray_o[k] = L.ray_o[k].as<float4>(); w.ray_d[k] = L.ray_d[k].as<float4>(); }
-    w.hit = L.hit.as<float4>(); w.sh_o = L.sh_o[0].as<float4>(); w.sh_d = L.sh_d[0].as<float4>();
+    w.hit = L.hit.as<float4>(); w.sh_o = L.sh_o.as<float4>(); w.sh_d = L.sh_d.as<float4>();
     w.pv_pdf = L.pv_pdf.as<float>(); w.pv_flags = L.pv_flags.as<int>(); w.dim = L.dim.as<int>();
     w.term = L.term.as<float4>(); w.vtx = L.vtx.as<float4>();
     w.rng = B.rng.as<uint2>(); w.lacc = B.lacc.as<float4>(); w.fb_list = L.fb_list.as<int>();
-    w.sfb_list = L.sfb_list.as<int>();
-    w.n_slots = int(n_slots); w.width = W; w.row_begin = p->row_begin; w.max_depth = D; w.accel = p->accel;
+    w.n_slots = int(n_slots); w.width = W; w.row_begin = p->row_begin; w.max_depth = D;
+    w.row_band = p->row_band; w.row_parts = p->row_parts; w.row_part = p->row_part; w.accel = p->accel;
   }
 
   uint64_t launches = 0;
@@ -1000,12 +1001,6 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       k_shade_terminal<<<sm_grid(live, 256, 8), 256, 0, ls>>>(sc, w, depth);
       launches += 2;
       if (depth + 1 < D) {
-        if (shadow_async) {
-          LaneBuffers& L = B.lane[l];
-          if (depth >= 2) PB2_CUDA_CHECK(cudaStreamWaitEvent(ls, L.shadowed[depth & 1], 0));
-          w.sh_o = L.sh_o[depth & 1].as<float4>();
-          w.sh_d = L.sh_d[depth & 1].as<float4>();
-        }
         const int sg = sm_grid(live, 128, 16);
         const unsigned mk = ctx->material_kinds;
         const bool blue = sc.sampler_kind == PB2_SAMPLER_BLUE && ctx->only_area_lights;
@@ -1021,27 +1016,18 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       }
       mark(2);
       if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
-        cudaStream_t ss = ls;
-        if (shadow_async) {
-          ss = B.lane[l].side;
-          PB2_CUDA_CHECK(cudaEventRecord(B.lane[l].shaded, ls));
-          PB2_CUDA_CHECK(cudaStreamWaitEvent(ss, B.lane[l].shaded, 0));
-        }
         if (any_wide_ok) {
-          k_shadow<<<pgrid, kTraceBlock, 0, ss>>>(sc, w, depth);
-          k_shadow_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ss>>>(sc, w, depth);
+          k_shadow<<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+          k_shadow_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
           launches += 2;
         } else {
-          k_shadow_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ss>>>(sc, w, depth);
+          k_shadow_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ls>>>(sc, w, depth);
           launches++;
         }
-        if (shadow_async) PB2_CUDA_CHECK(cudaEventRecord(B.lane[l].shadowed[depth & 1], ss));
         mark(1);
         if (rec) { int rc2 = record(w, true, depth); if (rc2) return rc2; }
       }
     }
-    if (shadow_async)
-      for (int k = 0; k < 2 && k < D - 1; k++) PB2_CUDA_CHECK(cudaStreamWaitEvent(ls, B.lane[l].shadowed[k], 0));
     k_fold_resolve<<<sm_grid(w.pixels, 256, 8), 256, 0, ls>>>(w);
     launches++; mark(3);
     return PB2_OK;
@@ -1066,8 +1052,8 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       PB2_CUDA_CHECK(cudaStreamWaitEvent(st, B.lane[l].done, 0));
     }
   const float alpha = float(n_samples) / float(p->spp);
-  k_film<<<sm_grid(int(P), 256, 8), 256, 0, st>>>(B.lacc.as<float4>(), ctx->film.as<float4>(), int(P),
-                                                  p->row_begin * W, p->spp, alpha);
+  k_film<<<sm_grid(int(P), 256, 8), 256, 0, st>>>(B.lacc.as<float4>(), ctx->film.as<float4>(), int(P), W,
+                                                  p->row_begin, p->row_band, p->row_parts, p->row_part, p->spp, alpha);
   launches++; mark(3);
   PB2_CUDA_CHECK(cudaEventRecord(ctx->ev1, st));
   PB2_CUDA_CHECK(cudaGetLastError());

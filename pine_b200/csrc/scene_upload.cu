@@ -38,6 +38,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   if (!ctx || !sd) { set_error("null argument"); return PB2_E_INVALID; }
   if (ctx->device >= 0) PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
   ctx->host_scene_ready = false;
+  ctx->host_view = nullptr;
   auto t0 = std::chrono::steady_clock::now();
   const bool verbose = std::getenv("PB2_VERBOSE") != nullptr;
   auto stage = [&](const char* name) {
@@ -305,15 +306,15 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
 
   // ---- staging list + page-lock ----
   uint64_t bytes = 0;
-  auto item = [&](DBuf& dst, const void* src, size_t n) {
-    H.items.push_back(HostScene::Item{&dst, src, n});
+  auto item = [&](DBuf pb2_context::* dst, const void* src, size_t n) {
+    H.items.push_back(HostScene::Item{dst, src, n});
     bytes += n;
     if (n >= (1u << 16) && cudaHostRegister(const_cast<void*>(src), n, cudaHostRegisterDefault) == cudaSuccess)
       H.registered.push_back(const_cast<void*>(src));
     else
       cudaGetLastError();
   };
-#define ITEM(buf, vec) item(ctx->buf, (vec).data(), (vec).size() * sizeof((vec)[0]))
+#define ITEM(buf, vec) item(&pb2_context::buf, (vec).data(), (vec).size() * sizeof((vec)[0]))
   ITEM(nodes2, lay.nodes2); ITEM(nodes8, lay.nodes8); ITEM(leaves, lay.leaves);
   ITEM(wide_prims, lay.wide_prims); ITEM(box_shapes, lay.box_shapes); ITEM(leaf_prims, lay.leaf_prims);
   ITEM(top_prims, H.top_prims); ITEM(meshes, H.meshes); ITEM(geoms, H.geoms); ITEM(lights, H.lights); ITEM(light_recs, H.light_recs);
@@ -324,6 +325,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
 #undef ITEM
   stage("page-lock");
   ctx->counters.scene_bytes = bytes;
+  if (ctx->defer_staging) return PB2_OK;  // pb2_multi_upload_scene stages the replicas itself (sharded + all-gather)
   int rc = pb2_restage_scene(ctx, nullptr);
   if (rc) return rc;
   PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
@@ -348,23 +350,25 @@ int restage(pb2_context* ctx, void* cuda_stream, int part, int n_parts, pb2_devi
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream;
   auto t0 = std::chrono::steady_clock::now();
   int n_out = 0;
-  for (const HostScene::Item& it : ctx->host.items) {
+  const HostScene& host = ctx->host_view ? *ctx->host_view : ctx->host;
+  for (const HostScene::Item& it : host.items) {
+    DBuf& dst = ctx->*(it.dst);
     if (n_parts == 1 || it.bytes < kShardMinBytes) {
-      PB2_CUDA_CHECK(it.dst->reserve(it.bytes));
-      if (it.bytes) PB2_CUDA_CHECK(cudaMemcpyAsync(it.dst->ptr, it.src, it.bytes, cudaMemcpyHostToDevice, st));
+      PB2_CUDA_CHECK(dst.reserve(it.bytes));
+      if (it.bytes) PB2_CUDA_CHECK(cudaMemcpyAsync(dst.ptr, it.src, it.bytes, cudaMemcpyHostToDevice, st));
       continue;
     }
     const size_t part_bytes = ((it.bytes + size_t(n_parts) - 1) / size_t(n_parts) + 255) / 256 * 256;
-    PB2_CUDA_CHECK(it.dst->reserve(part_bytes * size_t(n_parts)));
+    PB2_CUDA_CHECK(dst.reserve(part_bytes * size_t(n_parts)));
     const size_t off = part_bytes * size_t(part);
     if (off < it.bytes) {
       const size_t len = std::min(part_bytes, it.bytes - off);
-      PB2_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(it.dst->ptr) + off, static_cast<const char*>(it.src) + off, len,
+      PB2_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(dst.ptr) + off, static_cast<const char*>(it.src) + off, len,
                                      cudaMemcpyHostToDevice, st));
     }
     if (arrays) {
       if (n_out >= max_arrays) { set_error("pb2_restage_scene_part: max_arrays too small"); return PB2_E_INVALID; }
-      arrays[n_out] = pb2_device_array{it.dst->ptr, uint64_t(part_bytes) * uint64_t(n_parts), uint64_t(part_bytes)};
+      arrays[n_out] = pb2_device_array{dst.ptr, uint64_t(part_bytes) * uint64_t(n_parts), uint64_t(part_bytes)};
     }
     n_out++;
   }

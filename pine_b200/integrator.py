@@ -160,8 +160,9 @@ class Backend:
                                                  rnk.ctypes.data))
         self._tables_loaded.add(spp)
 
-    def _params(self, spp, depth, rows=None, samples=None, accel=0, flags=0):
-        """`spp`: an int (BlueSampler's spp) or a sampler object (BlueSampler/SobolSampler/UniformSampler)."""
+    def _params(self, spp, depth, rows=None, samples=None, accel=0, flags=0, bands=None):
+        """`spp`: an int (BlueSampler's spp) or a sampler object (BlueSampler/SobolSampler/UniformSampler).
+        `bands` = (band, parts, part): only the interleaved row bands of this part (pb2_render_params)."""
         spp, kind, seed = _sampler_of(spp)
         if kind == A.SAMPLER_BLUE:
             self.upload_tables(spp)
@@ -171,6 +172,8 @@ class Backend:
         p.row_begin, p.row_end = rows if rows else (0, self.size[1])
         p.sample_begin, p.sample_end = samples if samples else (0, spp)
         p.accel, p.flags = accel, flags
+        if bands:
+            p.row_band, p.row_parts, p.row_part = bands
         return p
 
     def restage(self, stream=None):
@@ -186,12 +189,12 @@ class Backend:
         A.check(self.L.pb2_restage_scene_part(self.h, stream, part, n_parts, arr, 64, C.byref(n)))
         return [(int(arr[i].device_ptr), int(arr[i].bytes), int(arr[i].part_bytes)) for i in range(n.value)]
 
-    def render(self, spp, depth, rows=None, samples=None, accel=0, out=None, flags=0):
+    def render(self, spp, depth, rows=None, samples=None, accel=0, out=None, flags=0, bands=None):
         """-> film float32 [h, w, 4] in host memory (pre-tonemap). `out` may be any writable
         C-contiguous float32 buffer object of that size (e.g. a pinned torch tensor's numpy view)."""
         w, h = self.size
         film = out if out is not None else np.empty((h, w, 4), np.float32)
-        p = self._params(spp, depth, rows, samples, accel, flags)
+        p = self._params(spp, depth, rows, samples, accel, flags, bands)
         A.check(self.L.pb2_render(self.h, C.byref(p), film.ctypes.data))
         return film
 
@@ -216,9 +219,9 @@ class Backend:
         out = {k: (v[:ns] if k.startswith("shadow") else v[:nc]) for k, v in bufs.items()}
         return film, out
 
-    def render_device(self, spp, depth, rows=None, samples=None, accel=0, stream=None, flags=0):
+    def render_device(self, spp, depth, rows=None, samples=None, accel=0, stream=None, flags=0, bands=None):
         """-> device pointer (int) of the float4 film owned by the context."""
-        p = self._params(spp, depth, rows, samples, accel, flags)
+        p = self._params(spp, depth, rows, samples, accel, flags, bands)
         ptr = C.c_void_p()
         A.check(self.L.pb2_render_device(self.h, C.byref(p), stream, C.byref(ptr)))
         return ptr.value
@@ -295,6 +298,76 @@ class Backend:
                                          leaf_range.ctypes.data, leaf_prims.ctypes.data))
         return {"root": root.value, "aabbs": aabbs, "children": children,
                 "leaf_range": leaf_range, "leaf_prims": leaf_prims[:npr.value]}
+
+
+class MultiBackend:
+    """One pb2_multi: every GPU of the box (or `devices`) behind one render call, inside the library --
+    one host build, replicas staged 1/N through PCIe + in-place ncclAllGather, shards rendered by one host
+    thread per GPU, ONE ncclReduce(sum) of the float film (include/pine_b200.h pb2_multi_*)."""
+
+    def __init__(self, devices=None):
+        self.L = A.lib()
+        h = C.c_void_p()
+        if devices is None:
+            A.check(self.L.pb2_create_multi(None, 0, C.byref(h)))
+        else:
+            arr = (C.c_int * len(devices))(*devices)
+            A.check(self.L.pb2_create_multi(arr, len(devices), C.byref(h)))
+        self.h = h
+        self.n = self.L.pb2_multi_size(h)
+        self._tables_loaded = set()
+        self._scene_keep = None
+        self.size = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.pb2_destroy_multi(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def upload_scene(self, scene):
+        d, keep = scene.desc()
+        A.check(self.L.pb2_multi_upload_scene(self.h, C.byref(d)))
+        self._scene_keep = (scene, keep)
+        self.size = scene.size
+
+    def restage(self):
+        A.check(self.L.pb2_multi_restage_scene(self.h))
+
+    def upload_tables(self, spp):
+        if spp in self._tables_loaded:
+            return
+        if spp not in sampler_tables():
+            raise A.PineB200Error(-1, f"spp must be BlueSobolSampler::spp(): a power of two <= 256, got {spp}")
+        sob, scr, rnk = sampler_tables()[spp]
+        A.check(self.L.pb2_multi_upload_sampler_tables(self.h, spp, sob.ctypes.data, scr.ctypes.data, rnk.ctypes.data))
+        self._tables_loaded.add(spp)
+
+    def render(self, spp, depth, mode="samples", accel=0, out=None, flags=0):
+        """-> film float32 [h, w, 4] on the host. mode "samples" (statistically equal to one GPU) or "rows"
+        (bit-identical to one GPU)."""
+        spp, kind, seed = _sampler_of(spp)
+        if kind == A.SAMPLER_BLUE:
+            self.upload_tables(spp)
+        w, h = self.size
+        film = out if out is not None else np.empty((h, w, 4), np.float32)
+        p = A.RenderParams()
+        p.spp, p.max_path_length, p.sampler, p.sampler_seed = spp, depth, kind, seed
+        p.row_begin, p.row_end, p.sample_begin, p.sample_end = 0, h, 0, spp
+        p.accel, p.flags = accel, flags
+        A.check(self.L.pb2_multi_render(self.h, C.byref(p), A.SHARD_ROWS if mode == "rows" else A.SHARD_SAMPLES,
+                                        film.ctypes.data))
+        return film
+
+    def counters(self):
+        c = A.Counters()
+        r, s = C.c_double(), C.c_double()
+        A.check(self.L.pb2_multi_get_counters(self.h, C.byref(c), C.byref(r), C.byref(s)))
+        out = {k: getattr(c, k) for k, _ in A.Counters._fields_}
+        out["reduce_ms"], out["stage_ms"] = r.value, s.value
+        return out
 
 
 class PathIntegrator:

@@ -60,13 +60,32 @@ class ShardedRenderer:
         bands = row_bands(h, self.world, self.rank, self.band)
         return [(b, (0, spp), PB2_RENDER_KEEP_FILM if i else 0) for i, b in enumerate(bands)]
 
+    def _torch_stream(self, stream):
+        """The ONE stream the render, the staging copies and the NCCL collectives of this rank are ordered on.
+        The context's own stream is created cudaStreamNonBlocking and NCCL orders only against torch's current
+        stream, so passing no stream (or the legacy default stream, handle 0) would let a collective start
+        before the render that feeds it has finished: a real torch stream is required and made current."""
+        import torch
+        if stream is None:
+            if getattr(self, "_stream", None) is None:
+                self._stream = torch.cuda.Stream(device=self.backend.device)
+            stream = self._stream
+        if not hasattr(stream, "cuda_stream") or stream.cuda_stream == 0:
+            raise ValueError("multi-GPU rendering needs a non-default torch.cuda.Stream (got the legacy default "
+                             "stream or a raw handle): the render and NCCL must share one ordered stream")
+        return stream
+
     def _partial(self, spp, depth, stream=None):
         """This rank's film as a torch tensor [h, w, 4] on its device (zeros where not rendered)."""
         import torch
         w, h = self.backend.size
         ptr = None
-        for rows, samples, flags in self.plan(spp):
-            ptr = self.backend.render_device(spp, depth, rows=rows, samples=samples, stream=stream, flags=flags)
+        cs = stream.cuda_stream if stream is not None else None
+        if self.mode == "samples":
+            for rows, samples, flags in self.plan(spp):
+                ptr = self.backend.render_device(spp, depth, rows=rows, samples=samples, stream=cs, flags=flags)
+        elif self.plan(spp):  # the interleaved bands of this rank in ONE call (pb2_render_params.row_band/parts/part)
+            ptr = self.backend.render_device(spp, depth, stream=cs, bands=(self.band, self.world, self.rank))
         if ptr is None:  # nothing dealt to this rank (more ranks than bands/samples)
             return torch.zeros((h, w, 4), dtype=torch.float32, device=f"cuda:{self.backend.device}")
 
@@ -76,11 +95,20 @@ class ShardedRenderer:
         return torch.as_tensor(_P(), device=f"cuda:{self.backend.device}")
 
     def render(self, spp, depth, dst=0, stream=None):
-        """-> the full film tensor on rank `dst` (other ranks get their partial back)."""
-        film = self._partial(spp, depth, stream)
-        if self.world > 1:
-            import torch.distributed as dist
-            dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM, group=self.group)
+        """-> the full film tensor on rank `dst` (other ranks get their partial back). Asynchronous on
+        `stream` (a torch.cuda.Stream; one is created when None and world > 1): synchronise it before
+        reading the film."""
+        import contextlib
+        st, ctx = None, contextlib.nullcontext()
+        if self.backend.device != "cpu" and (self.world > 1 or stream is not None):
+            import torch
+            st = self._torch_stream(stream)
+            ctx = torch.cuda.stream(st)
+        with ctx:
+            film = self._partial(spp, depth, st)
+            if self.world > 1:
+                import torch.distributed as dist
+                dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM, group=self.group)
         return film
 
 
@@ -88,19 +116,24 @@ def restage_sharded(backend, rank, world, stream=None, group=None):
     """Re-stage a scene that every rank of one NVLink domain holds a replica of: each rank pulls 1/world of
     every large array through PCIe from its pinned host copy (pb2_restage_scene_part) and the slices are
     all-gathered in place over NVLink / NVSwitch -- world x less host traffic per GPU than world full copies,
-    which is what bounds the end-to-end step at 8 GPUs (1.43 GB per replica on C5). Collectives run on
-    torch's current stream; `stream` must be that stream (or None with a synchronised context stream)."""
-    arrays = backend.restage_part(rank, world, stream)
+    which is what bounds the end-to-end step at 8 GPUs (1.43 GB per replica on C5). `stream`: the
+    torch.cuda.Stream the copies AND the collectives are issued on (required when world > 1; the legacy
+    default stream is rejected, see ShardedRenderer._torch_stream); the caller renders on the same stream."""
     if world == 1:
+        backend.restage_part(rank, world, stream.cuda_stream if stream is not None else None)
         return 0
     import torch
     import torch.distributed as dist
+    if stream is None or not hasattr(stream, "cuda_stream") or stream.cuda_stream == 0:
+        raise ValueError("restage_sharded needs a non-default torch.cuda.Stream when world > 1")
     moved = 0
-    for ptr, nbytes, part in arrays:
-        class _P:
-            __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
-                                        "version": 3, "strides": None}
-        full = torch.as_tensor(_P(), device=f"cuda:{backend.device}")
-        dist.all_gather_into_tensor(full, full[rank * part:(rank + 1) * part], group=group)
-        moved += nbytes
+    with torch.cuda.stream(stream):
+        arrays = backend.restage_part(rank, world, stream.cuda_stream)
+        for ptr, nbytes, part in arrays:
+            class _P:
+                __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                            "version": 3, "strides": None}
+            full = torch.as_tensor(_P(), device=f"cuda:{backend.device}")
+            dist.all_gather_into_tensor(full, full[rank * part:(rank + 1) * part], group=group)
+            moved += nbytes
     return moved

@@ -36,7 +36,7 @@ def test_struct_sizes_match_header():
     assert C.sizeof(A.Rect) == 80 and C.sizeof(A.Obb) == 152 and C.sizeof(A.Cone) == 96
     assert C.sizeof(A.Disk) == 52 and C.sizeof(A.Sphere) == 16 and C.sizeof(A.Triangle) == 48
     assert C.sizeof(A.Material) == 56 and C.sizeof(A.Geometry) == 12
-    assert C.sizeof(A.RenderParams) == 40
+    assert C.sizeof(A.RenderParams) == 52
 
 
 def test_round_spp_and_sampler_ctor():

@@ -107,11 +107,16 @@ def test_pixel_means_within_three_sigma_of_the_oracle(name):
     B.close()
 
 
-def test_sample_sharded_film_converges_like_the_reference(golden):
-    """Four sample shards (per-shard RNG streams seeded hash(p, first_sample)) summed: the error
-    against the converged 4096-spp reference film is the reference's own error at that spp within 2 %."""
+@pytest.mark.parametrize("name", ["c1_64", "cones_48"])
+def test_sample_shards_equal_the_references_own_shards(golden, name):
+    """Four sample shards: every shard's film equals the film the REFERENCE renders for the same
+    sample range with its sampler started at the shard's first sample (Sampler::start_pixel(p, sample_index),
+    sampler.h:286-290) to relMSE <= 1e-4, and the summed film's error against the converged 4096-spp film is
+    the reference's own sharded error within 2 %. (Re-seeding per shard changes the estimate -- on cones_48 the
+    shard starting at sample 48 carries a firefly in BOTH implementations -- which is why the comparison is
+    with the reference's shards, not with its unsharded film.)"""
     from oracle import ref
-    name, spp = "c1_64", 64
+    spp = 64
     g = golden(name)
     R, S = ref.RefScene(), pb.Scene()
     common.build(R, name)
@@ -119,10 +124,14 @@ def test_sample_sharded_film_converges_like_the_reference(golden):
     depth = common.SMALL_SCENES[name][3]
     B = pb.Backend(0)
     B.upload_scene(S)
-    film_ref, _ = R.render(spp, depth)
-    acc = sum(B.render(spp, depth, samples=(s, s + spp // 4)).astype(np.float64) for s in range(0, spp, spp // 4))
+    acc, acc_ref = 0, 0
+    for s in range(0, spp, spp // 4):
+        f, fr = B.render(spp, depth, samples=(s, s + spp // 4)), R.render_sample_range(spp, depth, s, s + spp // 4)
+        assert relmse(f * 4, fr * 4) <= FILM_RELMSE_TOL, s
+        assert np.array_equal(f[..., 3], fr[..., 3])
+        acc, acc_ref = acc + f.astype(np.float64), acc_ref + fr.astype(np.float64)
     assert np.allclose(acc[..., 3], 1.0)
-    e_shard, e_ref = relmse(acc, g["film_converged"]), relmse(film_ref, g["film_converged"])
+    e_shard, e_ref = relmse(acc, g["film_converged"]), relmse(acc_ref, g["film_converged"])
     assert abs(e_shard - e_ref) <= 0.02 * e_ref + 1e-6, (e_shard, e_ref)
     B.close()
 
@@ -157,8 +166,7 @@ def test_wave_plan_splits_are_bit_identical(fn, kw):
                 {"PB2_MAX_SLOTS": w * 7 * 3, "PB2_LANES": 2, "PB2_MIN_LANE_SLOTS": 1},
                 {"PB2_LANES": 2, "PB2_MIN_LANE_SLOTS": 1},                      # two half-film waves in flight
                 {"PB2_LANES": 4, "PB2_MIN_LANE_SLOTS": 1, "PB2_MAX_SLOTS": w * 5 * 2},
-                {"PB2_LANES": 2, "PB2_MIN_LANE_SLOTS": 1, "PB2_SHADOW_ASYNC": 1},  # shadow(d) beside trace(d + 1)
-                {"PB2_LANES": 1, "PB2_SHADOW_ASYNC": 1, "PB2_MAX_SLOTS": w * 9}):
+                {"PB2_LANES": 3, "PB2_MIN_LANE_SLOTS": 1}):
         film = _with_env(env, lambda: B.render(spp, depth))
         assert np.array_equal(u32(film), u32(base)), env
     rows = _with_env({"PB2_LANES": 2, "PB2_MIN_LANE_SLOTS": 1}, lambda: B.render(spp, depth, rows=(5, 38)))
