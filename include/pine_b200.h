@@ -305,6 +305,10 @@ int pb2_test_sampler_kind(pb2_context* ctx, int sampler, int spp, int sampler_se
                           int sample_index, const char* pattern, int n_samples, float* out_draws);
 int pb2_test_primary_rays(pb2_context* ctx, int sample_index, float* rays_host);
 int pb2_get_counters(pb2_context* ctx, pb2_counters* out);
+/* Measurement hook (SURVEY 8(d) asks for a measured L2 peak beside the HBM peak): sustained read bandwidth in
+ * GB/s of a `bytes`-sized device buffer read `iters` times by a full grid with L1 bypassed (ld.global.cg).
+ * bytes << 126 MB: the L2; bytes >> 126 MB: HBM. */
+int pb2_measure_read_gbs(pb2_context* ctx, size_t bytes, int iters, double* gbs);
 /* Debug hook (meaningful in -DPB2_COUNT tuning builds only; zeros otherwise): wide-walk node and
  * primitive tests since the last call, see pine_b200/csrc/api.cu. */
 int pb2_debug_walk_stats(pb2_context* ctx, uint64_t* out10);

@@ -234,6 +234,50 @@ extern "C" int pb2_debug_walk_stats(pb2_context* ctx, uint64_t* out10) {
   return PB2_OK;
 }
 
+// ---- read-bandwidth microbenchmark ("L2 peak to be measured with a resident-buffer read") ------
+namespace pb2 {
+__global__ void __launch_bounds__(256) k_read_bw(const uint4* __restrict__ buf, size_t n_vec, int iters, uint4* sink) {
+  uint4 acc = make_uint4(0, 0, 0, 0);
+  const size_t tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x, stride = size_t(gridDim.x) * blockDim.x;
+  for (int it = 0; it < iters; it++) {
+    size_t i = tid;
+    for (; i + 3 * stride < n_vec; i += 4 * stride) {  // four independent 128-bit loads in flight per thread
+      const uint4 a = __ldcg(buf + i), b = __ldcg(buf + i + stride), c = __ldcg(buf + i + 2 * stride),
+                  d = __ldcg(buf + i + 3 * stride);  // ld.global.cg: cached in L2 only, so L1 hits cannot inflate it
+      acc.x ^= a.x ^ b.x ^ c.x ^ d.x; acc.y ^= a.y ^ b.y ^ c.y ^ d.y;
+      acc.z ^= a.z ^ b.z ^ c.z ^ d.z; acc.w ^= a.w ^ b.w ^ c.w ^ d.w;
+    }
+    for (; i < n_vec; i += stride) { const uint4 a = __ldcg(buf + i); acc.x ^= a.x; acc.y ^= a.y; acc.z ^= a.z; acc.w ^= a.w; }
+  }
+  if ((acc.x ^ acc.y ^ acc.z ^ acc.w) == 0x9e3779b9u) sink[tid % 32] = acc;  // keeps the loads alive
+}
+}  // namespace pb2
+
+// Sustained read bandwidth of a `bytes`-sized device buffer read `iters` times back to back by a full grid
+// (after one untimed pass): bytes well below the 126 MB L2 measure the L2, bytes far above it the HBM.
+extern "C" int pb2_measure_read_gbs(pb2_context* ctx, size_t bytes, int iters, double* gbs) {
+  if (!ctx || !gbs || bytes < 4096 || iters <= 0) { set_error("invalid argument"); return PB2_E_INVALID; }
+  if (ctx->device < 0) { set_error("host-only context: no CUDA device, and there is no CPU fallback"); return PB2_E_CUDA; }
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  DBuf buf, sink;
+  PB2_CUDA_CHECK(buf.reserve(bytes));
+  PB2_CUDA_CHECK(sink.reserve(32 * 16));
+  PB2_CUDA_CHECK(cudaMemsetAsync(buf.ptr, 1, bytes, ctx->stream));
+  const size_t n_vec = bytes / 16;
+  const int grid = kNumSMs * 8;
+  k_read_bw<<<grid, 256, 0, ctx->stream>>>(buf.as<uint4>(), n_vec, 1, sink.as<uint4>());
+  PB2_CUDA_CHECK(cudaEventRecord(ctx->ev2, ctx->stream));
+  k_read_bw<<<grid, 256, 0, ctx->stream>>>(buf.as<uint4>(), n_vec, iters, sink.as<uint4>());
+  PB2_CUDA_CHECK(cudaEventRecord(ctx->ev3, ctx->stream));
+  ctx->counters.kernel_launches += 2;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  float ms = 0;
+  PB2_CUDA_CHECK(cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3));
+  *gbs = double(n_vec) * 16.0 * iters / (double(ms) * 1e-3) / 1e9;
+  return PB2_OK;
+}
+
 extern "C" int pb2_get_counters(pb2_context* ctx, pb2_counters* out) {
   if (!ctx || !out) { set_error("null argument"); return PB2_E_INVALID; }
   *out = ctx->counters;

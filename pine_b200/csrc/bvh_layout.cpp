@@ -14,29 +14,47 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
 namespace pb2 {
 
-DTree append_binary(const Tree2& t, LayoutOut& out) {
+namespace {
+// Runs fn(0..n-1) on up to `threads` host threads (dynamic distribution).
+template <class F>
+void parallel_for_index(size_t n, int threads, F&& fn) {
+  if (n == 0) return;
+  std::atomic<size_t> next{0};
+  auto work = [&] { for (size_t i; (i = next.fetch_add(1)) < n;) fn(i); };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads && size_t(t) < n; t++) pool.emplace_back(work);
+  work();
+  for (auto& th : pool) th.join();
+}
+int count_internal(const Tree2& t) {
+  int n = 0;
+  for (const Node2& nd : t.nodes) n += nd.leaf_count == 0;
+  return n;
+}
+// Writes tree `t` into nodes2[node_base ...] / leaf_prims[leaf_base ...] (ranges sized by the caller).
+// Internal nodes only get a DNode2; children that are leaves are folded into the parent's link/count.
+// Node indices are remapped densely over internal nodes.
+DTree fill_binary(const Tree2& t, int node_base, int leaf_base, DNode2* nodes2, int32_t* leaf_prims) {
   DTree d{-1, 0, 0, 0};
   if (t.root < 0) return d;
-  const int node_base = int(out.nodes2.size());
-  const int leaf_base = int(out.leaf_prims.size());
-  out.leaf_prims.insert(out.leaf_prims.end(), t.leaf_prims.begin(), t.leaf_prims.end());
-  // Internal nodes only get a DNode2; children that are leaves are folded into the parent's
-  // link/count. Node indices are remapped densely over internal nodes.
+  std::memcpy(leaf_prims + leaf_base, t.leaf_prims.data(), t.leaf_prims.size() * sizeof(int32_t));
   std::vector<int> remap(t.nodes.size(), -1);
   int n_internal = 0;
   for (size_t i = 0; i < t.nodes.size(); i++)
     if (!t.nodes[i].leaf_count) remap[i] = node_base + n_internal++;
-  out.nodes2.resize(size_t(node_base) + n_internal);
   for (size_t i = 0; i < t.nodes.size(); i++) {
     const Node2& nd = t.nodes[i];
     if (nd.leaf_count) continue;
-    DNode2& o = out.nodes2[remap[i]];
+    DNode2& o = nodes2[remap[i]];
     for (int c = 0; c < 2; c++) {
       for (int k = 0; k < 3; k++) { o.box[c][k] = nd.box[c].lower[k]; o.box[c][3 + k] = nd.box[c].upper[k]; }
       const Node2& ch = t.nodes[nd.child[c]];
@@ -53,6 +71,37 @@ DTree append_binary(const Tree2& t, LayoutOut& out) {
     d.root = remap[t.root];
   }
   return d;
+}
+}  // namespace
+
+DTree append_binary(const Tree2& t, LayoutOut& out) {
+  if (t.root < 0) return DTree{-1, 0, 0, 0};
+  const int node_base = int(out.nodes2.size()), leaf_base = int(out.leaf_prims.size());
+  out.nodes2.resize(size_t(node_base) + count_internal(t));
+  out.leaf_prims.resize(size_t(leaf_base) + t.leaf_prims.size());
+  return fill_binary(t, node_base, leaf_base, out.nodes2.data(), out.leaf_prims.data());
+}
+
+std::vector<DTree> append_binary_many(const std::vector<const Tree2*>& trees, LayoutOut& out, int threads) {
+  const size_t n = trees.size();
+  std::vector<int> n_internal(n, 0);
+  parallel_for_index(n, threads, [&](size_t i) { if (trees[i]->root >= 0) n_internal[i] = count_internal(*trees[i]); });
+  std::vector<int> node_base(n), leaf_base(n);
+  size_t nodes = out.nodes2.size(), leaves = out.leaf_prims.size();
+  for (size_t i = 0; i < n; i++) {
+    node_base[i] = int(nodes);
+    leaf_base[i] = int(leaves);
+    if (trees[i]->root < 0) continue;
+    nodes += size_t(n_internal[i]);
+    leaves += trees[i]->leaf_prims.size();
+  }
+  out.nodes2.resize(nodes);
+  out.leaf_prims.resize(leaves);
+  std::vector<DTree> roots(n, DTree{-1, 0, 0, 0});
+  parallel_for_index(n, threads, [&](size_t i) {
+    roots[i] = fill_binary(*trees[i], node_base[i], leaf_base[i], out.nodes2.data(), out.leaf_prims.data());
+  });
+  return roots;
 }
 
 namespace {
@@ -71,8 +120,8 @@ struct Slot {
 };
 
 struct Frag {
-  std::vector<DNode8> nodes;
-  std::vector<DPrim> prims;
+  raw_vector<DNode8> nodes;
+  raw_vector<DPrim> prims;
 };
 
 struct Wide {
@@ -224,7 +273,7 @@ struct Wide {
     }
   }
 
-  void emit_prims(const Handle& h, std::vector<DPrim>& prims) const {
+  void emit_prims(const Handle& h, raw_vector<DPrim>& prims) const {
     if (h.kind == H_SHAPE) {
       const DTopPrim& tp = (*in.top_prims)[h.node];
       DPrim d;
@@ -276,7 +325,7 @@ struct Wide {
 
   // Builds the wide node for `slots` (collapsed already) into `node`; appends terminals to `prims`
   // and the handles of its internal children, in child order, to `kids`.
-  void make_node(std::vector<Slot>& slots, DNode8& node, std::vector<DPrim>& prims,
+  void make_node(std::vector<Slot>& slots, DNode8& node, raw_vector<DPrim>& prims,
                  std::vector<Handle>& kids, uint32_t child_base) const {
     const int n = int(slots.size());
     Box3 bounds;
@@ -402,11 +451,19 @@ struct Wide {
 }  // namespace
 
 void build_wide(const WideInput& in, LayoutOut& out, int threads) {
+  const bool verbose = std::getenv("PB2_VERBOSE") != nullptr;
+  auto t0 = std::chrono::steady_clock::now();
+  auto stage = [&](const char* name) {
+    if (verbose)
+      fprintf(stderr, "[build_wide] %-24s +%.1f ms\n", name,
+              std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+  };
   out.nodes8.clear();
   out.leaves.clear();
   out.wide_prims.clear();
   const Tree2& top = *in.top;
   if (top.root < 0) return;
+  threads = std::max(1, threads);
   Wide w{in};
   w.mark_unbounded();
   auto push_gate = [&](const Box3& b) {
@@ -438,14 +495,34 @@ void build_wide(const WideInput& in, LayoutOut& out, int threads) {
       w.tree_mesh[k] = tp.index;
       w.tree_geom[k] = tp.geom;
     }
+  // the mesh trees' gates: sizes by prefix sum, then every tree fills its own range of `leaves` in parallel
   w.mesh_leaf_gate.resize(n_trees);
-  for (size_t k = 0; k < n_trees; k++) {
-    const Tree2& t = (*in.mesh_trees)[k];
-    w.mesh_leaf_gate[k].assign(t.nodes.size(), -1);
-    for (size_t i = 0; i < t.nodes.size(); i++)
-      if (t.nodes[i].leaf_count && int(i) != t.root) w.mesh_leaf_gate[k][i] = push_gate(t.nodes[i].box[0]);
+  {
+    std::vector<size_t> first(n_trees + 1, out.leaves.size());
+    parallel_for_index(n_trees, threads, [&](size_t k) {
+      const Tree2& t = (*in.mesh_trees)[k];
+      size_t n = 0;
+      for (size_t i = 0; i < t.nodes.size(); i++) n += t.nodes[i].leaf_count && int(i) != t.root;
+      first[k + 1] = n;
+    });
+    for (size_t k = 0; k < n_trees; k++) first[k + 1] += first[k];
+    out.leaves.resize(first[n_trees]);
+    parallel_for_index(n_trees, threads, [&](size_t k) {
+      const Tree2& t = (*in.mesh_trees)[k];
+      w.mesh_leaf_gate[k].assign(t.nodes.size(), -1);
+      size_t at = first[k];
+      for (size_t i = 0; i < t.nodes.size(); i++)
+        if (t.nodes[i].leaf_count && int(i) != t.root) {
+          const Box3& b = t.nodes[i].box[0];
+          DLeaf& L = out.leaves[at];
+          for (int c = 0; c < 3; c++) { L.box[c] = b.lower[c]; L.box[3 + c] = b.upper[c]; }
+          L.pad[0] = L.pad[1] = 0;
+          w.mesh_leaf_gate[k][i] = int(at++);
+        }
+    });
   }
 
+  stage("gates");
   Handle root;
   const Node2& rn = top.nodes[top.root];
   if (rn.leaf_count) {
@@ -457,10 +534,10 @@ void build_wide(const WideInput& in, LayoutOut& out, int threads) {
   }
 
   // top part sequentially (breadth first), then one fragment per pending node in parallel
-  threads = std::max(1, threads);
   Frag head;
   std::vector<std::pair<Handle, uint32_t>> pending;
   w.build_fragment(root, head, threads > 1 ? size_t(threads) * 8 : 0, &pending);
+  stage("head fragment");
   std::vector<Frag> frags(pending.size());
   if (!pending.empty()) {
     std::atomic<size_t> next{0};
@@ -472,27 +549,34 @@ void build_wide(const WideInput& in, LayoutOut& out, int threads) {
     work();
     for (auto& th : pool) th.join();
   }
-  size_t total_nodes = head.nodes.size(), total_prims = head.prims.size();
-  for (auto& f : frags) { total_nodes += f.nodes.size() - 1; total_prims += f.prims.size(); }
+  stage("fragments");
+  // merge: fragment i's nodes 1.. land at node_base[i] .. (node 0 fills the slot reserved for it in the head
+  // part), its primitives at prim_base[i]; offsets by prefix sum, copies in parallel
+  std::vector<size_t> node_base(frags.size() + 1), prim_base(frags.size() + 1);
+  node_base[0] = head.nodes.size();
+  prim_base[0] = head.prims.size();
+  for (size_t i = 0; i < frags.size(); i++) {
+    node_base[i + 1] = node_base[i] + frags[i].nodes.size() - 1;
+    prim_base[i + 1] = prim_base[i] + frags[i].prims.size();
+  }
   out.nodes8 = std::move(head.nodes);
   out.wide_prims = std::move(head.prims);
-  out.nodes8.reserve(total_nodes);
-  out.wide_prims.reserve(total_prims);
-  for (size_t i = 0; i < frags.size(); i++) {
+  out.nodes8.resize(node_base[frags.size()]);
+  out.wide_prims.resize(prim_base[frags.size()]);
+  parallel_for_index(frags.size(), threads, [&](size_t i) {
     Frag& f = frags[i];
-    // local node j >= 1 lands at node_base + j - 1; local node 0 fills the slot reserved for it
-    const uint32_t node_base = uint32_t(out.nodes8.size()), prim_base = uint32_t(out.wide_prims.size());
     for (size_t j = 0; j < f.nodes.size(); j++) {
       DNode8 nd = f.nodes[j];
-      nd.child_base += node_base - 1;
-      nd.prim_base += prim_base;
+      nd.child_base += uint32_t(node_base[i]) - 1;
+      nd.prim_base += uint32_t(prim_base[i]);  // the kNoCullBit in the top bit is untouched: bases stay below 2^31
       if (j == 0) out.nodes8[pending[i].second] = nd;
-      else out.nodes8.push_back(nd);
+      else out.nodes8[node_base[i] + j - 1] = nd;
     }
-    out.wide_prims.insert(out.wide_prims.end(), f.prims.begin(), f.prims.end());
+    if (!f.prims.empty()) std::memcpy(&out.wide_prims[prim_base[i]], f.prims.data(), f.prims.size() * sizeof(DPrim));
     Frag().nodes.swap(f.nodes);
     Frag().prims.swap(f.prims);
-  }
+  });
+  stage("merge");
 }
 
 }  // namespace pb2

@@ -274,9 +274,16 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
 
   // ---- device layouts ----
   LayoutOut& lay = H.lay;
-  DTree top_tree = append_binary(ctx->top_tree, lay);
-  for (uint32_t k = 0; k < sd->n_meshes; k++)
-    if (mesh_tree_of[k] >= 0) H.meshes[k].tree = append_binary(ctx->mesh_trees[mesh_tree_of[k]], lay);
+  DTree top_tree;
+  {
+    std::vector<const Tree2*> trees{&ctx->top_tree};
+    std::vector<uint32_t> mesh_of_entry;
+    for (uint32_t k = 0; k < sd->n_meshes; k++)
+      if (mesh_tree_of[k] >= 0) { trees.push_back(&ctx->mesh_trees[mesh_tree_of[k]]); mesh_of_entry.push_back(k); }
+    const std::vector<DTree> roots = append_binary_many(trees, lay, n_threads);
+    top_tree = roots[0];
+    for (size_t i = 0; i < mesh_of_entry.size(); i++) H.meshes[mesh_of_entry[i]].tree = roots[i + 1];
+  }
   stage("top tree + binary layout");
   WideInput wi;
   wi.top = &ctx->top_tree; wi.top_prims = &H.top_prims; wi.top_boxes = &top_boxes;

@@ -281,6 +281,13 @@ class Backend:
         A.check(self.L.pb2_test_primary_rays(self.h, si, rays.ctypes.data))
         return rays
 
+    def measure_read_gbs(self, nbytes, iters):
+        """Sustained device read bandwidth in GB/s of an `nbytes` buffer read `iters` times (L1 bypassed):
+        nbytes well below the 126 MB L2 measures the L2, far above it the HBM."""
+        g = C.c_double()
+        A.check(self.L.pb2_measure_read_gbs(self.h, nbytes, iters, C.byref(g)))
+        return g.value
+
     def counters(self):
         c = A.Counters()
         A.check(self.L.pb2_get_counters(self.h, C.byref(c)))

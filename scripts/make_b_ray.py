@@ -5,10 +5,11 @@
 with n_node = binary BVH nodes visited and the primitive tests made by the REFERENCE traversal
 (BVHImpl::Intersect / ::hit, bvh.cpp:321-451), counted by the oracle port (oracle/oracle_port.cpp,
 pinned against the compiled reference by tests/test_oracle.py) on a sample of the workload's own
-rays: camera rays of sample 0 on a pixel grid, plus one cosine-free random bounce ray and one
-shadow-length ray from each hit point. Writes profiles/b_ray.json, which bench.py reads.
-
-    python scripts/make_b_ray.py [workload ...]        (CPU only; C5 takes a few minutes)
+rays. With a CUDA device (the GPU box: `python scripts/make_b_ray.py --recorded [workload ...]`) the rays are
+the ones a production render of the workload actually traces -- every closest-hit and shadow ray of all depths
+of a reduced-film, 1-spp recorded render (pb2_set_ray_record), so the depth mix is the render's own. Without
+one: camera rays of sample 0 on a pixel grid, plus one random bounce ray and one shadow-length ray from each
+hit point (round 1's method). Writes profiles/b_ray.json, which bench.py reads.
 """
 import ctypes as C
 import json
@@ -78,13 +79,55 @@ def one(workload):
     return {k: (float(v) if isinstance(v, (np.floating, np.integer)) else v) for k, v in e.items()}
 
 
+def recorded(workload, max_rays=1_500_000):
+    """B_ray from the rays of a recorded production render at a reduced film size (same camera, same depth)."""
+    S = pb.Scene()
+    cfg = bench.build_scene(S, workload)
+    w, h = S.size
+    depth = cfg["depth"]
+    scale = max(1, int(np.ceil(np.sqrt(w * h * (2 * depth - 1) / max_rays))))
+    fn, kw, _ = bench.WORKLOADS[workload]
+    kw = dict(kw, size=(max(16, w // scale), max(16, h // scale)))
+    from pine_b200 import scenes
+    S = pb.Scene()
+    scenes.SCENES[fn](S, **kw)
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    _, rec = B.render_recorded(1, depth, accel=0)
+    B.close()
+    t0 = time.time()
+    P = port.PortScene(S)
+    build_s = time.time() - t0
+    P.trace_closest(rec["closest_rays"])
+    tc = totals()
+    P.trace_any(rec["shadow_rays"])
+    ta = totals()
+    n_c, n_s = len(rec["closest_rays"]), max(len(rec["shadow_rays"]), 1)
+    return {
+        "ray_source": f"every ray of a recorded 1-spp production render at {kw['size'][0]}x{kw['size'][1]}, depth {depth} "
+                      f"({n_c} closest-hit + {n_s} shadow rays, all depths)",
+        "rays_sampled": {"closest": n_c, "shadow": n_s, "camera_share_of_closest": kw["size"][0] * kw["size"][1] / n_c},
+        "closest": {"nodes_per_ray": tc[0] / n_c, "prim_tests_per_ray": tc[1] / n_c, "prim_bytes_per_ray": tc[2] / n_c},
+        "shadow": {"nodes_per_ray": ta[0] / n_s, "prim_tests_per_ray": ta[1] / n_s, "prim_bytes_per_ray": ta[2] / n_s},
+        "b_ray_closest": float(32 + 16 + 56 * tc[0] / n_c + tc[2] / n_c),
+        "b_ray_shadow": float(32 + 4 + 56 * ta[0] / n_s + ta[2] / n_s),
+        "oracle_build_s": build_s,
+    }
+
+
 def main():
-    names = sys.argv[1:] or ["c1", "c3", "c4", "c5"]
+    argv = [a for a in sys.argv[1:] if a != "--recorded"]
+    use_recorded = "--recorded" in sys.argv[1:]
+    global OUT
+    if os.environ.get("PB2_B_RAY_OUT"):
+        OUT = os.environ["PB2_B_RAY_OUT"]
+    names = argv or ["c1", "c3", "c4", "c4_field", "c5"]
     out = json.load(open(OUT)) if os.path.exists(OUT) else {}
     for n in names:
-        e = one(n)
+        e = recorded(n) if use_recorded else one(n)
+        e = json.loads(json.dumps(e, default=float))
         old = out.get(n, {})
-        for keep in ("ncu_dram_bytes_per_launch",):
+        for keep in ("ncu_dram_bytes_per_launch", "ncu_source"):
             if keep in old:
                 e[keep] = old[keep]
         out[n] = e
