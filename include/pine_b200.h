@@ -273,6 +273,11 @@ int pb2_render_device(pb2_context* ctx, const pb2_render_params* params, void* c
  * tone-map, gamma 1/2.2, *256 clamp, optional y-flip. rgba8_host: width*height*4 bytes. */
 int pb2_film_finalize(pb2_context* ctx, const float* film_rgba_host, int flip_y,
                       uint8_t* rgba8_host, float* tonemapped_rgba_host);
+/* The same epilogue on the film the last pb2_render* LEFT ON THE DEVICE: no upload, and 4 bytes per pixel come
+ * back instead of 16 (what Film::save needs: save_film_as_image, film.cpp:12-15). tonemapper: 0 Uncharted2,
+ * 1 ACES, -1 the uploaded camera's. Either output may be NULL. */
+int pb2_film_finalize_device(pb2_context* ctx, int tonemapper, int flip_y, uint8_t* rgba8_host,
+                             float* tonemapped_rgba_host);
 /* Test hooks == Accel::intersect / Accel::hit (accel.h:16-24) on a caller ray set.
  * rays: n x {o.xyz, d.xyz, tmin, tmax}. geom/prim = -1 on miss, t = ray.tmax after traversal.
  * surf (optional, n x 8) = p, n, uv from compute_surface_info. accel as in pb2_render_params. */
@@ -349,6 +354,9 @@ int pb2_multi_upload_scene(pb2_multi* m, const pb2_scene_desc* scene);
 int pb2_multi_restage_scene(pb2_multi* m);
 /* pb2_render over all devices; film_rgba_host as in pb2_render. Blocking. */
 int pb2_multi_render(pb2_multi* m, const pb2_render_params* params, int shard_mode, float* film_rgba_host);
+/* pb2_film_finalize_device on the reduced film (first device) of the last pb2_multi_render. */
+int pb2_multi_film_finalize(pb2_multi* m, int tonemapper, int flip_y, uint8_t* rgba8_host,
+                            float* tonemapped_rgba_host);
 /* Counters summed over the devices (last_render_ms: the slowest device's); optional host wall times of the
  * last film reduce and the last staging, in ms. */
 int pb2_multi_get_counters(pb2_multi* m, pb2_counters* out, double* reduce_ms, double* stage_ms);

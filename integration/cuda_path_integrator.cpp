@@ -7,9 +7,18 @@
 // parameters are Node graphs (node.h:46-103); the CUDA path takes constants, so every parameter is
 // evaluated at several unrelated NodeEvalCtx points and the scene is rejected (SEVERE, like the
 // reference's own argument checks, log.h:44-49) when the values differ -- there is no CPU fallback.
+// Image-node material parameters (what scene_from_gltf builds for baseColorTexture / metallicRoughnessTexture,
+// fileio.cpp:285-292) have to be recognised structurally, and Mnode<T>::value, NodeImage::{p, image} and
+// NodeComponent::{x, n} are private (node.h:69-70, 102-103, 181-193, 236-243). A maintainer adds two accessors
+// (INTEGRATION.md section 2); this file, which must compile against the UNMODIFIED headers, opens `private`
+// around node.h only -- access specifiers do not change the layout.
+#define private public
+#include <pine/core/node.h>
+#undef private
 #include "cuda_path_integrator.h"
 
 #include <pine/core/scene.h>
+#include <pine/core/image.h>
 #include <pine/core/log.h>
 
 #include <cstdlib>
@@ -59,7 +68,13 @@ auto constant_of(const N& node, const char* what) {
 }
 void put3(float* dst, vec3 v) { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
 
-pb2_material flatten_material(const Material& m) {
+struct Flat;
+// NodeImage(NodeUV(), image) (node.cpp:20-23) over an 8-bit RGBA image -> 1-based pb2_texture index; 0 if
+// `node` is not an image node. Any other non-constant node is rejected by constant_of afterwards.
+int32_t image_texture(Flat& f, const Node3f& node);
+int32_t component_texture(Flat& f, const Nodef& node, int component, const char* what);
+
+pb2_material flatten_material(Flat& f, const Material& m) {
   pb2_material o{};
   o.ior = 1.4f;
   if (m.is<EmissiveMaterial>()) {
@@ -88,9 +103,13 @@ pb2_material flatten_material(const Material& m) {
   } else if (m.is<UberMaterial>()) {
     auto& x = m.as<UberMaterial>();
     o.kind = PB2_MAT_UBER;
-    put3(o.color, constant_of(x.albedo, "Uber.albedo"));
-    o.roughness = constant_of(x.roughness, "Uber.roughness");
-    o.metallic = constant_of(x.metallic, "Uber.metallic");
+    // image nodes become device textures; the constants they replace are unused (render.cu material_bxdf)
+    o.color_texture = image_texture(f, x.albedo);
+    o.roughness_texture = component_texture(f, x.roughness, 1, "Uber.roughness");
+    o.metallic_texture = component_texture(f, x.metallic, 2, "Uber.metallic");
+    if (!o.color_texture) put3(o.color, constant_of(x.albedo, "Uber.albedo"));
+    if (!o.roughness_texture) o.roughness = constant_of(x.roughness, "Uber.roughness");
+    if (!o.metallic_texture) o.metallic = constant_of(x.metallic, "Uber.metallic");
     o.transmission = constant_of(x.transmission, "Uber.transmission");
     o.ior = x.ior;
   } else {
@@ -118,8 +137,40 @@ struct Flat {
   std::vector<pb2_mesh> meshes;
   std::vector<int32_t> lights;
   std::vector<pb2_light> light_records;
+  std::vector<pb2_texture> textures;
+  std::vector<const Image*> texture_keys;
   pb2_scene_desc desc{};
 };
+
+int32_t image_texture(Flat& f, const Node3f& node) {
+  if (!node.value->is<NodeImage>()) return 0;
+  const NodeImage& ni = node.value->as<NodeImage>();
+  if (!ni.p.value->is<NodeUV>())
+    SEVERE("[CudaPathIntegrator]image nodes are supported with UV coordinates only (NodeImage(NodeUV(), image))");
+  const Image* img = ni.image.get();
+  if (!img || !img->is<Array2d<vec4u8>>())
+    SEVERE("[CudaPathIntegrator]image nodes need an 8-bit RGBA image (what scene_from_gltf loads)");
+  for (size_t i = 0; i < f.texture_keys.size(); i++)
+    if (f.texture_keys[i] == img) return int32_t(i) + 1;
+  const auto& px = img->as<Array2d<vec4u8>>();
+  pb2_texture t{};
+  t.rgba = reinterpret_cast<const uint8_t*>(px.data());
+  t.width = px.size().x;
+  t.height = px.size().y;
+  f.texture_keys.push_back(img);
+  f.textures.push_back(t);
+  return int32_t(f.textures.size());
+}
+int32_t component_texture(Flat& f, const Nodef& node, int component, const char* what) {
+  if (!node.value->is<NodeComponent>()) return 0;
+  const NodeComponent& nc = node.value->as<NodeComponent>();
+  const int32_t t = image_texture(f, nc.x);
+  if (!t) return 0;  // a component of something else: constant_of decides
+  if (nc.n != component)
+    SEVERE("[CudaPathIntegrator]`", what, "` reads component ", nc.n, " of an image; the CUDA path binds "
+           "roughness to G and metallic to B as scene_from_gltf does (fileio.cpp:288-291)");
+  return t;
+}
 
 template <typename T, typename S>
 int32_t push(std::vector<T>& v, const S& s) {
@@ -142,7 +193,7 @@ void flatten(Scene& scene, Flat& f) {
     while (mi < f.material_keys.size() && f.material_keys[mi] != key) mi++;
     if (mi == f.material_keys.size()) {
       f.material_keys.push_back(key);
-      f.materials.push_back(flatten_material(*key));
+      f.materials.push_back(flatten_material(f, *key));
     }
     rec.material = int32_t(mi);
     const Shape& s = g.shape;
@@ -237,6 +288,7 @@ void flatten(Scene& scene, Flat& f) {
   d.disks = f.disks.data();           d.n_disks = uint32_t(f.disks.size());
   d.meshes = f.meshes.data();         d.n_meshes = uint32_t(f.meshes.size());
   d.light_geometries = f.lights.data(); d.n_lights = uint32_t(f.lights.size());
+  d.textures = f.textures.data();     d.n_textures = uint32_t(f.textures.size());
   if (!only_area) { d.light_records = f.light_records.data(); d.n_light_records = uint32_t(f.light_records.size()); }
 }
 
@@ -300,6 +352,20 @@ void CudaPathIntegrator::render(Scene& scene) {
   last_shadow_ = c.last_shadow_rays;
   launches_ = c.kernel_launches;
   last_ms_ = c.last_render_ms;
+}
+
+void CudaPathIntegrator::finalize_rgba8(const Film& film, unsigned char* rgba8, bool flip_y) {
+  if (!multi_) SEVERE("[CudaPathIntegrator]finalize_rgba8 needs a render() first");
+  // Film keeps its ToneMapper private; a copy carries it. Shrink the copy to one probe pixel, let the reference
+  // finalize it, and see which operator it applied.
+  Film probe = film;
+  probe.pixels = Array2d<vec4>(vec2i(1, 1));
+  probe[vec2i(0, 0)] = vec4(0.5f, 1.0f, 4.0f, 1.0f);
+  probe.finalize();
+  const vec3 u2 = Uncharted2ToneMapper()(vec3(0.5f, 1.0f, 4.0f));
+  const vec4 got = probe[vec2i(0, 0)];
+  const int tonemapper = (got.x == u2.x && got.y == u2.y && got.z == u2.z) ? 0 : 1;
+  check(pb2_multi_film_finalize(multi_, tonemapper, flip_y ? 1 : 0, rgba8, nullptr), "pb2_multi_film_finalize");
 }
 
 }  // namespace pine

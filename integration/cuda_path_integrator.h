@@ -34,6 +34,12 @@ class CudaPathIntegrator : public Integrator {
 
   void render(Scene& scene) override;
 
+  // Film::save's epilogue on the GPU (save_film_as_image, film.cpp:12-15: Film::finalize + gamma 1/2.2, x256,
+  // clamp, optional y-flip, fileio.cpp:42-54) applied to the film the last render() left on the device, so only
+  // 4 bytes per pixel cross PCIe. rgba8: width * height * 4 bytes. The tone mapper is read from `film` (it is
+  // private there: a one-pixel copy of the Film is finalized on the host and compared with Uncharted2's value).
+  void finalize_rgba8(const Film& film, unsigned char* rgba8, bool flip_y = true);
+
   // Which CUDA devices to use -- not part of the reference interface. Default: EVERY visible device (the scene
   // is replicated, interleaved 16-row bands of the film are dealt to the GPUs and ONE ncclReduce assembles the
   // film: bit-identical to a single-GPU render). set_device(d) pins the render to one device.

@@ -30,6 +30,8 @@ def shim():
         S = C.CDLL(SHIM_PATH)
         S.ref_render_cuda_kind.restype = C.c_double
         S.ref_render_cuda_kind.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        S.ref_render_cuda_rgba8.restype = C.c_double
+        S.ref_render_cuda_rgba8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         _shim = S
     return _shim
 
@@ -226,6 +228,15 @@ class RefScene:
         mean = s1 / spp
         var = np.maximum(s2 / spp - mean ** 2, 0.0) * (spp / max(spp - 1, 1))
         return film, mean, np.sqrt(var / spp)
+
+    def render_cuda_rgba8(self, spp, depth, device=0):
+        """pine::CudaPathIntegrator::render + ::finalize_rgba8 (the device epilogue of Film::save) on THIS scene
+        -> (film float32, rgba8 uint8 [h, w, 4], y-flipped)."""
+        w, h = self.size
+        film = np.zeros((h, w, 4), np.float32)
+        rgba8 = np.zeros((h, w, 4), np.uint8)
+        shim().ref_render_cuda_rgba8(self.h, spp, depth, device, film.ctypes.data, rgba8.ctypes.data)
+        return film, rgba8
 
     def bounded_prepare(self, spp, depth):
         """RTIntegrator::render prologue (sampler clones, BVH::build, light list) of a

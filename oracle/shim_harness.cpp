@@ -49,6 +49,20 @@ double ref_render_cuda_kind(void* h, int sampler_kind, int spp, int depth, int d
   }
   return std::chrono::duration<double>(t1 - t0).count();
 }
+// render through the shim, then the shim's device epilogue: rgba8 = w * h * 4 bytes, y-flipped like
+// save_film_as_image (film.cpp:12-15)
+double ref_render_cuda_rgba8(void* h, int spp, int depth, int device, float* film_rgba, unsigned char* rgba8) {
+  Scene& scene = *(Scene*)ref_scene_ptr(h);
+  auto integrator = CudaPathIntegrator(Accel(BVH()), Sampler(BlueSobolSampler(spp)), LightSampler(UniformLightSampler()), depth);
+  if (device >= 0) integrator.set_device(device);
+  auto t0 = std::chrono::steady_clock::now();
+  integrator.render(scene);
+  auto& film = scene.camera.film();
+  integrator.finalize_rgba8(film, rgba8, true);
+  auto t1 = std::chrono::steady_clock::now();
+  if (film_rgba) std::memcpy(film_rgba, film.data(), sizeof(float) * 4 * size_t(film.width()) * film.height());
+  return std::chrono::duration<double>(t1 - t0).count();
+}
 double ref_render_cuda(void* h, int spp, int depth, int device, float* film_rgba, double* stats) {
   return ref_render_cuda_kind(h, 0, spp, depth, device, film_rgba, stats);
 }

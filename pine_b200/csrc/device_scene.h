@@ -105,6 +105,8 @@ struct DScene {
   const DPrim* wide_prims;
   const int32_t* leaf_prims;
   const DBoxShape* box_shapes;
+  int32_t n_nodes8;             // nodes in nodes8
+  float node_origin_absmax[3];  // max |DNode8::origin| per axis: bounds |origin * inv| per ray (traverse.cuh WideRay::err)
   int32_t n_box_shapes;     // > kMaxBoxShapes: any-hit walks the reference-order tree instead
   int32_t wide_ready;       // 1: nodes8/wide_prims hold a tree (root = node 0)
   int32_t order_dependent;  // 1: more than kMaxBoxShapes AABB/OBB shapes, whose closest-hit result

@@ -327,6 +327,13 @@ extern "C" int pb2_multi_render(pb2_multi* m, const pb2_render_params* p, int sh
   return PB2_OK;
 }
 
+extern "C" int pb2_multi_film_finalize(pb2_multi* m, int tonemapper, int flip_y, uint8_t* rgba8_host,
+                                       float* tonemapped_rgba_host) {
+  if (!m || !m->scene_ready) { set_error("pb2_multi_upload_scene has not succeeded"); return PB2_E_STATE; }
+  // after pb2_multi_render the first device holds the reduced film
+  return pb2_film_finalize_device(m->ctx[0], tonemapper, flip_y, rgba8_host, tonemapped_rgba_host);
+}
+
 extern "C" int pb2_multi_get_counters(pb2_multi* m, pb2_counters* out, double* reduce_ms, double* stage_ms) {
   if (!m || !out) { set_error("null argument"); return PB2_E_INVALID; }
   *out = m->ctx[0]->counters;

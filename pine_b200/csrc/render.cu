@@ -1195,6 +1195,31 @@ extern "C" int pb2_film_finalize(pb2_context* ctx, const float* film_rgba_host, 
   return PB2_OK;
 }
 
+// The same epilogue on the film the last render LEFT ON THE DEVICE (after the multi-GPU reduce: the first
+// device's film): nothing is uploaded, and 4 bytes per pixel come back instead of 16.
+extern "C" int pb2_film_finalize_device(pb2_context* ctx, int tonemapper, int flip_y, uint8_t* rgba8_host,
+                                        float* tonemapped_rgba_host) {
+  if (!ctx || ctx->device < 0 || !ctx->scene_ready) { set_error("no device scene"); return PB2_E_STATE; }
+  const int W = ctx->scene.camera.width, H = ctx->scene.camera.height;
+  const size_t n = size_t(W) * H;
+  if (!ctx->film.ptr || ctx->film_pixels != n) { set_error("no film on the device: render first"); return PB2_E_STATE; }
+  if (tonemapper < 0) tonemapper = ctx->scene.camera.tonemapper;
+  if (tonemapper > 1) { set_error("unknown tone mapper"); return PB2_E_INVALID; }
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  const size_t q_bytes = ((n * 4 + 15) / 16) * 16;  // RGBA8 first, then (optionally) the tone-mapped float film
+  PB2_CUDA_CHECK(ctx->film_accum.reserve(q_bytes + (tonemapped_rgba_host ? n * 16 : 0)));
+  uchar4* q = ctx->film_accum.as<uchar4>();
+  float4* mapped = tonemapped_rgba_host ? reinterpret_cast<float4*>(static_cast<char*>(ctx->film_accum.ptr) + q_bytes) : nullptr;
+  k_finalize<<<kNumSMs * 4, 256, 0, ctx->stream>>>(ctx->film.as<float4>(), W, H, tonemapper, flip_y, mapped, q);
+  ctx->counters.kernel_launches++;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  if (rgba8_host) PB2_CUDA_CHECK(cudaMemcpyAsync(rgba8_host, q, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (tonemapped_rgba_host)
+    PB2_CUDA_CHECK(cudaMemcpyAsync(tonemapped_rgba_host, mapped, n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  return PB2_OK;
+}
+
 extern "C" int pb2_test_sampler(pb2_context* ctx, int spp, int px, int py, int sample_index, int n_rand,
                                 float* out_rand, const char* pattern, int n_samples, float* out_draws) {
   if (!ctx || ctx->device < 0) { set_error("no CUDA device, and there is no CPU fallback"); return PB2_E_CUDA; }

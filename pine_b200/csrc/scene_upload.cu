@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -27,6 +28,22 @@ void parallel_jobs(size_t n, int threads, F&& fn) {
   work();
   for (auto& th : pool) th.join();
 }
+
+// Height of a binary tree in internal nodes along the longest root-to-leaf path: the deepest the reference-order
+// walk's stack can get (it holds at most one deferred sibling per internal node on the current path). The
+// builder numbers nodes in post-order, children before their parent.
+int tree_height(const Tree2& t) {
+  std::vector<int> h(t.nodes.size(), 0);
+  int best = 0;
+  for (size_t i = 0; i < t.nodes.size(); i++) {
+    const Node2& nd = t.nodes[i];
+    if (nd.leaf_count) continue;
+    h[i] = 1 + std::max(h[nd.child[0]], h[nd.child[1]]);
+    best = std::max(best, h[i]);
+  }
+  return best;
+}
+constexpr int kRefOrderStack = 64;  // traverse.cuh kStack
 
 bool valid_material(const pb2_material& m) {
   return m.kind >= PB2_MAT_EMISSIVE && m.kind <= PB2_MAT_SUBSURFACE;
@@ -228,6 +245,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     jobs.push_back(MeshJob{i, g.shape_index});
   }
   ctx->mesh_trees.resize(jobs.size());
+  std::atomic<int> max_height{0};
   // Small meshes: one job per mesh. Big meshes additionally split inside build_sah_binary.
   set_build_threads(jobs.size() >= size_t(n_threads) ? 1 : n_threads);
   parallel_jobs(jobs.size(), n_threads, [&](size_t j) {
@@ -240,6 +258,8 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
       prims[t].index = int(t);
     }
     build_sah_binary(std::move(prims), ctx->mesh_trees[j]);
+    int h = tree_height(ctx->mesh_trees[j]), seen = max_height.load();
+    while (h > seen && !max_height.compare_exchange_weak(seen, h)) {}
   });
   for (size_t j = 0; j < jobs.size(); j++) {
     BuildPrim tp;
@@ -271,6 +291,14 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   std::vector<Box3> top_boxes(top.size());
   for (size_t i = 0; i < top.size(); i++) top_boxes[i] = top[i].box;
   build_sah_binary(top, ctx->top_tree);
+  // The reference-order walk (verification path and certified fallback) keeps a 64-entry stack per tree level
+  // (the reference itself has 32 and undefined behaviour beyond, bvh.cpp:363): a deeper tree -- degenerate
+  // input such as thousands of coincident centroids -- is refused instead of being walked with dropped pushes.
+  if (std::max(max_height.load(), tree_height(ctx->top_tree)) > kRefOrderStack) {
+    set_error("a BVH is deeper than " + std::to_string(kRefOrderStack) +
+              " levels (degenerate geometry): the reference-order traversal stack would overflow");
+    return PB2_E_UNSUPPORTED;
+  }
 
   // ---- device layouts ----
   LayoutOut& lay = H.lay;
@@ -304,6 +332,10 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   for (int k = 0; k < 3; k++) s.env_color[k] = env_color[k];
   s.n_geoms = int32_t(sd->n_geometries);
   s.wide_ready = lay.nodes8.empty() ? 0 : 1;
+  s.n_nodes8 = int32_t(lay.nodes8.size());
+  for (int k = 0; k < 3; k++) s.node_origin_absmax[k] = 0.0f;
+  for (const DNode8& nd : lay.nodes8)
+    for (int k = 0; k < 3; k++) s.node_origin_absmax[k] = std::max(s.node_origin_absmax[k], std::fabs(nd.origin[k]));
   s.n_box_shapes = int32_t(lay.box_shapes.size());
   s.order_dependent = order_dependent ? 1 : 0;
   s.camera = sd->camera;

@@ -53,7 +53,8 @@ __device__ __forceinline__ void load_node(const DNode2* nodes, int idx, float (&
   count[0] = __float_as_int(a3.z); count[1] = __float_as_int(a3.w);
 }
 
-constexpr int kStack = 64;  // the reference uses 32 and has undefined behaviour beyond it
+constexpr int kStack = 64;  // the reference uses 32 and has undefined behaviour beyond it; pb2_upload_scene refuses
+                            // scenes with a deeper tree (scene_upload.cu kRefOrderStack), so no push is ever dropped
 
 // Generic reference-order walk. `leaf(prim_id)` returns true on an accepted hit; for closest-hit it
 // also shrinks ray.tmax; when ANY is set the walk returns at the first true.
@@ -187,6 +188,12 @@ __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) 
 //         every box shape is rejected at the ray's incoming tmax (shape test AND leaf gate) never
 //         has one accepted by the reference either: such rays take the wide walk with the box
 //         shapes left out, all others go to the reference-order walk (wide_persistent.cuh),
+//   (iii') of the rays a box shape COULD accept (probe at the incoming tmax), those whose winner among the other
+//         primitives lies in front of every such box in both measures the reference uses -- t < e, the slab
+//         entry it compares with tmax (local units for an OBB), and t < tb, the t the box would report -- keep
+//         the wide result: reached after the winner the box is refused (e > tmax), reached before it the box
+//         leaves tmax = tb behind the winner, which is then still found; origin-inside boxes, misses and boxes
+//         in front (or straddling: the scaled-OBB quirk) walk in reference order (wide_persistent.cuh),
 //   (iv)  every primitive the reference accepts is also tested here. For primitives that lie
 //         inside their leaf box this follows from box containment; a Cone does not (it is
 //         unbounded below its base, geometry.cpp:415-446) and can be hit BEFORE the ray enters its
@@ -216,14 +223,23 @@ __device__ __forceinline__ bool leaf_gate(const DLeaf* leaves, int leaf, const O
 }
 
 // Per-ray constants of the conservative child-box test. For axis k the exact plane q of a node is
-// P = origin + q * 2^e; the reference evaluates fl(fl(P * inv) - ood). We evaluate
-// fma(q, a, b -/+ delta) with a = 2^e * inv (exact), b = fl(fl(origin * inv) - ood) and
-// delta = 2^-21 * (|origin * inv| + 255 |a| + |ood|), which bounds the difference of the two
-// expressions (at most ~6 roundings of magnitude <= that sum), so near planes come out no larger
-// and far planes no smaller than the reference's value for any box inside the quantised one.
-// (q enters the fma as 2^15 + q with the bias folded into the constant, see byte_biased.)
+// P_q = origin + q * 2^e; for a box plane P inside the quantised box the reference evaluates
+// R = fl(fl(P * inv) - ood) (bbox.h:59-72), which is monotone in P. We evaluate
+//   t = fma(2^15 + q, a, base -/+ m),  a = 2^e * inv (exact),  base = fma(-2^15, a, fma(origin, inv, -ood))
+// (the bias 2^15 + q is what byte_biased builds with one PRMT). With u = 2^-24 and X = q a + origin inv - ood:
+//   t  = X -/+ m + e1,  |e1| <= u (|b| + |base| + |base -/+ m| + |t|)             (four roundings of ours)
+//   R_q = X + e2,       |e2| <= u (|P_q inv| + |R_q|)                               (two of the reference's)
+// and |b| <= |origin inv| + |ood|, |base| <= |b| + 2^15 |a|, |P_q inv| <= |origin inv| + 255 |a|, so
+//   |e1| + |e2| <= u (6 |origin inv| + 5 |ood| + 66301 |a| + 2 m).
+// m = 2^-21 (8447 |a|) + err with err >= 2^-21 (|origin inv| + |ood|), i.e. m >= u (8 |origin inv| + 8 |ood| +
+// 67576 |a|), exceeds that bound, so near planes come out no larger and far planes no smaller than the
+// reference's value for any box inside the quantised one. err depends on the node only through
+// |origin inv| <= absmax|origin| * |inv| and is therefore computed ONCE per ray (WideRay::err); the margin is
+// ~1e-6 of the ray's coordinate range, two orders below one quantisation step of a leaf-level node.
 struct WideRay {
   V3 inv, ood;
+  V3 err;            // 2^-21 (absmax |node origin| * |inv| + |ood|) per axis: the part of delta that does not
+                     // depend on the node (|origin * inv| <= absmax * |inv|), hoisted out of the node test
   uint32_t octinv4;  // (7 ^ octant) replicated into 4 bytes
   uint32_t neg;      // bit k: d[k] < 0
 };
@@ -255,11 +271,32 @@ __device__ __forceinline__ PrimRec load_prim(const DPrim* prims, uint32_t idx) {
 // `lim` culls by the current best t; nodes flagged kNoCullBit (an unbounded shape somewhere below,
 // see the header comment) are tested against `lim_nocull` = the ray's incoming tmax instead.
 constexpr uint32_t kNoCullBit = 0x80000000u;  // in DNode8::prim_base
+// PB2_SMEM_TOP = N (north_star: "node data staged through shared memory"): the first N nodes of the breadth-first
+// array -- the top levels -- are copied into shared memory by every block of the persistent kernels and read
+// from there. Measured on B200 (profiles/r2/s7_smem_variants.txt, two runs each, C5 / C4 Msamples/s):
+//   N = 0: 531 / 274    N = 9 (root + its children): 544 / 277    N = 73: 540 / 274    N = 201: 540 / 273
+//   N = 585 (four levels, 47 KB per block): 359 / 189 -- the copies (one per block, 8 per SM) cost more L1
+//   capacity and occupancy than the few lines the top levels take when the SM's blocks share them through L1.
+// Kept: N = 9 -- every ray starts at the root and nearly every ray visits several of its children, so these
+// are the node fetches with the most reuse and their latency is on every ray's critical path.
+#ifndef PB2_SMEM_TOP
+#define PB2_SMEM_TOP 9
+#endif
 __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx, const WideRay& w, float tmin,
                                                float lim, float lim_nocull, uint32_t& child_base,
-                                               uint32_t& prim_base, uint32_t& imask) {
+                                               uint32_t& prim_base, uint32_t& imask, const uint4* s_top = nullptr) {
   const uint4* p = reinterpret_cast<const uint4*>(nodes + idx);
+#if PB2_SMEM_TOP > 0
+  uint4 n0, n1, n2, n3, n4;
+  if (idx < uint32_t(PB2_SMEM_TOP)) {
+    const uint4* q = s_top + idx * 5u;
+    n0 = q[0]; n1 = q[1]; n2 = q[2]; n3 = q[3]; n4 = q[4];
+  } else {
+    n0 = __ldg(p); n1 = __ldg(p + 1); n2 = __ldg(p + 2); n3 = __ldg(p + 3); n4 = __ldg(p + 4);
+  }
+#else
   const uint4 n0 = __ldg(p), n1 = __ldg(p + 1), n2 = __ldg(p + 2), n3 = __ldg(p + 3), n4 = __ldg(p + 4);
+#endif
   const float ox = __uint_as_float(n0.x), oy = __uint_as_float(n0.y), oz = __uint_as_float(n0.z);
   const float ax = __uint_as_float((n0.w & 0xffu) << 23) * w.inv.x;
   const float ay = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * w.inv.y;
@@ -268,17 +305,17 @@ __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx
   child_base = n1.x;
   prim_base = n1.y & ~kNoCullBit;
   if (n1.y & kNoCullBit) lim = lim_nocull;
-  const float ux = ox * w.inv.x, uy = oy * w.inv.y, uz = oz * w.inv.z;
-  // fma(2^15 + q, a, (b -/+ delta) - 2^15 a) == q a + b -/+ delta up to ONE more rounding, of a value
-  // no larger than |b| + delta + 2^15 |a|, so delta grows by 2^-23 * 2^15 |a| = 2^-21 * 2^13 |a|
-  // (0.4% of a quantisation step): 255 |a| + 8192 |a| below.
-  const float ex = (fabsf(ux) + 8447.0f * fabsf(ax) + fabsf(w.ood.x)) * 4.76837158203125e-7f;
-  const float ey = (fabsf(uy) + 8447.0f * fabsf(ay) + fabsf(w.ood.y)) * 4.76837158203125e-7f;
-  const float ez = (fabsf(uz) + 8447.0f * fabsf(az) + fabsf(w.ood.z)) * 4.76837158203125e-7f;
-  const float bx = ux - w.ood.x, by = uy - w.ood.y, bz = uz - w.ood.z;
-  const float sx = kByteBias * ax, sy = kByteBias * ay, sz = kByteBias * az;  // exact (power of two)
-  const float bnx = (bx - ex) - sx, bfx = (bx + ex) - sx, bny = (by - ey) - sy, bfy = (by + ey) - sy,
-              bnz = (bz - ez) - sz, bfz = (bz + ez) - sz;
+  // b = origin * inv - ood with ONE rounding (the reference's fl(fl(P inv) - ood) has two, and delta below
+  // bounds the distance of both expressions from the exact value), then the byte bias: base = b - 2^15 a.
+  // delta = w.err + 2^-21 * 8447 |a| (see the derivation above; w.err >= 2^-21 (|origin inv| + |ood|)), and
+  // the whole margin is ONE fma per axis because its node-independent part is per ray.
+  const float mx = __fmaf_rn(fabsf(ax), 8447.0f * 4.76837158203125e-7f, w.err.x);
+  const float my = __fmaf_rn(fabsf(ay), 8447.0f * 4.76837158203125e-7f, w.err.y);
+  const float mz = __fmaf_rn(fabsf(az), 8447.0f * 4.76837158203125e-7f, w.err.z);
+  const float basex = __fmaf_rn(-kByteBias, ax, __fmaf_rn(ox, w.inv.x, -w.ood.x));
+  const float basey = __fmaf_rn(-kByteBias, ay, __fmaf_rn(oy, w.inv.y, -w.ood.y));
+  const float basez = __fmaf_rn(-kByteBias, az, __fmaf_rn(oz, w.inv.z, -w.ood.z));
+  const float bnx = basex - mx, bfx = basex + mx, bny = basey - my, bfy = basey + my, bnz = basez - mz, bfz = basez + mz;
   // qlo: x = n2.xy, y = n2.zw, z = n3.xy; qhi: x = n3.zw, y = n4.xy, z = n4.zw. near = lo unless d < 0
   const bool nx = w.neg & 1, ny = w.neg & 2, nz = w.neg & 4;
   uint32_t hitmask = 0;
@@ -292,8 +329,8 @@ __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx
     const uint32_t qnz = nz ? hiz : loz, qfz = nz ? loz : hiz;
     const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
     const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-    const uint32_t bit_index4 = (meta4 ^ (w.octinv4 & inner_mask4)) & 0x1f1f1f1fu;
-    const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+    // byte k: count bits (unary, 3) << 5 | bit index (5): internal children get slot ^ octant in the low 3 bits
+    const uint32_t m4 = meta4 ^ (w.octinv4 & inner_mask4);
 #pragma unroll
     for (int k = 0; k < 4; k++) {
       const float tnx = __fmaf_rn(byte_biased(qnx, k), ax, bnx), tfx = __fmaf_rn(byte_biased(qfx, k), ax, bfx);
@@ -301,16 +338,21 @@ __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx
       const float tnz = __fmaf_rn(byte_biased(qnz, k), az, bnz), tfz = __fmaf_rn(byte_biased(qfz, k), az, bfz);
       const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
       const float tf = fminf(fminf(tfx, tfy), fminf(tfz, lim));
-      if (tn <= tf) hitmask |= ((child_bits4 >> (8 * k)) & 0xffu) << ((bit_index4 >> (8 * k)) & 0xffu);
+      const uint32_t b = (m4 >> (8 * k)) & 0xffu;
+      if (tn <= tf) hitmask |= (b >> 5) << (b & 31u);
     }
   }
   return hitmask;
 }
 
-__device__ __forceinline__ WideRay make_wide_ray(const Ray& ray, const Octant& q) {
+__device__ __forceinline__ WideRay make_wide_ray(const DScene& sc, const Ray& ray, const Octant& q) {
   WideRay w;
   w.inv = q.inv;
   w.ood = q.ood;
+  // rounded UP a little (1 + 2^-10): the three roundings of this expression must not shrink the bound
+  w.err = V3((sc.node_origin_absmax[0] * fabsf(q.inv.x) + fabsf(q.ood.x)) * 4.7730281949043274e-7f,
+             (sc.node_origin_absmax[1] * fabsf(q.inv.y) + fabsf(q.ood.y)) * 4.7730281949043274e-7f,
+             (sc.node_origin_absmax[2] * fabsf(q.inv.z) + fabsf(q.ood.z)) * 4.7730281949043274e-7f);
   w.neg = (ray.d.x < 0 ? 1u : 0u) | (ray.d.y < 0 ? 2u : 0u) | (ray.d.z < 0 ? 4u : 0u);
   w.octinv4 = (7u ^ w.neg) * 0x01010101u;
   return w;

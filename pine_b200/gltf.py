@@ -77,21 +77,44 @@ def parse(data, base_dir=None):
         else:
             if base_dir is None:
                 raise GltfError(f"buffer {i} refers to the external file `{uri}`")
-            with open(os.path.join(base_dir, uri), "rb") as f:
+            with open(_inside(base_dir, uri, f"buffer {i}"), "rb") as f:
                 buffers.append(f.read())
     return doc, buffers
+
+
+def _inside(base_dir, uri, what):
+    """base_dir / uri, refusing uris that leave base_dir (absolute paths, `..`): the file is untrusted input."""
+    from urllib.parse import unquote
+    rel = unquote(uri)
+    root = os.path.realpath(base_dir)
+    path = os.path.realpath(os.path.join(root, rel))
+    if os.path.isabs(rel) or (path != root and not path.startswith(root + os.sep)):
+        raise GltfError(f"{what}: uri `{uri}` points outside the directory of the .gltf file")
+    return path
 
 
 def _accessor(doc, buffers, index):
     acc = doc["accessors"][index]
     if "sparse" in acc:
         raise GltfError("sparse accessors are not supported")
-    view = doc["bufferViews"][acc["bufferView"]]
-    dt, width = np.dtype(_COMPONENT[acc["componentType"]]), _WIDTH[acc["type"]]
-    start = view.get("byteOffset", 0) + acc.get("byteOffset", 0)
-    stride = view.get("byteStride", 0) or dt.itemsize * width
-    raw = np.frombuffer(buffers[view["buffer"]], np.uint8)
-    count = acc["count"]
+    try:
+        view = doc["bufferViews"][acc["bufferView"]]
+        dt, width = np.dtype(_COMPONENT[acc["componentType"]]), _WIDTH[acc["type"]]
+        raw = np.frombuffer(buffers[view["buffer"]], np.uint8)
+    except (KeyError, IndexError, TypeError) as e:
+        raise GltfError(f"accessor {index}: bad bufferView / buffer / type reference ({e})")
+    view_start, acc_off = int(view.get("byteOffset", 0)), int(acc.get("byteOffset", 0))
+    start = view_start + acc_off
+    stride = int(view.get("byteStride", 0)) or dt.itemsize * width
+    count = int(acc["count"])
+    # the file is untrusted: the last element must end inside the bufferView and the buffer
+    elem = dt.itemsize * width
+    view_len = int(view.get("byteLength", len(raw) - view_start))
+    end = acc_off + (count - 1) * stride + elem if count > 0 else acc_off
+    if (count < 0 or view_start < 0 or acc_off < 0 or stride < elem or view_start + view_len > len(raw)
+            or end > view_len):
+        raise GltfError(f"accessor {index}: {count} elements of {elem} bytes (stride {stride}) at offset {acc_off} "
+                        f"do not fit its bufferView ({view_len} bytes) / buffer ({len(raw)} bytes)")
     if stride == dt.itemsize * width:
         out = raw[start:start + count * stride].view(dt).reshape(count, width)
     else:
@@ -131,11 +154,13 @@ def _image(doc, buffers, index, base_dir):
     if "bufferView" in img:
         view = doc["bufferViews"][img["bufferView"]]
         start = view.get("byteOffset", 0)
+        if start < 0 or start + view["byteLength"] > len(buffers[view["buffer"]]):
+            raise GltfError(f"image {index}: its bufferView does not fit the buffer")
         raw = bytes(buffers[view["buffer"]][start:start + view["byteLength"]])
     elif img.get("uri", "").startswith("data:"):
         raw = base64.b64decode(img["uri"].split(",", 1)[1])
     elif "uri" in img and base_dir is not None:
-        with open(os.path.join(base_dir, img["uri"]), "rb") as f:
+        with open(_inside(base_dir, img["uri"], f"image {index}"), "rb") as f:
             raw = f.read()
     else:
         raise GltfError(f"image {index} has no readable source")
@@ -244,6 +269,11 @@ def scene_from_gltf(scene, source, transform=None):
                         uvs = arr.copy()
                 if verts is None:
                     raise GltfError("primitive without POSITION")
+                for what, arr in (("NORMAL", normals), ("TEXCOORD_0", uvs)):
+                    if arr is not None and len(arr) != len(verts):
+                        raise GltfError(f"{what} has {len(arr)} elements but POSITION has {len(verts)}")
+                if len(idx) and int(idx.max()) >= len(verts):
+                    raise GltfError("an index refers to a vertex beyond POSITION's count")
                 n_norm = 0 if normals is None else len(normals)
                 A.lib().pb2h_mesh_apply(_fp(_col(tr)), _fp(verts), len(verts),
                                         _fp(normals) if n_norm else None, n_norm)

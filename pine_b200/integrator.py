@@ -235,6 +235,16 @@ class Backend:
                                          mapped.ctypes.data))
         return rgba8, mapped
 
+    def finalize_device(self, flip_y=True, tonemapper=-1, want_mapped=False):
+        """Film::finalize + quantise on the film the last render left on the device -> RGBA8 [h, w, 4]
+        (and the tone-mapped float film when asked): 4 bytes per pixel cross PCIe instead of 16."""
+        w, h = self.size
+        rgba8 = np.empty((h, w, 4), np.uint8)
+        mapped = np.empty((h, w, 4), np.float32) if want_mapped else None
+        A.check(self.L.pb2_film_finalize_device(self.h, tonemapper, int(flip_y), rgba8.ctypes.data,
+                                                mapped.ctypes.data if want_mapped else None))
+        return (rgba8, mapped) if want_mapped else rgba8
+
     def trace_closest(self, rays, accel=0, surf=False):
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
         n = len(rays)
@@ -368,6 +378,13 @@ class MultiBackend:
                                         film.ctypes.data))
         return film
 
+    def finalize_device(self, flip_y=True, tonemapper=-1):
+        """RGBA8 of the reduced film of the last render (tone-mapped on the first device)."""
+        w, h = self.size
+        rgba8 = np.empty((h, w, 4), np.uint8)
+        A.check(self.L.pb2_multi_film_finalize(self.h, tonemapper, int(flip_y), rgba8.ctypes.data, None))
+        return rgba8
+
     def counters(self):
         c = A.Counters()
         r, s = C.c_double(), C.c_double()
@@ -396,6 +413,7 @@ class PathIntegrator:
         film = self.backend.render(self.sampler, self.max_path_length, accel=self.accel)
         scene.camera.film().pixels = film
         scene._backend = self.backend
+        scene._rendered_film = film  # the array whose device twin is still in the context (save_film)
         return film
 
 
@@ -418,6 +436,10 @@ def save_film(film, path, scene=None):
     backend = getattr(scene, "_backend", None) if scene is not None else None
     if backend is None:
         raise RuntimeError("save needs the scene that was rendered (its device context)")
-    rgba8, _ = backend.finalize(film.pixels, flip_y=True)
+    if film.pixels is getattr(scene, "_rendered_film", None):
+        # the film of the render is still on the device: tone-map it there and fetch 4 bytes per pixel
+        rgba8 = backend.finalize_device(flip_y=True)
+    else:  # the caller replaced or edited Film::pixels: finalize what it holds now
+        rgba8, _ = backend.finalize(film.pixels, flip_y=True)
     os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
     write_png(path, rgba8)

@@ -212,6 +212,13 @@ class Scene:
         i = np.ascontiguousarray(idx, dtype=np.uint32).reshape(-1, 3)
         n = _f(normals).reshape(-1, 3) if normals is not None else None
         t = _f(uvs).reshape(-1, 2) if uvs is not None else None
+        # pb2_upload_scene copies n_vertices normals / texcoords: shorter arrays would be read out of bounds
+        if n is not None and len(n) != len(v):
+            raise ValueError(f"mesh has {len(v)} vertices but {len(n)} normals")
+        if t is not None and len(t) != len(v):
+            raise ValueError(f"mesh has {len(v)} vertices but {len(t)} texture coordinates")
+        if len(i) and int(i.max()) >= len(v):
+            raise ValueError("mesh index out of range")
         self.mesh_data.append((v, i, n, t))
         m = A.Mesh()
         m.vertices, m.indices = v.ctypes.data, i.ctypes.data

@@ -169,6 +169,48 @@ def test_unsupported_content_is_an_error():
         gltf.scene_from_gltf(pb.Scene(), b"glTF" + struct.pack("<II", 1, 12))
 
 
+def test_malformed_buffers_are_rejected_not_read_out_of_bounds(tmp_path):
+    """Untrusted input: accessors that run past their bufferView / buffer, attribute counts that differ from
+    POSITION's, indices beyond the vertex count and uris that leave the file's directory are errors."""
+    def too_many(doc):
+        doc["accessors"][doc["meshes"][0]["primitives"][0]["attributes"]["POSITION"]]["count"] = 1 << 20
+    with pytest.raises(gltf.GltfError, match="do not fit"):
+        gltf.scene_from_gltf(pb.Scene(), _rewrite(too_many))
+
+    def huge_stride(doc):
+        a = doc["accessors"][doc["meshes"][0]["primitives"][0]["attributes"]["POSITION"]]
+        doc["bufferViews"][a["bufferView"]]["byteStride"] = 1 << 16
+    with pytest.raises(gltf.GltfError, match="do not fit"):
+        gltf.scene_from_gltf(pb.Scene(), _rewrite(huge_stride))
+
+    def short_normals(doc):
+        at = doc["meshes"][0]["primitives"][0]["attributes"]
+        if "NORMAL" not in at:
+            at["NORMAL"] = at["POSITION"]
+        doc["accessors"].append(dict(doc["accessors"][at["NORMAL"]], count=1))
+        at["NORMAL"] = len(doc["accessors"]) - 1
+    with pytest.raises(gltf.GltfError, match="NORMAL has 1 elements"):
+        gltf.scene_from_gltf(pb.Scene(), _rewrite(short_normals))
+
+    def few_vertices(doc):
+        at = doc["meshes"][0]["primitives"][0]["attributes"]
+        at.pop("NORMAL", None); at.pop("TEXCOORD_0", None)
+        doc["accessors"].append(dict(doc["accessors"][at["POSITION"]], count=2))
+        doc["accessors"][-1].pop("min", None); doc["accessors"][-1].pop("max", None)
+        at["POSITION"] = len(doc["accessors"]) - 1
+    with pytest.raises(gltf.GltfError, match="beyond POSITION"):
+        gltf.scene_from_gltf(pb.Scene(), _rewrite(few_vertices))
+
+    (tmp_path / "sub").mkdir()
+    (tmp_path / "secret.bin").write_bytes(b"\0" * 64)
+    doc = {"asset": {"version": "2.0"}, "buffers": [{"uri": "../secret.bin", "byteLength": 64}]}
+    (tmp_path / "sub" / "x.gltf").write_text(json.dumps(doc))
+    with pytest.raises(gltf.GltfError, match="outside the directory"):
+        gltf.scene_from_gltf(pb.Scene(), str(tmp_path / "sub" / "x.gltf"))
+    with pytest.raises(ValueError):
+        pb.Scene().add_mesh(np.zeros((3, 3), np.float32), [[0, 1, 2]], 0, normals=np.zeros((2, 3), np.float32))
+
+
 def test_prl_scene_load(tmp_path, loaded):
     from pine_b200 import prl
     script = tmp_path / "room.pine"

@@ -79,6 +79,31 @@ def test_reference_loader_plus_shim_equals_product_loader():
     B.close()
 
 
+def test_textured_glb_through_the_reference_loader_and_the_shim():
+    """Image-node Uber materials (baseColorTexture / metallicRoughnessTexture) loaded by the REFERENCE's
+    scene_from_gltf (fileio.cpp:285-292) reach the device through the shim's flatten as pb2_texture records:
+    the film equals the product loader's bit for bit and the reference's own render to 1e-4."""
+    import os
+    import common
+    import pine_b200 as pb
+    from oracle import ref
+    path = os.path.join(common.GOLDEN, "room_textured.glb")
+    cam = ((96, 64), (0.3, 1.6, 3.6), (0.0, 0.8, 0.0), 0.45)
+    R = ref.RefScene()
+    R.load_gltf(path)
+    R.set_camera(*cam)
+    film_cuda, _, _ = R.render_cuda(8, 4)
+    film_ref, _ = R.render(8, 4)
+    assert relmse(film_cuda, film_ref) <= 1e-4
+    S = pb.load_scene(path)
+    S.set_camera(*cam)
+    assert any(m.color_texture or m.roughness_texture or m.metallic_texture for m in S.materials)
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    assert np.array_equal(B.render(8, 4).view(np.uint32), film_cuda.view(np.uint32))
+    B.close()
+
+
 def test_shim_keeps_the_reference_error_behaviour():
     """max_path_length <= 0 is SEVERE -> abort in the reference (path.cpp:12-13); the shim does the
     same, so it is checked in a child process."""
@@ -92,3 +117,20 @@ def test_shim_keeps_the_reference_error_behaviour():
                        capture_output=True, text=True, timeout=120)
     assert r.returncode != 0
     assert "max_path_length" in (r.stdout + r.stderr)
+
+
+@pytest.mark.parametrize("tonemapper", ["uncharted2", "aces"])
+def test_shim_device_epilogue_is_film_save(tonemapper):
+    """CudaPathIntegrator::finalize_rgba8 -- Film::finalize + gamma / x256 / clamp / y-flip on the film still on
+    the device, 4 bytes per pixel back (save_film_as_image, film.cpp:12-27, fileio.cpp:42-54) -- against the
+    reference's own Film::finalize of the same film; the shim finds the Film's private tone mapper by itself."""
+    from oracle import ref
+    from pine_b200 import scenes
+    R = ref.RefScene()
+    cfg = scenes.cbox_readme(R, size=(96, 64))
+    R.set_camera((96, 64), (0, 1, -4), (0, 1, 0), 0.25, tonemapper=tonemapper)
+    film, rgba8 = R.render_cuda_rgba8(8, cfg["depth"])
+    want = R.finalize(film)  # the reference's tone mapping of that film (host)
+    q = np.clip(np.power(want[..., :3].astype(np.float32), np.float32(1 / 2.2)) * 256, 0, 255).astype(np.uint8)
+    assert (np.abs(rgba8[::-1, :, :3].astype(int) - q.astype(int)) <= 1).all()
+    assert (rgba8[..., 3] == 255).all()

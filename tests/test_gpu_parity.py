@@ -269,4 +269,10 @@ def test_live_reference_c1_160(gpu):
     np.testing.assert_allclose(mapped[..., :3], want[..., :3], rtol=2e-6, atol=1e-7)
     q = np.clip(np.power(want[..., :3].astype(np.float32), np.float32(1 / 2.2)) * 256, 0, 255).astype(np.uint8)
     assert (np.abs(rgba8[..., :3].astype(int) - q.astype(int)) <= 1).all()
+    # the same epilogue on the film the render left on the device (no upload, 4 B per pixel back) gives the
+    # bytes the host-film entry point gives for that film
+    r8_dev, mapped_dev = B.finalize_device(flip_y=False, want_mapped=True)
+    r8_host, mapped_host = B.finalize(film, flip_y=False)
+    assert np.array_equal(r8_dev, r8_host) and np.array_equal(u32(mapped_dev), u32(mapped_host))
+    assert np.array_equal(B.finalize_device(flip_y=True), r8_host[::-1])
     B.close()
