@@ -84,31 +84,6 @@ __device__ __forceinline__ bool obb_intersect(const pb2_obb& s, Ray& ray, bool* 
   ray.tmax = tmin > ray.tmin ? tmin : tmax;
   return true;
 }
-// What a Box shape (AABB / OBB) does to a closest-hit ray, for the order analysis of traverse.cuh (iii'):
-// accepted at the ray's own tmax?  `e` = the slab entry distance the acceptance test compares with tmax (LOCAL
-// units for an OBB: bbox.cpp:149-161 feeds the world-space tmax into the local-space test), `tb` = the t the
-// shape reports when the origin is outside, `inside` = origin inside (reported t = exit clipped by tmax).
-// Neither e nor tb depends on tmax; the reference accepts the shape at any later tmax' iff e <= tmax' too.
-__device__ __forceinline__ bool box_probe(const DScene& sc, int kind, int index, const Ray& ray, float& e, float& tb,
-                                          bool& inside) {
-  float tmin = ray.tmin, tmax = ray.tmax;
-  if (kind == PB2_SHAPE_AABB) {
-    const pb2_aabb& s = sc.aabbs[index];
-    if (!aabb_slabs(ldv(s.lower), ldv(s.upper), ray.o, ray.d, tmin, tmax)) return false;
-    e = tmin;
-    tb = tmin;
-  } else {
-    const pb2_obb& s = sc.obbs[index];
-    M4 m_inv = ld_m4_dev(s.m_inv);
-    V3 o = mul_point(m_inv, ray.o);
-    V3 d = normalize(upper3(m_inv) * ray.d);
-    if (!aabb_slabs(ldv(s.base.lower), ldv(s.base.upper), o, d, tmin, tmax)) return false;
-    e = tmin;
-    tb = distance(mul_point(ld_m4_dev(s.m), o + tmin * d), ray.o);
-  }
-  inside = !(tb > ray.tmin);
-  return true;
-}
 __device__ __forceinline__ bool obb_hit(const pb2_obb& s, const Ray& ray) {
   M4 m_inv = ld_m4_dev(s.m_inv);
   V3 o = mul_point(m_inv, ray.o);

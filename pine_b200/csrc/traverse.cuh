@@ -188,12 +188,6 @@ __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) 
 //         every box shape is rejected at the ray's incoming tmax (shape test AND leaf gate) never
 //         has one accepted by the reference either: such rays take the wide walk with the box
 //         shapes left out, all others go to the reference-order walk (wide_persistent.cuh),
-//   (iii') of the rays a box shape COULD accept (probe at the incoming tmax), those whose winner among the other
-//         primitives lies in front of every such box in both measures the reference uses -- t < e, the slab
-//         entry it compares with tmax (local units for an OBB), and t < tb, the t the box would report -- keep
-//         the wide result: reached after the winner the box is refused (e > tmax), reached before it the box
-//         leaves tmax = tb behind the winner, which is then still found; origin-inside boxes, misses and boxes
-//         in front (or straddling: the scaled-OBB quirk) walk in reference order (wide_persistent.cuh),
 //   (iv)  every primitive the reference accepts is also tested here. For primitives that lie
 //         inside their leaf box this follows from box containment; a Cone does not (it is
 //         unbounded below its base, geometry.cpp:415-446) and can be hit BEFORE the ray enters its

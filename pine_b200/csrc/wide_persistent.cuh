@@ -53,7 +53,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
 #else
   const uint4* s_top = nullptr;
 #endif
-  uint2 stack[kWideStack + 1];  // [kWideStack]: the closest-hit ray's Box summary (min e, min tb), see refill
+  uint2 stack[kWideStack];
   int sp = 0;
   bool active = false, drained = false;
   int idx = 0;
@@ -94,25 +94,19 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
           have = false; ambiguous = false; tie_t = -1.0f; win_leaf = -1; t2 = kFloatMax;
           h.geom = h.prim = -1;
           active = true;
-          if (sc.n_box_shapes) {  // see DBoxShape and traverse.cuh (iii), (iii')
-            bool fallback = false;
-            float min_e = kFloatMax, min_tb = kFloatMax;
-            for (int i = 0; i < sc.n_box_shapes && !fallback; i++) {
+          if (sc.n_box_shapes) {  // see DBoxShape and traverse.cuh (iii)
+            bool touched = false;
+            for (int i = 0; i < sc.n_box_shapes && !touched; i++) {
               const int4 b = __ldg(reinterpret_cast<const int4*>(sc.box_shapes) + i);
               if (ANY) {
-                fallback = shape_hit(sc, b.x, b.y, ray) && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax);
+                touched = shape_hit(sc, b.x, b.y, ray);
               } else {
-                float e, tb;
-                bool inside;
-                if (box_probe(sc, b.x, b.y, ray, e, tb, inside) && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax)) {
-                  if (inside) fallback = true;  // reports the exit clipped by the tmax of the moment
-                  min_e = pmin(min_e, e);
-                  min_tb = pmin(min_tb, tb);
-                }
+                Ray r2 = ray;
+                touched = shape_intersect(sc, b.x, b.y, r2);
               }
+              touched = touched && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax);
             }
-            if (!ANY) stack[kWideStack] = make_uint2(__float_as_uint(min_e), __float_as_uint(min_tb));
-            if (fallback) {
+            if (touched) {
               if (ANY) io.store_any(idx, true);
               else wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
 #ifdef PB2_COUNT
@@ -226,25 +220,6 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
 #ifdef PB2_COUNT
           if (ambiguous && sc.walk_stats) atomicAdd(sc.walk_stats + (tie_t == ray.tmax ? 8 : 9), 1ull);
 #endif
-        }
-        if (!ambiguous && sc.n_box_shapes) {
-          // (iii') Box shapes the ray could be accepted by were left out of the walk. If the winner is in
-          // front of every one of them in BOTH measures the reference uses -- t < e (the box is refused whenever
-          // the reference reaches it after the winner) and t < tb (a box accepted earlier leaves tmax = tb
-          // behind the winner, which is then still found) -- the boxes cannot change the result. Otherwise
-          // (a box in front, a miss, or a box whose local-space entry and world-space t straddle the winner:
-          // the scaled-OBB quirk of bbox.cpp:149-161) the visiting order decides: reference-order walk.
-          const uint2 bx = stack[kWideStack];
-          const float min_e = __uint_as_float(bx.x), min_tb = __uint_as_float(bx.y);
-          // (tb beyond half_slack_of(t), not just t: the certificate (ii') above assumed the reference's tmax on
-          // arrival at the winner's leaf is tmax_in or the t of a candidate the walk has seen -- a box's tb is
-          // now a third possibility and must not undercut U)
-          if (min_tb < kFloatMax && !(have && ray.tmax < min_e && half_slack_of(ray.tmax) < min_tb)) {
-            ambiguous = true;
-#ifdef PB2_COUNT
-            if (sc.walk_stats) atomicAdd(sc.walk_stats + 6, 1ull);
-#endif
-          }
         }
         if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
         else io.store_closest(sc, idx, ray, have, h);
