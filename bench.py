@@ -124,11 +124,16 @@ class _DevicePtr:
                                          "version": 3, "strides": None}
 
 
-def run_reference(workload, steps, warmup, step_seconds):
+def run_reference(workload, steps, warmup, step_seconds, accel="bvh"):
     """The reference's own PathIntegrator (oracle/_ref: the unmodified C++ compiled in place) on
     all host threads. Each step renders a bounded sample of the workload's film: every `row_step`-th
-    row, all spp, BVH built once before the steps (oracle/ref_harness.cpp BoundedPath)."""
+    row, all spp, BVH built once before the steps (oracle/ref_harness.cpp BoundedPath).
+    accel "bvh": pine::BVH (the bit-exact oracle); "embree": EmbreeAccel over the vendored Embree 4.3.1, the
+    accel PRL's PathIntegrator(sampler, depth) really constructs (program_context.cpp:79-81) -- needs a process
+    started with PINE_REF_EMBREE=1 (see run_reference_embree)."""
     from oracle import ref
+    if accel == "embree":
+        ref.use_embree_accel(True)
     if not ref.available():
         raise RuntimeError("oracle/_ref/libpine_ref.so missing (built by __graft_entry__.build() "
                            "where /root/reference exists; it travels with the repo snapshot)")
@@ -155,11 +160,27 @@ def run_reference(workload, steps, warmup, step_seconds):
     secs = float(np.mean(times)) if times else float("nan")
     samples = n_rows * w * spp
     return {"value": samples / secs / 1e6, "unit": "Msamples/s", "cores": int(cores), "kind": "reference",
+            "accel": "EmbreeAccel (vendored Embree 4.3.1, ISAs <= AVX2, tasking INTERNAL)" if accel == "embree" else "pine::BVH",
             "film": [w, h], "spp": spp, "max_path_length": depth,
             "sample": f"{n_rows} of {h} rows (every {row_step}th) x {w} px x {spp} spp per step = "
                       f"{samples} samples; pine::BVH built once before the steps ({prep_s:.2f} s, "
                       f"excluded); mean of {len(times)} steps of {secs:.2f} s",
             "seconds_per_step": secs, "bvh_build_s": prep_s}
+
+
+def run_reference_embree(workload, step_seconds):
+    """The Embree-backed reference in a child process (its library exports the same symbols as the oracle's)."""
+    from oracle import ref
+    if not ref.embree_available():
+        return {"value": None, "sample": "oracle/_ref/libpine_ref_embree.so not built (`make -C oracle embree`)"}
+    env = dict(os.environ, PINE_REF_EMBREE="1")
+    r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--accel", "embree",
+                        "--workload", workload, "--steps", "1", "--warmup", "0", "--ref-step-seconds", str(step_seconds)],
+                       env=env, capture_output=True, text=True, timeout=900)
+    try:
+        return json.loads(r.stdout.strip().splitlines()[-1])["cpu_baseline"]
+    except Exception:
+        return {"value": None, "sample": "embree reference run failed: " + (r.stderr or r.stdout)[-300:]}
 
 
 def _config(workload, w, h, spp, depth):
@@ -453,6 +474,8 @@ def run_gpu(args):
         if world == 1 and not args.no_cpu_baseline:
             try:
                 out["cpu_baseline"] = run_reference(args.workload, 1, 0, args.cpu_seconds)
+                # beside it: the same reference with the accel PRL really uses (faster than pine::BVH; not bit-exact)
+                out["cpu_baseline_embree"] = run_reference_embree(args.workload, max(3.0, args.cpu_seconds / 2))
             except Exception as e:  # the checker is missing: say so, do not fail the GPU number
                 out["cpu_baseline"] = {"value": None, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "reference",
                                        "sample": f"unavailable: {e}"}
@@ -474,11 +497,12 @@ def main():
     ap.add_argument("--ref-step-seconds", type=float, default=6.0, help="--impl reference: size of one step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-scenes", action="store_true", help="skip the C1/C3/C4 lines of the `scenes` key")
+    ap.add_argument("--accel", default="bvh", choices=["bvh", "embree"], help="--impl reference: which Accel")
     args = ap.parse_args()
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) != 0:
             return
-        r = run_reference(args.workload, args.steps, args.warmup, args.ref_step_seconds)
+        r = run_reference(args.workload, args.steps, args.warmup, args.ref_step_seconds, args.accel)
         out = {"impl": "reference", "metric": "Msamples/s", "value": r["value"], "unit": "Msamples/s",
                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": r["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "strong",

@@ -15,6 +15,12 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_ref", "libpine_ref.so")
+# The same harness with the reference's real PRL-default accel (EmbreeAccel over the vendored Embree 4.3.1,
+# `make -C oracle embree`): a TIMING baseline only, selected per process with PINE_REF_EMBREE=1 (the two
+# libraries export the same symbols, so one process loads one of them).
+EMBREE_LIB_PATH = os.path.join(_HERE, "_ref", "libpine_ref_embree.so")
+if os.environ.get("PINE_REF_EMBREE") == "1":
+    LIB_PATH = EMBREE_LIB_PATH
 
 SHIM_PATH = os.path.join(_HERE, "_ref", "libpine_shim.so")
 _lib = None
@@ -38,6 +44,18 @@ def shim():
 
 def available():
     return os.path.exists(LIB_PATH)
+
+
+def embree_available():
+    return os.path.exists(EMBREE_LIB_PATH)
+
+
+def use_embree_accel(on=True):
+    """bounded_prepare / bounded_render_rows then run PathIntegrator(EmbreeAccel(), ...) (needs PINE_REF_EMBREE=1)."""
+    L = lib()
+    if on and not L.ref_has_embree():
+        raise RuntimeError("this process loaded libpine_ref.so (pine::BVH only): set PINE_REF_EMBREE=1")
+    L.ref_set_bounded_accel(1 if on else 0)
 
 
 def _f(a):

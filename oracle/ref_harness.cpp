@@ -28,6 +28,7 @@
 #include <pine/core/profiler.h>
 #include <pine/core/rng.h>
 #include <pine/impl/integrator/path.h>
+#include <pine/impl/accel/embree.h>
 
 #include <pine/impl/accel/bvh.cpp>
 #include <pine/impl/integrator/path.cpp>
@@ -256,10 +257,21 @@ double ref_render(void* h, int sampler_kind, int spp, int depth, float* film_rgb
 }
 // Bounded-sample variant for timing (see BoundedPath): prepare once (returns the seconds the
 // prologue took, dominated by BVH::build), then render row subsets. BlueSobolSampler only.
+// 1 when this library carries the reference's EmbreeAccel (libpine_ref_embree.so, vendored Embree 4.3.1), else 0
+int ref_has_embree() {
+#ifdef PINE_REF_WITH_EMBREE
+  return 1;
+#else
+  return 0;
+#endif
+}
+static int g_bounded_accel = 0;  // 0: pine::BVH (the bit-exact oracle), 1: EmbreeAccel (the PRL default,
+                                 // program_context.cpp:79-81) -- timing baseline only
+void ref_set_bounded_accel(int accel) { g_bounded_accel = accel; }
 double ref_bounded_prepare(void* h, int spp, int depth) {
   auto& S = *(RefScene*)h;
   delete S.bounded;
-  S.bounded = new BoundedPath(Accel(BVH()), Sampler(BlueSobolSampler(spp)),
+  S.bounded = new BoundedPath(g_bounded_accel == 1 ? Accel(EmbreeAccel()) : Accel(BVH()), Sampler(BlueSobolSampler(spp)),
                               LightSampler(UniformLightSampler()), depth);
   auto t0 = std::chrono::steady_clock::now();
   S.bounded->prepare(S.scene);

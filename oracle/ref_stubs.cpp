@@ -14,9 +14,11 @@ namespace pine {
   std::fprintf(stderr, "[oracle] %s is not available in this build\n", what);
   std::abort();
 }
+#ifndef PINE_REF_WITH_EMBREE  // libpine_ref_embree.so compiles the reference's own embree.cpp instead (oracle/Makefile)
 void EmbreeAccel::build(const Scene*) { unavailable("EmbreeAccel::build"); }
 bool EmbreeAccel::hit(Ray) const { unavailable("EmbreeAccel::hit"); }
 uint8_t EmbreeAccel::hit8(psl::span<const Ray>) const { unavailable("EmbreeAccel::hit8"); }
 bool EmbreeAccel::intersect(Ray&, SurfaceInteraction&) const { unavailable("EmbreeAccel::intersect"); }
+#endif
 void jit_interpret(Context&, psl::string) { unavailable("jit_interpret (PRL)"); }
 }  // namespace pine

@@ -6,6 +6,8 @@ against them bit for bit: hash / RNG / BlueSobol sampler, camera rays, spawn_ray
 builder and the reference-order closest-hit / any-hit walks. Where oracle/_ref itself is present it is
 re-run and must reproduce the committed vectors (the fixtures are not stale).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -197,3 +199,27 @@ def test_compiled_reference_reproduces_the_fixtures(golden, name):
     assert np.array_equal(R.trace_any(g["shadow"]), g["shadow_occ"])
     film, _ = R.render(spp, depth)
     assert np.array_equal(u32(film), u32(g["film"]))  # the reference render is deterministic
+
+
+def test_embree_backed_reference_renders_the_same_film(tmp_path):
+    """oracle/_ref/libpine_ref_embree.so = the same reference with its PRL-default accel (EmbreeAccel over the
+    vendored Embree 4.3.1; `make -C oracle embree`). It is a TIMING baseline (bench.py cpu_baseline_embree); here
+    its film is checked against the pine::BVH reference's: same integrator and sampler streams, different
+    triangle kernels => equal up to rounding-induced path changes."""
+    import subprocess
+    import sys
+    from oracle import ref
+    if not (ref.available() and ref.embree_available()):
+        pytest.skip("Embree-backed reference not built")
+    code = ("import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r + '/tests');"
+            "import common; from oracle import ref; R = ref.RefScene(); common.build(R, 'mesh_48');"
+            "ref.use_embree_accel(%s); R.bounded_prepare(4, 5); t, f = R.bounded_render_rows(0, R.size[1], 1, True);"
+            "np.save(%r, f)")
+    films = {}
+    for name, flag, env in (("bvh", "False", {}), ("embree", "True", {"PINE_REF_EMBREE": "1"})):
+        out = str(tmp_path / f"{name}.npy")
+        r = subprocess.run([sys.executable, "-c", code % (common.ROOT, common.ROOT, flag, out)],
+                           env=dict(os.environ, **env), capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-500:]
+        films[name] = np.load(out)
+    assert common.relmse(films["embree"], films["bvh"]) <= 1e-3
