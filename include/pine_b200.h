@@ -259,7 +259,7 @@ int pb2_restage_scene_part(pb2_context* ctx, void* cuda_stream, int part, int n_
  * sobol[256*256], scramble[128*128*8], rank[128*128*8]. */
 int pb2_upload_sampler_tables(pb2_context* ctx, int spp_pow2, const uint8_t* sobol,
                               const uint8_t* scramble, const uint8_t* rank);
-/* Same, read from the blob oracle/extract_tables.cpp extracts from those sources (path NULL or "" =
+/* Same, read from the blob pine_b200/tools/extract_tables.cpp extracts from those sources (path NULL or "" =
  * pine_b200/data/bluesobol_tables.bin beside the library); what a C++ caller without the arrays uses. */
 int pb2_load_sampler_tables_file(pb2_context* ctx, const char* path, int spp_pow2);
 /* Replaces: PathIntegrator::render's pixel loop (path.cpp:31-40). film_rgba: caller-owned HOST

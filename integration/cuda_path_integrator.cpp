@@ -29,7 +29,7 @@
 
 // The Heitz et al. tables the reference links in (src/contrib/bluesobol/bluenoise_<N>spp.cpp:2-12)
 // are file-static there; a maintainer exposes them with three accessor lines per file. Until then
-// the shim reads the same bytes from the blob oracle/extract_tables.cpp wrote from those sources.
+// the shim reads the same bytes from the blob pine_b200/tools/extract_tables.cpp wrote from those sources.
 
 namespace pine {
 

@@ -87,7 +87,7 @@ extern "C" int pb2_upload_sampler_tables(pb2_context* ctx, int spp_pow2, const u
   return PB2_OK;
 }
 
-// Reads one spp variant from the table blob oracle/extract_tables.cpp writes ("PB2BLUE1", u32 count,
+// Reads one spp variant from the table blob pine_b200/tools/extract_tables.cpp writes ("PB2BLUE1", u32 count,
 // then per variant u32 spp, u32 pad, sobol[65536], scramble[131072], rank[131072]) and registers it.
 // path NULL/"" = pine_b200/data/bluesobol_tables.bin next to this library.
 extern "C" int pb2_load_sampler_tables_file(pb2_context* ctx, const char* path, int spp_pow2) {

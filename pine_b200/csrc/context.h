@@ -86,9 +86,20 @@ struct HostScene {
   struct Item { DBuf pb2_context::* dst; const void* src; size_t bytes; };
   std::vector<Item> items;
   std::vector<void*> registered;    // ranges currently page-locked
+  bool pinned = false;
+  void pin() {  // page-lock the large staging arrays (once): repeated staging then runs at PCIe speed
+    if (pinned) return;
+    pinned = true;
+    for (const Item& it : items)
+      if (it.bytes >= (1u << 16) && cudaHostRegister(const_cast<void*>(it.src), it.bytes, cudaHostRegisterDefault) == cudaSuccess)
+        registered.push_back(const_cast<void*>(it.src));
+      else
+        cudaGetLastError();
+  }
   void unpin() {
     for (void* p : registered) cudaHostUnregister(p);
     registered.clear();
+    pinned = false;
   }
 };
 

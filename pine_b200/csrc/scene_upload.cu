@@ -51,6 +51,8 @@ bool valid_material(const pb2_material& m) {
 
 }  // namespace
 
+int restage_unpinned(pb2_context* ctx);  // first staging of a fresh scene: from pageable memory (below)
+
 extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   if (!ctx || !sd) { set_error("null argument"); return PB2_E_INVALID; }
   if (ctx->device >= 0) PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
@@ -348,10 +350,6 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   auto item = [&](DBuf pb2_context::* dst, const void* src, size_t n) {
     H.items.push_back(HostScene::Item{dst, src, n});
     bytes += n;
-    if (n >= (1u << 16) && cudaHostRegister(const_cast<void*>(src), n, cudaHostRegisterDefault) == cudaSuccess)
-      H.registered.push_back(const_cast<void*>(src));
-    else
-      cudaGetLastError();
   };
 #define ITEM(buf, vec) item(&pb2_context::buf, (vec).data(), (vec).size() * sizeof((vec)[0]))
   ITEM(nodes2, lay.nodes2); ITEM(nodes8, lay.nodes8); ITEM(leaves, lay.leaves);
@@ -362,10 +360,12 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   ITEM(materials, H.materials); ITEM(aabbs, H.aabbs); ITEM(obbs, H.obbs); ITEM(spheres, H.spheres);
   ITEM(triangles, H.triangles); ITEM(cones, H.cones); ITEM(rects, H.rects); ITEM(disks, H.disks);
 #undef ITEM
-  stage("page-lock");
+  // Page-locking 1.4 GB costs ~0.4 s, more than copying it once from pageable memory: the first staging (this
+  // call) copies from pageable memory and the arrays are page-locked by the first RE-staging (HostScene::pin),
+  // which is the caller that profits from pinned copies.
   ctx->counters.scene_bytes = bytes;
   if (ctx->defer_staging) return PB2_OK;  // pb2_multi_upload_scene stages the replicas itself (sharded + all-gather)
-  int rc = pb2_restage_scene(ctx, nullptr);
+  int rc = restage_unpinned(ctx);
   if (rc) return rc;
   PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
 #ifdef PB2_COUNT
@@ -382,7 +382,7 @@ namespace {
 // device pointers of ctx->scene.
 constexpr size_t kShardMinBytes = size_t(1) << 20;
 int restage(pb2_context* ctx, void* cuda_stream, int part, int n_parts, pb2_device_array* arrays, int max_arrays,
-            int* n_arrays) {
+            int* n_arrays, bool pin = true) {
   if (!ctx || !ctx->host_scene_ready || ctx->device < 0) { set_error("no host scene / no device"); return PB2_E_STATE; }
   if (n_parts < 1 || part < 0 || part >= n_parts) { set_error("part out of range"); return PB2_E_INVALID; }
   PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
@@ -390,6 +390,8 @@ int restage(pb2_context* ctx, void* cuda_stream, int part, int n_parts, pb2_devi
   auto t0 = std::chrono::steady_clock::now();
   int n_out = 0;
   const HostScene& host = ctx->host_view ? *ctx->host_view : ctx->host;
+  // page-lock on the first RE-staging only (the first staging of a fresh scene copies from pageable memory)
+  if (pin && ctx->scene_ready) const_cast<HostScene&>(host).pin();
   for (const HostScene::Item& it : host.items) {
     DBuf& dst = ctx->*(it.dst);
     if (n_parts == 1 || it.bytes < kShardMinBytes) {
@@ -441,6 +443,7 @@ int restage(pb2_context* ctx, void* cuda_stream, int part, int n_parts, pb2_devi
 }
 }  // namespace
 
+int restage_unpinned(pb2_context* ctx) { return restage(ctx, nullptr, 0, 1, nullptr, 0, nullptr, false); }
 extern "C" int pb2_restage_scene(pb2_context* ctx, void* cuda_stream) {
   return restage(ctx, cuda_stream, 0, 1, nullptr, 0, nullptr);
 }

@@ -276,21 +276,11 @@ constexpr uint32_t kNoCullBit = 0x80000000u;  // in DNode8::prim_base
 #ifndef PB2_SMEM_TOP
 #define PB2_SMEM_TOP 9
 #endif
-__device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx, const WideRay& w, float tmin,
-                                               float lim, float lim_nocull, uint32_t& child_base,
-                                               uint32_t& prim_base, uint32_t& imask, const uint4* s_top = nullptr) {
-  const uint4* p = reinterpret_cast<const uint4*>(nodes + idx);
-#if PB2_SMEM_TOP > 0
-  uint4 n0, n1, n2, n3, n4;
-  if (idx < uint32_t(PB2_SMEM_TOP)) {
-    const uint4* q = s_top + idx * 5u;
-    n0 = q[0]; n1 = q[1]; n2 = q[2]; n3 = q[3]; n4 = q[4];
-  } else {
-    n0 = __ldg(p); n1 = __ldg(p + 1); n2 = __ldg(p + 2); n3 = __ldg(p + 3); n4 = __ldg(p + 4);
-  }
-#else
-  const uint4 n0 = __ldg(p), n1 = __ldg(p + 1), n2 = __ldg(p + 2), n3 = __ldg(p + 3), n4 = __ldg(p + 4);
-#endif
+// The test on a node already in registers (n0..n4 = its five 128-bit words).
+__device__ __forceinline__ uint32_t test_node8_regs(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
+                                                    const uint4 n4, const WideRay& w, float tmin, float lim,
+                                                    float lim_nocull, uint32_t& child_base, uint32_t& prim_base,
+                                                    uint32_t& imask) {
   const float ox = __uint_as_float(n0.x), oy = __uint_as_float(n0.y), oz = __uint_as_float(n0.z);
   const float ax = __uint_as_float((n0.w & 0xffu) << 23) * w.inv.x;
   const float ay = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * w.inv.y;
@@ -337,6 +327,23 @@ __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx
     }
   }
   return hitmask;
+}
+__device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx, const WideRay& w, float tmin,
+                                               float lim, float lim_nocull, uint32_t& child_base,
+                                               uint32_t& prim_base, uint32_t& imask, const uint4* s_top = nullptr) {
+  const uint4* p = reinterpret_cast<const uint4*>(nodes + idx);
+#if PB2_SMEM_TOP > 0
+  uint4 n0, n1, n2, n3, n4;
+  if (idx < uint32_t(PB2_SMEM_TOP)) {
+    const uint4* q = s_top + idx * 5u;
+    n0 = q[0]; n1 = q[1]; n2 = q[2]; n3 = q[3]; n4 = q[4];
+  } else {
+    n0 = __ldg(p); n1 = __ldg(p + 1); n2 = __ldg(p + 2); n3 = __ldg(p + 3); n4 = __ldg(p + 4);
+  }
+#else
+  const uint4 n0 = __ldg(p), n1 = __ldg(p + 1), n2 = __ldg(p + 2), n3 = __ldg(p + 3), n4 = __ldg(p + 4);
+#endif
+  return test_node8_regs(n0, n1, n2, n3, n4, w, tmin, lim, lim_nocull, child_base, prim_base, imask);
 }
 
 __device__ __forceinline__ WideRay make_wide_ray(const DScene& sc, const Ray& ray, const Octant& q) {

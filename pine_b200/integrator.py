@@ -21,7 +21,7 @@ _tables = None
 
 def sampler_tables():
     """{spp: (sobol u8[65536], scramble u8[131072], rank u8[131072])} from the extracted blob
-    (oracle/extract_tables.cpp documents the layout and provenance)."""
+    (pine_b200/tools/extract_tables.cpp documents the layout and provenance)."""
     global _tables
     if _tables is None:
         if not os.path.exists(TABLES_PATH):

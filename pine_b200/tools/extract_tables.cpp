@@ -1,4 +1,4 @@
-// oracle/extract_tables.cpp -- TEST/BUILD INFRASTRUCTURE.
+// pine_b200/tools/extract_tables.cpp -- PRODUCT BUILD STEP (pine_b200/csrc/Makefile `tables`).
 // Extracts the Heitz et al. 2019 blue-noise Sobol tables (third-party data vendored by the
 // reference under src/contrib/bluesobol/, see CITATION.txt there) by COMPILING the vendored table
 // sources into this program and dumping the arrays as u8. Nothing is retyped or copied as source.
