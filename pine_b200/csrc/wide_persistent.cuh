@@ -25,9 +25,6 @@ constexpr int kRefillThreshold = PB2_REFILL;  // refill a warp when at least thi
 #ifndef PB2_TIGHT_LANES
 #define PB2_TIGHT_LANES 16
 #endif
-#ifndef PB2_UNIFIED_FETCH
-#define PB2_UNIFIED_FETCH 0
-#endif
 
 struct WideQueue {
   int* next;      // next unclaimed queue index (zero before the launch)
@@ -130,7 +127,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
     }
 
     bool done = false;
-    // one primitive record against the lane's ray (shared by both loop variants)
+    // one primitive record against the lane's ray 
     auto test_prim = [&](const PrimRec& r) {
         if (ANY) {
         bool ok;
@@ -161,85 +158,6 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         }
       }
     };
-#if PB2_UNIFIED_FETCH
-    // ---- unified fetch: a lane either walks (node test) or owns primitives left by an EARLIER node test.
-    // Both kinds of lane issue their 128-bit loads first -- the same three load instructions, from the node or
-    // from the primitive record -- and only then does the warp run the node code and the primitive code, so an
-    // iteration exposes ONE memory latency instead of the node fetch's and then the primitive fetch's. The
-    // price: the first primitive of a freshly tested node waits for the next iteration.
-    const bool walking = active && tgroup.y == 0u;
-    const bool owns = active && tgroup.y != 0u;
-    uint32_t fetch = 0;  // node index (walking) or primitive index (owns)
-    if (walking) {
-      const uint32_t hits = ngroup.y, imask = hits & 0xffu;
-      const int bit = 31 - __clz(hits);
-      ngroup.y &= ~(1u << bit);
-      if (ngroup.y > 0x00ffffffu) {
-        if (sp < kWideStack) stack[sp++] = ngroup;
-        else ambiguous = true;
-      }
-      const uint32_t slot = uint32_t(bit - 24) ^ (w.octinv4 & 7u);
-      fetch = ngroup.x + __popc(imask & ~(0xffffffffu << slot));
-    } else if (owns) {
-      const int i = __ffs(tgroup.y) - 1;
-      tgroup.y &= tgroup.y - 1;
-      fetch = tgroup.x + i;
-    }
-    const uint4* fp = walking ? reinterpret_cast<const uint4*>(sc.nodes8 + fetch)
-                              : reinterpret_cast<const uint4*>(sc.wide_prims + fetch);
-    uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0, r2 = r0;
-#if PB2_SMEM_TOP > 0
-    if (walking && fetch < uint32_t(PB2_SMEM_TOP)) fp = s_top + fetch * 5u;
-    if (active) { r0 = fp[0]; r1 = fp[1]; r2 = fp[2]; }  // generic loads: shared or global
-#else
-    if (active) { r0 = __ldg(fp); r1 = __ldg(fp + 1); r2 = __ldg(fp + 2); }
-#endif
-    const bool tight = __popc(__ballot_sync(0xffffffffu, owns)) >= PB2_TIGHT_LANES;
-    if (walking) {
-#if PB2_SMEM_TOP > 0
-      const uint4 r3 = fp[3], r4 = fp[4];
-#else
-      const uint4 r3 = __ldg(fp + 3), r4 = __ldg(fp + 4);
-#endif
-      uint32_t child_base, prim_base, cmask;
-#ifdef PB2_COUNT
-      c_nodes++;
-#endif
-      const uint32_t hm = test_node8_regs(r0, r1, r2, r3, r4, w, ray.tmin, ANY ? ray.tmax : slack_of(ray.tmax),
-                                          ANY ? ray.tmax : tmax_in, child_base, prim_base, cmask);
-      ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
-      tgroup = make_uint2(prim_base, hm & 0x00ffffffu);
-      if (ambiguous) {
-        done = true;
-      } else if (tgroup.y == 0u && ngroup.y <= 0x00ffffffu) {
-        if (sp == 0) done = true;
-        else ngroup = stack[--sp];
-      }
-    }
-    if (owns) {
-      PrimRec r;
-      r.v0 = V3(__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z));
-      r.v1 = V3(__uint_as_float(r0.w), __uint_as_float(r1.x), __uint_as_float(r1.y));
-      r.v2 = V3(__uint_as_float(r1.z), __uint_as_float(r1.w), __uint_as_float(r2.x));
-      r.prim = int(r2.y); r.geom = int(r2.z); r.leaf = int(r2.w);
-#ifdef PB2_COUNT
-      c_prims++;
-#endif
-      test_prim(r);
-      while (tight && tgroup.y != 0u && !done) {  // coherent warp: drain the group
-        const int i = __ffs(tgroup.y) - 1;
-        tgroup.y &= tgroup.y - 1;
-#ifdef PB2_COUNT
-        c_prims++;
-#endif
-        test_prim(load_prim(sc.wide_prims, tgroup.x + i));
-      }
-      if (!done && tgroup.y == 0u && ngroup.y <= 0x00ffffffu) {  // back to walking: restore the invariant
-        if (sp == 0) done = true;
-        else ngroup = stack[--sp];
-      }
-    }
-#else
     // ---- node step: every lane that has no primitives left to test ----
     const bool walking = active && tgroup.y == 0u;
     if (walking) {
@@ -285,7 +203,6 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         else ngroup = stack[--sp];
       }
     }
-#endif
     if (done) {
       if (ANY) {
         if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
