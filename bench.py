@@ -229,7 +229,21 @@ def measure(args, workload, steps, warmup, world, rank, dev, ts, l2_gbs=None, ma
     B.upload_tables(spp)
     barrier()
     t0 = time.perf_counter()
-    B.upload_scene(S)
+    if world == 1:
+        B.upload_scene(S)
+    else:
+        # ONE host build per node: rank 0 builds and exports its built scene to /dev/shm, the other ranks map it
+        # (pb2_export_host_scene / pb2_import_host_scene) instead of building the same tree N times on one host
+        shared = f"/dev/shm/pb2_scene_{os.environ.get('MASTER_PORT', '0')}_{workload}.bin"
+        if rank == 0:
+            B.upload_scene(S)
+            B.export_scene(shared)
+        dist.barrier()
+        if rank != 0:
+            B.import_scene(shared, S.size)
+        dist.barrier()
+        if rank == 0:
+            os.unlink(shared)
     upload_s = time.perf_counter() - t0
     film_t = None
 
@@ -404,8 +418,10 @@ def measure(args, workload, steps, warmup, world, rank, dev, ts, l2_gbs=None, ma
         "e2e_cold": {"value": total_samples / cold_s / 1e6, "unit": "Msamples/s", "seconds": cold_s,
                      "scene_description_s": t_scene,
                      "what": "ONE drop-in call as Integrator::render(Scene&) makes it: pb2_upload_scene (host SAH "
-                             "build + wide layout + page-lock + H2D) + render + film to the host, first call on a "
-                             "fresh context (allocations included); max over ranks"},
+                             "build + wide layout + H2D) + render + film to the host, first call on a fresh context "
+                             "(allocations included); max over ranks"
+                             + ("" if world == 1 else "; rank 0 builds once and shares the built scene with the other "
+                                "ranks through /dev/shm (pb2_export_host_scene / pb2_import_host_scene)")},
         "gpu_launches": int(launches),
         "clocks": clock_info,
         "roofline": roof,
@@ -435,8 +451,6 @@ def run_gpu(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # every rank builds the same tree on the same host: share the cores instead of oversubscribing them
-        os.environ.setdefault("PB2_BUILD_THREADS", str(max(1, (os.cpu_count() or 8) // world)))
         dist.init_process_group("nccl", device_id=dev)
     # render, staging copies and collectives share ONE non-default stream (the context's own stream is
     # non-blocking and NCCL orders against torch's current stream only)

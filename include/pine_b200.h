@@ -242,6 +242,14 @@ int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* scene);
  * context's stream). What pb2_upload_scene does after the host build; exposed so that a caller
  * (bench.py's end-to-end leg) can put the host->device transfer inside a timed region. */
 int pb2_restage_scene(pb2_context* ctx, void* cuda_stream);
+/* One host build for all the PROCESSES of a node (one process per GPU): the process that ran pb2_upload_scene
+ * writes its built scene -- BVHs, primitive records, pools, scalar state -- to `path` (use /dev/shm: page cache,
+ * no disk), and the others call pb2_import_host_scene INSTEAD of pb2_upload_scene: the file is mapped, staged to
+ * the device, and from then on the context behaves as if it had built the scene (pb2_restage_scene[_part],
+ * renders); only the tree dumps pb2_bvh_info / pb2_bvh_nodes stay with the builder. The file may be unlinked
+ * once every importer has returned. (Inside one process pb2_multi shares the build without a file.) */
+int pb2_export_host_scene(pb2_context* ctx, const char* path);
+int pb2_import_host_scene(pb2_context* ctx, const char* path);
 /* Staging for REPLICAS on one NVLink domain (one context per GPU, same scene on each): instead of every GPU
  * pulling the whole scene through PCIe, part `part` of `n_parts` copies only its 1/n_parts slice of every large
  * array (>= 1 MiB) from pinned host memory -- small arrays and the sampler tables whole -- and the caller

@@ -148,6 +148,7 @@ ABI_SYMBOLS = [
     "pb2_create_multi", "pb2_destroy_multi", "pb2_multi_size", "pb2_multi_context", "pb2_multi_upload_sampler_tables",
     "pb2_multi_load_sampler_tables_file", "pb2_multi_upload_scene", "pb2_multi_restage_scene", "pb2_multi_render",
     "pb2_multi_get_counters", "pb2_measure_read_gbs", "pb2_film_finalize_device", "pb2_multi_film_finalize",
+    "pb2_export_host_scene", "pb2_import_host_scene",
 ]
 SHARD_SAMPLES, SHARD_ROWS = 0, 1
 
@@ -200,6 +201,8 @@ def lib():
                                     C.c_void_p]
         L.pb2_film_finalize_device.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.pb2_multi_film_finalize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.pb2_export_host_scene.argtypes = [C.c_void_p, C.c_char_p]
+        L.pb2_import_host_scene.argtypes = [C.c_void_p, C.c_char_p]
         L.pb2_measure_read_gbs.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_double)]
         L.pb2_create_multi.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
         L.pb2_destroy_multi.argtypes = [C.c_void_p]

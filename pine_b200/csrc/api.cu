@@ -65,6 +65,7 @@ extern "C" void pb2_destroy(pb2_context* ctx) {
     if (ctx->ev3) cudaEventDestroy(ctx->ev3);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
   }
+  ctx->host.unmap();
   delete ctx;
 }
 

@@ -86,6 +86,11 @@ struct HostScene {
   struct Item { DBuf pb2_context::* dst; const void* src; size_t bytes; };
   std::vector<Item> items;
   std::vector<void*> registered;    // ranges currently page-locked
+  // pb2_import_host_scene: the arrays live in a private file mapping (written by another process's
+  // pb2_export_host_scene) instead of the vectors above
+  void* map_base = nullptr;
+  size_t map_size = 0;
+  void unmap();
   bool pinned = false;
   void pin() {  // page-lock the large staging arrays (once): repeated staging then runs at PCIe speed
     if (pinned) return;

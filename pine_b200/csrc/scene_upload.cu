@@ -10,6 +10,11 @@
 #include <cstring>
 #include <thread>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include "bvh_layout.h"
 #include "context.h"
 
@@ -158,6 +163,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   // ---- host copies (kept, pinned, for re-staging) ----
   HostScene& H = ctx->host;
   H.unpin();
+  H.unmap();
   H = HostScene();
   H.geoms = std::move(geoms);
   H.lights = std::move(lights);
@@ -343,7 +349,6 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   s.camera = sd->camera;
   ctx->n_pixels = sd->camera.width * sd->camera.height;
   ctx->host_scene_ready = true;
-  if (ctx->device < 0) return PB2_OK;  // host-only context: builder inspection, no device work
 
   // ---- staging list + page-lock ----
   uint64_t bytes = 0;
@@ -364,6 +369,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   // call) copies from pageable memory and the arrays are page-locked by the first RE-staging (HostScene::pin),
   // which is the caller that profits from pinned copies.
   ctx->counters.scene_bytes = bytes;
+  if (ctx->device < 0) return PB2_OK;  // host-only context: builder inspection / export, no device work
   if (ctx->defer_staging) return PB2_OK;  // pb2_multi_upload_scene stages the replicas itself (sharded + all-gather)
   int rc = restage_unpinned(ctx);
   if (rc) return rc;
@@ -450,6 +456,129 @@ extern "C" int pb2_restage_scene(pb2_context* ctx, void* cuda_stream) {
 extern "C" int pb2_restage_scene_part(pb2_context* ctx, void* cuda_stream, int part, int n_parts,
                                       pb2_device_array* arrays, int max_arrays, int* n_arrays) {
   return restage(ctx, cuda_stream, part, n_parts, arrays, max_arrays, n_arrays);
+}
+
+// ---- sharing one host build between the processes of a node ---------------------------------------------------
+// With one process per GPU (torchrun) every rank would build the same tree on the same host. Instead ONE rank
+// builds (pb2_upload_scene) and writes its staging arrays plus the scalar scene state to a file -- /dev/shm: page
+// cache, no disk -- and the others map that file and stage from it; everything downstream (pb2_restage_scene,
+// pb2_restage_scene_part, the renders) is unchanged because a HostScene is just a list of (member, pointer, bytes).
+namespace {
+struct SharedHeader {
+  char magic[8];  // "PB2SCN02"
+  uint32_t sizeof_dscene, n_items;
+  DScene scene;   // device pointers inside are meaningless to the importer and rebound by the staging
+  int32_t only_area_lights, needs_rng_in_shading, n_pixels;
+  uint32_t material_kinds;
+  pb2_counters counters;
+};
+// the staging members in the order pb2_upload_scene lists them (ITEM(...) above)
+DBuf pb2_context::* const kStageMembers[] = {
+    &pb2_context::nodes2, &pb2_context::nodes8, &pb2_context::leaves, &pb2_context::wide_prims, &pb2_context::box_shapes,
+    &pb2_context::leaf_prims, &pb2_context::top_prims, &pb2_context::meshes, &pb2_context::geoms, &pb2_context::lights,
+    &pb2_context::light_recs, &pb2_context::verts, &pb2_context::tris, &pb2_context::normals, &pb2_context::uvs,
+    &pb2_context::texels, &pb2_context::textures, &pb2_context::srgb_lut, &pb2_context::materials, &pb2_context::aabbs,
+    &pb2_context::obbs, &pb2_context::spheres, &pb2_context::triangles, &pb2_context::cones, &pb2_context::rects,
+    &pb2_context::disks};
+constexpr uint32_t kNumStageMembers = sizeof(kStageMembers) / sizeof(kStageMembers[0]);
+constexpr size_t kShareAlign = 4096;
+size_t align_up(size_t v) { return (v + kShareAlign - 1) / kShareAlign * kShareAlign; }
+}  // namespace
+
+void pb2::HostScene::unmap() {
+  if (map_base) munmap(map_base, map_size);
+  map_base = nullptr;
+  map_size = 0;
+}
+
+extern "C" int pb2_export_host_scene(pb2_context* ctx, const char* path) {
+  if (!ctx || !path) { set_error("null argument"); return PB2_E_INVALID; }
+  if (!ctx->host_scene_ready || ctx->host_view) { set_error("pb2_export_host_scene needs a scene this context built"); return PB2_E_STATE; }
+  const HostScene& H = ctx->host;
+  if (H.items.size() != kNumStageMembers) { set_error("staging list out of date"); return PB2_E_STATE; }
+  for (uint32_t i = 0; i < kNumStageMembers; i++)
+    if (H.items[i].dst != kStageMembers[i]) { set_error("staging list order changed"); return PB2_E_STATE; }
+  SharedHeader hd{};
+  std::memcpy(hd.magic, "PB2SCN02", 8);
+  hd.sizeof_dscene = uint32_t(sizeof(DScene));
+  hd.n_items = kNumStageMembers;
+  hd.scene = ctx->scene;
+  hd.only_area_lights = ctx->only_area_lights; hd.needs_rng_in_shading = ctx->needs_rng_in_shading;
+  hd.n_pixels = ctx->n_pixels; hd.material_kinds = ctx->material_kinds;
+  hd.counters = ctx->counters;
+  std::vector<uint64_t> table(2 * size_t(kNumStageMembers));
+  size_t off = align_up(sizeof(SharedHeader) + table.size() * 8);
+  for (uint32_t i = 0; i < kNumStageMembers; i++) {
+    table[2 * i] = H.items[i].bytes;
+    table[2 * i + 1] = off;
+    off += align_up(H.items[i].bytes);
+  }
+  const std::string tmp = std::string(path) + ".tmp";
+  int fd = open(tmp.c_str(), O_CREAT | O_TRUNC | O_RDWR, 0600);
+  if (fd < 0) { set_error("cannot create " + tmp); return PB2_E_INVALID; }
+  bool ok = ftruncate(fd, off_t(off)) == 0;
+  void* base = ok ? mmap(nullptr, off, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0) : MAP_FAILED;
+  close(fd);
+  if (base == MAP_FAILED) { unlink(tmp.c_str()); set_error("cannot map " + tmp); return PB2_E_INVALID; }
+  std::memcpy(base, &hd, sizeof(hd));
+  std::memcpy(static_cast<char*>(base) + sizeof(hd), table.data(), table.size() * 8);
+  // the copies are the cost of this call (1.4 GB on C5): spread them over the builder's threads
+  const int threads = int(std::max<uint32_t>(1, ctx->counters.build_threads));
+  parallel_jobs(kNumStageMembers, threads, [&](size_t i) {
+    if (H.items[i].bytes) std::memcpy(static_cast<char*>(base) + table[2 * i + 1], H.items[i].src, H.items[i].bytes);
+  });
+  munmap(base, off);
+  if (rename(tmp.c_str(), path) != 0) { unlink(tmp.c_str()); set_error(std::string("cannot rename to ") + path); return PB2_E_INVALID; }
+  return PB2_OK;
+}
+
+extern "C" int pb2_import_host_scene(pb2_context* ctx, const char* path) {
+  if (!ctx || !path) { set_error("null argument"); return PB2_E_INVALID; }
+  if (ctx->device >= 0) PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  int fd = open(path, O_RDONLY);
+  if (fd < 0) { set_error(std::string("cannot open ") + path); return PB2_E_INVALID; }
+  struct stat st{};
+  if (fstat(fd, &st) != 0 || size_t(st.st_size) < sizeof(SharedHeader)) { close(fd); set_error("shared scene file too small"); return PB2_E_INVALID; }
+  // private mapping: pages stay shared with the page cache until written (never), and can be page-locked
+  void* base = mmap(nullptr, size_t(st.st_size), PROT_READ | PROT_WRITE, MAP_PRIVATE, fd, 0);
+  close(fd);
+  if (base == MAP_FAILED) { set_error("cannot map the shared scene file"); return PB2_E_INVALID; }
+  SharedHeader hd;
+  std::memcpy(&hd, base, sizeof(hd));
+  const uint64_t* table = reinterpret_cast<const uint64_t*>(static_cast<const char*>(base) + sizeof(hd));
+  bool ok = std::memcmp(hd.magic, "PB2SCN02", 8) == 0 && hd.sizeof_dscene == sizeof(DScene) && hd.n_items == kNumStageMembers &&
+            size_t(st.st_size) >= sizeof(hd) + size_t(hd.n_items) * 16;
+  for (uint32_t i = 0; ok && i < hd.n_items; i++) ok = table[2 * i + 1] + table[2 * i] <= uint64_t(st.st_size);
+  if (!ok) { munmap(base, size_t(st.st_size)); set_error("not a scene file of this library version"); return PB2_E_INVALID; }
+  ctx->scene_ready = false;
+  ctx->host_scene_ready = false;
+  ctx->host_view = nullptr;
+  HostScene& H = ctx->host;
+  H.unpin();
+  H.unmap();
+  H = HostScene();
+  H.map_base = base;
+  H.map_size = size_t(st.st_size);
+  for (uint32_t i = 0; i < hd.n_items; i++)
+    H.items.push_back(HostScene::Item{kStageMembers[i], static_cast<const char*>(base) + table[2 * i + 1], size_t(table[2 * i])});
+  ctx->top_tree = Tree2();  // the tree dumps (pb2_bvh_nodes) stay with the process that built
+  ctx->mesh_trees.clear();
+  ctx->scene = hd.scene;
+  ctx->only_area_lights = hd.only_area_lights != 0;
+  ctx->needs_rng_in_shading = hd.needs_rng_in_shading != 0;
+  ctx->n_pixels = hd.n_pixels;
+  ctx->material_kinds = hd.material_kinds;
+  const pb2_counters keep = ctx->counters;
+  ctx->counters = hd.counters;
+  ctx->counters.closest_rays = keep.closest_rays; ctx->counters.shadow_rays = keep.shadow_rays;
+  ctx->counters.camera_samples = keep.camera_samples; ctx->counters.kernel_launches = keep.kernel_launches;
+  ctx->host_scene_ready = true;
+  if (ctx->device < 0) return PB2_OK;
+  int rc = restage_unpinned(ctx);
+  if (rc) return rc;
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+  ctx->scene_ready = true;
+  return PB2_OK;
 }
 
 extern "C" int pb2_bvh_info(pb2_context* ctx, int which, int32_t* n_nodes, int32_t* root,

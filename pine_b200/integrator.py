@@ -150,6 +150,15 @@ class Backend:
         self._scene_keep = (scene, keep)
         self.size = scene.size
 
+    def export_scene(self, path):
+        """Write the scene this backend BUILT to `path` (/dev/shm/...) for the other processes of the node."""
+        A.check(self.L.pb2_export_host_scene(self.h, os.fsencode(path)))
+
+    def import_scene(self, path, size):
+        """Adopt a scene another process built and exported (instead of upload_scene); `size` = (w, h) of its film."""
+        A.check(self.L.pb2_import_host_scene(self.h, os.fsencode(path)))
+        self.size = (int(size[0]), int(size[1]))
+
     def upload_tables(self, spp):
         if spp in self._tables_loaded:
             return

@@ -93,3 +93,26 @@ def test_empty_scene_builds():
     S.set_camera((4, 4), (0, 0, -3), (0, 0, 0), 0.3)
     B.upload_scene(S)
     assert B.counters()["wide_nodes"] == 0
+
+
+def test_built_scene_is_shared_between_contexts_through_a_file(tmp_path):
+    """pb2_export_host_scene / pb2_import_host_scene (one host build per node with one process per GPU): the
+    importer holds the same staging bytes and scene state as the builder -- its own export is the same file."""
+    from pine_b200 import scenes
+    S = pb.Scene()
+    scenes.mesh_field(S, n_instances=27, subdiv=2, seed=3, size=(64, 48))
+    builder, importer = pb.Backend(-1), pb.Backend(-1)
+    builder.upload_scene(S)
+    a, b = str(tmp_path / "a.bin"), str(tmp_path / "b.bin")
+    builder.export_scene(a)
+    importer.import_scene(a, S.size)
+    ca, cb = builder.counters(), importer.counters()
+    assert all(ca[k] == cb[k] for k in ("bvh2_nodes", "wide_nodes", "n_primitives", "scene_bytes"))
+    importer.export_scene(b)
+    assert open(a, "rb").read() == open(b, "rb").read()
+    with open(a, "r+b") as f:  # a foreign / truncated file is refused
+        f.write(b"XXXXXXXX")
+    with pytest.raises(pb.PineB200Error):
+        pb.Backend(-1).import_scene(a, S.size)
+    with pytest.raises(pb.PineB200Error):
+        pb.Backend(-1).export_scene(b)  # nothing built

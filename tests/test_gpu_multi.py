@@ -133,3 +133,31 @@ def test_dropin_shim_uses_every_gpu_and_matches_one_gpu():
     assert stn["closest_rays"] == st1["closest_rays"]
     film_ref, _ = R.render(16, cfg["depth"])
     assert relmse(allg, film_ref) <= 1e-4
+
+
+def test_imported_scene_renders_like_the_built_one(tmp_path):
+    """One host build per node for one-process-per-GPU setups: a context that IMPORTS the scene another context
+    built (pb2_export_host_scene / pb2_import_host_scene) renders the same film bits, before and after a
+    re-staging from the mapped file, and its sharded staging slices are usable (bench.py at N > 1)."""
+    S = pb.Scene()
+    cfg = scenes.mesh_field(S, n_instances=64, subdiv=3, seed=11, size=(160, 96), spp=8, depth=5, with_shapes=True)
+    A = pb.Backend(0)
+    A.upload_scene(S)
+    want = A.render(8, 5)
+    path = str(tmp_path / "scene.bin")
+    A.export_scene(path)
+    B = pb.Backend(0)
+    B.import_scene(path, S.size)
+    import os
+    os.unlink(path)  # the mapping keeps the pages
+    assert np.array_equal(u32(B.render(8, 5)), u32(want))
+    B.restage()
+    assert np.array_equal(u32(B.render(8, 5)), u32(want))
+    for part in range(2):  # both halves of the sharded staging, one after the other = the whole scene again
+        B.restage_part(part, 2)
+    assert np.array_equal(u32(B.render(8, 5)), u32(want))
+    rays = A.primary_rays(0)
+    ha, hb = A.trace_closest(rays), B.trace_closest(rays)
+    assert np.array_equal(ha["prim"], hb["prim"]) and np.array_equal(u32(ha["t"]), u32(hb["t"]))
+    A.close()
+    B.close()
