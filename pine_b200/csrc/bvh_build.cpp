@@ -48,7 +48,11 @@ struct Builder {
   // each primitive's bucket (same float expressions per primitive and axis, and min/max and integer
   // counts do not depend on the order they are accumulated in, so every number is the reference's).
   std::vector<uint8_t> bucket_scratch;  // [3][count] of the range being split
-  BuildPrim* choose_split(BuildPrim* first, BuildPrim* last, const Box3& bounds, Box3 (&child_box)[2]) {
+  // `cb` (optional): the centroid bounds of [first,last) if the caller already has them -- the parent's
+  // partition pass computes its children's while it computes their boxes, which saves the separate pass over
+  // the range (min / max accumulate exactly, in any order). `child_cb` receives the children's.
+  BuildPrim* choose_split(BuildPrim* first, BuildPrim* last, const Box3& bounds, Box3 (&child_box)[2],
+                          const Box3* cb, Box3 (&child_cb)[2]) {
     const int count = int(last - first);
     if (count == 1) return nullptr;
 
@@ -59,13 +63,17 @@ struct Builder {
     // and never leaves the registers.
     const __m128 half = _mm_set1_ps(0.5f);
     __m128 clo = _mm_set1_ps(kFloatMax), chi = _mm_set1_ps(-kFloatMax);
-    for (int i = 0; i < count; i++) {
-      const __m128 c = _mm_mul_ps(_mm_add_ps(_mm_loadu_ps(&first[i].box.lower.x), _mm_loadu_ps(&first[i].box.upper.x)), half);
-      clo = _mm_min_ps(clo, c);
-      chi = _mm_max_ps(chi, c);
-    }
     Box3 cbounds;
-    {
+    if (cb) {
+      cbounds = *cb;
+      clo = _mm_setr_ps(cb->lower.x, cb->lower.y, cb->lower.z, 0.0f);
+      chi = _mm_setr_ps(cb->upper.x, cb->upper.y, cb->upper.z, 0.0f);
+    } else {
+      for (int i = 0; i < count; i++) {
+        const __m128 c = _mm_mul_ps(_mm_add_ps(_mm_loadu_ps(&first[i].box.lower.x), _mm_loadu_ps(&first[i].box.upper.x)), half);
+        clo = _mm_min_ps(clo, c);
+        chi = _mm_max_ps(chi, c);
+      }
       float t[4];
       _mm_storeu_ps(t, clo); cbounds.lower = V3(t[0], t[1], t[2]);
       _mm_storeu_ps(t, chi); cbounds.upper = V3(t[0], t[1], t[2]);
@@ -116,7 +124,8 @@ struct Builder {
       }
 #else
     Box3 cbounds;
-    for (int i = 0; i < count; i++) cbounds.extend(first[i].box.centroid());
+    if (cb) cbounds = *cb;
+    else for (int i = 0; i < count; i++) cbounds.extend(first[i].box.centroid());
     const float parent_area = bounds.surface_area();
 
     const bool live[3] = {!cbounds.degenerated(0), !cbounds.degenerated(1), !cbounds.degenerated(2)};
@@ -208,27 +217,36 @@ struct Builder {
 #ifdef PB2_BUILD_SSE
     for (int c = 0; c < 2; c++) {
       __m128 lo = _mm_set1_ps(kFloatMax), hi = _mm_set1_ps(-kFloatMax);
+      __m128 cl = lo, ch = hi;
       for (BuildPrim* p = c ? mid : first; p != (c ? last : mid); ++p) {
-        lo = _mm_min_ps(lo, _mm_loadu_ps(&p->box.lower.x));
-        hi = _mm_max_ps(hi, _mm_loadu_ps(&p->box.upper.x));
+        const __m128 pl = _mm_loadu_ps(&p->box.lower.x), ph = _mm_loadu_ps(&p->box.upper.x);
+        lo = _mm_min_ps(lo, pl);
+        hi = _mm_max_ps(hi, ph);
+        const __m128 ctr = _mm_mul_ps(_mm_add_ps(pl, ph), half);
+        cl = _mm_min_ps(cl, ctr);
+        ch = _mm_max_ps(ch, ctr);
       }
       float t[4];
       _mm_storeu_ps(t, lo); child_box[c].lower = V3(t[0], t[1], t[2]);
       _mm_storeu_ps(t, hi); child_box[c].upper = V3(t[0], t[1], t[2]);
+      _mm_storeu_ps(t, cl); child_cb[c].lower = V3(t[0], t[1], t[2]);
+      _mm_storeu_ps(t, ch); child_cb[c].upper = V3(t[0], t[1], t[2]);
     }
 #else
-    for (BuildPrim* p = first; p != mid; ++p) child_box[0].extend(p->box);
-    for (BuildPrim* p = mid; p != last; ++p) child_box[1].extend(p->box);
+    child_cb[0] = child_cb[1] = Box3();
+    for (BuildPrim* p = first; p != mid; ++p) { child_box[0].extend(p->box); child_cb[0].extend(p->box.centroid()); }
+    for (BuildPrim* p = mid; p != last; ++p) { child_box[1].extend(p->box); child_cb[1].extend(p->box.centroid()); }
 #endif
     return mid;
   }
 
-  int split(BuildPrim* first, BuildPrim* last, const Box3& bounds) {
+  int split(BuildPrim* first, BuildPrim* last, const Box3& bounds, const Box3* cb = nullptr) {
     Node2 node;
-    BuildPrim* mid = choose_split(first, last, bounds, node.box);
+    Box3 child_cb[2];
+    BuildPrim* mid = choose_split(first, last, bounds, node.box, cb, child_cb);
     if (!mid) return make_leaf(first, last);
-    node.child[0] = split(first, mid, node.box[0]);
-    node.child[1] = split(mid, last, node.box[1]);
+    node.child[0] = split(first, mid, node.box[0], &child_cb[0]);
+    node.child[1] = split(mid, last, node.box[1], &child_cb[1]);
     tree.nodes.push_back(node);
     return int(tree.nodes.size()) - 1;
   }
@@ -253,7 +271,8 @@ void split_parallel(BuildPrim* first, BuildPrim* last, const Box3& bounds, Tree2
   Builder b{out};
   if (last - first < kParallelMin) { b.split(first, last, bounds); return; }
   Node2 node;
-  BuildPrim* mid = b.choose_split(first, last, bounds, node.box);
+  Box3 child_cb[2];
+  BuildPrim* mid = b.choose_split(first, last, bounds, node.box, nullptr, child_cb);
   if (!mid) { b.make_leaf(first, last); return; }
   Tree2 right;
   if (g_spare_threads.fetch_sub(1) > 0) {

@@ -68,8 +68,8 @@ struct HostScene {
   std::vector<DGeom> geoms;
   std::vector<int32_t> lights;
   std::vector<pb2_light> light_recs;
-  std::vector<float> verts, normals, uvs;
-  std::vector<uint32_t> tris;
+  raw_vector<float> verts, normals, uvs;  // (raw_vector: no zero-fill of pools the upload overwrites completely)
+  raw_vector<uint32_t> tris;
   std::vector<pb2_material> materials;
   std::vector<uint32_t> texels;
   std::vector<DTexture> textures;
