@@ -23,7 +23,9 @@ void launch_trace_any(const DScene& sc, const float* rays, size_t n, int accel, 
 
 constexpr int kNumSMs = 148;  // B200
 constexpr int kTraceBlock = 128;
-constexpr int kFallbackBlocksPerSM = 6;  // reference-order re-trace: one ray per thread, latency bound
+constexpr int kFallbackBlocksPerSM = 8;  // reference-order re-trace: one ray per thread, latency bound. ncu on C1
+                                         // (profiles/r2/s17): at 6 blocks x 72 registers the kernel ran 24 of 64 warps
+                                         // per SM; 8 blocks at <= 64 registers (launch bounds) fill the register file
 #ifndef PB2_TRACE_MINBLOCKS
 #define PB2_TRACE_MINBLOCKS 8  // __launch_bounds__ min blocks per SM of the persistent traversal kernels
 #endif

@@ -207,7 +207,7 @@ __device__ __forceinline__ ShadowIO shadow_io(const WaveView& w, int depth) {
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_trace(DScene sc, WaveView w, int depth) {
   wide_persistent<false>(sc, w.counts[depth], wave_queue(w, depth, 0), trace_io(w, depth));
 }
-__global__ void __launch_bounds__(kTraceBlock) k_trace_fallback(DScene sc, WaveView w, int depth) {
+__global__ void __launch_bounds__(kTraceBlock, kFallbackBlocksPerSM) k_trace_fallback(DScene sc, WaveView w, int depth) {
   wide_fallback<false>(sc, wave_queue(w, depth, 0), trace_io(w, depth));
 }
 __global__ void __launch_bounds__(kTraceBlock) k_trace_ref(DScene sc, WaveView w, int depth) {
@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace_ref(DScene sc, WaveView w
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_shadow(DScene sc, WaveView w, int depth) {
   wide_persistent<true>(sc, w.counts[w.max_depth + 1 + depth], wave_queue(w, depth, 1), shadow_io(w, depth));
 }
-__global__ void __launch_bounds__(kTraceBlock) k_shadow_fallback(DScene sc, WaveView w, int depth) {
+__global__ void __launch_bounds__(kTraceBlock, kFallbackBlocksPerSM) k_shadow_fallback(DScene sc, WaveView w, int depth) {
   wide_fallback<true>(sc, wave_queue(w, depth, 1), shadow_io(w, depth));
 }
 __global__ void __launch_bounds__(kTraceBlock) k_shadow_ref(DScene sc, WaveView w, int depth) {

@@ -29,7 +29,7 @@ class PrlError(Exception):
 _TOKEN = re.compile(r"""
     (?P<ws>\s+|\#[^\n]*)
   | (?P<num>\d+\.\d*(?:[eE][-+]?\d+)?|\.\d+(?:[eE][-+]?\d+)?|\d+[eE][-+]?\d+|\d+)
-  | (?P<str>"[^"\n]*")
+  | (?P<str>"[^"\n]*"|'[^'\n]*')
   | (?P<id>[A-Za-z_][A-Za-z_0-9]*)
   | (?P<op>:=|[-+*/~.,;(){}\[\]=])
 """, re.X)
@@ -223,6 +223,11 @@ def _vec(v, n=3):
 def _arith(op, a, b):
     """int op int stays int (jit.cpp integer ops); otherwise binary32, element-wise over vectors,
     4x4 * 4x4 through the C++ host mirror of vecmath.h."""
+    if isinstance(a, str) or isinstance(b, str):  # 'images/pine' + f + '.png' (jit.cpp string concatenation)
+        if op != "+":
+            raise PrlError("only + is defined on strings")
+        fmt = lambda v: v if isinstance(v, str) else (str(v) if isinstance(v, int) else repr(float(v)))
+        return fmt(a) + fmt(b)
     is_mat = lambda x: isinstance(x, np.ndarray) and x.shape == (4, 4)
     if is_mat(a) or is_mat(b):
         if op == "*" and is_mat(a) and is_mat(b):
@@ -382,6 +387,12 @@ def _globals(make_scene):
         "Glossy": lambda c, r, ior=1.4: _Material("glossy", _vec(c), roughness=float(_f32(r)), ior=float(_f32(ior))),
         "Glass": lambda c, r, ior=1.4: _Material("glass", _vec(c), roughness=float(_f32(r)), ior=float(_f32(ior))),
         "Subsurface": _subsurface,
+        # UberMaterial(albedo, roughness, metallic = 0, transmission = 0, ior = 1.45) (material.h:80-87, .cpp:53-57)
+        "Uber": lambda c, r, metallic=0.0, transmission=0.0, ior=1.45: _Material(
+            "uber", _vec(c), roughness=float(_f32(r)), metallic=float(_f32(metallic)),
+            transmission=float(_f32(transmission)), ior=float(_f32(ior))),
+        "Pi": np.float32(3.14159265358979323846),  # ctx.var("Pi") (math.cpp:7)
+        "print": lambda *a: None, "println": lambda *a: None,  # LOG output only (program_context.cpp:41)
         "translate": lambda v: mat4.translate(_vec(v)), "scale": lambda v: mat4.scale(_vec(v)),
         "rotate_x": lambda r: mat4.rotate_x(float(_f32(r))), "rotate_y": lambda r: mat4.rotate_y(float(_f32(r))),
         "rotate_z": lambda r: mat4.rotate_z(float(_f32(r))),

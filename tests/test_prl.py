@@ -204,3 +204,35 @@ def test_minimal_scene_renders_like_the_reference(golden, tmp_path):
     assert abs(float(film[..., :3].astype(np.float64).sum()) / float(g["film_sum"][0]) - 1) < 1e-5
     assert relmse(film, g["film"].astype(np.float32)) <= 1e-4  # the fixture is stored as float16
     assert (tmp_path / "minimal.png").stat().st_size > 1000
+
+
+@needs_reference_tree
+def test_pine_pine_loads_through_the_subset():
+    """scenes/pine.pine: single-quoted strings, a `for f in 0.0~0.2~Pi` loop that builds a scene per iteration,
+    string + number concatenation for the file name, println -- 16 PathIntegrator(BlueSampler(4), 3) renders of
+    a Cone under a Rect emitter, the second scene.set(camera) winning."""
+    calls = []
+    text = open(os.path.join(REFERENCE, "scenes", "pine.pine")).read()
+    sps = prl.load(text, pb.Scene, on_render=lambda sp, spp, depth: calls.append(("render", spp, depth)),
+                   on_save=lambda *a: calls.append(("save", a[-1])))
+    assert len(sps) == 16
+    assert [c for c in calls if c[0] == "render"] == [("render", 4, 3)] * 16
+    saves = [c[1] for c in calls if c[0] == "save"]
+    assert saves[0] == "images/pine0.0.png" and len(set(saves)) == 16
+    S = sps[-1].target
+    d, keep = S.desc()
+    assert d.n_cones == 1 and d.n_rects == 1 and d.n_geometries == 2 and d.n_lights == 1
+    assert tuple(d.camera.position) == (0.0, 0.0, -8.0) and (d.camera.width, d.camera.height) == (640, 360)
+
+
+def test_uber_material_and_string_rules():
+    sp, = prl.load("""
+        scene = Scene();
+        scene.add('m', Uber([0.98, 0.55, 0.02], 0.25, 1.0));
+        scene.add(Sphere([0, 1, 0], 1), 'm');
+        name = 'a' + 2 + "b";
+    """, pb.Scene)
+    m = sp.target.materials[0]
+    assert m.kind == A.MATERIAL_KINDS["uber"] and abs(m.metallic - 1.0) < 1e-7 and abs(m.ior - 1.45) < 1e-6
+    with pytest.raises(prl.PrlError):
+        prl.load("x = 'a' * 2;", pb.Scene)
