@@ -297,6 +297,21 @@ int pb2_trace_any(pb2_context* ctx, const float* rays_host, size_t n, int accel,
 int pb2_trace_closest_device(pb2_context* ctx, const float* rays_dev, size_t n, int accel,
                              int32_t* geom_dev, int32_t* prim_dev, float* t_dev,
                              void* cuda_stream);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * pb2_trace_closest_device with its scratch (the persistent walk's claim counter, fallback count and fallback
+ * list, which the entry point above reserves with cudaMalloc as n grows) in a file-scope static __device__ array
+ * of PB2_NOALLOC_MAX_RAYS + 64 ints = 4 MiB + 256 B, which every GPU that loads the library holds until exit.
+ * Same arguments, same results bit for bit; the caller passes device inputs and outputs. Calls no cudaMalloc,
+ * cudaFree or allocating library routine. n > PB2_NOALLOC_MAX_RAYS => PB2_E_INVALID (split the batch). The
+ * first call on a device looks the array's address up (cudaGetSymbolAddress; n = 0 does only that, so make that
+ * call once outside any capture). Every call on a device shares the array and it keeps the last call's contents:
+ * the two counters are cleared on the launch stream before each launch, but two calls that OVERLAP on the GPU
+ * (different streams with no ordering between them) race on it -- order them, or use the entry point above. */
+#define PB2_NOALLOC_MAX_RAYS (1 << 20)
+int pb2_trace_closest_device_noalloc(pb2_context* ctx, const float* rays_dev, size_t n, int accel,
+                                     int32_t* geom_dev, int32_t* prim_dev, float* t_dev,
+                                     void* cuda_stream);
 /* Known-answer hooks for the sampler/camera kernels (Sampler wrapper sampler.h:286-309,
  * BlueSobolSampler sampler.h:166-201, ThinLenCamera::gen_ray camera.cpp:22-33). */
 /* Test hook: every ray a render traces. Set before pb2_render* (NULL clears). The render must fit
