@@ -25,6 +25,15 @@ constexpr int kRefillThreshold = PB2_REFILL;  // refill a warp when at least thi
 #ifndef PB2_TIGHT_LANES
 #define PB2_TIGHT_LANES 16
 #endif
+#ifndef PB2_BATCH_FINISH
+#define PB2_BATCH_FINISH 1  // 1: finished lanes certify and store their result together, when the warp refills
+#endif
+#ifndef PB2_NODE_PREFETCH
+#define PB2_NODE_PREFETCH 0  // 1: prefetch.global.L1 of the next iteration's node before the primitive step
+#endif
+#ifndef PB2_SMEM_STACK
+#define PB2_SMEM_STACK 0  // N > 0: the first N stack levels of every lane in shared memory, the rest in local memory
+#endif
 
 struct WideQueue {
   int* next;      // next unclaimed queue index (zero before the launch)
@@ -56,8 +65,23 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
 #else
   const uint4* s_top = nullptr;
 #endif
+#if PB2_SMEM_STACK > 0
+  __shared__ uint2 s_stack[PB2_SMEM_STACK][kTraceBlock];
+  uint2 stack[kWideStack - PB2_SMEM_STACK];
+  auto push = [&](int at, uint2 v) {
+    if (at < PB2_SMEM_STACK) s_stack[at][threadIdx.x] = v;
+    else stack[at - PB2_SMEM_STACK] = v;
+  };
+  auto pop = [&](int at) { return at < PB2_SMEM_STACK ? s_stack[at][threadIdx.x] : stack[at - PB2_SMEM_STACK]; };
+#else
   uint2 stack[kWideStack];
+  auto push = [&](int at, uint2 v) { stack[at] = v; };
+  auto pop = [&](int at) { return stack[at]; };
+#endif
   int sp = 0;
+#if PB2_BATCH_FINISH
+  bool pending = false;
+#endif
   bool active = false, drained = false;
   int idx = 0;
   Ray ray;
@@ -74,9 +98,42 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
   unsigned long long c_nodes = 0, c_prims = 0, c_rays = 0;
 #endif
 
+  // certification of a finished ray and its store (or its push onto the fallback list)
+  auto finish = [&]() {
+    if (ANY) {
+      if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
+      else io.store_any(idx, have);
+    } else {
+#ifdef PB2_COUNT
+      if (ambiguous && sc.walk_stats) atomicAdd(sc.walk_stats + 7, 1ull);
+#endif
+      if (have && !ambiguous) {
+        if (tie_t == ray.tmax) ambiguous = true;
+        else if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, ray.tmax)) {
+          // The exact leaf box can come out a few ulps BEHIND the hit it contains (flat boxes of
+          // Rects and axis-aligned triangles: two different float expressions for one distance).
+          // The reference still reaches the leaf if its tmax at that moment is large enough, and
+          // that tmax is tmax_in or the t of another primitive hit before: >= U (traverse.cuh (ii')).
+          const float U = pmin(pmin(tmax_in, t2), half_slack_of(ray.tmax));
+          if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, U)) ambiguous = true;
+        }
+#ifdef PB2_COUNT
+        if (ambiguous && sc.walk_stats) atomicAdd(sc.walk_stats + (tie_t == ray.tmax ? 8 : 9), 1ull);
+#endif
+      }
+      if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
+      else io.store_closest(sc, idx, ray, have, h);
+    }
+  };
+
   while (true) {
     // ---- refill idle lanes ----
     const unsigned idle = __ballot_sync(0xffffffffu, !active);
+#if PB2_BATCH_FINISH
+    if (idle == 0xffffffffu || (idle && !drained && __popc(idle) >= kRefillThreshold)) {
+      if (pending) { finish(); pending = false; }
+    }
+#endif
     if (idle && !drained && (__popc(idle) >= kRefillThreshold || idle == 0xffffffffu)) {
       int base = 0;
       const int want = __popc(idle);
@@ -165,7 +222,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
       const int bit = 31 - __clz(hits);
       ngroup.y &= ~(1u << bit);
       if (ngroup.y > 0x00ffffffu) {
-        if (sp < kWideStack) stack[sp++] = ngroup;
+        if (sp < kWideStack) push(sp++, ngroup);
         else ambiguous = true;
       }
       const uint32_t slot = uint32_t(bit - 24) ^ (w.octinv4 & 7u);
@@ -182,9 +239,22 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         done = true;
       } else if (tgroup.y == 0u && ngroup.y <= 0x00ffffffu) {
         if (sp == 0) done = true;
-        else ngroup = stack[--sp];
+        else ngroup = pop(--sp);
       }
     }
+#if PB2_NODE_PREFETCH
+    // The node this lane will test NEXT iteration is known now; its fetch then overlaps the primitive step.
+    if (active && !done && tgroup.y == 0u) {
+      const uint32_t nh = ngroup.y;
+      const uint32_t nslot = uint32_t(7 - __clz(nh)) ^ (w.octinv4 & 7u);
+      const uint32_t ni = ngroup.x + __popc(nh & 0xffu & ~(0xffffffffu << nslot));
+      if (ni >= uint32_t(PB2_SMEM_TOP)) {
+        const char* a = reinterpret_cast<const char*>(sc.nodes8 + ni);
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(a + 64));
+      }
+    }
+#endif
     // ---- primitive step ----
     const bool owns = active && !done && tgroup.y != 0u;
     const bool tight = __popc(__ballot_sync(0xffffffffu, owns)) >= PB2_TIGHT_LANES;
@@ -200,34 +270,15 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
       } while (tight && tgroup.y != 0u && !done);
       if (!done && tgroup.y == 0u && ngroup.y <= 0x00ffffffu) {  // back to walking: restore the invariant
         if (sp == 0) done = true;
-        else ngroup = stack[--sp];
+        else ngroup = pop(--sp);
       }
     }
     if (done) {
-      if (ANY) {
-        if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
-        else io.store_any(idx, have);
-      } else {
-#ifdef PB2_COUNT
-        if (ambiguous && sc.walk_stats) atomicAdd(sc.walk_stats + 7, 1ull);
+#if PB2_BATCH_FINISH
+      pending = true;
+#else
+      finish();
 #endif
-        if (have && !ambiguous) {
-          if (tie_t == ray.tmax) ambiguous = true;
-          else if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, ray.tmax)) {
-            // The exact leaf box can come out a few ulps BEHIND the hit it contains (flat boxes of
-            // Rects and axis-aligned triangles: two different float expressions for one distance).
-            // The reference still reaches the leaf if its tmax at that moment is large enough, and
-            // that tmax is tmax_in or the t of another primitive hit before: >= U (traverse.cuh (ii')).
-            const float U = pmin(pmin(tmax_in, t2), half_slack_of(ray.tmax));
-            if (!leaf_gate(sc.leaves, win_leaf, q, ray.tmin, U)) ambiguous = true;
-          }
-#ifdef PB2_COUNT
-          if (ambiguous && sc.walk_stats) atomicAdd(sc.walk_stats + (tie_t == ray.tmax ? 8 : 9), 1ull);
-#endif
-        }
-        if (ambiguous) wq.fb_list[atomicAdd(wq.fb_count, 1)] = idx;
-        else io.store_closest(sc, idx, ray, have, h);
-      }
       active = false;
       tgroup.y = 0u;
 #ifdef PB2_COUNT
