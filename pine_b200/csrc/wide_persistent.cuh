@@ -28,12 +28,6 @@ constexpr int kRefillThreshold = PB2_REFILL;  // refill a warp when at least thi
 #ifndef PB2_BATCH_FINISH
 #define PB2_BATCH_FINISH 1  // 1: finished lanes certify and store their result together, when the warp refills
 #endif
-#ifndef PB2_NODE_PREFETCH
-#define PB2_NODE_PREFETCH 0  // 1: prefetch.global.L1 of the next iteration's node before the primitive step
-#endif
-#ifndef PB2_SMEM_STACK
-#define PB2_SMEM_STACK 0  // N > 0: the first N stack levels of every lane in shared memory, the rest in local memory
-#endif
 
 struct WideQueue {
   int* next;      // next unclaimed queue index (zero before the launch)
@@ -65,19 +59,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
 #else
   const uint4* s_top = nullptr;
 #endif
-#if PB2_SMEM_STACK > 0
-  __shared__ uint2 s_stack[PB2_SMEM_STACK][kTraceBlock];
-  uint2 stack[kWideStack - PB2_SMEM_STACK];
-  auto push = [&](int at, uint2 v) {
-    if (at < PB2_SMEM_STACK) s_stack[at][threadIdx.x] = v;
-    else stack[at - PB2_SMEM_STACK] = v;
-  };
-  auto pop = [&](int at) { return at < PB2_SMEM_STACK ? s_stack[at][threadIdx.x] : stack[at - PB2_SMEM_STACK]; };
-#else
   uint2 stack[kWideStack];
-  auto push = [&](int at, uint2 v) { stack[at] = v; };
-  auto pop = [&](int at) { return stack[at]; };
-#endif
   int sp = 0;
 #if PB2_BATCH_FINISH
   bool pending = false;
@@ -222,7 +204,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
       const int bit = 31 - __clz(hits);
       ngroup.y &= ~(1u << bit);
       if (ngroup.y > 0x00ffffffu) {
-        if (sp < kWideStack) push(sp++, ngroup);
+        if (sp < kWideStack) stack[sp++] = ngroup;
         else ambiguous = true;
       }
       const uint32_t slot = uint32_t(bit - 24) ^ (w.octinv4 & 7u);
@@ -239,22 +221,9 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         done = true;
       } else if (tgroup.y == 0u && ngroup.y <= 0x00ffffffu) {
         if (sp == 0) done = true;
-        else ngroup = pop(--sp);
+        else ngroup = stack[--sp];
       }
     }
-#if PB2_NODE_PREFETCH
-    // The node this lane will test NEXT iteration is known now; its fetch then overlaps the primitive step.
-    if (active && !done && tgroup.y == 0u) {
-      const uint32_t nh = ngroup.y;
-      const uint32_t nslot = uint32_t(7 - __clz(nh)) ^ (w.octinv4 & 7u);
-      const uint32_t ni = ngroup.x + __popc(nh & 0xffu & ~(0xffffffffu << nslot));
-      if (ni >= uint32_t(PB2_SMEM_TOP)) {
-        const char* a = reinterpret_cast<const char*>(sc.nodes8 + ni);
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(a + 64));
-      }
-    }
-#endif
     // ---- primitive step ----
     const bool owns = active && !done && tgroup.y != 0u;
     const bool tight = __popc(__ballot_sync(0xffffffffu, owns)) >= PB2_TIGHT_LANES;
@@ -270,7 +239,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
       } while (tight && tgroup.y != 0u && !done);
       if (!done && tgroup.y == 0u && ngroup.y <= 0x00ffffffu) {  // back to walking: restore the invariant
         if (sp == 0) done = true;
-        else ngroup = pop(--sp);
+        else ngroup = stack[--sp];
       }
     }
     if (done) {
