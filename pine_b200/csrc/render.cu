@@ -270,7 +270,7 @@ __device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_materi
   }
   if (MAT == PB2_MAT_SUBSURFACE) {
     b.ior = 1.4f;  // SubsurfaceMaterial::ior (material.h:103)
-    float fr = FrDielectric(dot(wi_world, n), b.ior);
+    float fr = fresnel_unpolarized(dot(wi_world, n), b.ior);
     if (smp_get1d(sc, smp) < fr) { b.kind = BX_REFRACTIVE; b.roughness = pmax(m.roughness, min_roughness); }
     else if (diffused) b.kind = BX_DIFFUSE;
     else b.kind = BX_BSSRDF;
@@ -285,7 +285,7 @@ __device__ inline bool bssrdf_walk(const DScene& sc, const Bxdf& b, int geom, V3
                                    Smp& smp, Rng& g, V3& beta, V3& wi_out) {
   V3 p = it.p;
   V3 w = -wi_world;
-  if (!Refract(wi_world, it.n, b.ior, w)) return false;
+  if (!refract_through(wi_world, it.n, b.ior, w)) return false;
   int channel = int(rng_nextf(g) * 3);
   beta = V3(0.0f);
   beta[channel] = 3;
