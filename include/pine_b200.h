@@ -273,6 +273,13 @@ int pb2_load_sampler_tables_file(pb2_context* ctx, const char* path, int spp_pow
 /* Replaces: PathIntegrator::render's pixel loop (path.cpp:31-40). film_rgba: caller-owned HOST
  * buffer of width*height*4 floats, row-major p.x + p.y*width (array.h:51-55), pre-tonemap. */
 int pb2_render(pb2_context* ctx, const pb2_render_params* params, float* film_rgba_host);
+/* Replaces: `if (p.x % 64 == 0) set_progress(progress_2d(p, film.size()))` in the pixel loop (path.cpp:39;
+ * Atomic<float> g_progress, integrator.cpp:11-19, polled by the CLI's progress thread). While a render runs, `fn`
+ * is called with the fraction of its pixel waves that have COMPLETED on the device (monotone, ends at 1), from a
+ * CUDA driver thread (cudaLaunchHostFunc behind each wave): it must be thread-safe, return quickly and make no CUDA
+ * call -- storing an atomic, which is what pine::set_progress does, is the intended use. fn NULL clears. */
+typedef void (*pb2_progress_fn)(float fraction, void* user);
+int pb2_set_progress_callback(pb2_context* ctx, pb2_progress_fn fn, void* user);
 /* Same, but leaves the film in DEVICE memory (for the multi-GPU NCCL reduce); pointer stays owned
  * by ctx and valid until the next render/destroy. cuda_stream: a cudaStream_t or NULL. */
 int pb2_render_device(pb2_context* ctx, const pb2_render_params* params, void* cuda_stream,
@@ -377,6 +384,9 @@ int pb2_multi_upload_scene(pb2_multi* m, const pb2_scene_desc* scene);
 int pb2_multi_restage_scene(pb2_multi* m);
 /* pb2_render over all devices; film_rgba_host as in pb2_render. Blocking. */
 int pb2_multi_render(pb2_multi* m, const pb2_render_params* params, int shard_mode, float* film_rgba_host);
+/* pb2_set_progress_callback for the whole job: `fn` receives the mean of the devices' fractions (called from the
+ * devices' driver threads, possibly concurrently). */
+int pb2_multi_set_progress_callback(pb2_multi* m, pb2_progress_fn fn, void* user);
 /* pb2_film_finalize_device on the reduced film (first device) of the last pb2_multi_render. */
 int pb2_multi_film_finalize(pb2_multi* m, int tonemapper, int flip_y, uint8_t* rgba8_host,
                             float* tonemapped_rgba_host);

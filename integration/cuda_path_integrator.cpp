@@ -336,6 +336,10 @@ void CudaPathIntegrator::render(Scene& scene) {
     check(pb2_multi_load_sampler_tables_file(multi_, tables ? tables : "", spp), "pb2_multi_load_sampler_tables_file");
   }
   set_progress(0);
+  // path.cpp:39 publishes progress from the pixel loop; here every completed device wave does (driver threads;
+  // set_progress is an atomic store, integrator.cpp:11-16)
+  check(pb2_multi_set_progress_callback(multi_, [](float f, void*) { set_progress(f); }, nullptr),
+        "pb2_multi_set_progress_callback");
   pb2_render_params p{};
   p.spp = spp;
   p.max_path_length = max_path_length_;

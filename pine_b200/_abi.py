@@ -149,8 +149,10 @@ ABI_SYMBOLS = [
     "pb2_multi_load_sampler_tables_file", "pb2_multi_upload_scene", "pb2_multi_restage_scene", "pb2_multi_render",
     "pb2_multi_get_counters", "pb2_measure_read_gbs", "pb2_film_finalize_device", "pb2_multi_film_finalize",
     "pb2_export_host_scene", "pb2_import_host_scene", "pb2_trace_closest_device_noalloc",
+    "pb2_set_progress_callback", "pb2_multi_set_progress_callback",
 ]
 SHARD_SAMPLES, SHARD_ROWS = 0, 1
+PROGRESS_FN = C.CFUNCTYPE(None, C.c_float, C.c_void_p)  # pb2_progress_fn
 NOALLOC_MAX_RAYS = 1 << 20  # PB2_NOALLOC_MAX_RAYS
 
 _lib = None
@@ -190,6 +192,8 @@ def lib():
         L.pb2_trace_closest_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int,
                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pb2_trace_closest_device_noalloc.argtypes = L.pb2_trace_closest_device.argtypes
+        L.pb2_set_progress_callback.argtypes = [C.c_void_p, PROGRESS_FN, C.c_void_p]
+        L.pb2_multi_set_progress_callback.argtypes = [C.c_void_p, PROGRESS_FN, C.c_void_p]
         L.pb2_test_sampler_kind.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                             C.c_char_p, C.c_int, C.c_void_p]
         L.pb2_test_sampler.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,

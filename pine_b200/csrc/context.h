@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -146,6 +147,11 @@ struct pb2_context {
   pb2::WavefrontBuffers* wf = nullptr;
 
   pb2_ray_record* record = nullptr;  // test hook (pb2_set_ray_record)
+  // pb2_set_progress_callback: called from cudaLaunchHostFunc behind every wave of a render
+  pb2_progress_fn progress_fn = nullptr;
+  void* progress_user = nullptr;
+  std::atomic<int> progress_done{0};
+  int progress_total = 1;
 
   pb2_counters counters{};
 };

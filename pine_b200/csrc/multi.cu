@@ -15,6 +15,8 @@
 #include <chrono>
 #include <string>
 #include <thread>
+#include <atomic>
+#include <memory>
 #include <vector>
 
 #include "context.h"
@@ -70,7 +72,22 @@ struct pb2_multi {
   double last_render_ms = 0, last_reduce_ms = 0, last_stage_ms = 0;
   struct Acc { uint64_t closest = 0, shadow = 0, fb_closest = 0, fb_shadow = 0; double ms = 0; };
   std::vector<Acc> acc;  // per GPU, summed over the render calls of the last pb2_multi_render
+  // pb2_multi_set_progress_callback: every device reports its own fraction, the caller sees the mean
+  struct Progress { pb2_multi* m; int i; };
+  std::vector<Progress> progress_slot;
+  std::unique_ptr<std::atomic<float>[]> progress_of;
+  pb2_progress_fn progress_fn = nullptr;
+  void* progress_user = nullptr;
 };
+
+static void device_progress(float fraction, void* user) {
+  auto* slot = static_cast<pb2_multi::Progress*>(user);
+  pb2_multi* m = slot->m;
+  m->progress_of[slot->i].store(fraction, std::memory_order_relaxed);
+  float sum = 0;
+  for (size_t k = 0; k < m->ctx.size(); k++) sum += m->progress_of[k].load(std::memory_order_relaxed);
+  if (m->progress_fn) m->progress_fn(sum / float(m->ctx.size()), m->progress_user);
+}
 
 #define PB2_NCCL_CHECK(m, expr)                                                                       \
   do {                                                                                                \
@@ -315,6 +332,8 @@ static int render_and_reduce(pb2_multi* m, const pb2_render_params* p, int shard
 extern "C" int pb2_multi_render(pb2_multi* m, const pb2_render_params* p, int shard_mode, float* film_rgba_host) {
   if (!m || !p || !film_rgba_host) { set_error("null argument"); return PB2_E_INVALID; }
   if (!m->scene_ready) { set_error("pb2_multi_upload_scene has not succeeded"); return PB2_E_STATE; }
+  if (m->progress_of)
+    for (size_t i = 0; i < m->ctx.size(); i++) m->progress_of[i].store(0.0f);
   if (m->ctx.size() == 1) return pb2_render(m->ctx[0], p, film_rgba_host);
   float* dev = nullptr;
   int rc = render_and_reduce(m, p, shard_mode, &dev);
@@ -324,6 +343,23 @@ extern "C" int pb2_multi_render(pb2_multi* m, const pb2_render_params* p, int sh
   const size_t bytes = size_t(c0->scene.camera.width) * c0->scene.camera.height * 16;
   PB2_CUDA_CHECK(cudaMemcpyAsync(film_rgba_host, dev, bytes, cudaMemcpyDeviceToHost, c0->stream));
   PB2_CUDA_CHECK(cudaStreamSynchronize(c0->stream));
+  return PB2_OK;
+}
+
+extern "C" int pb2_multi_set_progress_callback(pb2_multi* m, pb2_progress_fn fn, void* user) {
+  if (!m) { set_error("null argument"); return PB2_E_INVALID; }
+  m->progress_fn = fn;
+  m->progress_user = user;
+  if (!m->progress_of) {
+    m->progress_of.reset(new std::atomic<float>[m->ctx.size()]);
+    m->progress_slot.resize(m->ctx.size());
+    for (size_t i = 0; i < m->ctx.size(); i++) m->progress_slot[i] = pb2_multi::Progress{m, int(i)};
+  }
+  for (size_t i = 0; i < m->ctx.size(); i++) {
+    m->progress_of[i].store(0.0f);
+    int rc = pb2_set_progress_callback(m->ctx[i], fn ? device_progress : nullptr, fn ? &m->progress_slot[i] : nullptr);
+    if (rc) return rc;
+  }
   return PB2_OK;
 }
 

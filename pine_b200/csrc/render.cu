@@ -719,6 +719,14 @@ int floor_log2(int v) {  // psl::log2i == hsb (psl/math.h:81,262)
 }
 // Binds the sampler of the next render to the device scene: table set for BlueSobolSampler,
 // log2_spp / nbase4_digits for SobolSampler (sampler.h:128-130, SobolSampler::init sampler.cpp:82-85).
+// cudaLaunchHostFunc target behind every wave: one more wave of the render is complete on the device.
+void CUDART_CB wave_completed(void* arg) {
+  pb2_context* ctx = static_cast<pb2_context*>(arg);
+  const pb2_progress_fn fn = ctx->progress_fn;
+  const int done = ++ctx->progress_done;
+  if (fn) fn(float(done) / float(ctx->progress_total > 0 ? ctx->progress_total : 1), ctx->progress_user);
+}
+
 int select_sampler(pb2_context* ctx, int kind, int spp, int seed) {
   DScene& sc = ctx->scene;
   sc.sampler_kind = kind;
@@ -1041,10 +1049,14 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
     }
   // pixel wave pw belongs to lane pw % n_lanes; launches are interleaved wave by wave so that every
   // lane's stream stays fed whatever the driver's launch-queue depth
+  ctx->progress_done = 0;
+  ctx->progress_total = n_waves;
   for (int pw0 = 0; pw0 < n_pixel_waves; pw0 += n_lanes)
     for (int sw = 0; sw < n_sample_waves; sw++)
-      for (int l = 0; l < n_lanes && pw0 + l < n_pixel_waves; l++)
+      for (int l = 0; l < n_lanes && pw0 + l < n_pixel_waves; l++) {
         if ((rc = enqueue_wave(l, pw0 + l, sw))) return rc;
+        if (ctx->progress_fn) PB2_CUDA_CHECK(cudaLaunchHostFunc(lane_stream[l], wave_completed, ctx));
+      }
   // join
   for (int l = 1; l < n_lanes; l++)
     if (lane_stream[l] != st) {
@@ -1093,6 +1105,13 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   ctx->counters.last_shadow_rays = shadow;
   ctx->counters.camera_samples += uint64_t(P) * n_samples;
   ctx->counters.kernel_launches += launches;
+  return PB2_OK;
+}
+
+extern "C" int pb2_set_progress_callback(pb2_context* ctx, pb2_progress_fn fn, void* user) {
+  if (!ctx) { set_error("null context"); return PB2_E_INVALID; }
+  ctx->progress_fn = fn;
+  ctx->progress_user = user;
   return PB2_OK;
 }
 

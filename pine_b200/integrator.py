@@ -141,6 +141,12 @@ class Backend:
             self.L.pb2_destroy(self.h)
             self.h = None
 
+    def set_progress_callback(self, fn):
+        """`fn(fraction)` is called as the render's waves complete on the device (path.cpp:39's set_progress); it
+        runs on a CUDA driver thread while the render call blocks. None clears."""
+        self._progress_keep = A.PROGRESS_FN((lambda f, _u: fn(f))) if fn else A.PROGRESS_FN()
+        A.check(self.L.pb2_set_progress_callback(self.h, self._progress_keep, None))
+
     def __del__(self):
         self.close()
 
@@ -349,6 +355,11 @@ class MultiBackend:
         if getattr(self, "h", None):
             self.L.pb2_destroy_multi(self.h)
             self.h = None
+
+    def set_progress_callback(self, fn):
+        """`fn(fraction)`: mean over the devices of their completed waves (called from the devices' driver threads)."""
+        self._progress_keep = A.PROGRESS_FN((lambda f, _u: fn(f))) if fn else A.PROGRESS_FN()
+        A.check(self.L.pb2_multi_set_progress_callback(self.h, self._progress_keep, None))
 
     def __del__(self):
         self.close()

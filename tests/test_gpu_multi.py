@@ -40,7 +40,11 @@ def test_multi_over_one_device_is_the_single_device_render():
     for mode in ("rows", "samples"):
         assert np.array_equal(u32(M.render(8, cfg["depth"], mode=mode)), u32(want))
     M.restage()
+    seen = []
+    M.set_progress_callback(seen.append)   # pb2_multi_set_progress_callback: mean of the devices' fractions
     assert np.array_equal(u32(M.render(8, cfg["depth"])), u32(want))
+    assert seen and seen[-1] == 1.0 and seen == sorted(seen)
+    M.set_progress_callback(None)
     c = M.counters()
     assert c["last_closest_rays"] == B.counters()["last_closest_rays"]
     M.close()
@@ -101,6 +105,21 @@ def test_two_gpus_rows_are_bit_identical_and_samples_statistically_equal():
 
 
 @two_gpus
+def test_two_gpus_report_progress_of_the_whole_job():
+    if A.lib().pb2_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    S, cfg = _scene()
+    M = pb.MultiBackend(devices=[0, 1])
+    M.upload_scene(S)
+    seen = []
+    M.set_progress_callback(seen.append)
+    for mode in ("rows", "samples"):
+        del seen[:]
+        M.render(8, cfg["depth"], mode=mode)
+        assert len(seen) >= 2 and max(seen) == 1.0 and min(seen) > 0.0, (mode, seen)
+    M.close()
+
+
 def test_two_gpus_large_mesh_replicas_are_complete():
     """A scene whose arrays exceed the sharded-staging threshold (1 MiB): 1/N through PCIe + in-place all-gather
     must leave the same BVH on every GPU -- rows mode is then bit-identical to one GPU."""

@@ -172,3 +172,31 @@ def test_wave_plan_splits_are_bit_identical(fn, kw):
     rows = _with_env({"PB2_LANES": 2, "PB2_MIN_LANE_SLOTS": 1}, lambda: B.render(spp, depth, rows=(5, 38)))
     assert np.array_equal(u32(rows[5:38]), u32(base[5:38])) and (rows[:5] == 0).all()
     B.close()
+
+
+def test_progress_callback_follows_the_completed_waves():
+    """pb2_set_progress_callback (path.cpp:39's set_progress): one call per completed wave, fractions k / n_waves
+    each reported once, ending at 1; the film is the film rendered without a callback."""
+    S = pb.Scene()
+    cfg = scenes.cbox_readme(S, size=(64, 64))
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    base = B.render(8, cfg["depth"])
+    seen = []
+    B.set_progress_callback(seen.append)
+    for env, n_waves in (({"PB2_LANES": 1}, 1),
+                         ({"PB2_MAX_SLOTS": 64 * 8 * 2, "PB2_LANES": 1}, 8 * 4),      # 4 pixel waves x 8 sample waves
+                         ({"PB2_MAX_SLOTS": 64 * 16 * 8, "PB2_LANES": 4, "PB2_MIN_LANE_SLOTS": 1}, 4)):
+        del seen[:]
+        film = _with_env(env, lambda: B.render(8, cfg["depth"]))
+        assert np.array_equal(u32(film), u32(base)), env
+        assert len(seen) == n_waves and max(seen) == 1.0, (env, seen)
+        assert sorted(seen) == [np.float32(k) / np.float32(n_waves) for k in range(1, n_waves + 1)]
+        if env.get("PB2_LANES") == 1:
+            assert seen == sorted(seen)   # one stream: waves complete in order
+    B.set_progress_callback(None)
+    del seen[:]
+    B.render(8, cfg["depth"])
+    assert seen == []
+    B.close()
+
