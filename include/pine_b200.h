@@ -83,7 +83,38 @@ enum pb2_shape_kind {
   PB2_SHAPE_MESH = 7
 };
 
-/* ---- materials (material.h:18-131); Node3f/Nodef parameters must be constants ---------------- */
+/* ---- procedural material parameters: Node3f / Nodef graphs (node.h:105-250, node.cpp:8-27) ------------------
+ * A graph is flattened to a POSTFIX program of pb2_node_instr, terminated by PB2_NODE_END, evaluated at the
+ * shading point with NodeEvalCtx{p, n, uv} (node.h:13-19). Every value on the evaluation stack is a vec3; a
+ * float-valued node (Nodef) carries its value in all three components, so the float operators are the vec3
+ * operators component by component -- the same float expressions the reference evaluates. At most
+ * PB2_NODE_MAX_STACK values are live. NodeNoisef / NodeNoise3f and NodeFunction (a PRL closure) have no
+ * device form: a material using them is rejected (PB2_E_UNSUPPORTED), there is no CPU fallback. */
+enum pb2_node_op {
+  PB2_NODE_END = 0,
+  PB2_NODE_CONST = 1,        /* push a[0..2]  (NodeConstant<vec3>; NodeConstant<float> v as {v, v, v}) */
+  PB2_NODE_POSITION = 2,     /* push ctx.p    (node.h:116-120) */
+  PB2_NODE_NORMAL = 3,       /* push ctx.n    (node.h:121-125) */
+  PB2_NODE_UV = 4,           /* push vec3(ctx.uv) = {u, v, 0} (node.h:126-130) */
+  PB2_NODE_ADD = 5, PB2_NODE_SUB = 6, PB2_NODE_MUL = 7, PB2_NODE_DIV = 8, /* pop b, pop a, push a op b (node.h:132-153) */
+  PB2_NODE_POW = 9,          /* powf per component */
+  PB2_NODE_NEG = 10, PB2_NODE_ABS = 11, PB2_NODE_SQR = 12, PB2_NODE_SQRT = 13,
+  PB2_NODE_FRACT = 14,       /* x - floor(x) (node.h:155-179, psl/math.h) */
+  PB2_NODE_COMPONENT = 15,   /* NodeComponent: pop x, push {x[k], x[k], x[k]}, k = int(a[0]) in 0..2 (node.h:181-193) */
+  PB2_NODE_VEC3 = 16,        /* NodeToVec3(x, y, z): pop z, y, x (floats), push {x, y, z}; the one-argument form is
+                              * the identity on this stack and emits nothing (node.h:195-207) */
+  PB2_NODE_CHECKERBOARD = 17, /* pop p; x = fract(p) - a[0]; push float(x.x * x.y * x.z > 0) (node.cpp:16-19) */
+  PB2_NODE_IMAGE = 18,       /* NodeImage: pop p, push the texel of texture int(a[0]) (1-based) at fract(p.xy)
+                              * (node.cpp:20-23) */
+  PB2_NODE_IMAGEF = 19       /* NodeImagef: the same texel's x, as a float (node.cpp:24-27) */
+};
+#define PB2_NODE_MAX_STACK 8
+typedef struct pb2_node_instr {
+  int32_t op; /* pb2_node_op */
+  float a[3];
+} pb2_node_instr;
+
+/* ---- materials (material.h:18-131); a Node3f/Nodef parameter is a constant, an image node or a program -- */
 enum pb2_material_kind {
   PB2_MAT_EMISSIVE = 0,
   PB2_MAT_DIFFUSE = 1,
@@ -104,6 +135,12 @@ typedef struct pb2_material {
    * roughness_texture: roughness = NodeComponent(NodeImage(...), 1), metallic_texture: metallic =
    * NodeComponent(NodeImage(...), 2) (node.h:181-193) replace `roughness` / `metallic`. */
   int32_t color_texture, roughness_texture, metallic_texture;
+  /* Any non-emissive material: 1-BASED index of the first instruction of the parameter's program in
+   * pb2_scene_desc.node_instrs, 0 = the constant above. color_node: albedo (Node3f); roughness_node; ior_node
+   * (Glossy / Glass only, material.h:57-85); metallic_node / transmission_node (Uber only, material.h:87-104).
+   * A program supersedes the constant and the image node of the same parameter. Emissive::color must stay a
+   * constant (the light sampler would need uv at the sampled point). */
+  int32_t color_node, roughness_node, ior_node, metallic_node, transmission_node;
 } pb2_material;
 
 /* pine::Image holding Array2d<vec4u8> (image.h:11; what tinygltf hands scene_from_gltf): row-major
@@ -169,6 +206,8 @@ typedef struct pb2_scene_desc {
   /* The full light list. NULL: area lights only, taken from light_geometries. Non-NULL: supersedes
    * light_geometries (whose entries must then equal the AREA records' geometries, or n_lights = 0). */
   const pb2_light* light_records;  uint32_t n_light_records;
+  /* Programs of the materials' *_node parameters, back to back, each ending in PB2_NODE_END. May be NULL / 0. */
+  const pb2_node_instr* node_instrs; uint32_t n_node_instrs;
 } pb2_scene_desc;
 
 typedef struct pb2_render_params {
@@ -339,6 +378,10 @@ int pb2_test_sampler(pb2_context* ctx, int spp, int px, int py, int sample_index
 int pb2_test_sampler_kind(pb2_context* ctx, int sampler, int spp, int sampler_seed, int px, int py,
                           int sample_index, const char* pattern, int n_samples, float* out_draws);
 int pb2_test_primary_rays(pb2_context* ctx, int sample_index, float* rays_host);
+/* Known-answer hook for the node programs: Mnode<T>::operator()(NodeEvalCtx{p, n, uv}) (node.h:13-19, 265-295) of
+ * the uploaded scene's program starting at `start` (1-based, as in pb2_material.*_node) at n points.
+ * ctx8: n x {p.xyz, n.xyz, uv}; out3: n x vec3 (a float node's value in all three components). */
+int pb2_test_eval_node(pb2_context* ctx, int start, size_t n, const float* ctx8_host, float* out3_host);
 int pb2_get_counters(pb2_context* ctx, pb2_counters* out);
 /* Measurement hook (SURVEY 8(d) asks for a measured L2 peak beside the HBM peak): sustained read bandwidth in
  * GB/s of a `bytes`-sized device buffer read `iters` times by a full grid with L1 bypassed (ld.global.cg).

@@ -4,9 +4,10 @@
 // data members of the reference structs in declaration order (geometry.h:44-139, bbox.h:29-109), so
 // a shape is copied bit for bit (the static_asserts below pin the layouts): both sides then
 // intersect the same numbers, including the host-computed OBB::m_inv (bbox.cpp:143-147). Material
-// parameters are Node graphs (node.h:46-103); the CUDA path takes constants, so every parameter is
-// evaluated at several unrelated NodeEvalCtx points and the scene is rejected (SEVERE, like the
-// reference's own argument checks, log.h:44-49) when the values differ -- there is no CPU fallback.
+// parameters are Node graphs (node.h:46-103): a NodeConstant is copied, scene_from_gltf's image patterns become
+// device textures, and any other graph is flattened to a postfix program the shade kernels evaluate
+// (pb2_node_op); noise and function nodes -- and a non-constant Emissive::color -- are rejected (SEVERE, like
+// the reference's own argument checks, log.h:44-49): there is no CPU fallback.
 // Image-node material parameters (what scene_from_gltf builds for baseColorTexture / metallicRoughnessTexture,
 // fileio.cpp:285-292) have to be recognised structurally, and Mnode<T>::value, NodeImage::{p, image} and
 // NodeComponent::{x, n} are private (node.h:69-70, 102-103, 181-193, 236-243). A maintainer adds two accessors
@@ -69,10 +70,28 @@ auto constant_of(const N& node, const char* what) {
 void put3(float* dst, vec3 v) { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
 
 struct Flat;
+// A parameter that is neither a constant nor one of scene_from_gltf's image patterns: the graph is flattened to
+// a postfix program (include/pine_b200.h pb2_node_op) appended to Flat::node_instrs -> 1-based start index.
+int32_t node_program(Flat& f, const Node3f& node, const char* what);
+int32_t node_program(Flat& f, const Nodef& node, const char* what);
+template <typename N>
+bool is_constant_node(const N& node) {
+  return node.value->template is<NodeConstant<decltype(node.eval(kProbe[0]))>>();
+}
 // NodeImage(NodeUV(), image) (node.cpp:20-23) over an 8-bit RGBA image -> 1-based pb2_texture index; 0 if
 // `node` is not an image node. Any other non-constant node is rejected by constant_of afterwards.
 int32_t image_texture(Flat& f, const Node3f& node);
 int32_t component_texture(Flat& f, const Nodef& node, int component, const char* what);
+
+// constant -> *dst, anything else -> a program in *node (Emissive::color keeps the constant-only rule)
+void param3(Flat& f, const Node3f& node, float* dst, int32_t* node_slot, const char* what) {
+  if (is_constant_node(node)) put3(dst, node.eval(kProbe[0]));
+  else *node_slot = node_program(f, node, what);
+}
+void paramf(Flat& f, const Nodef& node, float* dst, int32_t* node_slot, const char* what) {
+  if (is_constant_node(node)) *dst = node.eval(kProbe[0]);
+  else *node_slot = node_program(f, node, what);
+}
 
 pb2_material flatten_material(Flat& f, const Material& m) {
   pb2_material o{};
@@ -82,24 +101,24 @@ pb2_material flatten_material(Flat& f, const Material& m) {
     put3(o.color, constant_of(m.as<EmissiveMaterial>().color, "Emissive.color"));
   } else if (m.is<DiffuseMaterial>()) {
     o.kind = PB2_MAT_DIFFUSE;
-    put3(o.color, constant_of(m.as<DiffuseMaterial>().albedo, "Diffuse.albedo"));
+    param3(f, m.as<DiffuseMaterial>().albedo, o.color, &o.color_node, "Diffuse.albedo");
   } else if (m.is<MetalMaterial>()) {
     auto& x = m.as<MetalMaterial>();
     o.kind = PB2_MAT_METAL;
-    put3(o.color, constant_of(x.albedo, "Metal.albedo"));
-    o.roughness = constant_of(x.roughness, "Metal.roughness");
+    param3(f, x.albedo, o.color, &o.color_node, "Metal.albedo");
+    paramf(f, x.roughness, &o.roughness, &o.roughness_node, "Metal.roughness");
   } else if (m.is<GlossyMaterial>()) {
     auto& x = m.as<GlossyMaterial>();
     o.kind = PB2_MAT_GLOSSY;
-    put3(o.color, constant_of(x.albedo, "Glossy.albedo"));
-    o.roughness = constant_of(x.roughness, "Glossy.roughness");
-    o.ior = constant_of(x.ior, "Glossy.ior");
+    param3(f, x.albedo, o.color, &o.color_node, "Glossy.albedo");
+    paramf(f, x.roughness, &o.roughness, &o.roughness_node, "Glossy.roughness");
+    paramf(f, x.ior, &o.ior, &o.ior_node, "Glossy.ior");
   } else if (m.is<GlassMaterial>()) {
     auto& x = m.as<GlassMaterial>();
     o.kind = PB2_MAT_GLASS;
-    put3(o.color, constant_of(x.albedo, "Glass.albedo"));
-    o.roughness = constant_of(x.roughness, "Glass.roughness");
-    o.ior = constant_of(x.ior, "Glass.ior");
+    param3(f, x.albedo, o.color, &o.color_node, "Glass.albedo");
+    paramf(f, x.roughness, &o.roughness, &o.roughness_node, "Glass.roughness");
+    paramf(f, x.ior, &o.ior, &o.ior_node, "Glass.ior");
   } else if (m.is<UberMaterial>()) {
     auto& x = m.as<UberMaterial>();
     o.kind = PB2_MAT_UBER;
@@ -107,16 +126,16 @@ pb2_material flatten_material(Flat& f, const Material& m) {
     o.color_texture = image_texture(f, x.albedo);
     o.roughness_texture = component_texture(f, x.roughness, 1, "Uber.roughness");
     o.metallic_texture = component_texture(f, x.metallic, 2, "Uber.metallic");
-    if (!o.color_texture) put3(o.color, constant_of(x.albedo, "Uber.albedo"));
-    if (!o.roughness_texture) o.roughness = constant_of(x.roughness, "Uber.roughness");
-    if (!o.metallic_texture) o.metallic = constant_of(x.metallic, "Uber.metallic");
-    o.transmission = constant_of(x.transmission, "Uber.transmission");
+    if (!o.color_texture) param3(f, x.albedo, o.color, &o.color_node, "Uber.albedo");
+    if (!o.roughness_texture) paramf(f, x.roughness, &o.roughness, &o.roughness_node, "Uber.roughness");
+    if (!o.metallic_texture) paramf(f, x.metallic, &o.metallic, &o.metallic_node, "Uber.metallic");
+    paramf(f, x.transmission, &o.transmission, &o.transmission_node, "Uber.transmission");
     o.ior = x.ior;
   } else {
     auto& x = m.as<SubsurfaceMaterial>();
     o.kind = PB2_MAT_SUBSURFACE;
-    put3(o.color, constant_of(x.albedo, "Subsurface.albedo"));
-    o.roughness = constant_of(x.roughness, "Subsurface.roughness");
+    param3(f, x.albedo, o.color, &o.color_node, "Subsurface.albedo");
+    paramf(f, x.roughness, &o.roughness, &o.roughness_node, "Subsurface.roughness");
     put3(o.sigma_s, x.sigma_s);
     o.ior = x.ior;
   }
@@ -139,8 +158,84 @@ struct Flat {
   std::vector<pb2_light> light_records;
   std::vector<pb2_texture> textures;
   std::vector<const Image*> texture_keys;
+  std::vector<pb2_node_instr> node_instrs;
   pb2_scene_desc desc{};
 };
+
+// ---- Node graph -> postfix program (node.h:105-250) ----
+void emit(Flat& f, const Node3f& node, const char* what);
+void emit(Flat& f, const Nodef& node, const char* what);
+void ins(Flat& f, int op, float a0 = 0, float a1 = 0, float a2 = 0) {
+  f.node_instrs.push_back(pb2_node_instr{op, {a0, a1, a2}});
+}
+template <typename T, typename M>
+bool emit_arith(Flat& f, const M& node, const char* what) {
+  auto& v = *node.value;
+#define PB2_BIN(ch, code) \
+  if (v.template is<NodeBinary<T, ch>>()) { auto& x = v.template as<NodeBinary<T, ch>>(); emit(f, x.a, what); emit(f, x.b, what); ins(f, code); return true; }
+#define PB2_UN(ch, code) \
+  if (v.template is<NodeUnary<T, ch>>()) { emit(f, v.template as<NodeUnary<T, ch>>().x, what); ins(f, code); return true; }
+  PB2_BIN('+', PB2_NODE_ADD) PB2_BIN('-', PB2_NODE_SUB) PB2_BIN('*', PB2_NODE_MUL) PB2_BIN('/', PB2_NODE_DIV)
+  PB2_BIN('^', PB2_NODE_POW)
+  PB2_UN('-', PB2_NODE_NEG) PB2_UN('a', PB2_NODE_ABS) PB2_UN('s', PB2_NODE_SQR) PB2_UN('r', PB2_NODE_SQRT)
+  PB2_UN('f', PB2_NODE_FRACT)
+#undef PB2_BIN
+#undef PB2_UN
+  return false;
+}
+void emit(Flat& f, const Node3f& node, const char* what) {
+  auto& v = *node.value;
+  if (v.is<NodeConstant<vec3>>()) { const vec3 c = node.eval(kProbe[0]); ins(f, PB2_NODE_CONST, c.x, c.y, c.z); }
+  else if (v.is<NodePosition>()) ins(f, PB2_NODE_POSITION);
+  else if (v.is<NodeNormal>()) ins(f, PB2_NODE_NORMAL);
+  else if (v.is<NodeUV>()) ins(f, PB2_NODE_UV);
+  else if (emit_arith<vec3>(f, node, what)) {}
+  else if (v.is<NodeToVec3>()) {
+    auto& x = v.as<NodeToVec3>();
+    emit(f, x.x, what);  // the one-argument form is a broadcast: the identity on the device stack
+    if (x.y) { emit(f, *x.y, what); emit(f, *x.z, what); ins(f, PB2_NODE_VEC3); }
+  } else if (v.is<NodeImage>()) {
+    auto& x = v.as<NodeImage>();
+    emit(f, x.p, what);
+    Node3f over_uv{NodeImage(Node3f(NodeUV()), x.image)};
+    ins(f, PB2_NODE_IMAGE, float(image_texture(f, over_uv)));
+  } else
+    SEVERE("[CudaPathIntegrator]material parameter `", what, "` uses a noise or function node, which has no CUDA "
+           "form (and there is no CPU fallback)");
+}
+void emit(Flat& f, const Nodef& node, const char* what) {
+  auto& v = *node.value;
+  if (v.is<NodeConstant<float>>()) { const float c = node.eval(kProbe[0]); ins(f, PB2_NODE_CONST, c, c, c); }
+  else if (emit_arith<float>(f, node, what)) {}
+  else if (v.is<NodeComponent>()) {
+    auto& x = v.as<NodeComponent>();
+    emit(f, x.x, what);
+    ins(f, PB2_NODE_COMPONENT, float(x.n));
+  } else if (v.is<NodeCheckerboard>()) {
+    auto& x = v.as<NodeCheckerboard>();
+    emit(f, x.p, what);
+    ins(f, PB2_NODE_CHECKERBOARD, x.ratio);
+  } else if (v.is<NodeImagef>()) {
+    auto& x = v.as<NodeImagef>();
+    emit(f, x.p, what);
+    Node3f over_uv{NodeImage(Node3f(NodeUV()), x.image)};
+    ins(f, PB2_NODE_IMAGEF, float(image_texture(f, over_uv)));
+  } else
+    SEVERE("[CudaPathIntegrator]material parameter `", what, "` uses a noise or function node, which has no CUDA "
+           "form (and there is no CPU fallback)");
+}
+int32_t node_program(Flat& f, const Node3f& node, const char* what) {
+  const int32_t start = int32_t(f.node_instrs.size()) + 1;
+  emit(f, node, what);
+  ins(f, PB2_NODE_END);
+  return start;
+}
+int32_t node_program(Flat& f, const Nodef& node, const char* what) {
+  const int32_t start = int32_t(f.node_instrs.size()) + 1;
+  emit(f, node, what);
+  ins(f, PB2_NODE_END);
+  return start;
+}
 
 int32_t image_texture(Flat& f, const Node3f& node) {
   if (!node.value->is<NodeImage>()) return 0;
@@ -289,6 +384,7 @@ void flatten(Scene& scene, Flat& f) {
   d.meshes = f.meshes.data();         d.n_meshes = uint32_t(f.meshes.size());
   d.light_geometries = f.lights.data(); d.n_lights = uint32_t(f.lights.size());
   d.textures = f.textures.data();     d.n_textures = uint32_t(f.textures.size());
+  d.node_instrs = f.node_instrs.data(); d.n_node_instrs = uint32_t(f.node_instrs.size());
   if (!only_area) { d.light_records = f.light_records.data(); d.n_light_records = uint32_t(f.light_records.size()); }
 }
 

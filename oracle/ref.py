@@ -104,6 +104,26 @@ def pack_material(color, roughness=0.0, ior=1.4, metallic=0.0, transmission=0.0,
     return _f([*color, roughness, ior, metallic, transmission, *sigma_s])
 
 
+def _program_arrays(prog):
+    ops = np.ascontiguousarray([i[0] for i in prog], np.int32)
+    args = _f([c for i in prog for c in i[1:]])
+    return ops, args
+
+
+def eval_node(node, ctx8):
+    """The reference's own evaluation, Mnode<T>::operator()(NodeEvalCtx{p, n, uv}), of a pine_b200.nodes graph at
+    the points ctx8 = n x {p.xyz, n.xyz, uv} -> n x 3 (a Nodef's value in all three components)."""
+    prog = node.program() + [(0, 0.0, 0.0, 0.0)]
+    ops, args = _program_arrays(prog)
+    c = _f(ctx8).reshape(-1, 8)
+    out = np.zeros((len(c), 3), np.float32)
+    rc = lib().ref_eval_node(ops.ctypes.data_as(C.POINTER(C.c_int)), _fp(args), len(prog), 1, len(c),
+                             _fp(c), _fp(out))
+    if rc:
+        raise ValueError(f"ref_eval_node failed ({rc})")
+    return out
+
+
 def mat4(op, args):
     out = np.zeros(16, np.float32)
     a = _f(args)
@@ -132,8 +152,29 @@ class RefScene:
     # ---- builder interface (mirrors pine_b200.Scene) ----
     def add_material(self, kind, color, roughness=0.0, ior=1.4, metallic=0.0, transmission=0.0,
                      sigma_s=(0.0, 0.0, 0.0)):
-        p = pack_material(color, roughness, ior, metallic, transmission, sigma_s)
-        return self.L.ref_add_material(self.h, MATERIAL_KINDS[kind], _fp(p))
+        from pine_b200 import nodes as N
+        params = dict(color=color, roughness=roughness, ior=ior, metallic=metallic, transmission=transmission)
+        prog, starts = [], []
+        for slot in ("color", "roughness", "ior", "metallic", "transmission"):   # pb2_material.*_node order
+            if N.is_graph(params[slot]):
+                # the reference builds its OWN node objects from the typed program (ref_harness.cpp build_node)
+                starts.append(len(prog) + 1)
+                prog += params[slot].program() + [(0, 0.0, 0.0, 0.0)]
+                params[slot] = (0.0, 0.0, 0.0) if slot == "color" else 0.0
+            else:
+                starts.append(0)
+                params[slot] = N.constant_of(params[slot], slot != "color")
+        p = pack_material(params["color"], params["roughness"], params["ior"], params["metallic"],
+                          params["transmission"], sigma_s)
+        if not prog:
+            return self.L.ref_add_material(self.h, MATERIAL_KINDS[kind], _fp(p))
+        ops, args = _program_arrays(prog)
+        st = (C.c_int * 5)(*starts)
+        rc = self.L.ref_add_material_nodes(self.h, MATERIAL_KINDS[kind], _fp(p), ops.ctypes.data_as(C.POINTER(C.c_int)),
+                                           _fp(args), len(prog), st)
+        if rc < 0:
+            raise ValueError(f"ref_add_material_nodes failed ({rc})")
+        return rc
 
     def add_rect(self, pos, ex, ey, mat, flip=False):
         a, b, c = _f(pos), _f(ex), _f(ey)

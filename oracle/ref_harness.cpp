@@ -160,6 +160,119 @@ int ref_add_material(void* h, int kind, const float* p) {
   return int(S.materials.size()) - 1;
 }
 
+}  // extern "C"
+namespace {
+// A typed postfix program of pine_b200/nodes.py (op | 0x100 = the instruction yields a Nodef) rebuilt as the
+// reference's OWN node objects (node.h:105-250), so that the reference evaluates the graph with its own code.
+struct NodeValue {
+  bool is_float;
+  psl::optional<Nodef> f;
+  psl::optional<Node3f> v;
+};
+Node3f to3(const NodeValue& x) { return x.is_float ? Node3f(NodeToVec3(*x.f)) : *x.v; }
+template <char op>
+NodeValue binary(const NodeValue& a, const NodeValue& b, bool is_float) {
+  if (is_float) return NodeValue{true, Nodef(NodeBinary<float, op>(*a.f, *b.f)), psl::nullopt};
+  return NodeValue{false, psl::nullopt, Node3f(NodeBinary<vec3, op>(to3(a), to3(b)))};
+}
+template <char op>
+NodeValue unary(const NodeValue& x, bool is_float) {
+  if (is_float) return NodeValue{true, Nodef(NodeUnary<float, op>(*x.f)), psl::nullopt};
+  return NodeValue{false, psl::nullopt, Node3f(NodeUnary<vec3, op>(*x.v))};
+}
+// returns false on a malformed program or an op the harness does not build (image nodes: the glTF tests cover them)
+bool build_node(const int* ops, const float* args, int n, int start, NodeValue& out) {
+  std::vector<NodeValue> st;
+  for (int pc = start - 1; pc < n; pc++) {
+    const int op = ops[pc] & 0xff;
+    const bool is_float = (ops[pc] & 0x100) != 0;
+    const float* a = args + 3 * pc;
+    auto pop = [&]() { NodeValue x = st.back(); st.pop_back(); return x; };
+    if (op == 0) {
+      if (st.size() != 1) return false;
+      out = st.back();
+      return true;
+    }
+    const size_t need = (op >= 5 && op <= 9) ? 2 : (op == 16 ? 3 : (op >= 10 ? 1 : 0));
+    if (st.size() < need) return false;
+    switch (op) {
+      case 1:
+        if (is_float) st.push_back(NodeValue{true, Nodef(a[0]), psl::nullopt});
+        else st.push_back(NodeValue{false, psl::nullopt, Node3f(vec3(a[0], a[1], a[2]))});
+        break;
+      case 2: st.push_back(NodeValue{false, psl::nullopt, Node3f(NodePosition())}); break;
+      case 3: st.push_back(NodeValue{false, psl::nullopt, Node3f(NodeNormal())}); break;
+      case 4: st.push_back(NodeValue{false, psl::nullopt, Node3f(NodeUV())}); break;
+      case 5: { auto b = pop(), x = pop(); st.push_back(binary<'+'>(x, b, is_float)); break; }
+      case 6: { auto b = pop(), x = pop(); st.push_back(binary<'-'>(x, b, is_float)); break; }
+      case 7: { auto b = pop(), x = pop(); st.push_back(binary<'*'>(x, b, is_float)); break; }
+      case 8: { auto b = pop(), x = pop(); st.push_back(binary<'/'>(x, b, is_float)); break; }
+      case 9: { auto b = pop(), x = pop(); st.push_back(binary<'^'>(x, b, is_float)); break; }
+      case 10: { auto x = pop(); st.push_back(unary<'-'>(x, is_float)); break; }
+      case 11: { auto x = pop(); st.push_back(unary<'a'>(x, is_float)); break; }
+      case 12: { auto x = pop(); st.push_back(unary<'s'>(x, is_float)); break; }
+      case 13: { auto x = pop(); st.push_back(unary<'r'>(x, is_float)); break; }
+      case 14: { auto x = pop(); st.push_back(unary<'f'>(x, is_float)); break; }
+      case 15: { auto x = pop(); st.push_back(NodeValue{true, Nodef(NodeComponent(to3(x), int(a[0]))), psl::nullopt}); break; }
+      case 16: {
+        auto z = pop(), y = pop(), x = pop();
+        if (!x.is_float || !y.is_float || !z.is_float) return false;
+        st.push_back(NodeValue{false, psl::nullopt, Node3f(NodeToVec3(*x.f, *y.f, *z.f))});
+        break;
+      }
+      case 17: { auto x = pop(); st.push_back(NodeValue{true, Nodef(NodeCheckerboard(to3(x), a[0])), psl::nullopt}); break; }
+      default: return false;
+    }
+  }
+  return false;
+}
+}  // namespace
+extern "C" {
+
+// ref_add_material with graph parameters. starts[5]: 1-based program start per slot {color, roughness, ior,
+// metallic, transmission}, 0 = the constant of `p`. -1: unknown kind, -2: a program the harness cannot build.
+int ref_add_material_nodes(void* h, int kind, const float* p, const int* ops, const float* args, int n,
+                           const int* starts) {
+  auto& S = *(RefScene*)h;
+  Node3f color(v3(p));
+  Nodef rough(p[3]), ior(p[4]), metallic(p[5]), transmission(p[6]);
+  for (int slot = 0; slot < 5; slot++) {
+    if (!starts[slot]) continue;
+    NodeValue x;
+    if (!build_node(ops, args, n, starts[slot], x)) return -2;
+    if (slot == 0) color = to3(x);
+    else {
+      if (!x.is_float) return -2;
+      (slot == 1 ? rough : slot == 2 ? ior : slot == 3 ? metallic : transmission) = *x.f;
+    }
+  }
+  psl::shared_ptr<Material> m;
+  switch (kind) {
+    case 1: m = psl::make_shared<Material>(DiffuseMaterial(color)); break;
+    case 2: m = psl::make_shared<Material>(MetalMaterial(color, rough)); break;
+    case 3: m = psl::make_shared<Material>(GlossyMaterial(color, rough, ior)); break;
+    case 4: m = psl::make_shared<Material>(GlassMaterial(color, rough, ior)); break;
+    case 5: m = psl::make_shared<Material>(UberMaterial(color, rough, metallic, transmission, p[4])); break;
+    case 6: m = psl::make_shared<Material>(SubsurfaceMaterial(color, rough, v3(p + 7))); break;
+    default: return -1;
+  }
+  S.materials.push_back(m);
+  return int(S.materials.size()) - 1;
+}
+// Mnode<T>::operator()(NodeEvalCtx{p, n, uv}) of a program at n_pts points (ctx8: p, n, uv; out3: vec3, a Nodef's
+// value in all three components): the known answers for pb2_test_eval_node.
+int ref_eval_node(const int* ops, const float* args, int n, int start, int n_pts, const float* ctx8, float* out3) {
+  NodeValue x;
+  if (!build_node(ops, args, n, start, x)) return -2;
+  for (int i = 0; i < n_pts; i++) {
+    const float* c = ctx8 + 8 * i;
+    const NodeEvalCtx ec(v3(c), v3(c + 3), vec2(c[6], c[7]));
+    const vec3 v = x.is_float ? vec3((*x.f)(ec)) : (*x.v)(ec);
+    out3[3 * i] = v.x; out3[3 * i + 1] = v.y; out3[3 * i + 2] = v.z;
+  }
+  return 0;
+}
+
 static int add_shape(RefScene& S, Shape shape, int mat) {
   S.scene.add_geometry(MOVE(shape), S.materials[mat]);
   S.bvh_built = false;

@@ -57,7 +57,17 @@ class Material(C.Structure):
     _fields_ = [("kind", C.c_int32), ("color", f3), ("roughness", C.c_float), ("ior", C.c_float),
                 ("metallic", C.c_float), ("transmission", C.c_float), ("sigma_s", f3),
                 ("color_texture", C.c_int32), ("roughness_texture", C.c_int32),
-                ("metallic_texture", C.c_int32)]  # 1-based, 0 = none
+                ("metallic_texture", C.c_int32),  # 1-based, 0 = none
+                # 1-based start of the parameter's node program in SceneDesc.node_instrs, 0 = constant
+                ("color_node", C.c_int32), ("roughness_node", C.c_int32), ("ior_node", C.c_int32),
+                ("metallic_node", C.c_int32), ("transmission_node", C.c_int32)]
+
+
+class NodeInstr(C.Structure):
+    _fields_ = [("op", C.c_int32), ("a", f3)]
+
+
+NODE_SLOTS = ("color", "roughness", "ior", "metallic", "transmission")
 
 
 class Texture(C.Structure):
@@ -96,7 +106,8 @@ class SceneDesc(C.Structure):
                 _arr("cones", Cone) + _arr("rects", Rect) + _arr("disks", Disk) +
                 _arr("meshes", Mesh) +
                 [("light_geometries", C.POINTER(C.c_int32)), ("n_lights", C.c_uint32),
-                 ("camera", Camera)] + _arr("textures", Texture) + _arr("light_records", Light))
+                 ("camera", Camera)] + _arr("textures", Texture) + _arr("light_records", Light) +
+                _arr("node_instrs", NodeInstr))
 
 
 class RenderParams(C.Structure):
@@ -149,7 +160,7 @@ ABI_SYMBOLS = [
     "pb2_multi_load_sampler_tables_file", "pb2_multi_upload_scene", "pb2_multi_restage_scene", "pb2_multi_render",
     "pb2_multi_get_counters", "pb2_measure_read_gbs", "pb2_film_finalize_device", "pb2_multi_film_finalize",
     "pb2_export_host_scene", "pb2_import_host_scene", "pb2_trace_closest_device_noalloc",
-    "pb2_set_progress_callback", "pb2_multi_set_progress_callback",
+    "pb2_set_progress_callback", "pb2_multi_set_progress_callback", "pb2_test_eval_node",
 ]
 SHARD_SAMPLES, SHARD_ROWS = 0, 1
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_float, C.c_void_p)  # pb2_progress_fn
@@ -194,6 +205,7 @@ def lib():
         L.pb2_trace_closest_device_noalloc.argtypes = L.pb2_trace_closest_device.argtypes
         L.pb2_set_progress_callback.argtypes = [C.c_void_p, PROGRESS_FN, C.c_void_p]
         L.pb2_multi_set_progress_callback.argtypes = [C.c_void_p, PROGRESS_FN, C.c_void_p]
+        L.pb2_test_eval_node.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p]
         L.pb2_test_sampler_kind.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                             C.c_char_p, C.c_int, C.c_void_p]
         L.pb2_test_sampler.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,

@@ -75,6 +75,7 @@ struct HostScene {
   std::vector<uint32_t> texels;
   std::vector<DTexture> textures;
   std::vector<float> srgb_lut;
+  std::vector<pb2_node_instr> node_instrs;
   std::vector<pb2_aabb> aabbs;
   std::vector<pb2_obb> obbs;
   std::vector<pb2_sphere> spheres;
@@ -116,6 +117,7 @@ struct pb2_context {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
   bool scene_ready = false;       // device copy valid
+  bool has_node_programs = false;  // some material parameter is a node program: the GENERIC shade kernels run
   bool host_scene_ready = false;  // host trees valid (also on a host-only context, device = -1)
   bool defer_staging = false;     // pb2_upload_scene stops after the host build (pb2_multi stages the replicas)
 
@@ -128,7 +130,7 @@ struct pb2_context {
   pb2::DScene scene{};  // device pointers
   pb2::DBuf nodes2, nodes8, leaves, wide_prims, box_shapes, leaf_prims, top_prims, meshes, geoms, materials, lights, light_recs;
   pb2::DBuf aabbs, obbs, spheres, triangles, cones, rects, disks;
-  pb2::DBuf verts, tris, normals, uvs, texels, textures, srgb_lut;
+  pb2::DBuf verts, tris, normals, uvs, texels, textures, srgb_lut, node_instrs;
   pb2::DBuf tab_sobol, tab_scramble, tab_rank;
   pb2::DBuf halton_primes, halton_sums, halton_perms;  // HaltonSampler tables, made on first use
   int tables_spp = 0;

@@ -140,6 +140,8 @@ struct DScene {
   const uint32_t* texels;  // r | g << 8 | b << 16 | a << 24
   const DTexture* textures;
   const float* srgb_lut;
+  // postfix programs of the materials' *_node parameters (pb2_node_instr = one float4: op bits, a[0..2])
+  const pb2_node_instr* node_instrs;
   // sampler tables for the active spp variant
   const uint8_t* sobol;
   const uint8_t* scramble;

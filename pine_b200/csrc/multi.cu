@@ -221,6 +221,7 @@ extern "C" int pb2_multi_upload_scene(pb2_multi* m, const pb2_scene_desc* sd) {
     c->only_area_lights = c0->only_area_lights;
     c->material_kinds = c0->material_kinds;
     c->needs_rng_in_shading = c0->needs_rng_in_shading;
+    c->has_node_programs = c0->has_node_programs;
     c->n_pixels = c0->n_pixels;
     c->counters.bvh_build_ms = c0->counters.bvh_build_ms;
     c->counters.scene_bytes = c0->counters.scene_bytes;

@@ -245,33 +245,83 @@ __device__ __forceinline__ V3 image_node(const DScene& sc, int texture1, V2 uv) 
   return V3(__ldg(sc.srgb_lut + (c & 0xffu)), __ldg(sc.srgb_lut + ((c >> 8) & 0xffu)),
             __ldg(sc.srgb_lut + ((c >> 16) & 0xffu)));
 }
-template <int MAT, class Smp>
-__device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_material& m, V3 wi_world, V3 n, V2 uv,
+// Mnode<T>::operator()(NodeEvalCtx{p, n, uv}) for a graph flattened to a postfix program (include/pine_b200.h
+// pb2_node_op; node.h:105-250, node.cpp:8-27). Every stack value is a vec3; a float node's value sits in all
+// three components, so NodeBinary<float, op> is NodeBinary<vec3, op> component by component. `start` is 1-based.
+__device__ __noinline__ V3 eval_node_program(const DScene& sc, int start, V3 p, V3 n, V2 uv) {
+  V3 st[PB2_NODE_MAX_STACK];
+  int sp = 0;
+  for (const float4* pc = reinterpret_cast<const float4*>(sc.node_instrs) + (start - 1);; pc++) {
+    const float4 in = __ldg(pc);
+    const V3 a(in.y, in.z, in.w);
+    switch (__float_as_int(in.x)) {
+      case PB2_NODE_END: return st[sp - 1];
+      case PB2_NODE_CONST: st[sp++] = a; break;
+      case PB2_NODE_POSITION: st[sp++] = p; break;
+      case PB2_NODE_NORMAL: st[sp++] = n; break;
+      case PB2_NODE_UV: st[sp++] = V3(uv.x, uv.y, 0.0f); break;
+      case PB2_NODE_ADD: sp--; st[sp - 1] = st[sp - 1] + st[sp]; break;
+      case PB2_NODE_SUB: sp--; st[sp - 1] = st[sp - 1] - st[sp]; break;
+      case PB2_NODE_MUL: sp--; st[sp - 1] = st[sp - 1] * st[sp]; break;
+      case PB2_NODE_DIV: sp--; st[sp - 1] = V3(st[sp - 1].x / st[sp].x, st[sp - 1].y / st[sp].y, st[sp - 1].z / st[sp].z); break;
+      case PB2_NODE_POW: sp--; st[sp - 1] = V3(powf(st[sp - 1].x, st[sp].x), powf(st[sp - 1].y, st[sp].y), powf(st[sp - 1].z, st[sp].z)); break;
+      case PB2_NODE_NEG: st[sp - 1] = -st[sp - 1]; break;
+      case PB2_NODE_ABS: st[sp - 1] = V3(pabs(st[sp - 1].x), pabs(st[sp - 1].y), pabs(st[sp - 1].z)); break;
+      case PB2_NODE_SQR: st[sp - 1] = st[sp - 1] * st[sp - 1]; break;
+      case PB2_NODE_SQRT: st[sp - 1] = V3(sqrtf(st[sp - 1].x), sqrtf(st[sp - 1].y), sqrtf(st[sp - 1].z)); break;
+      case PB2_NODE_FRACT: st[sp - 1] = V3(st[sp - 1].x - floorf(st[sp - 1].x), st[sp - 1].y - floorf(st[sp - 1].y), st[sp - 1].z - floorf(st[sp - 1].z)); break;
+      case PB2_NODE_COMPONENT: { const float v = st[sp - 1][int(a.x)]; st[sp - 1] = V3(v); break; }
+      case PB2_NODE_VEC3: sp -= 2; st[sp - 1] = V3(st[sp - 1].x, st[sp].x, st[sp + 1].x); break;
+      case PB2_NODE_CHECKERBOARD: {
+        const V3 q = st[sp - 1];
+        const V3 x = V3(q.x - floorf(q.x), q.y - floorf(q.y), q.z - floorf(q.z)) - V3(a.x);
+        st[sp - 1] = V3(x.x * x.y * x.z > 0 ? 1.0f : 0.0f);
+        break;
+      }
+      case PB2_NODE_IMAGE: st[sp - 1] = image_node(sc, int(a.x), V2(st[sp - 1].x, st[sp - 1].y)); break;
+      case PB2_NODE_IMAGEF: st[sp - 1] = V3(image_node(sc, int(a.x), V2(st[sp - 1].x, st[sp - 1].y)).x); break;
+      default: return V3(0.0f);  // rejected at pb2_upload_scene
+    }
+  }
+}
+
+// NODES: the scene has node programs (only the GENERIC shade kernels are compiled with it)
+template <int MAT, bool NODES, class Smp>
+__device__ __forceinline__ Bxdf material_bxdf(const DScene& sc, const pb2_material& m, V3 wi_world, V3 p, V3 n, V2 uv,
                                               float min_roughness, bool diffused, Smp& smp, Rng& g) {
   Bxdf b;
   b.albedo = V3(m.color[0], m.color[1], m.color[2]);
   b.roughness = m.roughness;
-  float metallic = m.metallic;
+  float metallic = m.metallic, transmission = m.transmission;
   if (MAT == PB2_MAT_UBER) {
     if (m.color_texture) b.albedo = image_node(sc, m.color_texture, uv);
     if (m.roughness_texture) b.roughness = image_node(sc, m.roughness_texture, uv).y;
     if (m.metallic_texture) metallic = image_node(sc, m.metallic_texture, uv).z;
   }
   b.ior = m.ior;
+  if (NODES) {
+    if (m.color_node) b.albedo = eval_node_program(sc, m.color_node, p, n, uv);
+    if (m.roughness_node) b.roughness = eval_node_program(sc, m.roughness_node, p, n, uv).x;
+    if ((MAT == PB2_MAT_GLOSSY || MAT == PB2_MAT_GLASS) && m.ior_node) b.ior = eval_node_program(sc, m.ior_node, p, n, uv).x;
+    if (MAT == PB2_MAT_UBER) {
+      if (m.metallic_node) metallic = eval_node_program(sc, m.metallic_node, p, n, uv).x;
+      if (m.transmission_node) transmission = eval_node_program(sc, m.transmission_node, p, n, uv).x;
+    }
+  }
   b.sigma_s = V3(m.sigma_s[0], m.sigma_s[1], m.sigma_s[2]);
   b.kind = BX_DIFFUSE;
-  if (MAT == PB2_MAT_METAL) { b.kind = BX_CONDUCTOR; b.roughness = pmax(m.roughness, min_roughness); }
-  if (MAT == PB2_MAT_GLOSSY) { b.kind = BX_DIFF_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); }
-  if (MAT == PB2_MAT_GLASS) { b.kind = BX_REFR_DIELECTRIC; b.roughness = pmax(m.roughness, min_roughness); }
+  if (MAT == PB2_MAT_METAL) { b.kind = BX_CONDUCTOR; b.roughness = pmax(b.roughness, min_roughness); }
+  if (MAT == PB2_MAT_GLOSSY) { b.kind = BX_DIFF_DIELECTRIC; b.roughness = pmax(b.roughness, min_roughness); }
+  if (MAT == PB2_MAT_GLASS) { b.kind = BX_REFR_DIELECTRIC; b.roughness = pmax(b.roughness, min_roughness); }
   if (MAT == PB2_MAT_UBER) {
     if (with_probability(metallic, g)) b.kind = BX_CONDUCTOR;
-    else if (with_probability(m.transmission, g)) b.kind = BX_REFR_DIELECTRIC;
+    else if (with_probability(transmission, g)) b.kind = BX_REFR_DIELECTRIC;
     else b.kind = BX_DIFF_DIELECTRIC;
   }
   if (MAT == PB2_MAT_SUBSURFACE) {
     b.ior = 1.4f;  // SubsurfaceMaterial::ior (material.h:103)
     float fr = fresnel_unpolarized(dot(wi_world, n), b.ior);
-    if (smp_get1d(sc, smp) < fr) { b.kind = BX_REFRACTIVE; b.roughness = pmax(m.roughness, min_roughness); }
+    if (smp_get1d(sc, smp) < fr) { b.kind = BX_REFRACTIVE; b.roughness = pmax(b.roughness, min_roughness); }
     else if (diffused) b.kind = BX_DIFFUSE;
     else b.kind = BX_BSSRDF;
   }
@@ -481,7 +531,7 @@ __global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int de
       constexpr bool uses_rng = MAT == PB2_MAT_UBER || MAT == PB2_MAT_SUBSURFACE;
       if (uses_rng) g_rng = load_rng(w.rng, pix);
       const bool diffused = pv_diffuse > 0;
-      Bxdf bx = material_bxdf<MAT>(sc, m, wi, it.n, it.uv, diffused ? 0.6f : 0.0f, diffused, smp, g_rng);
+      Bxdf bx = material_bxdf<MAT, GENERIC>(sc, m, wi, it.p, it.n, it.uv, diffused ? 0.6f : 0.0f, diffused, smp, g_rng);
       M3 l2w = coordinate_system(it.n);
       M3 w2l = transpose(l2w);
       bx.wi = w2l * wi;
@@ -1011,7 +1061,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       if (depth + 1 < D) {
         const int sg = sm_grid(live, 128, 16);
         const unsigned mk = ctx->material_kinds;
-        const bool blue = sc.sampler_kind == PB2_SAMPLER_BLUE && ctx->only_area_lights;
+        const bool blue = sc.sampler_kind == PB2_SAMPLER_BLUE && ctx->only_area_lights && !ctx->has_node_programs;
 #define PB2_SHADE(MAT)                                                      \
   if (mk & (1u << MAT)) {                                                   \
     if (blue) k_shade_mat<MAT, false><<<sg, 128, 0, ls>>>(sc, w, depth);    \
@@ -1105,6 +1155,37 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   ctx->counters.last_shadow_rays = shadow;
   ctx->counters.camera_samples += uint64_t(P) * n_samples;
   ctx->counters.kernel_launches += launches;
+  return PB2_OK;
+}
+
+// Test hook: the uploaded scene's node program starting at `start` (1-based) evaluated at n points.
+namespace pb2 {
+__global__ void k_eval_node(DScene sc, int start, int n, const float* __restrict__ ctx8, float* __restrict__ out3) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* c = ctx8 + size_t(i) * 8;
+  const V3 v = eval_node_program(sc, start, V3(c[0], c[1], c[2]), V3(c[3], c[4], c[5]), V2(c[6], c[7]));
+  out3[size_t(i) * 3] = v.x; out3[size_t(i) * 3 + 1] = v.y; out3[size_t(i) * 3 + 2] = v.z;
+}
+}  // namespace pb2
+extern "C" int pb2_test_eval_node(pb2_context* ctx, int start, size_t n, const float* ctx8_host, float* out3_host) {
+  if (!ctx || !ctx8_host || !out3_host) { set_error("null argument"); return PB2_E_INVALID; }
+  if (ctx->device < 0) { set_error("host-only context: no CUDA device, and there is no CPU fallback"); return PB2_E_CUDA; }
+  if (!ctx->scene_ready) { set_error("pb2_upload_scene has not succeeded on this context"); return PB2_E_STATE; }
+  const HostScene& H = ctx->host_view ? *ctx->host_view : ctx->host;
+  bool is_start = start >= 1 && size_t(start) <= H.node_instrs.size() &&
+                  (start == 1 || H.node_instrs[size_t(start) - 2].op == PB2_NODE_END);
+  if (!is_start) { set_error("pb2_test_eval_node: not the start of a program of the uploaded scene"); return PB2_E_INVALID; }
+  if (n == 0) return PB2_OK;
+  PB2_CUDA_CHECK(cudaSetDevice(ctx->device));
+  PB2_CUDA_CHECK(ctx->rays.reserve(n * 32));
+  PB2_CUDA_CHECK(ctx->out_surf.reserve(n * 12));
+  PB2_CUDA_CHECK(cudaMemcpyAsync(ctx->rays.ptr, ctx8_host, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+  k_eval_node<<<unsigned((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->scene, start, int(n), ctx->rays.as<float>(), ctx->out_surf.as<float>());
+  ctx->counters.kernel_launches++;
+  PB2_CUDA_CHECK(cudaGetLastError());
+  PB2_CUDA_CHECK(cudaMemcpyAsync(out3_host, ctx->out_surf.ptr, n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+  PB2_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
   return PB2_OK;
 }
 

@@ -56,6 +56,7 @@ bool valid_material(const pb2_material& m) {
 
 }  // namespace
 
+static_assert(sizeof(pb2_material) == 76 && sizeof(pb2_node_instr) == 16, "pine_b200/_abi.py mirrors these layouts");
 int restage_unpinned(pb2_context* ctx);  // first staging of a fresh scene: from pageable memory (below)
 
 extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
@@ -90,6 +91,47 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     if ((tex[0] || tex[1] || tex[2]) && m.kind != PB2_MAT_UBER) {
       set_error("material " + std::to_string(i) + ": image nodes are supported on Uber materials only");
       return PB2_E_UNSUPPORTED;
+    }
+  }
+  // node programs: every *_node names the start of a well-formed postfix program
+  ctx->has_node_programs = false;
+  for (uint32_t i = 0; i < sd->n_materials; i++) {
+    const pb2_material& m = sd->materials[i];
+    const int32_t prog[5] = {m.color_node, m.roughness_node, m.ior_node, m.metallic_node, m.transmission_node};
+    for (int k = 0; k < 5; k++) {
+      if (!prog[k]) continue;
+      const std::string where = "material " + std::to_string(i) + " node program " + std::to_string(k) + ": ";
+      if (m.kind == PB2_MAT_EMISSIVE) { set_error(where + "Emissive::color must be a constant on the CUDA path"); return PB2_E_UNSUPPORTED; }
+      if (prog[k] < 0 || uint32_t(prog[k]) > sd->n_node_instrs || !sd->node_instrs) { set_error(where + "start out of range"); return PB2_E_INVALID; }
+      int depth = 0;
+      bool ended = false;
+      for (uint32_t pc = uint32_t(prog[k]) - 1; pc < sd->n_node_instrs && !ended; pc++) {
+        const pb2_node_instr& in = sd->node_instrs[pc];
+        int pops = 0, pushes = 1;
+        switch (in.op) {
+          case PB2_NODE_END: ended = true; pushes = 0; break;
+          case PB2_NODE_CONST: case PB2_NODE_POSITION: case PB2_NODE_NORMAL: case PB2_NODE_UV: break;
+          case PB2_NODE_ADD: case PB2_NODE_SUB: case PB2_NODE_MUL: case PB2_NODE_DIV: case PB2_NODE_POW: pops = 2; break;
+          case PB2_NODE_NEG: case PB2_NODE_ABS: case PB2_NODE_SQR: case PB2_NODE_SQRT: case PB2_NODE_FRACT:
+          case PB2_NODE_CHECKERBOARD: pops = 1; break;
+          case PB2_NODE_COMPONENT:
+            pops = 1;
+            if (!(in.a[0] == 0.0f || in.a[0] == 1.0f || in.a[0] == 2.0f)) { set_error(where + "component index must be 0, 1 or 2"); return PB2_E_INVALID; }
+            break;
+          case PB2_NODE_VEC3: pops = 3; break;
+          case PB2_NODE_IMAGE: case PB2_NODE_IMAGEF:
+            pops = 1;
+            if (!(in.a[0] >= 1.0f && in.a[0] <= float(sd->n_textures) && in.a[0] == float(int(in.a[0])))) { set_error(where + "texture index out of range"); return PB2_E_INVALID; }
+            break;
+          default: set_error(where + "unknown node op " + std::to_string(in.op) + " (noise and function nodes have no device form)"); return PB2_E_UNSUPPORTED;
+        }
+        if (ended) break;
+        if (depth < pops) { set_error(where + "stack underflow"); return PB2_E_INVALID; }
+        depth += pushes - pops;
+        if (depth > PB2_NODE_MAX_STACK) { set_error(where + "needs more than PB2_NODE_MAX_STACK values"); return PB2_E_UNSUPPORTED; }
+      }
+      if (!ended || depth != 1) { set_error(where + "does not end with exactly one value before PB2_NODE_END"); return PB2_E_INVALID; }
+      ctx->has_node_programs = true;
     }
   }
   for (uint32_t i = 0; i < sd->n_textures; i++)
@@ -178,6 +220,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     H.texels.resize(at + n);
     memcpy(H.texels.data() + at, t.rgba, n * 4);
   }
+  if (sd->node_instrs) H.node_instrs.assign(sd->node_instrs, sd->node_instrs + sd->n_node_instrs);
   H.srgb_lut.resize(256);
   // inverse_gamma_correction(value / 255.0f) = pow(v, 2.2f) (color.h:13-18) with the host's powf, as the
   // reference evaluates it per lookup
@@ -363,7 +406,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   ITEM(wide_prims, lay.wide_prims); ITEM(box_shapes, lay.box_shapes); ITEM(leaf_prims, lay.leaf_prims);
   ITEM(top_prims, H.top_prims); ITEM(meshes, H.meshes); ITEM(geoms, H.geoms); ITEM(lights, H.lights); ITEM(light_recs, H.light_recs);
   ITEM(verts, H.verts); ITEM(tris, H.tris); ITEM(normals, H.normals); ITEM(uvs, H.uvs);
-  ITEM(texels, H.texels); ITEM(textures, H.textures); ITEM(srgb_lut, H.srgb_lut);
+  ITEM(texels, H.texels); ITEM(textures, H.textures); ITEM(srgb_lut, H.srgb_lut); ITEM(node_instrs, H.node_instrs);
   ITEM(materials, H.materials); ITEM(aabbs, H.aabbs); ITEM(obbs, H.obbs); ITEM(spheres, H.spheres);
   ITEM(triangles, H.triangles); ITEM(cones, H.cones); ITEM(rects, H.rects); ITEM(disks, H.disks);
 #undef ITEM
@@ -476,7 +519,7 @@ int restage(pb2_context* ctx, void* cuda_stream, int part, int n_parts, pb2_devi
   s.verts = ctx->verts.as<float>(); s.tris = ctx->tris.as<uint32_t>();
   s.normals = ctx->normals.as<float>(); s.uvs = ctx->uvs.as<float>();
   s.texels = ctx->texels.as<uint32_t>(); s.textures = ctx->textures.as<DTexture>();
-  s.srgb_lut = ctx->srgb_lut.as<float>();
+  s.srgb_lut = ctx->srgb_lut.as<float>(); s.node_instrs = ctx->node_instrs.as<pb2_node_instr>();
   ctx->counters.upload_ms =
       std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   return PB2_OK;
@@ -499,10 +542,10 @@ extern "C" int pb2_restage_scene_part(pb2_context* ctx, void* cuda_stream, int p
 // pb2_restage_scene_part, the renders) is unchanged because a HostScene is just a list of (member, pointer, bytes).
 namespace {
 struct SharedHeader {
-  char magic[8];  // "PB2SCN02"
+  char magic[8];  // "PB2SCN03"
   uint32_t sizeof_dscene, n_items;
   DScene scene;   // device pointers inside are meaningless to the importer and rebound by the staging
-  int32_t only_area_lights, needs_rng_in_shading, n_pixels;
+  int32_t only_area_lights, needs_rng_in_shading, n_pixels, has_node_programs;
   uint32_t material_kinds;
   pb2_counters counters;
 };
@@ -511,7 +554,8 @@ DBuf pb2_context::* const kStageMembers[] = {
     &pb2_context::nodes2, &pb2_context::nodes8, &pb2_context::leaves, &pb2_context::wide_prims, &pb2_context::box_shapes,
     &pb2_context::leaf_prims, &pb2_context::top_prims, &pb2_context::meshes, &pb2_context::geoms, &pb2_context::lights,
     &pb2_context::light_recs, &pb2_context::verts, &pb2_context::tris, &pb2_context::normals, &pb2_context::uvs,
-    &pb2_context::texels, &pb2_context::textures, &pb2_context::srgb_lut, &pb2_context::materials, &pb2_context::aabbs,
+    &pb2_context::texels, &pb2_context::textures, &pb2_context::srgb_lut, &pb2_context::node_instrs,
+    &pb2_context::materials, &pb2_context::aabbs,
     &pb2_context::obbs, &pb2_context::spheres, &pb2_context::triangles, &pb2_context::cones, &pb2_context::rects,
     &pb2_context::disks};
 constexpr uint32_t kNumStageMembers = sizeof(kStageMembers) / sizeof(kStageMembers[0]);
@@ -533,11 +577,12 @@ extern "C" int pb2_export_host_scene(pb2_context* ctx, const char* path) {
   for (uint32_t i = 0; i < kNumStageMembers; i++)
     if (H.items[i].dst != kStageMembers[i]) { set_error("staging list order changed"); return PB2_E_STATE; }
   SharedHeader hd{};
-  std::memcpy(hd.magic, "PB2SCN02", 8);
+  std::memcpy(hd.magic, "PB2SCN03", 8);
   hd.sizeof_dscene = uint32_t(sizeof(DScene));
   hd.n_items = kNumStageMembers;
   hd.scene = ctx->scene;
   hd.only_area_lights = ctx->only_area_lights; hd.needs_rng_in_shading = ctx->needs_rng_in_shading;
+  hd.has_node_programs = ctx->has_node_programs;
   hd.n_pixels = ctx->n_pixels; hd.material_kinds = ctx->material_kinds;
   hd.counters = ctx->counters;
   std::vector<uint64_t> table(2 * size_t(kNumStageMembers));
@@ -580,7 +625,7 @@ extern "C" int pb2_import_host_scene(pb2_context* ctx, const char* path) {
   SharedHeader hd;
   std::memcpy(&hd, base, sizeof(hd));
   const uint64_t* table = reinterpret_cast<const uint64_t*>(static_cast<const char*>(base) + sizeof(hd));
-  bool ok = std::memcmp(hd.magic, "PB2SCN02", 8) == 0 && hd.sizeof_dscene == sizeof(DScene) && hd.n_items == kNumStageMembers &&
+  bool ok = std::memcmp(hd.magic, "PB2SCN03", 8) == 0 && hd.sizeof_dscene == sizeof(DScene) && hd.n_items == kNumStageMembers &&
             size_t(st.st_size) >= sizeof(hd) + size_t(hd.n_items) * 16;
   for (uint32_t i = 0; ok && i < hd.n_items; i++) ok = table[2 * i + 1] + table[2 * i] <= uint64_t(st.st_size);
   if (!ok) { munmap(base, size_t(st.st_size)); set_error("not a scene file of this library version"); return PB2_E_INVALID; }
@@ -600,6 +645,7 @@ extern "C" int pb2_import_host_scene(pb2_context* ctx, const char* path) {
   ctx->scene = hd.scene;
   ctx->only_area_lights = hd.only_area_lights != 0;
   ctx->needs_rng_in_shading = hd.needs_rng_in_shading != 0;
+  ctx->has_node_programs = hd.has_node_programs != 0;
   ctx->n_pixels = hd.n_pixels;
   ctx->material_kinds = hd.material_kinds;
   const pb2_counters keep = ctx->counters;

@@ -300,6 +300,14 @@ class Backend:
                                              n_samples, d.ctypes.data))
         return d[:width * n_samples].reshape(n_samples, width)
 
+    def eval_node(self, start, ctx8):
+        """The uploaded scene's node program starting at `start` (1-based: Material.*_node) at the points
+        ctx8 = n x {p.xyz, n.xyz, uv} -> n x 3 (pb2_test_eval_node)."""
+        c = np.ascontiguousarray(ctx8, np.float32).reshape(-1, 8)
+        out = np.zeros((len(c), 3), np.float32)
+        A.check(self.L.pb2_test_eval_node(self.h, int(start), len(c), c.ctypes.data, out.ctypes.data))
+        return out
+
     def primary_rays(self, si=0):
         w, h = self.size
         rays = np.empty((w * h, 8), np.float32)

@@ -19,6 +19,7 @@ import re
 
 import numpy as np
 
+from . import nodes as N
 from .scene import mat4
 
 
@@ -220,9 +221,24 @@ def _vec(v, n=3):
     return tuple(float(_f32(v)) for _ in range(n))
 
 
+def _node3(v):
+    """A Node3f parameter: a graph stays a graph, anything else becomes a vec3 constant."""
+    return v if isinstance(v, N.Node) else _vec(v)
+
+
+def _nodef(v):
+    return v if isinstance(v, N.Node) else float(_f32(v))
+
+
 def _arith(op, a, b):
     """int op int stays int (jit.cpp integer ops); otherwise binary32, element-wise over vectors,
     4x4 * 4x4 through the C++ host mirror of vecmath.h."""
+    if isinstance(a, N.Node) or isinstance(b, N.Node):  # ctx("+") ... ctx("/") on Nodef / Node3f (node.cpp:72-92)
+        try:
+            x, y = N.as_node(a), N.as_node(b)
+            return {"+": x + y, "-": x - y, "*": x * y, "/": x / y}[op]
+        except TypeError as e:
+            raise PrlError(str(e))
     if isinstance(a, str) or isinstance(b, str):  # 'images/pine' + f + '.png' (jit.cpp string concatenation)
         if op != "+":
             raise PrlError("only + is defined on strings")
@@ -372,7 +388,22 @@ class _FilmHandle:
 
 
 def _subsurface(albedo, roughness, sigma_s):
-    return _Material("subsurface", _vec(albedo), roughness=float(_f32(roughness)), sigma_s=_vec(sigma_s))
+    return _Material("subsurface", _node3(albedo), roughness=_nodef(roughness), sigma_s=_vec(sigma_s))
+
+
+def _lerp(t, a, b):
+    """ctx("lerp"): on nodes the graph form (node.cpp:94-110), on plain values psl::lerp(t, a, b) = (1 - t) a + t b."""
+    if any(isinstance(v, N.Node) for v in (t, a, b)):
+        wrap = lambda v: v if isinstance(v, N.Node) or not isinstance(v, list) else tuple(v)
+        try:
+            return N.lerp(wrap(t), wrap(a), wrap(b))
+        except TypeError as e:
+            raise PrlError(str(e))
+    return _arith("+", _arith("*", _arith("-", 1.0, t), a), _arith("*", t, b))
+
+
+def _node_or(node_fn, plain_fn):
+    return lambda v: node_fn(v) if isinstance(v, N.Node) else plain_fn(v)
 
 
 def _globals(make_scene):
@@ -381,16 +412,22 @@ def _globals(make_scene):
         "Scene": make_scene,
         "Rect": shape("rect"), "Box": shape("box"), "AABB": shape("aabb"), "Cone": shape("cone"),
         "Sphere": shape("sphere"), "Disk": shape("disk"), "Triangle": shape("triangle"),
-        "Diffuse": lambda c: _Material("diffuse", _vec(c)),
+        "Diffuse": lambda c: _Material("diffuse", _node3(c)),
         "Emissive": lambda c: _Material("emissive", _vec(c)),
-        "Metal": lambda c, r: _Material("metal", _vec(c), roughness=float(_f32(r))),
-        "Glossy": lambda c, r, ior=1.4: _Material("glossy", _vec(c), roughness=float(_f32(r)), ior=float(_f32(ior))),
-        "Glass": lambda c, r, ior=1.4: _Material("glass", _vec(c), roughness=float(_f32(r)), ior=float(_f32(ior))),
+        "Metal": lambda c, r: _Material("metal", _node3(c), roughness=_nodef(r)),
+        "Glossy": lambda c, r, ior=1.4: _Material("glossy", _node3(c), roughness=_nodef(r), ior=_nodef(ior)),
+        "Glass": lambda c, r, ior=1.4: _Material("glass", _node3(c), roughness=_nodef(r), ior=_nodef(ior)),
         "Subsurface": _subsurface,
         # UberMaterial(albedo, roughness, metallic = 0, transmission = 0, ior = 1.45) (material.h:80-87, .cpp:53-57)
         "Uber": lambda c, r, metallic=0.0, transmission=0.0, ior=1.45: _Material(
-            "uber", _vec(c), roughness=float(_f32(r)), metallic=float(_f32(metallic)),
-            transmission=float(_f32(transmission)), ior=float(_f32(ior))),
+            "uber", _node3(c), roughness=_nodef(r), metallic=_nodef(metallic),
+            transmission=_nodef(transmission), ior=float(_f32(ior))),
+        # material parameter graphs (node_context, node.cpp:29-132); noise and Function nodes have no device form
+        "Position": N.Position, "Normal": N.Normal, "UV": N.UV, "Checkerboard": N.Checkerboard,
+        "Comp": N.Comp, "Vec3": N.Vec3, "lerp": _lerp,
+        "abs": _node_or(N.abs_, lambda v: abs(v)), "sqr": _node_or(N.sqr, lambda v: _arith("*", v, v)),
+        "sqrt": _node_or(N.sqrt, lambda v: np.sqrt(_f32(v))),
+        "fract": _node_or(N.fract, lambda v: _f32(v) - np.floor(_f32(v))),
         "Pi": np.float32(3.14159265358979323846),  # ctx.var("Pi") (math.cpp:7)
         "print": lambda *a: None, "println": lambda *a: None,  # LOG output only (program_context.cpp:41)
         "translate": lambda v: mat4.translate(_vec(v)), "scale": lambda v: mat4.scale(_vec(v)),

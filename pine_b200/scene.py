@@ -13,6 +13,7 @@ import ctypes as C
 import numpy as np
 
 from . import _abi as A
+from . import nodes as N
 
 
 def _f(a):
@@ -60,7 +61,8 @@ class mat4:
 class _Mat:
     def __init__(self, kind, color, roughness=0.0, ior=1.4, metallic=0.0, transmission=0.0,
                  sigma_s=(0.0, 0.0, 0.0)):
-        self.kind, self.color, self.roughness, self.ior = kind, tuple(color), roughness, ior
+        self.kind, self.roughness, self.ior = kind, roughness, ior
+        self.color = color if isinstance(color, N.Node) else tuple(color)   # a Node3f graph stays a graph
         self.metallic, self.transmission, self.sigma_s = metallic, transmission, tuple(sigma_s)
 
 
@@ -129,6 +131,7 @@ class Scene:
         self.shapes = {k: [] for k in A.SHAPE_KINDS}
         self.mesh_data = []          # keeps numpy arrays alive
         self.textures = []           # uint8 [h, w, 4] arrays (pine::Image of vec4u8)
+        self.node_instrs = []        # A.NodeInstr: the materials' node programs, each ending in `end`
         self.extra_lights = []       # (position in Scene::lights order = n geometries added before, A.Light)
         self.env_light = None        # A.Light of kind "sky"
         self.camera = None
@@ -151,6 +154,20 @@ class Scene:
         """`*_texture`: indices from add_texture (Uber only): NodeImage(NodeUV(), image) as albedo, its
         component 1 as roughness, its component 2 as metallic (fileio.cpp:285-292)."""
         m = A.Material()
+        # a parameter given as a node graph (pine_b200.nodes) becomes a program; its constant stays 0
+        params = dict(color=color, roughness=roughness, ior=ior, metallic=metallic, transmission=transmission)
+        for slot in A.NODE_SLOTS:
+            if N.is_graph(params[slot]):
+                if kind == "emissive":
+                    raise ValueError("Emissive color must be a constant on the CUDA path")
+                setattr(m, slot + "_node", len(self.node_instrs) + 1)
+                for ins in params[slot].program() + [(0, 0.0, 0.0, 0.0)]:
+                    self.node_instrs.append(A.NodeInstr(ins[0] & 0xff, A.f3(*ins[1:])))
+                params[slot] = (0.0, 0.0, 0.0) if slot == "color" else 0.0
+            else:
+                params[slot] = N.constant_of(params[slot], slot != "color")
+        color, roughness, ior = params["color"], params["roughness"], params["ior"]
+        metallic, transmission = params["metallic"], params["transmission"]
         m.color_texture = 0 if color_texture is None else int(color_texture) + 1
         m.roughness_texture = 0 if roughness_texture is None else int(roughness_texture) + 1
         m.metallic_texture = 0 if metallic_texture is None else int(metallic_texture) + 1
@@ -369,6 +386,8 @@ class Scene:
             t.rgba, t.width, t.height = a.ctypes.data, a.shape[1], a.shape[0]
             texs.append(t)
         put("textures", A.Texture, texs)
+        if self.node_instrs:
+            put("node_instrs", A.NodeInstr, self.node_instrs)
         if self.extra_lights or self.env_light is not None:
             put("light_records", A.Light, self.light_records())
         ls = self.lights()

@@ -272,6 +272,31 @@ def materials_room(B, size=(96, 96)):
     return {"spp": 16, "depth": 6}
 
 
+def classic(B, size=(720, 360), skin=False):
+    """scenes/classic.pine:1-18: a checkerboard Uber floor -- albedo and roughness are node graphs,
+    lerp(Checkerboard(UV(), 0.95), a, b) -- under three unit spheres (the middle one Subsurface in the file;
+    Diffuse here unless `skin`, because the reference's BSSRDF walk is ill-defined on analytic shapes)
+    and a 2x2 Rect emitter. The file renders it with MicroRenderGI and keeps the PathIntegrator line commented."""
+    from . import nodes as N
+    check = lambda: N.Checkerboard(N.UV(), 0.95)
+    floor = B.add_material("uber", N.lerp(check(), (0.5, 0.7, 1.0), (0.01, 0.02, 0.03)),
+                           roughness=N.lerp(check(), 0.0, 0.4), metallic=0.0, transmission=0.0, ior=1.45)
+    if skin:
+        middle = B.add_material("subsurface", (0, 0, 0), roughness=0.0, sigma_s=(1.0, 0.8, 0.6))
+    else:
+        middle = B.add_material("diffuse", (0.8, 0.8, 0.8))
+    metal = B.add_material("uber", (1.0, 1.0, 1.0), roughness=0.0, metallic=1.0, transmission=0.0, ior=1.45)
+    glossy = B.add_material("uber", (0.98, 0.55, 0.02), roughness=0.0, metallic=0.0, transmission=0.0, ior=1.45)
+    B.add_disk((0, 0, 0), (0, 1, 0), 100.0, floor)
+    B.add_sphere((-3, 1, 0), 1.0, metal)
+    B.add_sphere((0, 1, 0), 1.0, middle)
+    B.add_sphere((3, 1, 0), 1.0, glossy)
+    light = B.add_material("emissive", tuple(np.float32(160) * np.float32(c) for c in (1, 1, 1)))
+    B.add_rect((-1, 3, -1), (1, 0, 0), (0, 0, 1), light)
+    B.set_camera(size, (0, 4, -8), (0, 1, 0), 0.3)
+    return {"spp": 64, "depth": 6}
+
+
 def lights_yard(B, size=(96, 64), sky=True, delta=True, area=True):
     """Parity scene for the lights the named configs never use (light.h:21-66): an open yard (ground, one
     wall, a sphere, a cone, a box) lit by a DirectionalLight, a PointLight, a SpotLight (with a cutoff band),
@@ -301,5 +326,5 @@ def lights_yard(B, size=(96, 64), sky=True, delta=True, area=True):
     return {"spp": 16, "depth": 5}
 
 
-SCENES = {"materials_room": materials_room, "lights_yard": lights_yard, "cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
+SCENES = {"materials_room": materials_room, "classic": classic, "lights_yard": lights_yard, "cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
           "mesh_field": mesh_field, "room_proc": room_proc}

@@ -35,7 +35,7 @@ def test_struct_sizes_match_header():
     # sizes the C side static_asserts / the header implies
     assert C.sizeof(A.Rect) == 80 and C.sizeof(A.Obb) == 152 and C.sizeof(A.Cone) == 96
     assert C.sizeof(A.Disk) == 52 and C.sizeof(A.Sphere) == 16 and C.sizeof(A.Triangle) == 48
-    assert C.sizeof(A.Material) == 56 and C.sizeof(A.Geometry) == 12
+    assert C.sizeof(A.Material) == 76 and C.sizeof(A.Geometry) == 12 and C.sizeof(A.NodeInstr) == 16
     assert C.sizeof(A.RenderParams) == 52
 
 

@@ -114,3 +114,82 @@ def test_sharded_restaging_rebuilds_the_replica():
     with pytest.raises(pb.PineB200Error):
         B.restage_part(2, 2)
     B.close()
+
+
+# ---- material parameter graphs (node.h:105-250): device programs vs the reference's own node objects -----------
+@needs_ref
+def test_node_programs_evaluate_like_the_reference_nodes():
+    """pb2_test_eval_node on the uploaded programs vs Mnode<T>::operator() of the reference's node objects built
+    from the same graphs: bit-identical (same float expressions; no transcendental in these graphs), and powf
+    graphs to 2 ulp."""
+    from oracle import ref
+    from pine_b200 import nodes as N
+    from test_nodes import GRAPHS, _points
+    graphs = {k: v() for k, v in GRAPHS.items()}
+    graphs["pow"] = (N.abs_(N.Position()) + (0.5, 0.5, 0.5)) ** N.Vec3(N.fract(N.UV()[0]) + 0.5)
+    S = pb.Scene()
+    starts = {}
+    for k, g in graphs.items():
+        m = S.add_material("diffuse", g if not g.is_float else N.Vec3(g) * (1.0, 1.0, 1.0))
+        starts[k] = S.materials[m].color_node
+    S.add_sphere((0, 0, 0), 1.0, 0)
+    S.set_camera((8, 8), (0, 0, -4), (0, 0, 0), 0.3)
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    c = _points(4099, seed=11)
+    for k, g in graphs.items():
+        want = ref.eval_node(g if not g.is_float else N.Vec3(g) * (1.0, 1.0, 1.0), c)
+        got = B.eval_node(starts[k], c)
+        if k == "pow":
+            np.testing.assert_allclose(got, want, rtol=3e-7, atol=0)
+        else:
+            assert np.array_equal(u32(got), u32(want)), k
+    with pytest.raises(pb.PineB200Error):
+        B.eval_node(starts["classic_rough"] + 1, c)   # not the start of a program
+    B.close()
+
+
+@needs_ref
+def test_classic_pine_checkerboard_floor_matches_the_reference():
+    """scenes/classic.pine's scene (checkerboard Uber floor: albedo AND roughness are lerp(Checkerboard(UV(), 0.95),
+    a, b) graphs) under PathIntegrator: film vs the live reference at equal spp, statistically as for the other
+    Uber scenes (its RNG coins amplify libm differences), and the floor's two albedos both show up."""
+    from oracle import ref
+    R, S = ref.RefScene(), pb.Scene()
+    scenes.classic(R, size=(180, 90))
+    scenes.classic(S, size=(180, 90))
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    spp, depth = 16, 6
+    film_ref, _ = R.render(spp, depth)
+    film = B.render(spp, depth)
+    assert np.isfinite(film).all() and (film[..., 3] == 1).all()
+    assert np.array_equal(u32(film), u32(B.render(spp, depth, accel=1)))
+    film_hi, _ = R.render(256, depth)
+    e_gpu, e_ref = relmse(film, film_hi), relmse(film_ref, film_hi)
+    assert e_gpu <= 1.25 * e_ref + 1e-4, (e_gpu, e_ref)
+    a, b = film[..., :3].astype(np.float64), film_ref[..., :3].astype(np.float64)
+    assert abs(a.sum() / b.sum() - 1) < 0.02
+    # without the graphs (constant floor) the film is a different one: the programs are really evaluated
+    S2 = pb.Scene()
+    scenes.classic(S2, size=(180, 90))
+    S2.materials[0].color_node = S2.materials[0].roughness_node = 0
+    B.upload_scene(S2)
+    assert relmse(B.render(spp, depth), film_hi) > 4 * e_gpu
+    B.close()
+
+
+@needs_ref
+def test_shim_flattens_node_graphs():
+    """pine::CudaPathIntegrator over the reference's own Scene whose Uber floor holds pine's node objects: the shim's
+    flatten emits the programs (integration/cuda_path_integrator.cpp emit), film bits equal the Python mirror's."""
+    from oracle import ref
+    R, S = ref.RefScene(), pb.Scene()
+    scenes.classic(R, size=(96, 48))
+    scenes.classic(S, size=(96, 48))
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    film = B.render(8, 5)
+    shim, _, stats = R.render_cuda(8, 5)
+    assert np.array_equal(u32(shim), u32(film)) and stats["closest_rays"] > 0
+    B.close()
