@@ -1,7 +1,7 @@
 #!/bin/bash
 # full bench line + reference arms + ncu evidence on the C5 size (round 2)
 set -u
-O=gpurun_out; mkdir -p $O; T=r2s10
+O=gpurun_out; mkdir -p $O; T=${1:-r2s10}
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O/${T}_smi.csv 2>&1
 ( time timeout 900 python bench.py --steps 5 --warmup 3 ) > $O/${T}_bench_c5.json 2> $O/${T}_bench_c5.err; echo "bench rc=$?"; tail -3 $O/${T}_bench_c5.err
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/${T}_bench_ref_c5.json 2> $O/${T}_bench_ref_c5.err; echo "ref rc=$?"
