@@ -265,6 +265,9 @@ class RefScene:
         film = np.zeros((h, w, 4), np.float32)
         stats = np.zeros(5, np.float64)
         kind = {"blue": 0, "sobol": 1, "uniform": 2, "halton": 3}[sampler]
+        if device < 0:  # the shim's pb2_multi binds NCCL at run time: keep it the one a later `import torch` expects
+            from pine_b200.integrator import _preload_bundled_nccl
+            _preload_bundled_nccl()
         secs = shim().ref_render_cuda_kind(self.h, kind, spp, depth, device, film.ctypes.data, stats.ctypes.data)
         return film, secs, {"closest_rays": int(stats[0]), "shadow_rays": int(stats[1]),
                             "kernel_launches": int(stats[2]), "render_ms": float(stats[3]), "n_devices": int(stats[4])}

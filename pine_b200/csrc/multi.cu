@@ -17,6 +17,7 @@
 #include <thread>
 #include <atomic>
 #include <memory>
+#include <cstdlib>
 #include <vector>
 
 #include "context.h"
@@ -39,9 +40,14 @@ struct Nccl {
   const char* (*GetErrorString)(int) = nullptr;
   bool load(std::string& err) {
     if (lib) return true;
+    // PB2_NCCL_LIB names a file; otherwise "libnccl.so.2" resolves to the NCCL the process has ALREADY loaded (same
+    // SONAME: e.g. the one bundled with PyTorch, which pine_b200/integrator.py pre-loads so that a later `import
+    // torch` finds its own version) or, failing that, to the system one.
+    const char* forced = std::getenv("PB2_NCCL_LIB");
+    if (forced && *forced) lib = dlopen(forced, RTLD_NOW | RTLD_LOCAL);
     for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
-      lib = dlopen(name, RTLD_NOW | RTLD_LOCAL);
       if (lib) break;
+      lib = dlopen(name, RTLD_NOW | RTLD_LOCAL);
     }
     if (!lib) { err = std::string("cannot load NCCL (libnccl.so.2): ") + dlerror(); return false; }
     auto sym = [&](const char* n) { return dlsym(lib, n); };

@@ -123,6 +123,30 @@ def host_sampler_draws(sampler, size, px, py, sample_index, pattern, n_samples):
     return d[:width * n_samples].reshape(n_samples, width)
 
 
+_nccl_preloaded = False
+
+
+def _preload_bundled_nccl():
+    """pb2_multi binds NCCL with dlopen("libnccl.so.2") at its first multi-GPU use. If that loaded the system
+    library and the process imported PyTorch LATER, torch's libtorch_cuda.so would be resolved against it (same
+    SONAME) and fail on symbols only its own, newer NCCL has. So when PyTorch's bundled NCCL is installed
+    (site-packages/nvidia/nccl/lib) it is loaded first and both sides share it; PB2_NCCL_LIB overrides."""
+    global _nccl_preloaded
+    if _nccl_preloaded or os.environ.get("PB2_NCCL_LIB"):
+        return
+    _nccl_preloaded = True
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (spec.submodule_search_locations if spec else []):
+            path = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                C.CDLL(path, mode=C.RTLD_GLOBAL)
+                return
+    except (ImportError, OSError, ValueError):
+        pass
+
+
 class Backend:
     """One pb2_context (one GPU). `device=-1` makes a host-only context (BVH builder inspection)."""
 
@@ -347,6 +371,7 @@ class MultiBackend:
 
     def __init__(self, devices=None):
         self.L = A.lib()
+        _preload_bundled_nccl()
         h = C.c_void_p()
         if devices is None:
             A.check(self.L.pb2_create_multi(None, 0, C.byref(h)))
