@@ -64,6 +64,18 @@ typedef struct pb2_triangle { /* pine::Triangle, geometry.h:98-116 */
   float v0[3], v1[3], v2[3], n[3];
 } pb2_triangle;
 
+typedef struct pb2_plane { /* pine::Plane, geometry.h:12-26; BVH::build bounds it by position +- 100 (geometry.cpp:52) */
+  float position[3], n[3], u[3], v[3];
+} pb2_plane;
+
+typedef struct pb2_cylinder { /* pine::Cylinder, geometry.h:139-155: the open tube between p0 and p1. Its two Disk
+                               * members both sit at p0 (geometry.h:141), so get_aabb() is the box of a sphere of
+                               * radius r around p0 -- kept: that box is what the reference's BVH tests */
+  float p0[3], p1[3], n[3];
+  float r;
+  pb2_disk bottom, top;
+} pb2_cylinder;
+
 typedef struct pb2_mesh { /* pine::Mesh, geometry.h:158-224 */
   const float* vertices; /* n_vertices x 3 */
   const uint32_t* indices; /* n_triangles x 3 */
@@ -80,7 +92,9 @@ enum pb2_shape_kind {
   PB2_SHAPE_CONE = 4,
   PB2_SHAPE_RECT = 5,
   PB2_SHAPE_DISK = 6,
-  PB2_SHAPE_MESH = 7
+  PB2_SHAPE_MESH = 7,
+  PB2_SHAPE_PLANE = 8,
+  PB2_SHAPE_CYLINDER = 9
 };
 
 /* ---- procedural material parameters: Node3f / Nodef graphs (node.h:105-250, node.cpp:8-27) ------------------
@@ -208,6 +222,8 @@ typedef struct pb2_scene_desc {
   const pb2_light* light_records;  uint32_t n_light_records;
   /* Programs of the materials' *_node parameters, back to back, each ending in PB2_NODE_END. May be NULL / 0. */
   const pb2_node_instr* node_instrs; uint32_t n_node_instrs;
+  const pb2_plane* planes;         uint32_t n_planes;    /* may be NULL / 0 */
+  const pb2_cylinder* cylinders;   uint32_t n_cylinders; /* may be NULL / 0 */
 } pb2_scene_desc;
 
 typedef struct pb2_render_params {

@@ -28,6 +28,8 @@ void pb2h_make_rect(const float* pos, const float* ex, const float* ey, int flip
 void pb2h_make_obb(const float* lo, const float* hi, const float* m_colmajor, pb2_obb* out);
 void pb2h_make_disk(const float* p, const float* n, float r, pb2_disk* out);
 void pb2h_make_cone(const float* p, const float* n, float r, float h, pb2_cone* out);
+void pb2h_make_plane(const float* position, const float* normal, pb2_plane* out);   /* geometry.cpp:31-34 */
+void pb2h_make_cylinder(const float* p0, const float* p1, float r, pb2_cylinder* out); /* geometry.h:140-141 */
 void pb2h_make_triangle(const float* a, const float* b, const float* c, pb2_triangle* out);
 void pb2h_make_camera(int w, int h, int tonemapper, const float* from, const float* to, float fov,
                       float len_radius, float focus, pb2_camera* out);

@@ -40,6 +40,8 @@ static_assert(sizeof(Rect) == sizeof(pb2_rect), "pb2_rect must mirror pine::Rect
 static_assert(sizeof(AABB) == sizeof(pb2_aabb), "pb2_aabb must mirror pine::AABB");
 static_assert(sizeof(OBB) == sizeof(pb2_obb), "pb2_obb must mirror pine::OBB");
 static_assert(sizeof(Disk) == sizeof(pb2_disk), "pb2_disk must mirror pine::Disk");
+static_assert(sizeof(Plane) == sizeof(pb2_plane), "pb2_plane must mirror pine::Plane");
+static_assert(sizeof(Cylinder) == sizeof(pb2_cylinder), "pb2_cylinder must mirror pine::Cylinder");
 static_assert(sizeof(Cone) == sizeof(pb2_cone), "pb2_cone must mirror pine::Cone");
 static_assert(sizeof(Sphere) == sizeof(pb2_sphere), "pb2_sphere must mirror pine::Sphere");
 static_assert(sizeof(Triangle) == sizeof(pb2_triangle), "pb2_triangle must mirror pine::Triangle");
@@ -153,6 +155,8 @@ struct Flat {
   std::vector<pb2_cone> cones;
   std::vector<pb2_rect> rects;
   std::vector<pb2_disk> disks;
+  std::vector<pb2_plane> planes;
+  std::vector<pb2_cylinder> cylinders;
   std::vector<pb2_mesh> meshes;
   std::vector<int32_t> lights;
   std::vector<pb2_light> light_records;
@@ -299,6 +303,8 @@ void flatten(Scene& scene, Flat& f) {
     else if (s.is<Sphere>()) { rec.shape_kind = PB2_SHAPE_SPHERE; rec.shape_index = push(f.spheres, s.as<Sphere>()); }
     else if (s.is<Disk>()) { rec.shape_kind = PB2_SHAPE_DISK; rec.shape_index = push(f.disks, s.as<Disk>()); }
     else if (s.is<Triangle>()) { rec.shape_kind = PB2_SHAPE_TRIANGLE; rec.shape_index = push(f.triangles, s.as<Triangle>()); }
+    else if (s.is<Plane>()) { rec.shape_kind = PB2_SHAPE_PLANE; rec.shape_index = push(f.planes, s.as<Plane>()); }
+    else if (s.is<Cylinder>()) { rec.shape_kind = PB2_SHAPE_CYLINDER; rec.shape_index = push(f.cylinders, s.as<Cylinder>()); }
     else if (s.is<Mesh>()) {
       const Mesh& m = s.as<Mesh>();
       pb2_mesh pm{};
@@ -313,7 +319,7 @@ void flatten(Scene& scene, Flat& f) {
       rec.shape_index = int32_t(f.meshes.size()) - 1;
     } else {
       SEVERE("[CudaPathIntegrator]geometry ", gi, " has a shape kind the CUDA path does not implement "
-             "(Plane/Cylinder/Line/SDF/CSG); there is no CPU fallback");
+             "(Line/SDF/CSG); there is no CPU fallback");
     }
     f.geometries.push_back(rec);
   }
@@ -385,6 +391,8 @@ void flatten(Scene& scene, Flat& f) {
   d.light_geometries = f.lights.data(); d.n_lights = uint32_t(f.lights.size());
   d.textures = f.textures.data();     d.n_textures = uint32_t(f.textures.size());
   d.node_instrs = f.node_instrs.data(); d.n_node_instrs = uint32_t(f.node_instrs.size());
+  d.planes = f.planes.data();         d.n_planes = uint32_t(f.planes.size());
+  d.cylinders = f.cylinders.data();   d.n_cylinders = uint32_t(f.cylinders.size());
   if (!only_area) { d.light_records = f.light_records.data(); d.n_light_records = uint32_t(f.light_records.size()); }
 }
 

@@ -87,7 +87,7 @@ def lib():
         L.ref_bluenoise.restype = C.c_float
         L.ref_hash_pixel.restype = C.c_uint64
         for name in ("ref_add_material", "ref_add_rect", "ref_add_box", "ref_add_aabb",
-                     "ref_add_cone", "ref_add_sphere", "ref_add_disk", "ref_add_triangle",
+                     "ref_add_cone", "ref_add_sphere", "ref_add_disk", "ref_add_triangle", "ref_add_plane", "ref_add_cylinder",
                      "ref_add_mesh", "ref_num_geometries", "ref_num_lights", "ref_bvh_info",
                      "ref_bvh_num_lbvh", "ref_bvh_num_indices", "ref_load_gltf"):
             getattr(L, name).restype = C.c_int
@@ -199,6 +199,14 @@ class RefScene:
     def add_disk(self, p, n, r, mat):
         a, b = _f(p), _f(n)
         return self.L.ref_add_disk(self.h, _fp(a), _fp(b), C.c_float(r), mat)
+
+    def add_plane(self, p, n, mat):
+        a, b = _f(p), _f(n)
+        return self.L.ref_add_plane(self.h, _fp(a), _fp(b), mat)
+
+    def add_cylinder(self, p0, p1, r, mat):
+        a, b = _f(p0), _f(p1)
+        return self.L.ref_add_cylinder(self.h, _fp(a), _fp(b), C.c_float(r), mat)
 
     def add_triangle(self, a, b, c, mat):
         a, b, c = _f(a), _f(b), _f(c)

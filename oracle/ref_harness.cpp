@@ -296,6 +296,12 @@ int ref_add_sphere(void* h, const float* c, float r, int mat) {
 int ref_add_disk(void* h, const float* p, const float* n, float r, int mat) {
   return add_shape(*(RefScene*)h, Disk(v3(p), v3(n), r), mat);
 }
+int ref_add_plane(void* h, const float* p, const float* n, int mat) {
+  return add_shape(*(RefScene*)h, Plane(v3(p), v3(n)), mat);
+}
+int ref_add_cylinder(void* h, const float* p0, const float* p1, float r, int mat) {
+  return add_shape(*(RefScene*)h, Cylinder(v3(p0), v3(p1), r), mat);
+}
 int ref_add_triangle(void* h, const float* a, const float* b, const float* c, int mat) {
   return add_shape(*(RefScene*)h, Triangle(v3(a), v3(b), v3(c)), mat);
 }

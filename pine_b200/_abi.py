@@ -40,6 +40,14 @@ class Cone(C.Structure):
                 ("A", C.c_float), ("A2", C.c_float), ("S", C.c_float)]
 
 
+class Plane(C.Structure):
+    _fields_ = [("position", f3), ("n", f3), ("u", f3), ("v", f3)]
+
+
+class Cylinder(C.Structure):
+    _fields_ = [("p0", f3), ("p1", f3), ("n", f3), ("r", C.c_float), ("bottom", Disk), ("top", Disk)]
+
+
 class Sphere(C.Structure):
     _fields_ = [("c", f3), ("r", C.c_float)]
 
@@ -107,7 +115,7 @@ class SceneDesc(C.Structure):
                 _arr("meshes", Mesh) +
                 [("light_geometries", C.POINTER(C.c_int32)), ("n_lights", C.c_uint32),
                  ("camera", Camera)] + _arr("textures", Texture) + _arr("light_records", Light) +
-                _arr("node_instrs", NodeInstr))
+                _arr("node_instrs", NodeInstr) + _arr("planes", Plane) + _arr("cylinders", Cylinder))
 
 
 class RenderParams(C.Structure):
@@ -143,7 +151,7 @@ class Counters(C.Structure):
 
 
 SHAPE_KINDS = {"aabb": 0, "obb": 1, "sphere": 2, "triangle": 3, "cone": 4, "rect": 5, "disk": 6,
-               "mesh": 7}
+               "mesh": 7, "plane": 8, "cylinder": 9}
 MATERIAL_KINDS = {"emissive": 0, "diffuse": 1, "metal": 2, "glossy": 3, "glass": 4, "uber": 5,
                   "subsurface": 6}
 
@@ -154,7 +162,7 @@ ABI_SYMBOLS = [
     "pb2_upload_sampler_tables", "pb2_load_sampler_tables_file", "pb2_render", "pb2_render_device", "pb2_film_finalize",
     "pb2_trace_closest", "pb2_trace_any", "pb2_trace_closest_device", "pb2_test_sampler", "pb2_test_sampler_kind",
     "pb2_test_primary_rays", "pb2_get_counters", "pb2_debug_walk_stats", "pb2_set_ray_record", "pb2_bvh_info", "pb2_bvh_nodes",
-    "pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_cone", "pb2h_make_triangle",
+    "pb2h_make_rect", "pb2h_make_obb", "pb2h_make_disk", "pb2h_make_plane", "pb2h_make_cylinder", "pb2h_make_cone", "pb2h_make_triangle",
     "pb2h_make_camera", "pb2h_mat4", "pb2h_mat4_mul", "pb2h_mesh_apply", "pb2h_cosf", "pb2h_round_spp", "pb2h_sampler_draws",
     "pb2_create_multi", "pb2_destroy_multi", "pb2_multi_size", "pb2_multi_context", "pb2_multi_upload_sampler_tables",
     "pb2_multi_load_sampler_tables_file", "pb2_multi_upload_scene", "pb2_multi_restage_scene", "pb2_multi_render",

@@ -132,7 +132,11 @@ struct Wide {
   std::vector<char> top_unbounded;               // top node -> a Cone somewhere below it
 
   // Shapes that can be hit outside their own box (traverse.cuh (iv)).
-  static bool unbounded_kind(int kind) { return kind == PB2_SHAPE_CONE; }
+  // shapes that can be hit outside their own BVH box: a Cone below its base, a Plane beyond +-100, a Cylinder
+  // beyond the radius-r box around p0 the reference gives it (geometry.h:141,147)
+  static bool unbounded_kind(int kind) {
+    return kind == PB2_SHAPE_CONE || kind == PB2_SHAPE_PLANE || kind == PB2_SHAPE_CYLINDER;
+  }
   void mark_unbounded() {
     const Tree2& t = top();
     top_unbounded.assign(t.nodes.size(), 0);

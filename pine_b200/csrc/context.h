@@ -83,6 +83,8 @@ struct HostScene {
   std::vector<pb2_cone> cones;
   std::vector<pb2_rect> rects;
   std::vector<pb2_disk> disks;
+  std::vector<pb2_plane> planes;
+  std::vector<pb2_cylinder> cylinders;
   // staging list, in upload order. `dst` names the destination by member so that the same list stages the
   // scene into ANY context: the replicas of a pb2_multi share the host scene their first context built.
   struct Item { DBuf pb2_context::* dst; const void* src; size_t bytes; };
@@ -129,7 +131,7 @@ struct pb2_context {
   const pb2::HostScene* host_view = nullptr;  // whose staging list restage() copies: &host, or the scene's owner (pb2_multi)
   pb2::DScene scene{};  // device pointers
   pb2::DBuf nodes2, nodes8, leaves, wide_prims, box_shapes, leaf_prims, top_prims, meshes, geoms, materials, lights, light_recs;
-  pb2::DBuf aabbs, obbs, spheres, triangles, cones, rects, disks;
+  pb2::DBuf aabbs, obbs, spheres, triangles, cones, rects, disks, planes, cylinders;
   pb2::DBuf verts, tris, normals, uvs, texels, textures, srgb_lut, node_instrs;
   pb2::DBuf tab_sobol, tab_scramble, tab_rank;
   pb2::DBuf halton_primes, halton_sums, halton_perms;  // HaltonSampler tables, made on first use

@@ -130,6 +130,8 @@ struct DScene {
   const pb2_cone* cones;
   const pb2_rect* rects;
   const pb2_disk* disks;
+  const pb2_plane* planes;
+  const pb2_cylinder* cylinders;
   // mesh pools
   const float* verts;
   const uint32_t* tris;
@@ -154,6 +156,7 @@ struct DScene {
   const int32_t* halton_sums;
   const uint16_t* halton_perms;
   int halton_inv0, halton_inv1;
+  int has_rare_shapes;  // a Plane or a Cylinder somewhere: the traversal kernels compiled with those two shapes run
   pb2_camera camera;
   unsigned long long* walk_stats;  // PB2_COUNT builds only: {closest nodes, closest prims, any nodes, any prims,
                                    // closest rays, any rays}; NULL otherwise

@@ -15,6 +15,12 @@ void pb2h_make_rect(const float* pos, const float* ex, const float* ey, int flip
 void pb2h_make_obb(const float* lo, const float* hi, const float* m_colmajor, pb2_obb* out) {
   *out = make_obb(ld3(lo), ld3(hi), ld_m4(m_colmajor));
 }
+void pb2h_make_plane(const float* position, const float* normal, pb2_plane* out) {
+  *out = make_plane(ld3(position), ld3(normal));
+}
+void pb2h_make_cylinder(const float* p0, const float* p1, float r, pb2_cylinder* out) {
+  *out = make_cylinder(ld3(p0), ld3(p1), r);
+}
 void pb2h_make_disk(const float* p, const float* n, float r, pb2_disk* out) {
   *out = make_disk(ld3(p), ld3(n), r);
 }

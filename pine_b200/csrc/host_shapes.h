@@ -164,6 +164,22 @@ inline pb2_cone make_cone(V3 p, V3 n, float r, float h) {
   c.S = r / sqrtf(r * r + h * h);
   return c;
 }
+inline pb2_plane make_plane(V3 position, V3 normal) {  // Plane::Plane (geometry.cpp:31-34)
+  pb2_plane q;
+  V3 n = normalize(normal);
+  M3 tbn = coordinate_system(n);
+  st3(q.position, position); st3(q.n, n); st3(q.u, tbn.x); st3(q.v, tbn.y);
+  return q;
+}
+inline pb2_cylinder make_cylinder(V3 p0, V3 p1, float r) {  // Cylinder::Cylinder (geometry.h:140-141)
+  pb2_cylinder c;
+  V3 n = normalize(p1 - p0);
+  st3(c.p0, p0); st3(c.p1, p1); st3(c.n, n);
+  c.r = r;
+  c.bottom = make_disk(p0, -n, r);
+  c.top = make_disk(p0, n, r);  // the reference puts BOTH disks at p0
+  return c;
+}
 inline pb2_obb make_obb(V3 lo, V3 hi, const M4& m) {
   pb2_obb o;
   st3(o.base.lower, lo); st3(o.base.upper, hi);
@@ -208,6 +224,16 @@ inline Box3 aabb_of_sphere(V3 c, float r) {
 }
 inline Box3 aabb_of(const pb2_sphere& s) { return aabb_of_sphere(ld3(s.c), s.r); }
 inline Box3 aabb_of(const pb2_disk& d) { return aabb_of_sphere(ld3(d.position), d.r); }
+inline Box3 aabb_of(const pb2_plane& q) {  // Plane::get_aabb (geometry.cpp:52)
+  Box3 b;
+  b.lower = ld3(q.position) + V3(-100.0f); b.upper = ld3(q.position) + V3(100.0f);
+  return b;
+}
+inline Box3 aabb_of(const pb2_cylinder& c) {  // union_(bottom.get_aabb(), top.get_aabb()) (geometry.h:147)
+  Box3 b = aabb_of(c.bottom);
+  b.extend(aabb_of(c.top));
+  return b;
+}
 inline Box3 aabb_of(const pb2_cone& c) {
   Box3 b = aabb_of(c.bottom);
   b.extend(ld3(c.p));

@@ -204,23 +204,30 @@ __device__ __forceinline__ TraceIO trace_io(const WaveView& w, int depth) {
 __device__ __forceinline__ ShadowIO shadow_io(const WaveView& w, int depth) {
   return ShadowIO{w.sh_o, w.sh_d, w.vtx + size_t(depth) * w.n_slots * 2, w.occ};
 }
+// RARE: the scene holds a Plane or a Cylinder (shapes.cuh shape_intersect<RARE>)
+template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_trace(DScene sc, WaveView w, int depth) {
-  wide_persistent<false>(sc, w.counts[depth], wave_queue(w, depth, 0), trace_io(w, depth));
+  wide_persistent<false, RARE>(sc, w.counts[depth], wave_queue(w, depth, 0), trace_io(w, depth));
 }
+template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock, kFallbackBlocksPerSM) k_trace_fallback(DScene sc, WaveView w, int depth) {
-  wide_fallback<false>(sc, wave_queue(w, depth, 0), trace_io(w, depth));
+  wide_fallback<false, RARE>(sc, wave_queue(w, depth, 0), trace_io(w, depth));
 }
+template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_trace_ref(DScene sc, WaveView w, int depth) {
-  ref_order_all<false>(sc, w.counts[depth], trace_io(w, depth));
+  ref_order_all<false, RARE>(sc, w.counts[depth], trace_io(w, depth));
 }
+template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_shadow(DScene sc, WaveView w, int depth) {
-  wide_persistent<true>(sc, w.counts[w.max_depth + 1 + depth], wave_queue(w, depth, 1), shadow_io(w, depth));
+  wide_persistent<true, RARE>(sc, w.counts[w.max_depth + 1 + depth], wave_queue(w, depth, 1), shadow_io(w, depth));
 }
+template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock, kFallbackBlocksPerSM) k_shadow_fallback(DScene sc, WaveView w, int depth) {
-  wide_fallback<true>(sc, wave_queue(w, depth, 1), shadow_io(w, depth));
+  wide_fallback<true, RARE>(sc, wave_queue(w, depth, 1), shadow_io(w, depth));
 }
+template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_shadow_ref(DScene sc, WaveView w, int depth) {
-  ref_order_all<true>(sc, w.counts[w.max_depth + 1 + depth], shadow_io(w, depth));
+  ref_order_all<true, RARE>(sc, w.counts[w.max_depth + 1 + depth], shadow_io(w, depth));
 }
 
 // sky_color(direction) (color.cpp:100-103): sqr(lerp(d.y / 2 + 0.7, warm, cool)), lerp = a (1 - t) + b t
@@ -365,7 +372,7 @@ __device__ inline bool bssrdf_walk(const DScene& sc, const Bxdf& b, int geom, V3
       });
       if (hit) surface_info(sc, geom, prim, ray.o + ray.tmax * ray.d, exit_it);
     } else {
-      hit = shape_intersect(sc, gm.kind, gm.index, ray);
+      hit = shape_intersect<false>(sc, gm.kind, gm.index, ray);  // Subsurface on a Plane / Cylinder is refused at upload
     }
     if (!hit) return false;
     float t = -logf(1 - smp_get1d(sc, smp)) * sigma_t_inv;
@@ -1046,11 +1053,14 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
     launches++; mark(3);
     for (int depth = 0; depth < D; depth++) {
       if (closest_wide_ok) {
-        k_trace<<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-        k_trace_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
+        if (sc.has_rare_shapes) k_trace<true><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+        else k_trace<false><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+        if (sc.has_rare_shapes) k_trace_fallback<true><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
+        else k_trace_fallback<false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
         launches += 2;
       } else {
-        k_trace_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ls>>>(sc, w, depth);
+        if (sc.has_rare_shapes) k_trace_ref<true><<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ls>>>(sc, w, depth);
+        else k_trace_ref<false><<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ls>>>(sc, w, depth);
         launches++;
       }
       mark(0);
@@ -1075,11 +1085,14 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       mark(2);
       if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
         if (any_wide_ok) {
-          k_shadow<<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-          k_shadow_fallback<<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
+          if (sc.has_rare_shapes) k_shadow<true><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+          else k_shadow<false><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+          if (sc.has_rare_shapes) k_shadow_fallback<true><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
+          else k_shadow_fallback<false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
           launches += 2;
         } else {
-          k_shadow_ref<<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ls>>>(sc, w, depth);
+          if (sc.has_rare_shapes) k_shadow_ref<true><<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ls>>>(sc, w, depth);
+          else k_shadow_ref<false><<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ls>>>(sc, w, depth);
           launches++;
         }
         mark(1);

@@ -76,8 +76,8 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     set_error("camera film size must be positive");
     return PB2_E_INVALID;
   }
-  const uint32_t counts[8] = {sd->n_aabbs, sd->n_obbs, sd->n_spheres, sd->n_triangles,
-                              sd->n_cones, sd->n_rects, sd->n_disks, sd->n_meshes};
+  const uint32_t counts[10] = {sd->n_aabbs, sd->n_obbs, sd->n_spheres, sd->n_triangles, sd->n_cones,
+                               sd->n_rects, sd->n_disks, sd->n_meshes, sd->n_planes, sd->n_cylinders};
   for (uint32_t i = 0; i < sd->n_materials; i++) {
     const pb2_material& m = sd->materials[i];
     if (!valid_material(m)) { set_error("unknown material kind"); return PB2_E_UNSUPPORTED; }
@@ -145,7 +145,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   ctx->material_kinds = 0;
   for (uint32_t i = 0; i < sd->n_geometries; i++) {
     const pb2_geometry& g = sd->geometries[i];
-    if (g.shape_kind < 0 || g.shape_kind > PB2_SHAPE_MESH) {
+    if (g.shape_kind < 0 || g.shape_kind > PB2_SHAPE_CYLINDER) {
       set_error("geometry " + std::to_string(i) + ": shape kind not supported by the CUDA path");
       return PB2_E_UNSUPPORTED;
     }
@@ -158,6 +158,16 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     if (m.kind == PB2_MAT_EMISSIVE && (g.shape_kind == PB2_SHAPE_AABB || g.shape_kind == PB2_SHAPE_OBB)) {
       // AABB::pdf / OBB::pdf are PINE_UNREACHABLE in the reference (bbox.h:87,103)
       set_error("emissive Box geometry is undefined in the reference; not supported");
+      return PB2_E_UNSUPPORTED;
+    }
+    if (m.kind == PB2_MAT_EMISSIVE && (g.shape_kind == PB2_SHAPE_PLANE || g.shape_kind == PB2_SHAPE_CYLINDER)) {
+      // Cylinder::sample / pdf / area are PINE_UNREACHABLE (geometry.h:148-150); a Plane light (area = float_max,
+      // hemisphere sampling, geometry.cpp:57-70) has no device sampler
+      set_error("emissive Plane / Cylinder geometry is not supported");
+      return PB2_E_UNSUPPORTED;
+    }
+    if (m.kind == PB2_MAT_SUBSURFACE && (g.shape_kind == PB2_SHAPE_PLANE || g.shape_kind == PB2_SHAPE_CYLINDER)) {
+      set_error("Subsurface on a Plane / Cylinder is not supported (the reference's walk is ill-defined there)");
       return PB2_E_UNSUPPORTED;
     }
     if (m.kind == PB2_MAT_UBER || m.kind == PB2_MAT_SUBSURFACE) ctx->needs_rng_in_shading = true;
@@ -232,6 +242,8 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   H.cones.assign(sd->cones, sd->cones + sd->n_cones);
   H.rects.assign(sd->rects, sd->rects + sd->n_rects);
   H.disks.assign(sd->disks, sd->disks + sd->n_disks);
+  if (sd->n_planes) H.planes.assign(sd->planes, sd->planes + sd->n_planes);
+  if (sd->n_cylinders) H.cylinders.assign(sd->cylinders, sd->cylinders + sd->n_cylinders);
 
   // ---- mesh pools ----
   H.meshes.resize(sd->n_meshes);
@@ -334,6 +346,8 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
       case PB2_SHAPE_CONE: tp.box = aabb_of(sd->cones[g.shape_index]); break;
       case PB2_SHAPE_RECT: tp.box = aabb_of(sd->rects[g.shape_index]); break;
       case PB2_SHAPE_DISK: tp.box = aabb_of(sd->disks[g.shape_index]); break;
+      case PB2_SHAPE_PLANE: tp.box = aabb_of(sd->planes[g.shape_index]); break;
+      case PB2_SHAPE_CYLINDER: tp.box = aabb_of(sd->cylinders[g.shape_index]); break;
     }
     tp.index = int(top.size());
     top.push_back(tp);
@@ -391,6 +405,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     for (int k = 0; k < 3; k++) s.node_origin_absmax[k] = std::max(s.node_origin_absmax[k], std::fabs(nd.origin[k]));
   s.n_box_shapes = int32_t(lay.box_shapes.size());
   s.order_dependent = order_dependent ? 1 : 0;
+  s.has_rare_shapes = (sd->n_planes || sd->n_cylinders) ? 1 : 0;
   s.camera = sd->camera;
   ctx->n_pixels = sd->camera.width * sd->camera.height;
   ctx->host_scene_ready = true;
@@ -409,6 +424,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
   ITEM(texels, H.texels); ITEM(textures, H.textures); ITEM(srgb_lut, H.srgb_lut); ITEM(node_instrs, H.node_instrs);
   ITEM(materials, H.materials); ITEM(aabbs, H.aabbs); ITEM(obbs, H.obbs); ITEM(spheres, H.spheres);
   ITEM(triangles, H.triangles); ITEM(cones, H.cones); ITEM(rects, H.rects); ITEM(disks, H.disks);
+  ITEM(planes, H.planes); ITEM(cylinders, H.cylinders);
 #undef ITEM
   // Page-locking 1.4 GB costs ~0.4 s, more than copying it once from pageable memory: the first staging (this
   // call) copies from pageable memory and the arrays are page-locked by the first RE-staging (HostScene::pin),
@@ -516,6 +532,7 @@ int restage(pb2_context* ctx, void* cuda_stream, int part, int n_parts, pb2_devi
   s.spheres = ctx->spheres.as<pb2_sphere>(); s.triangles = ctx->triangles.as<pb2_triangle>();
   s.cones = ctx->cones.as<pb2_cone>(); s.rects = ctx->rects.as<pb2_rect>();
   s.disks = ctx->disks.as<pb2_disk>();
+  s.planes = ctx->planes.as<pb2_plane>(); s.cylinders = ctx->cylinders.as<pb2_cylinder>();
   s.verts = ctx->verts.as<float>(); s.tris = ctx->tris.as<uint32_t>();
   s.normals = ctx->normals.as<float>(); s.uvs = ctx->uvs.as<float>();
   s.texels = ctx->texels.as<uint32_t>(); s.textures = ctx->textures.as<DTexture>();
@@ -542,7 +559,7 @@ extern "C" int pb2_restage_scene_part(pb2_context* ctx, void* cuda_stream, int p
 // pb2_restage_scene_part, the renders) is unchanged because a HostScene is just a list of (member, pointer, bytes).
 namespace {
 struct SharedHeader {
-  char magic[8];  // "PB2SCN03"
+  char magic[8];  // "PB2SCN04"
   uint32_t sizeof_dscene, n_items;
   DScene scene;   // device pointers inside are meaningless to the importer and rebound by the staging
   int32_t only_area_lights, needs_rng_in_shading, n_pixels, has_node_programs;
@@ -557,7 +574,7 @@ DBuf pb2_context::* const kStageMembers[] = {
     &pb2_context::texels, &pb2_context::textures, &pb2_context::srgb_lut, &pb2_context::node_instrs,
     &pb2_context::materials, &pb2_context::aabbs,
     &pb2_context::obbs, &pb2_context::spheres, &pb2_context::triangles, &pb2_context::cones, &pb2_context::rects,
-    &pb2_context::disks};
+    &pb2_context::disks, &pb2_context::planes, &pb2_context::cylinders};
 constexpr uint32_t kNumStageMembers = sizeof(kStageMembers) / sizeof(kStageMembers[0]);
 constexpr size_t kShareAlign = 4096;
 size_t align_up(size_t v) { return (v + kShareAlign - 1) / kShareAlign * kShareAlign; }
@@ -577,7 +594,7 @@ extern "C" int pb2_export_host_scene(pb2_context* ctx, const char* path) {
   for (uint32_t i = 0; i < kNumStageMembers; i++)
     if (H.items[i].dst != kStageMembers[i]) { set_error("staging list order changed"); return PB2_E_STATE; }
   SharedHeader hd{};
-  std::memcpy(hd.magic, "PB2SCN03", 8);
+  std::memcpy(hd.magic, "PB2SCN04", 8);
   hd.sizeof_dscene = uint32_t(sizeof(DScene));
   hd.n_items = kNumStageMembers;
   hd.scene = ctx->scene;
@@ -625,7 +642,7 @@ extern "C" int pb2_import_host_scene(pb2_context* ctx, const char* path) {
   SharedHeader hd;
   std::memcpy(&hd, base, sizeof(hd));
   const uint64_t* table = reinterpret_cast<const uint64_t*>(static_cast<const char*>(base) + sizeof(hd));
-  bool ok = std::memcmp(hd.magic, "PB2SCN03", 8) == 0 && hd.sizeof_dscene == sizeof(DScene) && hd.n_items == kNumStageMembers &&
+  bool ok = std::memcmp(hd.magic, "PB2SCN04", 8) == 0 && hd.sizeof_dscene == sizeof(DScene) && hd.n_items == kNumStageMembers &&
             size_t(st.st_size) >= sizeof(hd) + size_t(hd.n_items) * 16;
   for (uint32_t i = 0; ok && i < hd.n_items; i++) ok = table[2 * i + 1] + table[2 * i] <= uint64_t(st.st_size);
   if (!ok) { munmap(base, size_t(st.st_size)); set_error("not a scene file of this library version"); return PB2_E_INVALID; }

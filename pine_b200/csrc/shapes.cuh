@@ -229,7 +229,60 @@ __device__ __forceinline__ bool cone_hit(const pb2_cone& s, const Ray& ray) {
   return cone_root(s, ray, tmax, o) && dot(o + tmax * ray.d, ldv(s.n)) <= 0;
 }
 
+// ---- Plane (geometry.cpp:35-45) ---------------------------------------------------------------------
+// intersect accepts t == tmin and t == tmax (it rejects `t < tmin || t > tmax` only) and -- both comparisons
+// being false -- a NaN t (ray in the plane); hit is strict on tmin. Restated as written.
+__device__ __forceinline__ float plane_t(const pb2_plane& s, const Ray& ray) {
+  const V3 n = ldv(s.n);
+  return (dot(ldv(s.position), n) - dot(ray.o, n)) / dot(ray.d, n);
+}
+__device__ __forceinline__ bool plane_intersect(const pb2_plane& s, Ray& ray) {
+  const float t = plane_t(s, ray);
+  if (t < ray.tmin || t > ray.tmax) return false;
+  ray.tmax = t;
+  return true;
+}
+__device__ __forceinline__ bool plane_hit(const pb2_plane& s, const Ray& ray) {
+  const float t = plane_t(s, ray);
+  if (t <= ray.tmin) return false;
+  return t < ray.tmax;
+}
+// ---- Cylinder (geometry.cpp:466-517): the open tube; the far root is NOT re-checked against tmin ------
+__device__ __forceinline__ bool cylinder_root(const pb2_cylinder& s, const Ray& ray, float& t) {
+  const V3 p0 = ldv(s.p0), n = ldv(s.n);
+  const V3 m = ray.o - p0;
+  const V3 v = ray.d - dot(ray.d, n) * n;
+  const V3 w = m - dot(m, n) * n;
+  const float a = dot(v, v);
+  const float b = 2 * dot(v, w);
+  const float c = dot(w, w) - s.r * s.r;
+  const float discriminant = b * b - 4 * a * c;
+  if (discriminant < 0) return false;
+  const float sqrt_disc = sqrtf(discriminant);
+  t = (-b - sqrt_disc) / (2 * a);
+  if (t < ray.tmin) t = (-b + sqrt_disc) / (2 * a);
+  if (t > ray.tmax) return false;
+  const V3 hit_point = ray.o + t * ray.d;
+  const V3 projection = p0 + dot(hit_point - p0, n) * n;
+  if (dot(projection - p0, n) < 0 || dot(projection - ldv(s.p1), n) > 0) return false;
+  return true;
+}
+__device__ __forceinline__ bool cylinder_intersect(const pb2_cylinder& s, Ray& ray) {
+  float t;
+  if (!cylinder_root(s, ray, t)) return false;
+  ray.tmax = t;
+  return true;
+}
+__device__ __forceinline__ bool cylinder_hit(const pb2_cylinder& s, const Ray& ray) {
+  float t;
+  return cylinder_root(s, ray, t);
+}
+
 // ---- dispatch over the analytic shapes (Shape::intersect / Shape::hit, geometry.h:304-309) ---------
+// RARE = false compiles Plane and Cylinder OUT: the production traversal kernels are instantiated twice and scenes
+// without those shapes (every named configuration) run the instantiation without them -- with the two cases inlined
+// k_trace's register allocation changed and C5, which has triangles only, lost 2.4% (profiles/r2/s26_*).
+template <bool RARE = true>
 __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int index, Ray& ray,
                                                 bool* inside = nullptr) {
   switch (kind) {
@@ -248,9 +301,12 @@ __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int 
       const pb2_triangle& t = sc.triangles[index];
       return tri_intersect(ray, ldv(t.v0), ldv(t.v1), ldv(t.v2));
     }
+    case PB2_SHAPE_PLANE: if (RARE) return plane_intersect(sc.planes[index], ray); break;
+    case PB2_SHAPE_CYLINDER: if (RARE) return cylinder_intersect(sc.cylinders[index], ray); break;
   }
   return false;
 }
+template <bool RARE = true>
 __device__ __forceinline__ bool shape_hit(const DScene& sc, int kind, int index, const Ray& ray) {
   switch (kind) {
     case PB2_SHAPE_RECT: {
@@ -266,6 +322,8 @@ __device__ __forceinline__ bool shape_hit(const DScene& sc, int kind, int index,
       const pb2_triangle& t = sc.triangles[index];
       return tri_hit(ray, ldv(t.v0), ldv(t.v1), ldv(t.v2));
     }
+    case PB2_SHAPE_PLANE: if (RARE) return plane_hit(sc.planes[index], ray); break;
+    case PB2_SHAPE_CYLINDER: if (RARE) return cylinder_hit(sc.cylinders[index], ray); break;
   }
   return false;
 }

@@ -106,6 +106,21 @@ __device__ inline void surface_info(const DScene& sc, int geom, int prim, V3 p, 
       it.n = normalize(p - x);
       it.p = x + it.n * l * s.S;
     } break;
+    case PB2_SHAPE_PLANE: {  // Plane::compute_surface_info (geometry.cpp:46-51)
+      const pb2_plane& s = sc.planes[g.index];
+      const V3 pos = ldv(s.position), u = ldv(s.u), v = ldv(s.v);
+      it.n = ldv(s.n);
+      const V3 dp = p - pos;
+      it.uv = V2(dot(dp, u), dot(dp, v));
+      it.p = pos + it.uv.x * u + it.uv.y * v;
+    } break;
+    case PB2_SHAPE_CYLINDER: {  // what Cylinder::intersect leaves in `it` (geometry.cpp:511-513); uv stays 0
+      const pb2_cylinder& s = sc.cylinders[g.index];
+      const V3 p0 = ldv(s.p0), n = ldv(s.n);
+      const V3 projection = p0 + dot(p - p0, n) * n;
+      it.n = normalize(p - projection);
+      it.p = p;
+    } break;
     case PB2_SHAPE_MESH: {
       const DMesh& m = sc.meshes[g.index];
       const uint32_t* f = sc.tris + 3 * (size_t(m.tri_base) + prim);

@@ -45,17 +45,17 @@ struct HookIO {
   __device__ __forceinline__ void store_any(int i, bool occluded) const { occ[i] = occluded ? 1 : 0; }
 };
 
-template <bool ANY>
+template <bool ANY, bool RARE>
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_hook_wide(DScene sc, int n, WideQueue wq, HookIO io) {
-  wide_persistent<ANY>(sc, n, wq, io);
+  wide_persistent<ANY, RARE>(sc, n, wq, io);
 }
-template <bool ANY>
+template <bool ANY, bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_hook_fallback(DScene sc, WideQueue wq, HookIO io) {
-  wide_fallback<ANY>(sc, wq, io);
+  wide_fallback<ANY, RARE>(sc, wq, io);
 }
-template <bool ANY>
+template <bool ANY, bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_hook_ref(DScene sc, int n, HookIO io) {
-  ref_order_all<ANY>(sc, n, io);
+  ref_order_all<ANY, RARE>(sc, n, io);
 }
 
 template <bool ANY>
@@ -64,14 +64,17 @@ static void launch_hook(const DScene& sc, int n, int accel, const HookIO& io, in
                     (ANY ? sc.n_box_shapes <= kMaxBoxShapes : !sc.order_dependent);
   if (!wide) {
     int blocks = (n + kTraceBlock - 1) / kTraceBlock;
-    k_hook_ref<ANY><<<blocks, kTraceBlock, 0, st>>>(sc, n, io);
+    if (sc.has_rare_shapes) k_hook_ref<ANY, true><<<blocks, kTraceBlock, 0, st>>>(sc, n, io);
+    else k_hook_ref<ANY, false><<<blocks, kTraceBlock, 0, st>>>(sc, n, io);
     return;
   }
   // scratch: [0] next, [1] fb_count, [2..] fb_list
   cudaMemsetAsync(scratch, 0, 8, st);
   WideQueue wq{scratch, scratch + 1, scratch + 2};
-  k_hook_wide<ANY><<<persistent_grid(), kTraceBlock, 0, st>>>(sc, n, wq, io);
-  k_hook_fallback<ANY><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, wq, io);
+  if (sc.has_rare_shapes) k_hook_wide<ANY, true><<<persistent_grid(), kTraceBlock, 0, st>>>(sc, n, wq, io);
+  else k_hook_wide<ANY, false><<<persistent_grid(), kTraceBlock, 0, st>>>(sc, n, wq, io);
+  if (sc.has_rare_shapes) k_hook_fallback<ANY, true><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, wq, io);
+  else k_hook_fallback<ANY, false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, wq, io);
 }
 
 void launch_trace_closest(const DScene& sc, const float* rays, size_t n, int accel, int32_t* geom,
@@ -150,13 +153,17 @@ extern "C" int pb2_trace_closest_device_noalloc(pb2_context* ctx, const float* r
   HookIO io{rays_dev, geom_dev, prim_dev, t_dev, nullptr, nullptr};
   const bool wide = accel == 0 && sc.wide_ready && !sc.order_dependent;
   if (!wide) {  // reference-order walk: no scratch at all
-    k_hook_ref<false><<<(int(n) + kTraceBlock - 1) / kTraceBlock, kTraceBlock, 0, st>>>(sc, int(n), io);
+    const int blocks = (int(n) + kTraceBlock - 1) / kTraceBlock;
+    if (sc.has_rare_shapes) k_hook_ref<false, true><<<blocks, kTraceBlock, 0, st>>>(sc, int(n), io);
+    else k_hook_ref<false, false><<<blocks, kTraceBlock, 0, st>>>(sc, int(n), io);
     ctx->counters.kernel_launches++;
   } else {
     PB2_CUDA_CHECK(cudaMemsetAsync(scratch, 0, 2 * sizeof(int), st));  // claim counter and fallback count start at zero
     WideQueue wq{scratch, scratch + 1, scratch + kNoAllocListOffset};
-    k_hook_wide<false><<<persistent_grid(), kTraceBlock, 0, st>>>(sc, int(n), wq, io);
-    k_hook_fallback<false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, wq, io);
+    if (sc.has_rare_shapes) k_hook_wide<false, true><<<persistent_grid(), kTraceBlock, 0, st>>>(sc, int(n), wq, io);
+    else k_hook_wide<false, false><<<persistent_grid(), kTraceBlock, 0, st>>>(sc, int(n), wq, io);
+    if (sc.has_rare_shapes) k_hook_fallback<false, true><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, wq, io);
+    else k_hook_fallback<false, false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, st>>>(sc, wq, io);
     ctx->counters.kernel_launches += 2;
   }
   PB2_CUDA_CHECK(cudaGetLastError());

@@ -117,6 +117,7 @@ __device__ __forceinline__ bool walk_ref_order(const DScene& sc, const DTree& tr
 }
 
 // BVH::intersect (bvh.cpp:513-548). ray.tmax is shrunk to t; returns geom/prim of the winner.
+template <bool RARE = true>
 __device__ __forceinline__ bool closest_ref_order(const DScene& sc, Ray& ray, Hit& h) {
   Octant q = make_octant(ray);
   h.geom = -1;
@@ -136,13 +137,14 @@ __device__ __forceinline__ bool closest_ref_order(const DScene& sc, Ray& ray, Hi
       if (hit) { h.geom = tp.geom; h.prim = prim; }
       return hit;
     }
-    bool hit = shape_intersect(sc, tp.kind, tp.index, ray);
+    bool hit = shape_intersect<RARE>(sc, tp.kind, tp.index, ray);
     if (hit) { h.geom = tp.geom; h.prim = 0; }
     return hit;
   });
 }
 
 // BVH::hit (bvh.cpp:497-511).
+template <bool RARE = true>
 __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) {
   Octant q = make_octant(ray);
   return walk_ref_order<true>(sc, sc.top, ray, q, [&](int top_id) {
@@ -155,7 +157,7 @@ __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) 
         return tri_hit(ray, v0, v1, v2);
       });
     }
-    return shape_hit(sc, tp.kind, tp.index, ray);
+    return shape_hit<RARE>(sc, tp.kind, tp.index, ray);
   });
 }
 
@@ -190,7 +192,8 @@ __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) 
 //         shapes left out, all others go to the reference-order walk (wide_persistent.cuh),
 //   (iv)  every primitive the reference accepts is also tested here. For primitives that lie
 //         inside their leaf box this follows from box containment; a Cone does not (it is
-//         unbounded below its base, geometry.cpp:415-446) and can be hit BEFORE the ray enters its
+//         unbounded below its base, geometry.cpp:415-446; likewise a Plane beyond the +-100 box and a
+//         Cylinder beyond the radius-r box around p0 the reference bounds them by) and can be hit BEFORE the ray enters its
 //         leaf box, which the reference accepts if it reaches the leaf while tmax is still large.
 //         Nodes with a Cone anywhere below them (kNoCullBit) are therefore tested against the
 //         ray's incoming tmax, never the current best; a Cone hit outside its box then fails (ii).

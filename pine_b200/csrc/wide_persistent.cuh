@@ -45,7 +45,7 @@ struct WideQueue {
 // the 10 M-triangle scene and cost 2x on scenes that live in L1, so neither is here.
 // The order in which a ray's primitives are tested does not matter for the result (ties are
 // detected and sent to the fallback, see traverse.cuh).
-template <bool ANY, class IO>
+template <bool ANY, bool RARE = true, class IO>
 __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQueue wq, const IO& io) {
   const unsigned lane = threadIdx.x & 31u;
 #if PB2_SMEM_TOP > 0
@@ -141,10 +141,10 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
             for (int i = 0; i < sc.n_box_shapes && !touched; i++) {
               const int4 b = __ldg(reinterpret_cast<const int4*>(sc.box_shapes) + i);
               if (ANY) {
-                touched = shape_hit(sc, b.x, b.y, ray);
+                touched = shape_hit<false>(sc, b.x, b.y, ray);
               } else {
                 Ray r2 = ray;
-                touched = shape_intersect(sc, b.x, b.y, r2);
+                touched = shape_intersect<false>(sc, b.x, b.y, r2);
               }
               touched = touched && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax);
             }
@@ -172,7 +172,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         bool ok;
         if (r.prim >= 0) ok = tri_hit(ray, r.v0, r.v1, r.v2);
         else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: tested at refill
-        else ok = shape_hit(sc, -1 - r.prim, __float_as_int(r.v0.x), ray);
+        else ok = shape_hit<RARE>(sc, -1 - r.prim, __float_as_int(r.v0.x), ray);
         if (ok && leaf_gate(sc.leaves, r.leaf, q, ray.tmin, ray.tmax)) { have = true; done = true; }
       } else {
         // Accept candidates up to slack_of(best): t == best exposes ties, and every candidate a
@@ -183,7 +183,12 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         bool ok;
         if (r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
         else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: rays that touch one never get here
-        else ok = shape_intersect(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
+        else {
+          ok = shape_intersect<RARE>(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
+          // Plane::intersect lets a NaN t through and Cylinder::intersect a far root below tmin (geometry.cpp:40-45,
+          // 502-504): what the reference does next depends on its visiting order, so it decides
+          if (RARE && ok && !(r2.tmax >= ray.tmin)) { ambiguous = true; done = true; ok = false; }
+        }
         if (ok) {
           if (r2.tmax < ray.tmax) {
             if (have) t2 = pmin(t2, ray.tmax);
@@ -265,32 +270,32 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
 }
 
 // Reference-order re-trace of the rays the wide walk could not certify.
-template <bool ANY, class IO>
+template <bool ANY, bool RARE = true, class IO>
 __device__ __forceinline__ void wide_fallback(const DScene& sc, WideQueue wq, const IO& io) {
   const int n = *wq.fb_count;
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
     const int idx = wq.fb_list[k];
     Ray ray = io.load(idx);
     if (ANY) {
-      io.store_any(idx, any_ref_order(sc, ray));
+      io.store_any(idx, any_ref_order<RARE>(sc, ray));
     } else {
       Hit h;
-      const bool hit = closest_ref_order(sc, ray, h);
+      const bool hit = closest_ref_order<RARE>(sc, ray, h);
       io.store_closest(sc, idx, ray, hit, h);
     }
   }
 }
 
 // One ray per thread in reference order (accel = 1, and closest hits of order-dependent scenes).
-template <bool ANY, class IO>
+template <bool ANY, bool RARE = true, class IO>
 __device__ __forceinline__ void ref_order_all(const DScene& sc, int n, const IO& io) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     Ray ray = io.load(i);
     if (ANY) {
-      io.store_any(i, any_ref_order(sc, ray));
+      io.store_any(i, any_ref_order<RARE>(sc, ray));
     } else {
       Hit h;
-      const bool hit = closest_ref_order(sc, ray, h);
+      const bool hit = closest_ref_order<RARE>(sc, ray, h);
       io.store_closest(sc, i, ray, hit, h);
     }
   }

@@ -319,6 +319,10 @@ class SceneProxy:
             self.target.add_disk(_vec(p[0]), _vec(p[1]), float(_f32(p[2])), mat)
         elif k == "triangle":
             self.target.add_triangle(_vec(p[0]), _vec(p[1]), _vec(p[2]), mat)
+        elif k == "plane":
+            self.target.add_plane(_vec(p[0]), _vec(p[1]), mat)
+        elif k == "cylinder":
+            self.target.add_cylinder(_vec(p[0]), _vec(p[1]), float(_f32(p[2])), mat)
         else:
             raise PrlError(f"shape {k} is not supported by the CUDA path")
 
@@ -412,6 +416,7 @@ def _globals(make_scene):
         "Scene": make_scene,
         "Rect": shape("rect"), "Box": shape("box"), "AABB": shape("aabb"), "Cone": shape("cone"),
         "Sphere": shape("sphere"), "Disk": shape("disk"), "Triangle": shape("triangle"),
+        "Plane": shape("plane"), "Cylinder": shape("cylinder"),
         "Diffuse": lambda c: _Material("diffuse", _node3(c)),
         "Emissive": lambda c: _Material("emissive", _vec(c)),
         "Metal": lambda c, r: _Material("metal", _node3(c), roughness=_nodef(r)),

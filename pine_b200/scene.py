@@ -96,6 +96,8 @@ def Cone(p, n, r, h): return _Shape("cone", p, n, r, h)
 def Sphere(c, r): return _Shape("sphere", c, r)
 def Disk(p, n, r): return _Shape("disk", p, n, r)
 def Triangle(a, b, c): return _Shape("triangle", a, b, c)
+def Plane(p, n): return _Shape("plane", p, n)
+def Cylinder(p0, p1, r): return _Shape("cylinder", p0, p1, r)
 def Mesh(verts, idx, normals=None, uvs=None): return _Shape("mesh", verts, idx, normals=normals, uvs=uvs)
 
 
@@ -218,6 +220,20 @@ class Scene:
         A.lib().pb2h_make_disk(_fp(a), _fp(b), r, C.byref(o))
         return self._add("disk", o, mat)
 
+    def add_plane(self, p, n, mat):
+        o = A.Plane()
+        a, b = _f(p), _f(n)
+        if not np.any(b):
+            raise ValueError("`Plane` can't have degenerated normal")  # geometry.cpp:32
+        A.lib().pb2h_make_plane(_fp(a), _fp(b), C.byref(o))
+        return self._add("plane", o, mat)
+
+    def add_cylinder(self, p0, p1, r, mat):
+        o = A.Cylinder()
+        a, b = _f(p0), _f(p1)
+        A.lib().pb2h_make_cylinder(_fp(a), _fp(b), C.c_float(r), C.byref(o))
+        return self._add("cylinder", o, mat)
+
     def add_triangle(self, a, b, c, mat):
         o = A.Triangle()
         a, b, c = _f(a), _f(b), _f(c)
@@ -333,6 +349,8 @@ class Scene:
               "sphere": lambda: self.add_sphere(*s.args, mat),
               "disk": lambda: self.add_disk(*s.args, mat),
               "triangle": lambda: self.add_triangle(*s.args, mat),
+              "plane": lambda: self.add_plane(*s.args, mat),
+              "cylinder": lambda: self.add_cylinder(*s.args, mat),
               "mesh": lambda: self.add_mesh(*s.args, mat, **s.kw)}[s.kind]
         return fn()
 
@@ -379,6 +397,10 @@ class Scene:
         put("cones", A.Cone, self.shapes["cone"])
         put("rects", A.Rect, self.shapes["rect"])
         put("disks", A.Disk, self.shapes["disk"])
+        if self.shapes["plane"]:
+            put("planes", A.Plane, self.shapes["plane"])
+        if self.shapes["cylinder"]:
+            put("cylinders", A.Cylinder, self.shapes["cylinder"])
         put("meshes", A.Mesh, self.shapes["mesh"])
         texs = []
         for a in self.textures:

@@ -297,6 +297,28 @@ def classic(B, size=(720, 360), skin=False):
     return {"spp": 64, "depth": 6}
 
 
+def plane_yard(B, size=(128, 96)):
+    """Parity scene for Plane and Cylinder (geometry.cpp:31-70, 466-517): a Plane floor and a Plane back wall (both
+    reach beyond the +-100 box the reference's BVH gives them), upright, lying and tilted Cylinders -- one long enough
+    to leave the radius-r box around p0 that is all the reference bounds it by --, two spheres and a Rect emitter."""
+    floor = B.add_material("diffuse", (0.8, 0.8, 0.8))
+    wall = B.add_material("glossy", (0.3, 0.5, 0.8), roughness=0.2)
+    red = B.add_material("diffuse", (0.9, 0.2, 0.1))
+    metal = B.add_material("metal", (0.9, 0.9, 0.9), roughness=0.1)
+    green = B.add_material("diffuse", (0.2, 0.8, 0.2))
+    B.add_plane((0, 0, 0), (0, 1, 0), floor)
+    B.add_plane((0, 0, 6), (0.1, 0.05, -1), wall)
+    B.add_cylinder((-2, 0, 2), (-2, 2.5, 2), 0.5, red)
+    B.add_cylinder((-1, 0.4, 1), (2.5, 0.4, 3), 0.4, metal)
+    B.add_cylinder((2, 0, 0.5), (3, 3, 2.5), 0.3, green)
+    B.add_sphere((0.5, 0.6, 2.5), 0.6, metal)
+    B.add_sphere((-0.5, 0.3, 0.5), 0.3, red)
+    light = B.add_material("emissive", (40.0, 36.0, 30.0))
+    B.add_rect((0, 5, 2), (2, 0, 0), (0, 0, 2), light)
+    B.set_camera(size, (0, 2.5, -6), (0, 1, 2), 0.35)
+    return {"spp": 16, "depth": 5}
+
+
 def lights_yard(B, size=(96, 64), sky=True, delta=True, area=True):
     """Parity scene for the lights the named configs never use (light.h:21-66): an open yard (ground, one
     wall, a sphere, a cone, a box) lit by a DirectionalLight, a PointLight, a SpotLight (with a cutoff band),
@@ -326,5 +348,5 @@ def lights_yard(B, size=(96, 64), sky=True, delta=True, area=True):
     return {"spp": 16, "depth": 5}
 
 
-SCENES = {"materials_room": materials_room, "classic": classic, "lights_yard": lights_yard, "cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
+SCENES = {"materials_room": materials_room, "classic": classic, "plane_yard": plane_yard, "lights_yard": lights_yard, "cbox_readme": cbox_readme, "cbox_readme_noboxes": cbox_readme_noboxes, "cbox_file": cbox_file, "cbox_indirect": cbox_indirect,
           "mesh_field": mesh_field, "room_proc": room_proc}

@@ -193,3 +193,54 @@ def test_shim_flattens_node_graphs():
     shim, _, stats = R.render_cuda(8, 5)
     assert np.array_equal(u32(shim), u32(film)) and stats["closest_rays"] > 0
     B.close()
+
+
+# ---- Plane and Cylinder (geometry.cpp:31-70, 466-517) --------------------------------------------------------------
+@needs_ref
+def test_plane_and_cylinder_hits_and_film_match_the_live_reference():
+    """Both shapes can be hit outside the box the reference's BVH gives them (Plane: position +- 100; Cylinder: a
+    sphere of radius r around p0), Plane::intersect is non-strict at both ends of the ray interval and
+    Cylinder::intersect takes its far root unchecked: closest hits (geom, prim, t) of the camera rays and of every
+    ray a recorded production render traced, and shadow occlusion, are BIT-identical to the live reference's BVH
+    walk; the film matches at equal spp; the reference-order device walk gives the same film bits."""
+    from oracle import ref
+    R, S = ref.RefScene(), pb.Scene()
+    scenes.plane_yard(R)
+    cfg = scenes.plane_yard(S)
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    spp, depth = cfg["spp"], cfg["depth"]
+    rays = R.primary_rays(0)
+    assert np.array_equal(u32(rays), u32(B.primary_rays(0)))
+    film4, rec = B.render_recorded(4, depth, accel=0)
+    closest = np.concatenate([rays, rec["closest_rays"]])
+    got = B.trace_closest(rays, accel=0, surf=True)
+    want = R.trace_closest(closest)
+    g = np.concatenate([got["geom"], rec["closest_geom"]])
+    t = np.concatenate([got["t"], rec["closest_t"]])
+    assert set(np.unique(g)) >= {0, 1, 2, 3, 4, 5, 6}            # both planes, all three cylinders, the spheres
+    assert np.array_equal(g, want["geom"]), int((g != want["geom"]).sum())
+    assert np.array_equal(u32(t), u32(want["t"])), int((u32(t) != u32(want["t"])).sum())
+    assert np.array_equal(rec["shadow_occluded"], R.trace_any(rec["shadow_rays"]))
+    assert len(closest) + len(rec["shadow_rays"]) > 150_000
+    # surface point and normal of the camera hits: same float expressions => same bits
+    ws = R.trace_closest(rays, surf=True)
+    assert np.array_equal(u32(got["surf"][:, :6]), u32(ws["surf"][:, :6]))
+    np.testing.assert_allclose(got["surf"][:, 6:], ws["surf"][:, 6:], rtol=0, atol=2e-6)   # Sphere uv: libm
+    film_ref, _ = R.render(spp, depth)
+    film = B.render(spp, depth)
+    assert np.isfinite(film).all() and film[..., :3].mean() > 0.01
+    assert relmse(film, film_ref) <= 1e-4
+    assert np.array_equal(u32(film), u32(B.render(spp, depth, accel=1)))
+    shim, _, _ = R.render_cuda(spp, depth)
+    assert np.array_equal(u32(shim), u32(film))
+    B.close()
+
+
+def test_emissive_plane_or_cylinder_is_rejected():
+    for add in (lambda S, m: S.add_plane((0, 0, 0), (0, 1, 0), m), lambda S, m: S.add_cylinder((0, 0, 0), (0, 1, 0), 0.2, m)):
+        S = pb.Scene()
+        add(S, S.add_material("emissive", (1, 1, 1)))
+        S.set_camera((8, 8), (0, 1, -4), (0, 0, 0), 0.3)
+        with pytest.raises(pb.PineB200Error):
+            pb.Backend(0).upload_scene(S)

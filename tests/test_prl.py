@@ -99,7 +99,7 @@ def test_arithmetic_follows_the_jit_types():
 @pytest.mark.parametrize("src, msg", [
     ("scene := Scene(); scene.add(Rect([0,0,0],[1,0,0],[0,1,0]), \"nope\");", "unknown material"),
     ("x := foo(1);", "unknown name"),
-    ("scene := Scene(); scene.add(Plane([0,0,0],[0,1,0]), Diffuse([1,1,1]));", "unknown name"),
+    ("scene := Scene(); scene.add(Line([0,0,0],[0,1,0], 0.1), Diffuse([1,1,1]));", "unknown name"),
     ("x := [1, 2] + [1, 2, 3];", "size mismatch"),
     ("x := 1 $ 2;", "unexpected character"),
     ("x := (1 + 2;", "expected"),
@@ -236,3 +236,26 @@ def test_uber_material_and_string_rules():
     assert m.kind == A.MATERIAL_KINDS["uber"] and abs(m.metallic - 1.0) < 1e-7 and abs(m.ior - 1.45) < 1e-6
     with pytest.raises(prl.PrlError):
         prl.load("x = 'a' * 2;", pb.Scene)
+
+
+def test_plane_and_cylinder_in_a_script():
+    """Plane(position, normal) and Cylinder(p0, p1, r) (program_context / geometry_context names) build the records
+    of the builder scene."""
+    text = """
+scene = Scene();
+scene.add(Plane([0, 0, 0], [0, 1, 0]), Diffuse([0.8, 0.8, 0.8]));
+scene.add(Cylinder([-2, 0, 2], [-2, 2.5, 2], 0.5), Diffuse([0.9, 0.2, 0.1]));
+scene.set(ThinLenCamera(Film([32, 24]), [0, 2.5, -6], [0, 1, 2], 0.35));
+"""
+    it = prl.Interpreter(pb.Scene)
+    it.run(text)
+    S = it.scenes[0].target
+    W = pb.Scene()
+    W.add_plane((0, 0, 0), (0, 1, 0), W.add_material("diffuse", (0.8, 0.8, 0.8)))
+    W.add_cylinder((-2, 0, 2), (-2, 2.5, 2), 0.5, W.add_material("diffuse", (0.9, 0.2, 0.1)))
+    for k in ("plane", "cylinder"):
+        assert [bytes(memoryview(x)) for x in S.shapes[k]] == [bytes(memoryview(x)) for x in W.shapes[k]] and S.shapes[k]
+    B = pb.Backend(-1)
+    B.upload_scene(S)   # host-only context: validation, BVH over the +-100 / radius-r boxes
+    assert B.counters()["n_primitives"] == 2
+    B.close()
