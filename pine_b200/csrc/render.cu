@@ -204,10 +204,11 @@ __device__ __forceinline__ TraceIO trace_io(const WaveView& w, int depth) {
 __device__ __forceinline__ ShadowIO shadow_io(const WaveView& w, int depth) {
   return ShadowIO{w.sh_o, w.sh_d, w.vtx + size_t(depth) * w.n_slots * 2, w.occ};
 }
-// RARE: the scene holds a Plane or a Cylinder (shapes.cuh shape_intersect<RARE>)
-template <bool RARE>
+// SHAPES: which analytic shapes are compiled in (shapes.cuh kShapes*); the reference-order kernels below know two
+// levels only (false = kShapesCommon, true = kShapesAll: the scene holds a Plane or a Cylinder)
+template <int SHAPES>
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_trace(DScene sc, WaveView w, int depth) {
-  wide_persistent<false, RARE>(sc, w.counts[depth], wave_queue(w, depth, 0), trace_io(w, depth));
+  wide_persistent<false, SHAPES>(sc, w.counts[depth], wave_queue(w, depth, 0), trace_io(w, depth));
 }
 template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock, kFallbackBlocksPerSM) k_trace_fallback(DScene sc, WaveView w, int depth) {
@@ -217,9 +218,9 @@ template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_trace_ref(DScene sc, WaveView w, int depth) {
   ref_order_all<false, RARE>(sc, w.counts[depth], trace_io(w, depth));
 }
-template <bool RARE>
+template <int SHAPES>
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_shadow(DScene sc, WaveView w, int depth) {
-  wide_persistent<true, RARE>(sc, w.counts[w.max_depth + 1 + depth], wave_queue(w, depth, 1), shadow_io(w, depth));
+  wide_persistent<true, SHAPES>(sc, w.counts[w.max_depth + 1 + depth], wave_queue(w, depth, 1), shadow_io(w, depth));
 }
 template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock, kFallbackBlocksPerSM) k_shadow_fallback(DScene sc, WaveView w, int depth) {
@@ -1053,8 +1054,12 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
     launches++; mark(3);
     for (int depth = 0; depth < D; depth++) {
       if (closest_wide_ok) {
-        if (sc.has_rare_shapes) k_trace<true><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-        else k_trace<false><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+        // the tightest instantiation that covers the scene; with meshes the closest-hit kernel stops at kShapesNoBox
+        // (its Rect-only form is 2.5% slower in kernel on C5's deep trees: profiles/r2/s28_s31_*)
+        if (sc.has_rare_shapes) k_trace<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+        else if (sc.only_rects && !sc.has_meshes) k_trace<kShapesRect><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+        else if (sc.n_box_shapes == 0) k_trace<kShapesNoBox><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+        else k_trace<kShapesCommon><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
         if (sc.has_rare_shapes) k_trace_fallback<true><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
         else k_trace_fallback<false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
         launches += 2;
@@ -1085,8 +1090,10 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       mark(2);
       if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
         if (any_wide_ok) {
-          if (sc.has_rare_shapes) k_shadow<true><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-          else k_shadow<false><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+          if (sc.has_rare_shapes) k_shadow<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+          else if (sc.only_rects) k_shadow<kShapesRect><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+          else if (sc.n_box_shapes == 0) k_shadow<kShapesNoBox><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+          else k_shadow<kShapesCommon><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
           if (sc.has_rare_shapes) k_shadow_fallback<true><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
           else k_shadow_fallback<false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
           launches += 2;

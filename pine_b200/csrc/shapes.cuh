@@ -279,12 +279,23 @@ __device__ __forceinline__ bool cylinder_hit(const pb2_cylinder& s, const Ray& r
 }
 
 // ---- dispatch over the analytic shapes (Shape::intersect / Shape::hit, geometry.h:304-309) ---------
-// RARE = false compiles Plane and Cylinder OUT: the production traversal kernels are instantiated twice and scenes
-// without those shapes (every named configuration) run the instantiation without them -- with the two cases inlined
-// k_trace's register allocation changed and C5, which has triangles only, lost 2.4% (profiles/r2/s26_*).
-template <bool RARE = true>
+// Which analytic shapes a traversal kernel has compiled IN (SHAPES): kShapesCommon = everything but Plane and
+// Cylinder, kShapesAll = everything, kShapesRect = Rect only. The production kernels are instantiated per level and
+// a scene runs the tightest one that covers it, because the cases inlined here decide the register allocation of the
+// whole persistent loop: with Plane and Cylinder inlined C5 (triangles + Rects) lost 2.4%; with the AABB / OBB code
+// (incl. the per-ray box pre-test of wide_persistent.cuh) compiled out of both kernels and only the Rect case left
+// in the shadow kernel C5 gains 3.2% (557 -> 575), C4 2.9%, C3 4.2% (profiles/r2/s26_s27_*, s28_s31_*). `false` /
+// `true` of the reference-order kernels convert to kShapesCommon / kShapesAll.
+constexpr int kShapesCommon = 0, kShapesAll = 1, kShapesRect = 2, kShapesNoBox = 3;  // NoBox: Common without AABB / OBB
+template <int SHAPES = kShapesAll>
 __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int index, Ray& ray,
                                                 bool* inside = nullptr) {
+  if (SHAPES == kShapesRect) {
+    float t;
+    if (kind != PB2_SHAPE_RECT || !rect_test(sc.rects[index], ray, t)) return false;
+    ray.tmax = t;
+    return true;
+  }
   switch (kind) {
     case PB2_SHAPE_RECT: {
       float t;
@@ -293,37 +304,41 @@ __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int 
       return true;
     }
     case PB2_SHAPE_CONE: return cone_intersect(sc.cones[index], ray);
-    case PB2_SHAPE_OBB: return obb_intersect(sc.obbs[index], ray, inside);
-    case PB2_SHAPE_AABB: return aabb_intersect(sc.aabbs[index], ray, inside);
+    case PB2_SHAPE_OBB: if (SHAPES != kShapesNoBox) return obb_intersect(sc.obbs[index], ray, inside); break;
+    case PB2_SHAPE_AABB: if (SHAPES != kShapesNoBox) return aabb_intersect(sc.aabbs[index], ray, inside); break;
     case PB2_SHAPE_SPHERE: return sphere_intersect(sc.spheres[index], ray);
     case PB2_SHAPE_DISK: return disk_intersect(sc.disks[index], ray);
     case PB2_SHAPE_TRIANGLE: {
       const pb2_triangle& t = sc.triangles[index];
       return tri_intersect(ray, ldv(t.v0), ldv(t.v1), ldv(t.v2));
     }
-    case PB2_SHAPE_PLANE: if (RARE) return plane_intersect(sc.planes[index], ray); break;
-    case PB2_SHAPE_CYLINDER: if (RARE) return cylinder_intersect(sc.cylinders[index], ray); break;
+    case PB2_SHAPE_PLANE: if (SHAPES == kShapesAll) return plane_intersect(sc.planes[index], ray); break;
+    case PB2_SHAPE_CYLINDER: if (SHAPES == kShapesAll) return cylinder_intersect(sc.cylinders[index], ray); break;
   }
   return false;
 }
-template <bool RARE = true>
+template <int SHAPES = kShapesAll>
 __device__ __forceinline__ bool shape_hit(const DScene& sc, int kind, int index, const Ray& ray) {
+  if (SHAPES == kShapesRect) {
+    float t;
+    return kind == PB2_SHAPE_RECT && rect_test(sc.rects[index], ray, t);
+  }
   switch (kind) {
     case PB2_SHAPE_RECT: {
       float t;
       return rect_test(sc.rects[index], ray, t);
     }
     case PB2_SHAPE_CONE: return cone_hit(sc.cones[index], ray);
-    case PB2_SHAPE_OBB: return obb_hit(sc.obbs[index], ray);
-    case PB2_SHAPE_AABB: return aabb_hit(sc.aabbs[index], ray.o, ray.d, ray.tmin, ray.tmax);
+    case PB2_SHAPE_OBB: if (SHAPES != kShapesNoBox) return obb_hit(sc.obbs[index], ray); break;
+    case PB2_SHAPE_AABB: if (SHAPES != kShapesNoBox) return aabb_hit(sc.aabbs[index], ray.o, ray.d, ray.tmin, ray.tmax); break;
     case PB2_SHAPE_SPHERE: return sphere_hit(sc.spheres[index], ray);
     case PB2_SHAPE_DISK: return disk_hit(sc.disks[index], ray);
     case PB2_SHAPE_TRIANGLE: {
       const pb2_triangle& t = sc.triangles[index];
       return tri_hit(ray, ldv(t.v0), ldv(t.v1), ldv(t.v2));
     }
-    case PB2_SHAPE_PLANE: if (RARE) return plane_hit(sc.planes[index], ray); break;
-    case PB2_SHAPE_CYLINDER: if (RARE) return cylinder_hit(sc.cylinders[index], ray); break;
+    case PB2_SHAPE_PLANE: if (SHAPES == kShapesAll) return plane_hit(sc.planes[index], ray); break;
+    case PB2_SHAPE_CYLINDER: if (SHAPES == kShapesAll) return cylinder_hit(sc.cylinders[index], ray); break;
   }
   return false;
 }
