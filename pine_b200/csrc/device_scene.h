@@ -156,8 +156,9 @@ struct DScene {
   const int32_t* halton_sums;
   const uint16_t* halton_perms;
   int halton_inv0, halton_inv1;
-  int has_rare_shapes;  // a Plane or a Cylinder somewhere: the traversal kernels compiled with those two shapes run
-  int only_rects;       // every analytic (non-mesh) geometry is a Rect: the Rect-only traversal kernels cover the scene
+  int shape_mask;       // OR of 1 << pb2_shape_kind over the analytic (non-mesh) geometries: picks the traversal
+                        // kernels' instantiation (shapes.cuh kShapes*)
+  int has_rare_shapes;  // a Plane or a Cylinder somewhere (the reference-order kernels' two-way switch)
   int has_meshes;       // some geometry is a non-empty Mesh
   pb2_camera camera;
   unsigned long long* walk_stats;  // PB2_COUNT builds only: {closest nodes, closest prims, any nodes, any prims,

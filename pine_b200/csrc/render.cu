@@ -1041,6 +1041,15 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   PB2_CUDA_CHECK(cudaEventRecord(ctx->ev0, st));
   mark(-1);
   // One wave on one lane: raygen, then per depth trace / classify / shade / shadow, then the unwind.
+  // The smallest instantiated shape mask that contains the scene's analytic kinds (shapes.cuh): the code compiled
+  // into the persistent loop decides its register allocation. With meshes the closest-hit kernel skips the
+  // Rect-only form (2.5% slower in kernel on C5's deep trees than the no-box form: profiles/r2/s28_s31_*).
+  auto shapes_level = [&](bool closest) {
+    for (int m : {kShapesRect, kShapesNoBox, kShapesCbox, kShapesCommon})
+      if ((sc.shape_mask & ~m) == 0 && !(m == kShapesRect && closest && sc.has_meshes)) return m;
+    return kShapesAll;
+  };
+  const int trace_shapes = shapes_level(true), shadow_shapes = shapes_level(false);
   auto enqueue_wave = [&](int l, int pw, int sw) -> int {
     WaveView& w = lane_view[l];
     cudaStream_t ls = lane_stream[l];
@@ -1054,12 +1063,12 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
     launches++; mark(3);
     for (int depth = 0; depth < D; depth++) {
       if (closest_wide_ok) {
-        // the tightest instantiation that covers the scene; with meshes the closest-hit kernel stops at kShapesNoBox
-        // (its Rect-only form is 2.5% slower in kernel on C5's deep trees: profiles/r2/s28_s31_*)
-        if (sc.has_rare_shapes) k_trace<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-        else if (sc.only_rects && !sc.has_meshes) k_trace<kShapesRect><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-        else if (sc.n_box_shapes == 0) k_trace<kShapesNoBox><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-        else k_trace<kShapesCommon><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+        switch (trace_shapes) {
+#define PB2_TRACE(M) case M: k_trace<M><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth); break;
+          PB2_TRACE(kShapesRect) PB2_TRACE(kShapesNoBox) PB2_TRACE(kShapesCbox) PB2_TRACE(kShapesCommon)
+          default: k_trace<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+#undef PB2_TRACE
+        }
         if (sc.has_rare_shapes) k_trace_fallback<true><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
         else k_trace_fallback<false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
         launches += 2;
@@ -1090,10 +1099,12 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       mark(2);
       if (depth + 1 < D) {  // the last vertex never samples a light (path.cpp:89)
         if (any_wide_ok) {
-          if (sc.has_rare_shapes) k_shadow<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-          else if (sc.only_rects) k_shadow<kShapesRect><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-          else if (sc.n_box_shapes == 0) k_shadow<kShapesNoBox><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
-          else k_shadow<kShapesCommon><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+          switch (shadow_shapes) {
+#define PB2_SHADOW(M) case M: k_shadow<M><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth); break;
+            PB2_SHADOW(kShapesRect) PB2_SHADOW(kShapesNoBox) PB2_SHADOW(kShapesCbox) PB2_SHADOW(kShapesCommon)
+            default: k_shadow<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
+#undef PB2_SHADOW
+          }
           if (sc.has_rare_shapes) k_shadow_fallback<true><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
           else k_shadow_fallback<false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
           launches += 2;

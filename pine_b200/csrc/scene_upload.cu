@@ -405,11 +405,11 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     for (int k = 0; k < 3; k++) s.node_origin_absmax[k] = std::max(s.node_origin_absmax[k], std::fabs(nd.origin[k]));
   s.n_box_shapes = int32_t(lay.box_shapes.size());
   s.order_dependent = order_dependent ? 1 : 0;
-  s.has_rare_shapes = (sd->n_planes || sd->n_cylinders) ? 1 : 0;
-  s.only_rects = 1;
-  s.has_meshes = jobs.empty() ? 0 : 1;
+  s.shape_mask = 0;
   for (uint32_t i = 0; i < sd->n_geometries; i++)
-    if (sd->geometries[i].shape_kind != PB2_SHAPE_RECT && sd->geometries[i].shape_kind != PB2_SHAPE_MESH) s.only_rects = 0;
+    if (sd->geometries[i].shape_kind != PB2_SHAPE_MESH) s.shape_mask |= 1 << sd->geometries[i].shape_kind;
+  s.has_rare_shapes = (s.shape_mask & ((1 << PB2_SHAPE_PLANE) | (1 << PB2_SHAPE_CYLINDER))) ? 1 : 0;
+  s.has_meshes = jobs.empty() ? 0 : 1;
   s.camera = sd->camera;
   ctx->n_pixels = sd->camera.width * sd->camera.height;
   ctx->host_scene_ready = true;
@@ -563,7 +563,7 @@ extern "C" int pb2_restage_scene_part(pb2_context* ctx, void* cuda_stream, int p
 // pb2_restage_scene_part, the renders) is unchanged because a HostScene is just a list of (member, pointer, bytes).
 namespace {
 struct SharedHeader {
-  char magic[8];  // "PB2SCN05"
+  char magic[8];  // "PB2SCN06"
   uint32_t sizeof_dscene, n_items;
   DScene scene;   // device pointers inside are meaningless to the importer and rebound by the staging
   int32_t only_area_lights, needs_rng_in_shading, n_pixels, has_node_programs;
@@ -598,7 +598,7 @@ extern "C" int pb2_export_host_scene(pb2_context* ctx, const char* path) {
   for (uint32_t i = 0; i < kNumStageMembers; i++)
     if (H.items[i].dst != kStageMembers[i]) { set_error("staging list order changed"); return PB2_E_STATE; }
   SharedHeader hd{};
-  std::memcpy(hd.magic, "PB2SCN05", 8);
+  std::memcpy(hd.magic, "PB2SCN06", 8);
   hd.sizeof_dscene = uint32_t(sizeof(DScene));
   hd.n_items = kNumStageMembers;
   hd.scene = ctx->scene;
@@ -646,7 +646,7 @@ extern "C" int pb2_import_host_scene(pb2_context* ctx, const char* path) {
   SharedHeader hd;
   std::memcpy(&hd, base, sizeof(hd));
   const uint64_t* table = reinterpret_cast<const uint64_t*>(static_cast<const char*>(base) + sizeof(hd));
-  bool ok = std::memcmp(hd.magic, "PB2SCN05", 8) == 0 && hd.sizeof_dscene == sizeof(DScene) && hd.n_items == kNumStageMembers &&
+  bool ok = std::memcmp(hd.magic, "PB2SCN06", 8) == 0 && hd.sizeof_dscene == sizeof(DScene) && hd.n_items == kNumStageMembers &&
             size_t(st.st_size) >= sizeof(hd) + size_t(hd.n_items) * 16;
   for (uint32_t i = 0; ok && i < hd.n_items; i++) ok = table[2 * i + 1] + table[2 * i] <= uint64_t(st.st_size);
   if (!ok) { munmap(base, size_t(st.st_size)); set_error("not a scene file of this library version"); return PB2_E_INVALID; }

@@ -284,9 +284,18 @@ __device__ __forceinline__ bool cylinder_hit(const pb2_cylinder& s, const Ray& r
 // a scene runs the tightest one that covers it, because the cases inlined here decide the register allocation of the
 // whole persistent loop: with Plane and Cylinder inlined C5 (triangles + Rects) lost 2.4%; with the AABB / OBB code
 // (incl. the per-ray box pre-test of wide_persistent.cuh) compiled out of both kernels and only the Rect case left
-// in the shadow kernel C5 gains 3.2% (557 -> 575), C4 2.9%, C3 4.2% (profiles/r2/s26_s27_*, s28_s31_*). `false` /
-// `true` of the reference-order kernels convert to kShapesCommon / kShapesAll.
-constexpr int kShapesCommon = 0, kShapesAll = 1, kShapesRect = 2, kShapesNoBox = 3;  // NoBox: Common without AABB / OBB
+// in the shadow kernel C5 gains 3.2% (557 -> 575), C4 2.9%, C3 4.2% (profiles/r2/s26_s27_*, s28_s31_*). The
+// reference-order kernels know two masks only (RARE: kShapesAll, else kShapesCommon).
+// SHAPES is a bit mask over pb2_shape_kind. Instantiated: the masks below; a scene runs the smallest one that contains
+// the kinds of its analytic geometries (render.cu shapes_level).
+constexpr int kShapeBit(int kind) { return 1 << kind; }
+constexpr int kShapesRect = kShapeBit(PB2_SHAPE_RECT);
+constexpr int kShapesBoxes = kShapeBit(PB2_SHAPE_AABB) | kShapeBit(PB2_SHAPE_OBB);
+constexpr int kShapesCbox = kShapesRect | kShapesBoxes | kShapeBit(PB2_SHAPE_CONE);  // the README Cornell box (C1)
+constexpr int kShapesCommon = kShapesCbox | kShapeBit(PB2_SHAPE_SPHERE) | kShapeBit(PB2_SHAPE_TRIANGLE) | kShapeBit(PB2_SHAPE_DISK);
+constexpr int kShapesNoBox = kShapesCommon & ~kShapesBoxes;
+constexpr int kShapesAll = kShapesCommon | kShapeBit(PB2_SHAPE_PLANE) | kShapeBit(PB2_SHAPE_CYLINDER);
+constexpr int kShapesRare = kShapesAll & ~kShapesCommon;
 template <int SHAPES = kShapesAll>
 __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int index, Ray& ray,
                                                 bool* inside = nullptr) {
@@ -297,23 +306,27 @@ __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int 
     return true;
   }
   switch (kind) {
-    case PB2_SHAPE_RECT: {
-      float t;
-      if (!rect_test(sc.rects[index], ray, t)) return false;
-      ray.tmax = t;
-      return true;
-    }
-    case PB2_SHAPE_CONE: return cone_intersect(sc.cones[index], ray);
-    case PB2_SHAPE_OBB: if (SHAPES != kShapesNoBox) return obb_intersect(sc.obbs[index], ray, inside); break;
-    case PB2_SHAPE_AABB: if (SHAPES != kShapesNoBox) return aabb_intersect(sc.aabbs[index], ray, inside); break;
-    case PB2_SHAPE_SPHERE: return sphere_intersect(sc.spheres[index], ray);
-    case PB2_SHAPE_DISK: return disk_intersect(sc.disks[index], ray);
-    case PB2_SHAPE_TRIANGLE: {
-      const pb2_triangle& t = sc.triangles[index];
-      return tri_intersect(ray, ldv(t.v0), ldv(t.v1), ldv(t.v2));
-    }
-    case PB2_SHAPE_PLANE: if (SHAPES == kShapesAll) return plane_intersect(sc.planes[index], ray); break;
-    case PB2_SHAPE_CYLINDER: if (SHAPES == kShapesAll) return cylinder_intersect(sc.cylinders[index], ray); break;
+    case PB2_SHAPE_RECT:
+      if (SHAPES & kShapesRect) {
+        float t;
+        if (!rect_test(sc.rects[index], ray, t)) return false;
+        ray.tmax = t;
+        return true;
+      }
+      break;
+    case PB2_SHAPE_CONE: if (SHAPES & kShapeBit(PB2_SHAPE_CONE)) return cone_intersect(sc.cones[index], ray); break;
+    case PB2_SHAPE_OBB: if (SHAPES & kShapeBit(PB2_SHAPE_OBB)) return obb_intersect(sc.obbs[index], ray, inside); break;
+    case PB2_SHAPE_AABB: if (SHAPES & kShapeBit(PB2_SHAPE_AABB)) return aabb_intersect(sc.aabbs[index], ray, inside); break;
+    case PB2_SHAPE_SPHERE: if (SHAPES & kShapeBit(PB2_SHAPE_SPHERE)) return sphere_intersect(sc.spheres[index], ray); break;
+    case PB2_SHAPE_DISK: if (SHAPES & kShapeBit(PB2_SHAPE_DISK)) return disk_intersect(sc.disks[index], ray); break;
+    case PB2_SHAPE_TRIANGLE:
+      if (SHAPES & kShapeBit(PB2_SHAPE_TRIANGLE)) {
+        const pb2_triangle& t = sc.triangles[index];
+        return tri_intersect(ray, ldv(t.v0), ldv(t.v1), ldv(t.v2));
+      }
+      break;
+    case PB2_SHAPE_PLANE: if (SHAPES & kShapeBit(PB2_SHAPE_PLANE)) return plane_intersect(sc.planes[index], ray); break;
+    case PB2_SHAPE_CYLINDER: if (SHAPES & kShapeBit(PB2_SHAPE_CYLINDER)) return cylinder_intersect(sc.cylinders[index], ray); break;
   }
   return false;
 }
@@ -324,21 +337,25 @@ __device__ __forceinline__ bool shape_hit(const DScene& sc, int kind, int index,
     return kind == PB2_SHAPE_RECT && rect_test(sc.rects[index], ray, t);
   }
   switch (kind) {
-    case PB2_SHAPE_RECT: {
-      float t;
-      return rect_test(sc.rects[index], ray, t);
-    }
-    case PB2_SHAPE_CONE: return cone_hit(sc.cones[index], ray);
-    case PB2_SHAPE_OBB: if (SHAPES != kShapesNoBox) return obb_hit(sc.obbs[index], ray); break;
-    case PB2_SHAPE_AABB: if (SHAPES != kShapesNoBox) return aabb_hit(sc.aabbs[index], ray.o, ray.d, ray.tmin, ray.tmax); break;
-    case PB2_SHAPE_SPHERE: return sphere_hit(sc.spheres[index], ray);
-    case PB2_SHAPE_DISK: return disk_hit(sc.disks[index], ray);
-    case PB2_SHAPE_TRIANGLE: {
-      const pb2_triangle& t = sc.triangles[index];
-      return tri_hit(ray, ldv(t.v0), ldv(t.v1), ldv(t.v2));
-    }
-    case PB2_SHAPE_PLANE: if (SHAPES == kShapesAll) return plane_hit(sc.planes[index], ray); break;
-    case PB2_SHAPE_CYLINDER: if (SHAPES == kShapesAll) return cylinder_hit(sc.cylinders[index], ray); break;
+    case PB2_SHAPE_RECT:
+      if (SHAPES & kShapesRect) {
+        float t;
+        return rect_test(sc.rects[index], ray, t);
+      }
+      break;
+    case PB2_SHAPE_CONE: if (SHAPES & kShapeBit(PB2_SHAPE_CONE)) return cone_hit(sc.cones[index], ray); break;
+    case PB2_SHAPE_OBB: if (SHAPES & kShapeBit(PB2_SHAPE_OBB)) return obb_hit(sc.obbs[index], ray); break;
+    case PB2_SHAPE_AABB: if (SHAPES & kShapeBit(PB2_SHAPE_AABB)) return aabb_hit(sc.aabbs[index], ray.o, ray.d, ray.tmin, ray.tmax); break;
+    case PB2_SHAPE_SPHERE: if (SHAPES & kShapeBit(PB2_SHAPE_SPHERE)) return sphere_hit(sc.spheres[index], ray); break;
+    case PB2_SHAPE_DISK: if (SHAPES & kShapeBit(PB2_SHAPE_DISK)) return disk_hit(sc.disks[index], ray); break;
+    case PB2_SHAPE_TRIANGLE:
+      if (SHAPES & kShapeBit(PB2_SHAPE_TRIANGLE)) {
+        const pb2_triangle& t = sc.triangles[index];
+        return tri_hit(ray, ldv(t.v0), ldv(t.v1), ldv(t.v2));
+      }
+      break;
+    case PB2_SHAPE_PLANE: if (SHAPES & kShapeBit(PB2_SHAPE_PLANE)) return plane_hit(sc.planes[index], ray); break;
+    case PB2_SHAPE_CYLINDER: if (SHAPES & kShapeBit(PB2_SHAPE_CYLINDER)) return cylinder_hit(sc.cylinders[index], ray); break;
   }
   return false;
 }

@@ -47,7 +47,7 @@ struct HookIO {
 
 template <bool ANY, bool RARE>
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_hook_wide(DScene sc, int n, WideQueue wq, HookIO io) {
-  wide_persistent<ANY, RARE>(sc, n, wq, io);
+  wide_persistent<ANY, (RARE ? kShapesAll : kShapesCommon)>(sc, n, wq, io);
 }
 template <bool ANY, bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_hook_fallback(DScene sc, WideQueue wq, HookIO io) {

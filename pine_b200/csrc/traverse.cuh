@@ -137,7 +137,7 @@ __device__ __forceinline__ bool closest_ref_order(const DScene& sc, Ray& ray, Hi
       if (hit) { h.geom = tp.geom; h.prim = prim; }
       return hit;
     }
-    bool hit = shape_intersect<RARE>(sc, tp.kind, tp.index, ray);
+    bool hit = shape_intersect<(RARE ? kShapesAll : kShapesCommon)>(sc, tp.kind, tp.index, ray);
     if (hit) { h.geom = tp.geom; h.prim = 0; }
     return hit;
   });
@@ -157,7 +157,7 @@ __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) 
         return tri_hit(ray, v0, v1, v2);
       });
     }
-    return shape_hit<RARE>(sc, tp.kind, tp.index, ray);
+    return shape_hit<(RARE ? kShapesAll : kShapesCommon)>(sc, tp.kind, tp.index, ray);
   });
 }
 

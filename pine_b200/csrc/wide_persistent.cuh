@@ -45,7 +45,7 @@ struct WideQueue {
 // the 10 M-triangle scene and cost 2x on scenes that live in L1, so neither is here.
 // The order in which a ray's primitives are tested does not matter for the result (ties are
 // detected and sent to the fallback, see traverse.cuh).
-template <bool ANY, int RARE = kShapesAll, class IO>  // RARE: a kShapes* level (shapes.cuh)
+template <bool ANY, int RARE = kShapesAll, class IO>  // RARE: a kShapes* mask (shapes.cuh)
 __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQueue wq, const IO& io) {
   const unsigned lane = threadIdx.x & 31u;
 #if PB2_SMEM_TOP > 0
@@ -136,15 +136,15 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
           have = false; ambiguous = false; tie_t = -1.0f; win_leaf = -1; t2 = kFloatMax;
           h.geom = h.prim = -1;
           active = true;
-          if (RARE != kShapesRect && RARE != kShapesNoBox && sc.n_box_shapes) {  // see DBoxShape and traverse.cuh (iii); a Rect-only scene has none
+          if ((RARE & kShapesBoxes) && sc.n_box_shapes) {  // see DBoxShape and traverse.cuh (iii); a Rect-only scene has none
             bool touched = false;
             for (int i = 0; i < sc.n_box_shapes && !touched; i++) {
               const int4 b = __ldg(reinterpret_cast<const int4*>(sc.box_shapes) + i);
               if (ANY) {
-                touched = shape_hit<kShapesCommon>(sc, b.x, b.y, ray);
+                touched = shape_hit<kShapesBoxes>(sc, b.x, b.y, ray);
               } else {
                 Ray r2 = ray;
-                touched = shape_intersect<kShapesCommon>(sc, b.x, b.y, r2);
+                touched = shape_intersect<kShapesBoxes>(sc, b.x, b.y, r2);
               }
               touched = touched && leaf_gate(sc.leaves, b.z, q, ray.tmin, ray.tmax);
             }
@@ -187,7 +187,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
           ok = shape_intersect<RARE>(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
           // Plane::intersect lets a NaN t through and Cylinder::intersect a far root below tmin (geometry.cpp:40-45,
           // 502-504): what the reference does next depends on its visiting order, so it decides
-          if (RARE == kShapesAll && ok && !(r2.tmax >= ray.tmin)) { ambiguous = true; done = true; ok = false; }
+          if ((RARE & kShapesRare) && ok && !(r2.tmax >= ray.tmin)) { ambiguous = true; done = true; ok = false; }
         }
         if (ok) {
           if (r2.tmax < ray.tmax) {
