@@ -1049,7 +1049,12 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       if ((sc.shape_mask & ~m) == 0 && !(m == kShapesRect && closest && sc.has_meshes)) return m;
     return kShapesAll;
   };
-  const int trace_shapes = shapes_level(true), shadow_shapes = shapes_level(false);
+  int trace_shapes = shapes_level(true), shadow_shapes = shapes_level(false);
+  {  // tuning knobs: force another instantiated mask (must still contain the scene's kinds)
+    const int ft = env_int("PB2_TRACE_SHAPES", -1), fs = env_int("PB2_SHADOW_SHAPES", -1);
+    if (ft >= 0 && (sc.shape_mask & ~ft) == 0) trace_shapes = ft;
+    if (fs >= 0 && (sc.shape_mask & ~fs) == 0) shadow_shapes = fs;
+  }
   auto enqueue_wave = [&](int l, int pw, int sw) -> int {
     WaveView& w = lane_view[l];
     cudaStream_t ls = lane_stream[l];
