@@ -156,7 +156,7 @@ struct DScene {
   const int32_t* halton_sums;
   const uint16_t* halton_perms;
   int halton_inv0, halton_inv1;
-  int shape_mask;       // OR of 1 << pb2_shape_kind over the analytic (non-mesh) geometries: picks the traversal
+  int shape_mask;       // OR of 1 << pb2_shape_kind over the geometries (Mesh: non-empty ones): picks the traversal
                         // kernels' instantiation (shapes.cuh kShapes*)
   int has_rare_shapes;  // a Plane or a Cylinder somewhere (the reference-order kernels' two-way switch)
   int has_meshes;       // some geometry is a non-empty Mesh

@@ -1041,12 +1041,12 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   PB2_CUDA_CHECK(cudaEventRecord(ctx->ev0, st));
   mark(-1);
   // One wave on one lane: raygen, then per depth trace / classify / shade / shadow, then the unwind.
-  // The smallest instantiated shape mask that contains the scene's analytic kinds (shapes.cuh): the code compiled
-  // into the persistent loop decides its register allocation. With meshes the closest-hit kernel skips the
-  // Rect-only form (2.5% slower in kernel on C5's deep trees than the no-box form: profiles/r2/s28_s31_*).
+  // The first instantiated shape mask (shapes.cuh) that contains the scene's geometry kinds: the code compiled into
+  // the persistent loop decides its register allocation. The closest-hit kernel skips the Rect + Mesh form (2.5%
+  // slower in kernel on C5's deep trees than the no-box form: profiles/r2/s28_s31_*, s34_*).
   auto shapes_level = [&](bool closest) {
-    for (int m : {kShapesRect, kShapesNoBox, kShapesCbox, kShapesCommon})
-      if ((sc.shape_mask & ~m) == 0 && !(m == kShapesRect && closest && sc.has_meshes)) return m;
+    for (int m : {kShapesRect, kShapesRectMesh, kShapesCbox, kShapesNoBox, kShapesCommon})
+      if ((sc.shape_mask & ~m) == 0 && !(m == kShapesRectMesh && closest)) return m;
     return kShapesAll;
   };
   int trace_shapes = shapes_level(true), shadow_shapes = shapes_level(false);
@@ -1070,7 +1070,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       if (closest_wide_ok) {
         switch (trace_shapes) {
 #define PB2_TRACE(M) case M: k_trace<M><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth); break;
-          PB2_TRACE(kShapesRect) PB2_TRACE(kShapesNoBox) PB2_TRACE(kShapesCbox) PB2_TRACE(kShapesCommon)
+          PB2_TRACE(kShapesRect) PB2_TRACE(kShapesRectMesh) PB2_TRACE(kShapesNoBox) PB2_TRACE(kShapesCbox) PB2_TRACE(kShapesCommon)
           default: k_trace<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
 #undef PB2_TRACE
         }
@@ -1106,7 +1106,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
         if (any_wide_ok) {
           switch (shadow_shapes) {
 #define PB2_SHADOW(M) case M: k_shadow<M><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth); break;
-            PB2_SHADOW(kShapesRect) PB2_SHADOW(kShapesNoBox) PB2_SHADOW(kShapesCbox) PB2_SHADOW(kShapesCommon)
+            PB2_SHADOW(kShapesRect) PB2_SHADOW(kShapesRectMesh) PB2_SHADOW(kShapesNoBox) PB2_SHADOW(kShapesCbox) PB2_SHADOW(kShapesCommon)
             default: k_shadow<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
 #undef PB2_SHADOW
           }

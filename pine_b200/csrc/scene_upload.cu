@@ -410,6 +410,7 @@ extern "C" int pb2_upload_scene(pb2_context* ctx, const pb2_scene_desc* sd) {
     if (sd->geometries[i].shape_kind != PB2_SHAPE_MESH) s.shape_mask |= 1 << sd->geometries[i].shape_kind;
   s.has_rare_shapes = (s.shape_mask & ((1 << PB2_SHAPE_PLANE) | (1 << PB2_SHAPE_CYLINDER))) ? 1 : 0;
   s.has_meshes = jobs.empty() ? 0 : 1;
+  if (s.has_meshes) s.shape_mask |= 1 << PB2_SHAPE_MESH;
   s.camera = sd->camera;
   ctx->n_pixels = sd->camera.width * sd->camera.height;
   ctx->host_scene_ready = true;

@@ -286,20 +286,23 @@ __device__ __forceinline__ bool cylinder_hit(const pb2_cylinder& s, const Ray& r
 // (incl. the per-ray box pre-test of wide_persistent.cuh) compiled out of both kernels and only the Rect case left
 // in the shadow kernel C5 gains 3.2% (557 -> 575), C4 2.9%, C3 4.2% (profiles/r2/s26_s27_*, s28_s31_*). The
 // reference-order kernels know two masks only (RARE: kShapesAll, else kShapesCommon).
-// SHAPES is a bit mask over pb2_shape_kind. Instantiated: the masks below; a scene runs the smallest one that contains
-// the kinds of its analytic geometries (render.cu shapes_level).
+// SHAPES is a bit mask over pb2_shape_kind. Instantiated: the masks below; a scene runs the first one (render.cu
+// shapes_level) that contains the kinds of its geometries.
 constexpr int kShapeBit(int kind) { return 1 << kind; }
-constexpr int kShapesRect = kShapeBit(PB2_SHAPE_RECT);
+constexpr int kShapesMesh = kShapeBit(PB2_SHAPE_MESH);  // triangles of Mesh geometries (tested inline, not through the switch)
+constexpr int kShapesRect = kShapeBit(PB2_SHAPE_RECT);                               // cbox-indirect (C3)
+constexpr int kShapesRectMesh = kShapesRect | kShapesMesh;                           // meshes + Rect emitters / walls (C4, C5)
 constexpr int kShapesBoxes = kShapeBit(PB2_SHAPE_AABB) | kShapeBit(PB2_SHAPE_OBB);
 constexpr int kShapesCbox = kShapesRect | kShapesBoxes | kShapeBit(PB2_SHAPE_CONE);  // the README Cornell box (C1)
-constexpr int kShapesCommon = kShapesCbox | kShapeBit(PB2_SHAPE_SPHERE) | kShapeBit(PB2_SHAPE_TRIANGLE) | kShapeBit(PB2_SHAPE_DISK);
+constexpr int kShapesCommon = kShapesCbox | kShapesMesh | kShapeBit(PB2_SHAPE_SPHERE) | kShapeBit(PB2_SHAPE_TRIANGLE) |
+                              kShapeBit(PB2_SHAPE_DISK);
 constexpr int kShapesNoBox = kShapesCommon & ~kShapesBoxes;
 constexpr int kShapesAll = kShapesCommon | kShapeBit(PB2_SHAPE_PLANE) | kShapeBit(PB2_SHAPE_CYLINDER);
 constexpr int kShapesRare = kShapesAll & ~kShapesCommon;
 template <int SHAPES = kShapesAll>
 __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int index, Ray& ray,
                                                 bool* inside = nullptr) {
-  if (SHAPES == kShapesRect) {
+  if ((SHAPES & ~kShapesMesh) == kShapesRect) {
     float t;
     if (kind != PB2_SHAPE_RECT || !rect_test(sc.rects[index], ray, t)) return false;
     ray.tmax = t;
@@ -332,7 +335,7 @@ __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int 
 }
 template <int SHAPES = kShapesAll>
 __device__ __forceinline__ bool shape_hit(const DScene& sc, int kind, int index, const Ray& ray) {
-  if (SHAPES == kShapesRect) {
+  if ((SHAPES & ~kShapesMesh) == kShapesRect) {
     float t;
     return kind == PB2_SHAPE_RECT && rect_test(sc.rects[index], ray, t);
   }

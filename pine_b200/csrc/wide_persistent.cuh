@@ -170,7 +170,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
     auto test_prim = [&](const PrimRec& r) {
         if (ANY) {
         bool ok;
-        if (r.prim >= 0) ok = tri_hit(ray, r.v0, r.v1, r.v2);
+        if ((RARE & kShapesMesh) && r.prim >= 0) ok = tri_hit(ray, r.v0, r.v1, r.v2);
         else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: tested at refill
         else ok = shape_hit<RARE>(sc, -1 - r.prim, __float_as_int(r.v0.x), ray);
         if (ok && leaf_gate(sc.leaves, r.leaf, q, ray.tmin, ray.tmax)) { have = true; done = true; }
@@ -181,7 +181,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
         Ray r2 = ray;
         r2.tmax = slack_of(ray.tmax);
         bool ok;
-        if (r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
+        if ((RARE & kShapesMesh) && r.prim >= 0) ok = tri_intersect(r2, r.v0, r.v1, r.v2);
         else if (r.prim >= -1 - PB2_SHAPE_OBB) ok = false;  // AABB/OBB: rays that touch one never get here
         else {
           ok = shape_intersect<RARE>(sc, -1 - r.prim, __float_as_int(r.v0.x), r2);
