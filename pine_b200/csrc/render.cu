@@ -500,7 +500,10 @@ __global__ void __launch_bounds__(256) k_shade_terminal(DScene sc, WaveView w, i
 
 // class MAT: NEE + BSDF sample at a surface vertex (path.cpp:74-120)
 template <int MAT, bool GENERIC>
-__global__ void __launch_bounds__(128) k_shade_mat(DScene sc, WaveView w, int depth) {
+#ifndef PB2_SHADE_MINBLOCKS
+#define PB2_SHADE_MINBLOCKS 1
+#endif
+__global__ void __launch_bounds__(128, PB2_SHADE_MINBLOCKS) k_shade_mat(DScene sc, WaveView w, int depth) {
   const int n = *list_count(w, depth, MAT);
   const int cur = depth & 1, nxt = cur ^ 1;
   int* next_count = w.counts + depth + 1;
