@@ -3,12 +3,13 @@
 
 ncu's `--page source --csv` lists SASS instructions with sampling counts but no file:line; nvdisasm
 -g on the same cubin lists file:line per SASS address. This joins the two by address.
-  python scripts/ncu_lines.py <report.ncu-rep> <kernel name> <cubin> [launch index]
+  python scripts/ncu_lines.py <report.ncu-rep> <kernel name> <cubin> [launch index] [mangled-name substring]
 """
 import csv, re, subprocess, sys, collections, io
 
 rep, kern, cubin = sys.argv[1:4]
 skip = sys.argv[4] if len(sys.argv) > 4 else "0"
+mangled = sys.argv[5] if len(sys.argv) > 5 else None  # substring of the cubin function (templated kernels), e.g. 7k_traceILi252E
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", kern, "--launch-skip", skip,
                       "--launch-count", "1"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
@@ -20,7 +21,7 @@ for ln in dis.splitlines():
     m = re.match(r"\s*\.text\.(\S+):", ln)
     if m:
         infn = re.search(r"\d+%s[A-Z]" % re.escape(kern), m.group(1)) is not None or m.group(1).endswith(kern)
-        infn = kern in m.group(1)
+        infn = (mangled in m.group(1)) if mangled else (kern in m.group(1))
         fn = m.group(1)
         cur = None
         continue
