@@ -200,3 +200,26 @@ def test_progress_callback_follows_the_completed_waves():
     assert seen == []
     B.close()
 
+
+
+@pytest.mark.parametrize("fn,kw,masks", [
+    ("cbox_indirect", dict(size=(64, 64)), (32, 160, 51, 252, 255, 1023)),                      # Rects only
+    ("mesh_field", dict(n_instances=8, subdiv=2, size=(64, 36), spp=4, depth=5, with_shapes=True), (252, 255, 1023)),
+    ("cbox_readme", dict(size=(64, 64)), (51, 255, 1023)),                                       # Rect + Cone + OBB
+])
+def test_every_shape_mask_instantiation_renders_the_same_film(fn, kw, masks):
+    """The traversal kernels are instantiated per shape-kind mask (shapes.cuh kShapes*) and a render picks the first
+    that covers the scene; every OTHER instantiation that covers it (forced with PB2_TRACE_SHAPES /
+    PB2_SHADOW_SHAPES) gives the same film bits, and a mask that does not cover the scene is ignored."""
+    S = pb.Scene()
+    cfg = scenes.SCENES[fn](S, **kw)
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    spp, depth = 4, cfg["depth"]
+    base = B.render(spp, depth)
+    for m in masks:
+        film = _with_env({"PB2_TRACE_SHAPES": m, "PB2_SHADOW_SHAPES": m}, lambda: B.render(spp, depth))
+        assert np.array_equal(u32(film), u32(base)), m
+    film = _with_env({"PB2_TRACE_SHAPES": 0, "PB2_SHADOW_SHAPES": 4}, lambda: B.render(spp, depth))  # not a cover
+    assert np.array_equal(u32(film), u32(base))
+    B.close()
