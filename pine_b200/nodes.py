@@ -122,6 +122,17 @@ def Checkerboard(p, ratio=0.5):
     return Node("checkerboard", (_v(p),), a=(ratio, 0, 0), is_float=True)
 
 
+def Texture(p, texture):
+    """ctx.type<NodeImage>("Texture") (node.cpp:64): the texel of scene texture `texture` (index from
+    Scene.add_texture) at fract(p.xy), nearest with wrap, gamma-decoded (node.cpp:20-23, image.cpp:7-18)."""
+    return Node("image", (_v(p),), a=(int(texture) + 1, 0, 0))
+
+
+def Texturef(p, texture):
+    """NodeImagef (node.cpp:24-27): the same texel's first channel as a Nodef."""
+    return Node("imagef", (_v(p),), a=(int(texture) + 1, 0, 0), is_float=True)
+
+
 def _unary(op):
     def make(x):
         x = as_node(x)

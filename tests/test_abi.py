@@ -101,6 +101,10 @@ def test_built_scene_is_shared_between_contexts_through_a_file(tmp_path):
     from pine_b200 import scenes
     S = pb.Scene()
     scenes.mesh_field(S, n_instances=27, subdiv=2, seed=3, size=(64, 48))
+    # round-2 arrays travel too: node programs, a Plane, a Cylinder
+    from pine_b200 import nodes as N
+    S.add_plane((0, -2, 0), (0, 1, 0), S.add_material("uber", N.lerp(N.Checkerboard(N.UV()), (1, 0, 0), (0, 0, 1)), roughness=0.3))
+    S.add_cylinder((0, 0, 0), (0, 1, 0), 0.2, 0)
     builder, importer = pb.Backend(-1), pb.Backend(-1)
     builder.upload_scene(S)
     a, b = str(tmp_path / "a.bin"), str(tmp_path / "b.bin")

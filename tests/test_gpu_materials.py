@@ -244,3 +244,56 @@ def test_emissive_plane_or_cylinder_is_rejected():
         S.set_camera((8, 8), (0, 1, -4), (0, 0, 0), 0.3)
         with pytest.raises(pb.PineB200Error):
             pb.Backend(0).upload_scene(S)
+
+
+def test_image_nodes_inside_a_program_equal_the_texture_path():
+    """NodeImage / NodeImagef as program instructions (PB2_NODE_IMAGE / IMAGEF): Texture(UV(), t) as a graph is the
+    image node the glTF path binds through pb2_material.color_texture -- same film bits; at scaled coordinates the
+    device lookup equals the nearest-with-wrap restatement (node.cpp:20-27, image.cpp:7-18)."""
+    from pine_b200 import nodes as N
+    rng = np.random.RandomState(5)
+    tex = rng.randint(0, 256, (8, 16, 4)).astype(np.uint8)
+
+    def scene(graph):
+        S = pb.Scene()
+        t = S.add_texture(tex)
+        if graph:
+            m = S.add_material("uber", N.Texture(N.UV(), t), roughness=N.Comp(N.Texture(N.UV(), t), 1), metallic=0.0)
+        else:
+            m = S.add_material("uber", (0, 0, 0), color_texture=t, roughness_texture=t, metallic=0.0)
+        S.add_rect((0, 0, 1), (2, 0, 0), (0, 0, 2), m)
+        S.add_sphere((0, 0.4, 1), 0.4, m)
+        S.add_rect((0, 1.9, 1), (0.6, 0, 0), (0, 0, 0.6), S.add_material("emissive", (30, 30, 30)))
+        S.set_camera((48, 48), (0, 1, -3), (0, 0.5, 1), 0.3)
+        return S, m
+    B = pb.Backend(0)
+    S0, _ = scene(False)
+    B.upload_scene(S0)
+    want = B.render(8, 4)
+    S1, m = scene(True)
+    B.upload_scene(S1)
+    assert np.array_equal(u32(B.render(8, 4)), u32(want))
+    # known answers at scaled / negative coordinates, incl. the float form
+    S2 = pb.Scene()
+    t = S2.add_texture(tex)
+    g3, gf = N.Texture(N.Position() * 3.0, t), N.Texturef(N.UV() * (2.0, -1.5, 1.0), t)
+    m3 = S2.add_material("diffuse", g3)
+    mf = S2.add_material("diffuse", N.Vec3(gf) * (1.0, 1.0, 1.0))
+    S2.add_sphere((0, 0, 0), 1.0, m3)
+    S2.set_camera((8, 8), (0, 0, -4), (0, 0, 0), 0.3)
+    B.upload_scene(S2)
+    c = rng.uniform(-2, 2, (513, 8)).astype(np.float32)
+    f32 = np.float32
+    lut = np.array([np.power(f32(v) / f32(255.0), f32(2.2), dtype=f32) for v in range(256)], f32)
+
+    def lookup(q):
+        fx, fy = (q[:, 0] - np.floor(q[:, 0])).astype(f32), (q[:, 1] - np.floor(q[:, 1])).astype(f32)
+        x = np.minimum((f32(16) * fx).astype(np.int32), 15)
+        y = np.minimum((f32(8) * fy).astype(np.int32), 7)
+        return tex[y, x]
+    got3 = B.eval_node(S2.materials[m3].color_node, c)
+    np.testing.assert_allclose(got3, lut[lookup(c[:, 0:3] * f32(3.0))[:, :3]], rtol=2e-7, atol=0)
+    gotf = B.eval_node(S2.materials[mf].color_node, c)
+    uv = np.stack([c[:, 6] * f32(2.0), c[:, 7] * f32(-1.5)], axis=1)
+    np.testing.assert_allclose(gotf[:, 0], lut[lookup(uv)[:, 0]], rtol=2e-7, atol=0)
+    B.close()
