@@ -1048,7 +1048,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
   // the persistent loop decides its register allocation. The closest-hit kernel skips the Rect + Mesh form (2.5%
   // slower in kernel on C5's deep trees than the no-box form: profiles/r2/s28_s31_*, s34_*).
   auto shapes_level = [&](bool closest) {
-    for (int m : {kShapesRect, kShapesRectMesh, kShapesCbox, kShapesNoBox, kShapesCommon})
+    for (int m : {kShapesRect, kShapesRectMesh, kShapesFlat, kShapesCbox, kShapesNoBox, kShapesCommon})
       if ((sc.shape_mask & ~m) == 0 && !(m == kShapesRectMesh && closest)) return m;
     return kShapesAll;
   };
@@ -1073,7 +1073,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
       if (closest_wide_ok) {
         switch (trace_shapes) {
 #define PB2_TRACE(M) case M: k_trace<M><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth); break;
-          PB2_TRACE(kShapesRect) PB2_TRACE(kShapesRectMesh) PB2_TRACE(kShapesNoBox) PB2_TRACE(kShapesCbox) PB2_TRACE(kShapesCommon)
+          PB2_TRACE(kShapesRect) PB2_TRACE(kShapesRectMesh) PB2_TRACE(kShapesFlat) PB2_TRACE(kShapesNoBox) PB2_TRACE(kShapesCbox) PB2_TRACE(kShapesCommon)
           default: k_trace<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
 #undef PB2_TRACE
         }
@@ -1109,7 +1109,7 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
         if (any_wide_ok) {
           switch (shadow_shapes) {
 #define PB2_SHADOW(M) case M: k_shadow<M><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth); break;
-            PB2_SHADOW(kShapesRect) PB2_SHADOW(kShapesRectMesh) PB2_SHADOW(kShapesNoBox) PB2_SHADOW(kShapesCbox) PB2_SHADOW(kShapesCommon)
+            PB2_SHADOW(kShapesRect) PB2_SHADOW(kShapesRectMesh) PB2_SHADOW(kShapesFlat) PB2_SHADOW(kShapesNoBox) PB2_SHADOW(kShapesCbox) PB2_SHADOW(kShapesCommon)
             default: k_shadow<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
 #undef PB2_SHADOW
           }

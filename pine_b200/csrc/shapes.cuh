@@ -297,6 +297,8 @@ constexpr int kShapesCbox = kShapesRect | kShapesBoxes | kShapeBit(PB2_SHAPE_CON
 constexpr int kShapesCommon = kShapesCbox | kShapesMesh | kShapeBit(PB2_SHAPE_SPHERE) | kShapeBit(PB2_SHAPE_TRIANGLE) |
                               kShapeBit(PB2_SHAPE_DISK);
 constexpr int kShapesNoBox = kShapesCommon & ~kShapesBoxes;
+constexpr int kShapesUnbounded = kShapeBit(PB2_SHAPE_CONE) | kShapeBit(PB2_SHAPE_PLANE) | kShapeBit(PB2_SHAPE_CYLINDER);
+constexpr int kShapesFlat = kShapesNoBox & ~kShapesUnbounded;  // no boxes, nothing that leaves its BVH box (kNoCullBit)
 constexpr int kShapesAll = kShapesCommon | kShapeBit(PB2_SHAPE_PLANE) | kShapeBit(PB2_SHAPE_CYLINDER);
 constexpr int kShapesRare = kShapesAll & ~kShapesCommon;
 template <int SHAPES = kShapesAll>

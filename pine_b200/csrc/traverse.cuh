@@ -280,6 +280,8 @@ constexpr uint32_t kNoCullBit = 0x80000000u;  // in DNode8::prim_base
 #define PB2_SMEM_TOP 9
 #endif
 // The test on a node already in registers (n0..n4 = its five 128-bit words).
+// NOCULL = false: the tree holds no unbounded shape (no node carries kNoCullBit), the switch of limits is compiled out.
+template <bool NOCULL = true>
 __device__ __forceinline__ uint32_t test_node8_regs(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
                                                     const uint4 n4, const WideRay& w, float tmin, float lim,
                                                     float lim_nocull, uint32_t& child_base, uint32_t& prim_base,
@@ -290,8 +292,8 @@ __device__ __forceinline__ uint32_t test_node8_regs(const uint4 n0, const uint4 
   const float az = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * w.inv.z;
   imask = n0.w >> 24;
   child_base = n1.x;
-  prim_base = n1.y & ~kNoCullBit;
-  if (n1.y & kNoCullBit) lim = lim_nocull;
+  prim_base = NOCULL ? (n1.y & ~kNoCullBit) : n1.y;
+  if (NOCULL && (n1.y & kNoCullBit)) lim = lim_nocull;
   // b = origin * inv - ood with ONE rounding (the reference's fl(fl(P inv) - ood) has two, and delta below
   // bounds the distance of both expressions from the exact value), then the byte bias: base = b - 2^15 a.
   // delta = w.err + 2^-21 * 8447 |a| (see the derivation above; w.err >= 2^-21 (|origin inv| + |ood|)), and
@@ -331,6 +333,7 @@ __device__ __forceinline__ uint32_t test_node8_regs(const uint4 n0, const uint4 
   }
   return hitmask;
 }
+template <bool NOCULL = true>
 __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx, const WideRay& w, float tmin,
                                                float lim, float lim_nocull, uint32_t& child_base,
                                                uint32_t& prim_base, uint32_t& imask, const uint4* s_top = nullptr) {
@@ -346,7 +349,7 @@ __device__ __forceinline__ uint32_t test_node8(const DNode8* nodes, uint32_t idx
 #else
   const uint4 n0 = __ldg(p), n1 = __ldg(p + 1), n2 = __ldg(p + 2), n3 = __ldg(p + 3), n4 = __ldg(p + 4);
 #endif
-  return test_node8_regs(n0, n1, n2, n3, n4, w, tmin, lim, lim_nocull, child_base, prim_base, imask);
+  return test_node8_regs<NOCULL>(n0, n1, n2, n3, n4, w, tmin, lim, lim_nocull, child_base, prim_base, imask);
 }
 
 __device__ __forceinline__ WideRay make_wide_ray(const DScene& sc, const Ray& ray, const Octant& q) {

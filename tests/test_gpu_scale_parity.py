@@ -203,8 +203,8 @@ def test_progress_callback_follows_the_completed_waves():
 
 
 @pytest.mark.parametrize("fn,kw,masks", [
-    ("cbox_indirect", dict(size=(64, 64)), (32, 160, 51, 252, 255, 1023)),                      # Rects only
-    ("mesh_field", dict(n_instances=8, subdiv=2, size=(64, 36), spp=4, depth=5, with_shapes=True), (252, 255, 1023)),
+    ("cbox_indirect", dict(size=(64, 64)), (32, 160, 236, 51, 252, 255, 1023)),                 # Rects only
+    ("mesh_field", dict(n_instances=8, subdiv=2, size=(64, 36), spp=4, depth=5, with_shapes=True), (236, 252, 255, 1023)),
     ("cbox_readme", dict(size=(64, 64)), (51, 255, 1023)),                                       # Rect + Cone + OBB
 ])
 def test_every_shape_mask_instantiation_renders_the_same_film(fn, kw, masks):
