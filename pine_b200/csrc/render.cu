@@ -373,7 +373,7 @@ __device__ inline bool bssrdf_walk(const DScene& sc, const Bxdf& b, int geom, V3
       });
       if (hit) surface_info(sc, geom, prim, ray.o + ray.tmax * ray.d, exit_it);
     } else {
-      hit = shape_intersect<false>(sc, gm.kind, gm.index, ray);  // Subsurface on a Plane / Cylinder is refused at upload
+      hit = shape_intersect<kShapesCommon>(sc, gm.kind, gm.index, ray);  // Subsurface on a Plane / Cylinder is refused at upload
     }
     if (!hit) return false;
     float t = -logf(1 - smp_get1d(sc, smp)) * sigma_t_inv;

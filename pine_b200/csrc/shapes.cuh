@@ -304,6 +304,7 @@ constexpr int kShapesRare = kShapesAll & ~kShapesCommon;
 template <int SHAPES = kShapesAll>
 __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int index, Ray& ray,
                                                 bool* inside = nullptr) {
+  static_assert(SHAPES > 1, "SHAPES is a kShapes* mask, not a bool");
   if ((SHAPES & ~kShapesMesh) == kShapesRect) {
     float t;
     if (kind != PB2_SHAPE_RECT || !rect_test(sc.rects[index], ray, t)) return false;
@@ -337,6 +338,7 @@ __device__ __forceinline__ bool shape_intersect(const DScene& sc, int kind, int 
 }
 template <int SHAPES = kShapesAll>
 __device__ __forceinline__ bool shape_hit(const DScene& sc, int kind, int index, const Ray& ray) {
+  static_assert(SHAPES > 1, "SHAPES is a kShapes* mask, not a bool");
   if ((SHAPES & ~kShapesMesh) == kShapesRect) {
     float t;
     return kind == PB2_SHAPE_RECT && rect_test(sc.rects[index], ray, t);
