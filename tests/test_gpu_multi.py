@@ -120,6 +120,27 @@ def test_two_gpus_report_progress_of_the_whole_job():
     M.close()
 
 
+@two_gpus
+@pytest.mark.parametrize("fn", ["classic", "plane_yard"])
+def test_two_gpus_carry_node_programs_planes_and_cylinders(fn):
+    """The round-2 scene content reaches every replica: node programs (and the switch to the generic shade kernels
+    they need), Plane / Cylinder records (and the traversal kernels compiled with them): rows over all GPUs equal
+    the single-GPU film bit for bit."""
+    S = pb.Scene()
+    cfg = scenes.SCENES[fn](S, size=(96, 64))
+    B = pb.Backend(0)
+    B.upload_scene(S)
+    want = B.render(8, cfg["depth"])
+    M = pb.MultiBackend()
+    M.upload_scene(S)
+    assert np.array_equal(u32(M.render(8, cfg["depth"], mode="rows")), u32(want))
+    M.restage()
+    assert np.array_equal(u32(M.render(8, cfg["depth"], mode="rows")), u32(want))
+    M.close()
+    B.close()
+
+
+@two_gpus
 def test_two_gpus_large_mesh_replicas_are_complete():
     """A scene whose arrays exceed the sharded-staging threshold (1 MiB): 1/N through PCIe + in-place all-gather
     must leave the same BVH on every GPU -- rows mode is then bit-identical to one GPU."""
