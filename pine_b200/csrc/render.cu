@@ -210,13 +210,13 @@ template <int SHAPES>
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_trace(DScene sc, WaveView w, int depth) {
   wide_persistent<false, SHAPES>(sc, w.counts[depth], wave_queue(w, depth, 0), trace_io(w, depth));
 }
-template <bool RARE>
+template <int SHAPES>
 __global__ void __launch_bounds__(kTraceBlock, kFallbackBlocksPerSM) k_trace_fallback(DScene sc, WaveView w, int depth) {
-  wide_fallback<false, RARE>(sc, wave_queue(w, depth, 0), trace_io(w, depth));
+  wide_fallback<false, SHAPES>(sc, wave_queue(w, depth, 0), trace_io(w, depth));
 }
 template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_trace_ref(DScene sc, WaveView w, int depth) {
-  ref_order_all<false, RARE>(sc, w.counts[depth], trace_io(w, depth));
+  ref_order_all<false, (RARE ? kShapesAll : kShapesCommon)>(sc, w.counts[depth], trace_io(w, depth));
 }
 template <int SHAPES>
 __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_shadow(DScene sc, WaveView w, int depth) {
@@ -224,11 +224,11 @@ __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_shadow(DSc
 }
 template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock, kFallbackBlocksPerSM) k_shadow_fallback(DScene sc, WaveView w, int depth) {
-  wide_fallback<true, RARE>(sc, wave_queue(w, depth, 1), shadow_io(w, depth));
+  wide_fallback<true, (RARE ? kShapesAll : kShapesCommon)>(sc, wave_queue(w, depth, 1), shadow_io(w, depth));
 }
 template <bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_shadow_ref(DScene sc, WaveView w, int depth) {
-  ref_order_all<true, RARE>(sc, w.counts[w.max_depth + 1 + depth], shadow_io(w, depth));
+  ref_order_all<true, (RARE ? kShapesAll : kShapesCommon)>(sc, w.counts[w.max_depth + 1 + depth], shadow_io(w, depth));
 }
 
 // sky_color(direction) (color.cpp:100-103): sqr(lerp(d.y / 2 + 0.7, warm, cool)), lerp = a (1 - t) + b t
@@ -1077,8 +1077,11 @@ extern "C" int pb2_render_device(pb2_context* ctx, const pb2_render_params* p, v
           default: k_trace<kShapesAll><<<pgrid, kTraceBlock, 0, ls>>>(sc, w, depth);
 #undef PB2_TRACE
         }
-        if (sc.has_rare_shapes) k_trace_fallback<true><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
-        else k_trace_fallback<false><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
+        // the reference-order re-trace: the README Cornell box sends a fifth of its rays here (its two Boxes), so
+        // it gets its own mask; everything else the common one
+        if (sc.has_rare_shapes) k_trace_fallback<kShapesAll><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
+        else if ((sc.shape_mask & ~kShapesCbox) == 0) k_trace_fallback<kShapesCbox><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
+        else k_trace_fallback<kShapesCommon><<<kNumSMs * kFallbackBlocksPerSM, kTraceBlock, 0, ls>>>(sc, w, depth);
         launches += 2;
       } else {
         if (sc.has_rare_shapes) k_trace_ref<true><<<sm_grid(live, kTraceBlock, 16), kTraceBlock, 0, ls>>>(sc, w, depth);

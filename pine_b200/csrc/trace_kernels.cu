@@ -51,11 +51,11 @@ __global__ void __launch_bounds__(kTraceBlock, PB2_TRACE_MINBLOCKS) k_hook_wide(
 }
 template <bool ANY, bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_hook_fallback(DScene sc, WideQueue wq, HookIO io) {
-  wide_fallback<ANY, RARE>(sc, wq, io);
+  wide_fallback<ANY, (RARE ? kShapesAll : kShapesCommon)>(sc, wq, io);
 }
 template <bool ANY, bool RARE>
 __global__ void __launch_bounds__(kTraceBlock) k_hook_ref(DScene sc, int n, HookIO io) {
-  ref_order_all<ANY, RARE>(sc, n, io);
+  ref_order_all<ANY, (RARE ? kShapesAll : kShapesCommon)>(sc, n, io);
 }
 
 template <bool ANY>

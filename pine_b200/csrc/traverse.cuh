@@ -117,14 +117,15 @@ __device__ __forceinline__ bool walk_ref_order(const DScene& sc, const DTree& tr
 }
 
 // BVH::intersect (bvh.cpp:513-548). ray.tmax is shrunk to t; returns geom/prim of the winner.
-template <bool RARE = true>
+// SHAPES: a kShapes* mask (shapes.cuh) that contains the scene's geometry kinds
+template <int SHAPES = kShapesAll>
 __device__ __forceinline__ bool closest_ref_order(const DScene& sc, Ray& ray, Hit& h) {
   Octant q = make_octant(ray);
   h.geom = -1;
   h.prim = -1;
   return walk_ref_order<false>(sc, sc.top, ray, q, [&](int top_id) {
     DTopPrim tp = sc.top_prims[top_id];
-    if (tp.kind == PB2_SHAPE_MESH) {
+    if ((SHAPES & kShapesMesh) && tp.kind == PB2_SHAPE_MESH) {
       const DMesh& m = sc.meshes[tp.index];
       int prim = -1;
       bool hit = walk_ref_order<false>(sc, m.tree, ray, q, [&](int tri) {
@@ -137,19 +138,19 @@ __device__ __forceinline__ bool closest_ref_order(const DScene& sc, Ray& ray, Hi
       if (hit) { h.geom = tp.geom; h.prim = prim; }
       return hit;
     }
-    bool hit = shape_intersect<(RARE ? kShapesAll : kShapesCommon)>(sc, tp.kind, tp.index, ray);
+    bool hit = shape_intersect<SHAPES>(sc, tp.kind, tp.index, ray);
     if (hit) { h.geom = tp.geom; h.prim = 0; }
     return hit;
   });
 }
 
 // BVH::hit (bvh.cpp:497-511).
-template <bool RARE = true>
+template <int SHAPES = kShapesAll>
 __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) {
   Octant q = make_octant(ray);
   return walk_ref_order<true>(sc, sc.top, ray, q, [&](int top_id) {
     DTopPrim tp = sc.top_prims[top_id];
-    if (tp.kind == PB2_SHAPE_MESH) {
+    if ((SHAPES & kShapesMesh) && tp.kind == PB2_SHAPE_MESH) {
       const DMesh& m = sc.meshes[tp.index];
       return walk_ref_order<true>(sc, m.tree, ray, q, [&](int tri) {
         V3 v0, v1, v2;
@@ -157,7 +158,7 @@ __device__ __forceinline__ bool any_ref_order(const DScene& sc, const Ray& ray) 
         return tri_hit(ray, v0, v1, v2);
       });
     }
-    return shape_hit<(RARE ? kShapesAll : kShapesCommon)>(sc, tp.kind, tp.index, ray);
+    return shape_hit<SHAPES>(sc, tp.kind, tp.index, ray);
   });
 }
 

@@ -270,7 +270,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
 }
 
 // Reference-order re-trace of the rays the wide walk could not certify.
-template <bool ANY, bool RARE = true, class IO>
+template <bool ANY, int RARE = kShapesAll, class IO>  // RARE: a kShapes* mask
 __device__ __forceinline__ void wide_fallback(const DScene& sc, WideQueue wq, const IO& io) {
   const int n = *wq.fb_count;
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
@@ -287,7 +287,7 @@ __device__ __forceinline__ void wide_fallback(const DScene& sc, WideQueue wq, co
 }
 
 // One ray per thread in reference order (accel = 1, and closest hits of order-dependent scenes).
-template <bool ANY, bool RARE = true, class IO>
+template <bool ANY, int RARE = kShapesAll, class IO>  // RARE: a kShapes* mask
 __device__ __forceinline__ void ref_order_all(const DScene& sc, int n, const IO& io) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     Ray ray = io.load(i);
