@@ -218,7 +218,7 @@ __device__ __forceinline__ void wide_persistent(const DScene& sc, int n, WideQue
 #ifdef PB2_COUNT
       c_nodes++;
 #endif
-      const uint32_t hm = test_node8<(RARE == kShapesFlat ? false : true)>(sc.nodes8, ngroup.x + rel, w, ray.tmin, ANY ? ray.tmax : slack_of(ray.tmax),
+      const uint32_t hm = test_node8<((RARE & kShapesUnbounded) != 0)>(sc.nodes8, ngroup.x + rel, w, ray.tmin, ANY ? ray.tmax : slack_of(ray.tmax),
                                      ANY ? ray.tmax : tmax_in, child_base, prim_base, cmask, s_top);
       ngroup = make_uint2(child_base, (hm & 0xff000000u) | cmask);
       tgroup = make_uint2(prim_base, hm & 0x00ffffffu);
