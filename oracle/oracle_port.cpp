@@ -131,6 +131,8 @@ struct Obb { Aabb base; float m[16], m_inv[16]; };
 struct Disk { float position[3], n[3], u[3], v[3], r; };
 struct Cone { Disk bottom; float p[3], n[3], r, h, A, A2, S; };
 struct Sphere { float c[3], r; };
+struct Plane { float position[3], n[3], u[3], v[3]; };
+struct Cylinder { float p0[3], p1[3], n[3], r; Disk bottom, top; };
 struct Tri { float v0[3], v1[3], v2[3], n[3]; };
 inline V3 ld(const float* p) { return {p[0], p[1], p[2]}; }
 
@@ -187,6 +189,40 @@ bool cone_test(const Cone& s, const Ray& ray, bool any, float& t_out) {
   float side = dot(o + tmax * d, n);
   if (any ? !(side <= 0) : !(side < 0)) return false;
   t_out = tmax;
+  return true;
+}
+// geometry.cpp:35-45: hit() is strict at tmin, intersect() non-strict at both ends (and lets a NaN t through)
+bool plane_test(const Plane& s, const Ray& ray, bool any, float& t_out) {
+  V3 n = ld(s.n);
+  float t = (dot(ld(s.position), n) - dot(ray.o, n)) / dot(ray.d, n);
+  if (any) {
+    if (t <= ray.tmin) return false;
+    if (!(t < ray.tmax)) return false;
+  } else {
+    if (t < ray.tmin || t > ray.tmax) return false;
+  }
+  t_out = t;
+  return true;
+}
+// geometry.cpp:466-517: the open tube; the far root is not re-checked against tmin
+bool cylinder_test(const Cylinder& s, const Ray& ray, float& t_out) {
+  V3 p0 = ld(s.p0), n = ld(s.n);
+  V3 m = ray.o - p0;
+  V3 v = ray.d - dot(ray.d, n) * n;
+  V3 w = m - dot(m, n) * n;
+  float a = dot(v, v);
+  float b = 2 * dot(v, w);
+  float c = dot(w, w) - s.r * s.r;
+  float discriminant = b * b - 4 * a * c;
+  if (discriminant < 0) return false;
+  float sqrt_disc = std::sqrt(discriminant);
+  float t = (-b - sqrt_disc) / (2 * a);
+  if (t < ray.tmin) t = (-b + sqrt_disc) / (2 * a);
+  if (t > ray.tmax) return false;
+  V3 hit_point = ray.at(t);
+  V3 projection = p0 + dot(hit_point - p0, n) * n;
+  if (dot(projection - p0, n) < 0 || dot(projection - ld(s.p1), n) > 0) return false;
+  t_out = t;
   return true;
 }
 // geometry.cpp:73-92
@@ -457,13 +493,14 @@ bool walk(const Tree& t, const Ray& ray, const Octant& q, Counters& cnt, F&& lea
   return hit;
 }
 
-enum Kind { K_AABB = 0, K_OBB, K_SPHERE, K_TRIANGLE, K_CONE, K_RECT, K_DISK, K_MESH };
+enum Kind { K_AABB = 0, K_OBB, K_SPHERE, K_TRIANGLE, K_CONE, K_RECT, K_DISK, K_MESH, K_PLANE, K_CYLINDER };
 struct Geom { int kind, index; };
 struct MeshData { std::vector<V3> verts; std::vector<uint32_t> idx; };
 struct Scene {
   std::vector<Geom> geoms;
   std::vector<Aabb> aabbs; std::vector<Obb> obbs; std::vector<Sphere> spheres; std::vector<Tri> tris;
   std::vector<Cone> cones; std::vector<Rect> rects; std::vector<Disk> disks; std::vector<MeshData> meshes;
+  std::vector<Plane> planes; std::vector<Cylinder> cylinders;
   Tree top;
   std::vector<Tree> lbvh;
   std::vector<int> indices;  // BVH::indices: top primitive -> geometry
@@ -489,6 +526,12 @@ struct Scene {
         const Cone& c = cones[g.index];
         b.lower = ld(c.bottom.position) - V3(c.bottom.r); b.upper = ld(c.bottom.position) + V3(c.bottom.r);
         b.extend(ld(c.p));
+      } break;
+      case K_PLANE: b.lower = ld(planes[g.index].position) + V3(-100.0f); b.upper = ld(planes[g.index].position) + V3(100.0f); break;  // geometry.cpp:52
+      case K_CYLINDER: {  // union_(bottom.get_aabb(), top.get_aabb()) (geometry.h:147): both disks sit at p0
+        const Cylinder& c = cylinders[g.index];
+        b.lower = ld(c.bottom.position) - V3(c.bottom.r); b.upper = ld(c.bottom.position) + V3(c.bottom.r);
+        b.extend(ld(c.top.position) - V3(c.top.r)); b.extend(ld(c.top.position) + V3(c.top.r));
       } break;
       case K_TRIANGLE: b.extend(ld(tris[g.index].v0)); b.extend(ld(tris[g.index].v1)); b.extend(ld(tris[g.index].v2)); break;
       case K_RECT: {
@@ -543,6 +586,8 @@ struct Scene {
         return rect_test(rects[g.index], ray, t);  // Rect::hit == Rect::intersect's test
       }
       case K_DISK: return disk_test(disks[g.index], ray, any, t);
+      case K_PLANE: return plane_test(planes[g.index], ray, any, t);
+      case K_CYLINDER: return cylinder_test(cylinders[g.index], ray, t);
     }
     return false;
   }
@@ -604,7 +649,7 @@ extern "C" {
 
 void* port_scene_new() { return new Scene(); }
 void port_scene_free(void* h) { delete static_cast<Scene*>(h); }
-// kind: pb2_shape_kind numbering (0 AABB .. 6 DISK); rec: the shape record (layout of include/pine_b200.h)
+// kind: pb2_shape_kind numbering (0 AABB .. 6 DISK, 8 PLANE, 9 CYLINDER); rec: the shape record (layout of include/pine_b200.h)
 int port_add_shape(void* h, int kind, const void* rec) {
   Scene& S = *static_cast<Scene*>(h);
   int index = -1;
@@ -616,6 +661,8 @@ int port_add_shape(void* h, int kind, const void* rec) {
     case K_CONE: S.cones.push_back(*static_cast<const Cone*>(rec)); index = int(S.cones.size()) - 1; break;
     case K_RECT: S.rects.push_back(*static_cast<const Rect*>(rec)); index = int(S.rects.size()) - 1; break;
     case K_DISK: S.disks.push_back(*static_cast<const Disk*>(rec)); index = int(S.disks.size()) - 1; break;
+    case K_PLANE: S.planes.push_back(*static_cast<const Plane*>(rec)); index = int(S.planes.size()) - 1; break;
+    case K_CYLINDER: S.cylinders.push_back(*static_cast<const Cylinder*>(rec)); index = int(S.cylinders.size()) - 1; break;
     default: return -1;
   }
   S.geoms.push_back(Geom{kind, index});

@@ -223,3 +223,30 @@ def test_embree_backed_reference_renders_the_same_film(tmp_path):
         assert r.returncode == 0, r.stderr[-500:]
         films[name] = np.load(out)
     assert common.relmse(films["embree"], films["bvh"]) <= 1e-3
+
+
+@needs_ref
+def test_port_plane_and_cylinder_match_the_live_reference():
+    """The oracle's restatement of Plane (geometry.cpp:31-70) and Cylinder (:466-517) -- boxes, the non-strict /
+    unchecked comparisons, the reference-order walk over shapes that can be hit outside their box -- against the
+    live reference: camera rays, bounce rays from the hit points and shadow-length rays, (geom, t) bit for bit."""
+    import pine_b200 as pb
+    from oracle import port, ref
+    from pine_b200 import scenes
+    R, S = ref.RefScene(), pb.Scene()
+    scenes.plane_yard(R, size=(96, 72))
+    scenes.plane_yard(S, size=(96, 72))
+    P = port.PortScene(S)
+    rays = R.primary_rays(0)
+    want = R.trace_closest(rays, surf=True)
+    got = P.trace_closest(rays)
+    assert set(np.unique(want["geom"])) >= {0, 1, 2, 3, 4}
+    assert np.array_equal(got["geom"], want["geom"]) and np.array_equal(common.u32(got["t"]), common.u32(want["t"]))
+    sec = common.secondary_inputs(want["surf"], want["geom"], 5)
+    # spawn rays off the surfaces (o = p + n * 1e-3, the direction of secondary_inputs), long and shadow-length
+    o = sec[:, 0:3] + sec[:, 3:6] * np.float32(1e-3)
+    bounce = np.concatenate([o, sec[:, 6:9], np.zeros((len(sec), 1), np.float32), sec[:, 9:10]], axis=1).astype(np.float32)
+    w2, g2 = R.trace_closest(bounce), P.trace_closest(bounce)
+    assert np.array_equal(g2["geom"], w2["geom"]) and np.array_equal(common.u32(g2["t"]), common.u32(w2["t"]))
+    shadow = common.shadow_from(bounce, 9)
+    assert np.array_equal(P.trace_any(shadow)["occluded"], R.trace_any(shadow))
