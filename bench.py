@@ -185,7 +185,10 @@ def run_reference_embree(workload, step_seconds):
 
 def _config(workload, w, h, spp, depth):
     return {"workload": WORKLOADS[workload][2], "name": workload, "width": w, "height": h, "spp": spp,
-            "max_path_length": depth, "integrator": "PathIntegrator(BlueSampler(spp), max_path_length)"}
+            "max_path_length": depth, "integrator": "PathIntegrator(BlueSampler(spp), max_path_length)",
+            # timing rule: no L2 flush between steps because a step's inputs are larger than the 126 MB L2 (the
+            # wavefront state of w*h*spp samples alone is GBs; C4 / C5 add a 0.3-1.4 GB scene); sizes in details.l2
+            "l2": "no flush: per-step inputs (wavefront state of width*height*spp samples + scene) exceed the 126 MB L2"}
 
 
 def _peaks():
